@@ -1,0 +1,266 @@
+/*
+ * b200phi.h -- C ABI of the B200-native phi reduce / broadcast hot path.
+ *
+ * Every entry point is plain C: pointers, sizes and small POD descriptors.
+ * No phi, torch or C++ types cross this boundary.  All device work is enqueued
+ * asynchronously on the caller's stream (a cudaStream_t passed as void*); no
+ * entry point synchronises the stream, allocates device memory or keeps a
+ * pointer after it returns.  Scratch memory, where a kernel needs some, is
+ * supplied by the caller (size from the matching *_workspace query), exactly
+ * like the reference obtains temporaries from dev_ctx.Alloc
+ * (paddle/phi/kernels/funcs/reduce_function.h:1118-1140).
+ *
+ * Return value: 0 on success, a b200phi_status otherwise; the message is
+ * available per host thread through b200phi_last_error().  The reference
+ * raises EnforceNotMet C++ exceptions for the same conditions
+ * (reduce_function.h:1052-1055, dims_simplifier.h:116-126); the phi adapter
+ * (adapter/phi_b200_kernels.cu) turns a non-zero status back into PADDLE_THROW.
+ *
+ * Tensors are contiguous row-major with int64 extents and rank <= 9
+ * (paddle/common/ddim.h:71, paddle/phi/core/dense_tensor.h:43-199).
+ */
+#ifndef B200PHI_H_
+#define B200PHI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200PHI_API __attribute__((visibility("default")))
+#else
+#define B200PHI_API
+#endif
+
+#define B200PHI_MAX_RANK 9
+#define B200PHI_MAX_ARITY 3
+
+/* Numeric values equal phi::DataType (paddle/phi/common/data_type.h:42-85) so
+ * the adapter can pass static_cast<int>(tensor.dtype()) straight through. */
+typedef enum {
+  B200PHI_UNDEFINED = 0,
+  B200PHI_BOOL = 1,
+  B200PHI_UINT8 = 2,
+  B200PHI_INT8 = 3,
+  B200PHI_INT16 = 5,
+  B200PHI_INT32 = 7,
+  B200PHI_INT64 = 9,
+  B200PHI_FLOAT32 = 10,
+  B200PHI_FLOAT64 = 11,
+  B200PHI_FLOAT16 = 15,
+  B200PHI_BFLOAT16 = 16
+} b200phi_dtype;
+
+typedef enum {
+  B200PHI_OK = 0,
+  B200PHI_INVALID_ARGUMENT = 1, /* EnforceNotMet(InvalidArgument) in phi */
+  B200PHI_UNSUPPORTED = 2,      /* dtype / op combination not built */
+  B200PHI_CUDA_ERROR = 3,
+  B200PHI_WORKSPACE_TOO_SMALL = 4,
+  B200PHI_NCCL_ERROR = 5
+} b200phi_status;
+
+/* ------------------------------------------------------------------------ */
+/* Reductions                                                               */
+/* ------------------------------------------------------------------------ */
+
+/* Replaces the op binding done per kernel in
+ * paddle/phi/kernels/kps/reduce_kernel.cu:35-133,185-271 and
+ * paddle/phi/kernels/legacy/kps/reduce_max_kernel.cu:22-33. */
+typedef enum {
+  B200PHI_SUM = 0,  /* kps::AddFunctor + IdentityFunctor            */
+  B200PHI_MEAN = 1, /* sum in MPType, then / reduce_num (IsMean)    */
+  B200PHI_MAX = 2,  /* kps::MaxFunctor                              */
+  B200PHI_MIN = 3,  /* kps::MinFunctor                              */
+  B200PHI_PROD = 4, /* kps::MulFunctor                              */
+  B200PHI_ANY = 5,  /* kps::LogicalOrFunctor on (x != 0), out BOOL  */
+  B200PHI_ALL = 6,  /* kps::LogicalAndFunctor on (x != 0), out BOOL */
+  B200PHI_AMAX = 7, /* same arithmetic as MAX (differs only in grad) */
+  B200PHI_AMIN = 8
+} b200phi_reduce_op;
+
+/* One reduction call.  Stands in for the argument list of
+ *   phi::SumKernel(ctx, x, IntArray dims, DataType out_dtype, bool keep_dim, out)
+ *   (paddle/phi/kernels/reduce_sum_kernel.h:22-37) and its siblings
+ *   MeanKernel/MaxKernel/MinKernel/ProdKernel/AnyKernel/AllKernel/AMax/AMin,
+ * after InferMeta has fixed out's dims/dtype.  keep_dim is not needed: it only
+ * changes out's shape, never its linear layout. */
+typedef struct {
+  int32_t op;         /* b200phi_reduce_op */
+  int32_t in_dtype;   /* b200phi_dtype of x */
+  int32_t out_dtype;  /* UNDEFINED => in_dtype (ANY/ALL: BOOL) */
+  int32_t rank;       /* 0..9; 0 => 0-D tensor with one element */
+  int64_t dims[B200PHI_MAX_RANK];
+  int32_t naxes;      /* 0 => reduce over every axis */
+  int32_t axes[B200PHI_MAX_RANK]; /* each in [-rank, rank) */
+  int32_t reduce_all; /* forces a full reduction, as the phi attribute does */
+  const void* x;      /* device pointer, element-aligned */
+  void* out;          /* device pointer, element-aligned */
+  void* workspace;    /* device scratch, >= b200phi_reduce_workspace() bytes, 256-B aligned; may be NULL if 0 */
+  size_t workspace_bytes;
+} b200phi_reduce_desc;
+
+/* Bytes of device scratch b200phi_reduce needs for this descriptor on the
+ * current device (0 for most shapes; non-zero when the reduced extent is split
+ * across thread blocks and finalised by the last block).  Replaces the
+ * temporary the reference allocates for its two-pass reduce
+ * (reduce_function.h:1118-1140, CubTensorReduce :938-969). Returns 0 on a bad
+ * descriptor; b200phi_reduce then reports the error. */
+B200PHI_API size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d);
+
+/* Replaces funcs::ReduceKernel<Tx,Ty,ReduceOp,TransformOp,IsMean>
+ * (reduce_function.h:1047-1198) together with phi::Reduce (gpu/reduce.h:32-80);
+ * the dtype change the reference does as a separate Cast pass (gpu/reduce.h:48-69)
+ * is fused into the load. */
+B200PHI_API int b200phi_reduce(const b200phi_reduce_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* argmax / argmin                                                          */
+/* ------------------------------------------------------------------------ */
+
+typedef enum { B200PHI_ARGMAX = 0, B200PHI_ARGMIN = 1 } b200phi_arg_op;
+
+/* Stands in for
+ *   phi::ArgMaxKernel(ctx, x, Scalar axis, bool keepdims, bool flatten, DataType dtype, out)
+ *   (paddle/phi/kernels/arg_min_max_kernel.h:22-38; GPU body
+ *    paddle/phi/kernels/gpu/arg_min_max_kernel.cu:58-254).
+ * Ties resolve to the lowest index, a slice whose every element equals the
+ * identity yields 0 (the CPU kernel's answer, cpu/arg_min_max_kernel.cc:46-59). */
+typedef struct {
+  int32_t op;          /* b200phi_arg_op */
+  int32_t in_dtype;
+  int32_t index_dtype; /* INT64 (default when UNDEFINED) or INT32 */
+  int32_t rank;
+  int64_t dims[B200PHI_MAX_RANK];
+  int64_t axis;        /* in [-rank, rank); ignored when flatten */
+  int32_t flatten;
+  const void* x;
+  void* out;
+  void* max_out;       /* optional: also write the extreme value (in_dtype); NULL to skip */
+} b200phi_argreduce_desc;
+
+B200PHI_API int b200phi_argreduce(const b200phi_argreduce_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* Row statistics: mean and variance over the last axis in one read         */
+/* ------------------------------------------------------------------------ */
+
+/* Replaces the Python composite paddle.var = mean -> subtract -> pow -> sum ->
+ * divide (python/paddle/tensor/stat.py:184-197) and the MeanRawKernel it starts
+ * with (kps/reduce_kernel.cu:110-120) for a [rows, cols] view reduced over
+ * cols.  var = sum((x-mean)^2) / (cols - unbiased), accumulated in fp32
+ * (fp64 for FLOAT64 input). */
+typedef struct {
+  int32_t in_dtype;  /* FLOAT32, FLOAT64, BFLOAT16, FLOAT16 */
+  int32_t out_dtype; /* UNDEFINED => in_dtype; FLOAT32 allowed for 16-bit inputs */
+  int64_t rows;
+  int64_t cols;
+  int32_t unbiased;  /* 1 => divide by cols-1 (paddle.var default) */
+  const void* x;
+  void* mean;        /* [rows] or NULL */
+  void* var;         /* [rows] or NULL */
+} b200phi_rowstats_desc;
+
+B200PHI_API int b200phi_rowstats(const b200phi_rowstats_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* n-ary broadcast / elementwise engine with fused unary epilogue           */
+/* ------------------------------------------------------------------------ */
+
+/* Binary functors of paddle/phi/kernels/funcs/elementwise_functor.h. */
+typedef enum {
+  B200PHI_ADD = 0,      /* AddFunctor :39-41 */
+  B200PHI_SUBTRACT = 1,
+  B200PHI_MULTIPLY = 2,
+  B200PHI_DIVIDE = 3,
+  B200PHI_MAXIMUM = 4,
+  B200PHI_MINIMUM = 5
+} b200phi_binary_op;
+
+/* Unary functors that can be fused around the binary one, as
+ * fused_elemwise_activation's functor_list does
+ * (paddle/phi/kernels/funcs/fused_elemwise_activation_functor.h:388-458). */
+typedef enum {
+  B200PHI_ACT_NONE = 0,
+  B200PHI_ACT_RELU = 1,  /* v > 0 ? v : 0   (ReluCPUFunctor, activation_functor.h:1473-1480) */
+  B200PHI_ACT_SCALE = 2, /* v * scale       (ScaleFunctor, functors.h) */
+  B200PHI_ACT_GELU = 3,  /* 0.5 v (1 + erf(v / sqrt 2)) */
+  B200PHI_ACT_SIGMOID = 4,
+  B200PHI_ACT_TANH = 5
+} b200phi_unary_op;
+
+typedef struct {
+  int32_t rank;
+  int64_t dims[B200PHI_MAX_RANK];
+  const void* data;
+} b200phi_tensor_view;
+
+/* One elementwise call.  Stands in for
+ *   funcs::BroadcastKernel<T>(ctx, ins, outs, functor, axis)  (broadcast_function.h:758-824)
+ *   funcs::ElementwiseKernel                                  (elementwise_base.h:807-845)
+ *   phi::AddRawKernel(ctx, x, y, axis, out) and siblings      (impl/elementwise_kernel_impl.h:50-62)
+ *   phi::FusedElemwiseAddActivationKernel                     (impl/fused_elemwise_activation_kernel_impl.h:202-222)
+ * compound == 0:  out = act(binary(in0, in1 [, in2]))    e.g. ["relu","elementwise_add"]
+ * compound == 1:  out = binary(in0, act(in1))            e.g. ["elementwise_add","relu"]
+ * With three inputs the functor folds left: binary(binary(in0,in1),in2)
+ * (test/cpp/phi/kernels/test_ternary_broadcast.cu:96-120).
+ * axis: -1 => numpy right-aligned broadcasting; >= 0 => the legacy left offset
+ * of the lower-rank operand (paddle/phi/kernels/funcs/common_shape.h:35-92). */
+typedef struct {
+  int32_t binary;   /* b200phi_binary_op */
+  int32_t act;      /* b200phi_unary_op */
+  int32_t compound; /* see above */
+  float scale;      /* for B200PHI_ACT_SCALE */
+  int32_t dtype;    /* all inputs and the output share it */
+  int32_t arity;    /* 1 (act only), 2 or 3 */
+  int32_t axis;
+  b200phi_tensor_view in[B200PHI_MAX_ARITY];
+  int32_t out_rank; /* out dims as InferMeta fixed them (binary.cc:1665-1740) */
+  int64_t out_dims[B200PHI_MAX_RANK];
+  void* out;
+  void* intermediate_out; /* optional save_intermediate_out; NULL to skip */
+} b200phi_elementwise_desc;
+
+B200PHI_API int b200phi_elementwise(const b200phi_elementwise_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* Sharded reduction: local reduce + allreduce of the partial               */
+/* ------------------------------------------------------------------------ */
+
+/* Communicator helpers.  Replace the lazy ncclGetUniqueId / ncclCommInitRank
+ * that CommContextManager does over a TCPStore
+ * (paddle/phi/core/distributed/comm_context_manager.cc:75,
+ *  nccl_comm_context.cc:37-46).  The caller moves the 128-byte id between
+ * processes with whatever rendezvous it has. NCCL is dlopen'ed on first use,
+ * as phi::dynload does. */
+B200PHI_API int b200phi_comm_unique_id(unsigned char id[128]);
+B200PHI_API int b200phi_comm_init_rank(const unsigned char id[128], int nranks, int rank, void** comm);
+B200PHI_API int b200phi_comm_destroy(void* comm);
+
+/* Each rank holds a contiguous block of rows of the global tensor (axis 0
+ * sharded); d describes the LOCAL shard.  The local partial is reduced into
+ * d->out and combined across ranks on the same stream with no host sync:
+ * ncclSum for SUM/MEAN (MEAN divides by global_reduce_count afterwards),
+ * ncclMax/Min/Prod for MAX/MIN/PROD.  Replaces the reference's
+ * SumKernel + ProcessGroupNCCL::AllReduce pair
+ * (process_group_nccl.cc:267-298 -> nccl_comm_context.cc:184-206) and the
+ * Partial->Replicate reshard (p_to_r_reshard_function.cc:67). With comm ==
+ * NULL (single GPU) it is b200phi_reduce and issues no collective. */
+B200PHI_API int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count,
+                           void* comm, void* stream);
+
+/* ------------------------------------------------------------------------ */
+
+/* Message of the last non-zero status returned on this host thread. */
+B200PHI_API const char* b200phi_last_error(void);
+
+/* "b200phi <version> sm_100a" -- lets a loader check it bound the right file. */
+B200PHI_API const char* b200phi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PHI_H_ */

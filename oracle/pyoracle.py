@@ -1,0 +1,272 @@
+"""TEST INFRASTRUCTURE -- numpy front-end of the two CPU checkers.
+
+  port()  oracle/libphi_oracle.so   plain-C restatement (oracle/phi_oracle.c)
+  ref()   oracle/_ref/libphi_ref.so the reference's own functors + vendored Eigen
+                                    (oracle/ref_src/*.cc compiled against /root/reference)
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference)
+import this module.  Nothing in paddle2_b200/ does.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_PATH = os.path.join(_HERE, "libphi_oracle.so")
+REF_PATH = os.path.join(_HERE, "_ref", "libphi_ref.so")
+
+BOOL, UINT8, INT8, INT16, INT32, INT64, F32, F64 = 1, 2, 3, 5, 7, 9, 10, 11
+_NP2DT = {np.dtype(np.bool_): BOOL, np.dtype(np.uint8): UINT8, np.dtype(np.int8): INT8,
+          np.dtype(np.int16): INT16, np.dtype(np.int32): INT32, np.dtype(np.int64): INT64,
+          np.dtype(np.float32): F32, np.dtype(np.float64): F64}
+OPS = {"sum": 0, "mean": 1, "max": 2, "min": 3, "prod": 4, "any": 5, "all": 6, "amax": 7, "amin": 8}
+BINARY = {"add": 0, "subtract": 1, "multiply": 2, "divide": 3, "maximum": 4, "minimum": 5}
+UNARY = {None: 0, "none": 0, "relu": 1, "scale": 2, "gelu": 3, "sigmoid": 4, "tanh": 5}
+
+_port = None
+_ref = None
+
+
+def build():
+    """Compile the port (and, where /root/reference exists, the reference build)."""
+    import subprocess
+    subprocess.run(["make", "-s", "-j8", "-C", _HERE, "all"], check=True)
+
+
+def port():
+    global _port
+    if _port is None:
+        if not os.path.exists(PORT_PATH):
+            build()
+        _port = C.CDLL(PORT_PATH)
+    return _port
+
+
+def have_ref():
+    return os.path.exists(REF_PATH)
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = C.CDLL(REF_PATH)
+    return _ref
+
+
+def bf16_bits_to_f32(bits):
+    """uint16 bf16 bit patterns -> float32 (exact)."""
+    bits = np.ascontiguousarray(bits, dtype=np.uint16)
+    return (bits.astype(np.uint32) << 16).view(np.float32)
+
+
+def f32_to_bf16_bits(x):
+    """float32 -> bf16 bit patterns, round-to-nearest-even."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    r = ((u >> 16) & 1) + 0x7FFF
+    return ((u + r) >> 16).astype(np.uint16)
+
+
+def _axes_list(axis, rank):
+    if axis is None:
+        return [], True
+    if isinstance(axis, (int, np.integer)):
+        axis = [int(axis)]
+    axis = [int(a) for a in axis]
+    if len(axis) == 0:
+        return [], True
+    norm = sorted({a + rank if a < 0 else a for a in axis})
+    return norm, len(norm) == rank or rank == 0
+
+
+def _out_shape(shape, axes, reduce_all, keepdim):
+    if reduce_all:
+        return [1] * len(shape) if keepdim else []
+    if keepdim:
+        return [1 if i in axes else s for i, s in enumerate(shape)]
+    return [s for i, s in enumerate(shape) if i not in axes]
+
+
+def sum_out_dtype(x_dtype, dtype=None):
+    """SumRawInferMeta (infermeta/unary.cc:4698-4707)."""
+    if dtype is not None:
+        return np.dtype(dtype)
+    if np.dtype(x_dtype) in (np.dtype(np.bool_), np.dtype(np.int32), np.dtype(np.int64)):
+        return np.dtype(np.int64)
+    return np.dtype(x_dtype)
+
+
+def reduce(op, x, axis=None, keepdim=False, out_dtype=None, impl="port"):
+    """Reduce like phi::Reduce<CPUContext> does. impl: 'port' or 'ref'."""
+    x = np.ascontiguousarray(x)
+    rank = x.ndim
+    axes, reduce_all = _axes_list(axis, rank)
+    logical = op in ("any", "all")
+    if out_dtype is None:
+        out_dtype = np.dtype(np.bool_) if logical else x.dtype
+    out_dtype = np.dtype(out_dtype)
+    out = np.empty(_out_shape(list(x.shape), axes, reduce_all, keepdim), dtype=out_dtype)
+    dims = (C.c_int64 * 9)(*x.shape)
+    if impl == "port":
+        ax = (C.c_int32 * 9)(*axes)
+        rc = port().phi_oracle_reduce(OPS[op], _NP2DT[x.dtype], _NP2DT[out_dtype], rank, dims,
+                                      len(axes), ax, int(reduce_all),
+                                      x.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise ValueError(f"phi_oracle_reduce status {rc}")
+        return out
+    # reference build: cast first (phi::Cast), then the typed functor
+    xin = x.astype(out_dtype) if x.dtype != out_dtype else x
+    if logical:
+        xin = (x != 0)
+    xin = np.ascontiguousarray(xin)
+    names = {np.dtype(np.float32): "float", np.dtype(np.float64): "double",
+             np.dtype(np.int32): "int32", np.dtype(np.int64): "int64", np.dtype(np.bool_): "bool"}
+    opname = {"amax": "max", "amin": "min"}.get(op, op)
+    fn = getattr(ref(), f"phi_ref_{opname}_{names[xin.dtype]}")
+    ax = (C.c_int64 * 9)(*axes)
+    rc = fn(xin.ctypes.data_as(C.c_void_p), rank, dims, len(axes), ax, int(reduce_all),
+            out.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise ValueError(f"phi_ref reduce status {rc}")
+    return out
+
+
+def argreduce(op, x, axis=None, keepdim=False, dtype=np.int64, impl="port"):
+    """argmax/argmin like the CPU kernel (Eigen argmax(axis).cast<Tout>())."""
+    x = np.ascontiguousarray(x)
+    rank = x.ndim
+    flatten = axis is None
+    ax = 0 if flatten else (axis + rank if axis < 0 else axis)
+    if flatten or rank == 0:
+        shape = [1] * rank if keepdim else []
+    elif keepdim:
+        shape = [1 if i == ax else s for i, s in enumerate(x.shape)]
+    else:
+        shape = [s for i, s in enumerate(x.shape) if i != ax]
+    out = np.empty(shape, dtype=np.int64)
+    dims = (C.c_int64 * 9)(*x.shape)
+    is_max = op == "argmax"
+    if impl == "port":
+        rc = port().phi_oracle_argreduce(0 if is_max else 1, _NP2DT[x.dtype], rank, dims,
+                                         C.c_int64(ax), int(flatten),
+                                         x.ctypes.data_as(C.c_void_p),
+                                         out.ctypes.data_as(C.POINTER(C.c_int64)))
+    else:
+        names = {np.dtype(np.float32): "float", np.dtype(np.float64): "double",
+                 np.dtype(np.int32): "int32", np.dtype(np.int64): "int64"}
+        fn = getattr(ref(), f"phi_ref_arg_{names[x.dtype]}")
+        rc = fn(x.ctypes.data_as(C.c_void_p), rank, dims, C.c_int64(ax), int(flatten), int(is_max),
+                out.ctypes.data_as(C.POINTER(C.c_int64)))
+    if rc != 0:
+        raise ValueError(f"oracle argreduce status {rc}")
+    return out.astype(dtype)
+
+
+def _padded_dims(shape, out_rank, offset):
+    d = [1] * out_rank
+    for k, s in enumerate(shape):
+        d[offset + k] = s
+    return d
+
+
+def broadcast_out_shape(xs, ys, axis=-1):
+    """GetBroadcastDimsArrays (common_shape.h:35-92) + ElementwiseInferMeta (binary.cc:1665-1740)."""
+    xs, ys = list(xs), list(ys)
+    R = max(len(xs), len(ys))
+    ax = abs(len(xs) - len(ys)) if axis < 0 else axis
+    if len(xs) >= len(ys):
+        xp, yp = _padded_dims(xs, R, 0), _padded_dims(ys, R, ax if len(ys) < len(xs) else 0)
+    else:
+        xp, yp = _padded_dims(xs, R, ax), _padded_dims(ys, R, 0)
+    out = []
+    for a, b in zip(xp, yp):
+        if not (a == b or a <= 1 or b <= 1):
+            raise ValueError("Broadcast dimension mismatch.")
+        out.append(0 if (a == 0 or b == 0) else max(a, b))
+    return out, xp, yp
+
+
+def elementwise(binary, ins, act=None, compound=0, scale=0.0, axis=-1, want_intermediate=False,
+                impl="port"):
+    """out = act(binary(x, y[, z])) (compound 0) or binary(x, act(y)) (compound 1)."""
+    ins = [np.ascontiguousarray(t) for t in ins]
+    dt = ins[0].dtype
+    if len(ins) == 1:
+        out_shape, pads = list(ins[0].shape), [list(ins[0].shape)]
+    else:
+        out_shape, xp, yp = broadcast_out_shape(ins[0].shape, ins[1].shape, axis)
+        pads = [xp, yp]
+        for t in ins[2:]:
+            prev = out_shape
+            out_shape, _, zp = broadcast_out_shape(prev, t.shape, -1)
+            pads = [_padded_dims(p, len(out_shape), len(out_shape) - len(p)) for p in pads] + [zp]
+    R = len(out_shape)
+    out = np.empty(out_shape, dtype=dt)
+    inter = np.empty(out_shape, dtype=dt) if want_intermediate else None
+    od = (C.c_int64 * 9)(*out_shape)
+    ptrs = (C.c_void_p * 3)(*[t.ctypes.data for t in ins] + [None] * (3 - len(ins)))
+    ip = inter.ctypes.data_as(C.c_void_p) if want_intermediate else None
+    if impl == "port":
+        flat = (C.c_int64 * 27)()
+        for i, p in enumerate(pads):
+            for k, s in enumerate(p):
+                flat[i * 9 + k] = s
+        rc = port().phi_oracle_elementwise(BINARY[binary], UNARY[act], int(compound),
+                                           C.c_float(scale), _NP2DT[dt], len(ins), R, od, flat,
+                                           ptrs, out.ctypes.data_as(C.c_void_p), ip)
+    else:
+        names = {np.dtype(np.float32): "float", np.dtype(np.float64): "double",
+                 np.dtype(np.int32): "int32", np.dtype(np.int64): "int64"}
+        rows = [(C.c_int64 * 9)(*p) for p in pads]
+        rowptrs = (C.POINTER(C.c_int64) * 3)(*[C.cast(r, C.POINTER(C.c_int64)) for r in rows] +
+                                             [None] * (3 - len(rows)))
+        fn = getattr(ref(), f"phi_ref_elementwise_{names[dt]}")
+        rc = fn(BINARY[binary], UNARY[act], int(compound), C.c_float(scale), len(ins), R, od,
+                rowptrs, ptrs, out.ctypes.data_as(C.c_void_p), ip)
+    if rc != 0:
+        raise ValueError(f"oracle elementwise status {rc}")
+    return (out, inter) if want_intermediate else out
+
+
+def rowstats_f32(x, unbiased=True):
+    """(mean, var) over the last axis of a float32 array: paddle.var's composite in fp32."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    cols = x.shape[-1]
+    rows = x.size // cols
+    mean = np.empty(x.shape[:-1], dtype=np.float32)
+    var = np.empty(x.shape[:-1], dtype=np.float32)
+    fn = port().phi_oracle_rowstats_f32
+    rc = fn(C.c_int64(rows), C.c_int64(cols), int(unbiased), x.ctypes.data_as(C.c_void_p),
+            mean.ctypes.data_as(C.c_void_p), var.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise ValueError(f"oracle rowstats status {rc}")
+    return mean, var
+
+
+def var_composite(x, axis=None, unbiased=True, keepdim=False, impl="port"):
+    """paddle.var as the reference composes it (stat.py:184-197), every step through
+    the oracle's reduce / elementwise, in x's own dtype (fp32 / fp64)."""
+    x = np.ascontiguousarray(x)
+    u = reduce("mean", x, axis, keepdim=True, impl=impl)
+    d = elementwise("subtract", [x, u], impl=impl)
+    sq = elementwise("multiply", [d, d], impl=impl)
+    s = reduce("sum", sq, axis, keepdim=keepdim, impl=impl)
+    axes, reduce_all = _axes_list(axis, x.ndim)
+    n = x.size if reduce_all else int(np.prod([x.shape[a] for a in axes]))
+    if unbiased:
+        n = n - 1 if n > 1 else 1
+    return (s / np.asarray(n, dtype=x.dtype)).astype(x.dtype)
+
+
+def sum_axis0_f32_mt(x, threads):
+    """bench.py only: axis-0 sum of a [rows, cols] fp32 array on `threads` host threads."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    rows, cols = x.shape
+    out = np.empty(cols, dtype=np.float32)
+    rc = port().phi_oracle_sum_axis0_f32_mt(C.c_int64(rows), C.c_int64(cols),
+                                            x.ctypes.data_as(C.c_void_p),
+                                            out.ctypes.data_as(C.c_void_p), int(threads))
+    if rc != 0:
+        raise ValueError("oracle sum_axis0 status %d" % rc)
+    return out

@@ -1,0 +1,22 @@
+// TEST INFRASTRUCTURE -- reference-compiled oracle, op 'prod' (see ref_common.h).
+#include "ref_common.h"
+REFPHI_EXPORT int phi_ref_prod_float(const void* in, int rank, const int64_t* dims, int naxes,
+    const int64_t* axes, int reduce_all, void* out) {
+  return refphi::reduce_impl<float, phi::funcs::ProdFunctor>(static_cast<const float*>(in), rank, dims, naxes, axes,
+                                                       reduce_all != 0, static_cast<float*>(out));
+}
+REFPHI_EXPORT int phi_ref_prod_double(const void* in, int rank, const int64_t* dims, int naxes,
+    const int64_t* axes, int reduce_all, void* out) {
+  return refphi::reduce_impl<double, phi::funcs::ProdFunctor>(static_cast<const double*>(in), rank, dims, naxes, axes,
+                                                       reduce_all != 0, static_cast<double*>(out));
+}
+REFPHI_EXPORT int phi_ref_prod_int32(const void* in, int rank, const int64_t* dims, int naxes,
+    const int64_t* axes, int reduce_all, void* out) {
+  return refphi::reduce_impl<int32_t, phi::funcs::ProdFunctor>(static_cast<const int32_t*>(in), rank, dims, naxes, axes,
+                                                       reduce_all != 0, static_cast<int32_t*>(out));
+}
+REFPHI_EXPORT int phi_ref_prod_int64(const void* in, int rank, const int64_t* dims, int naxes,
+    const int64_t* axes, int reduce_all, void* out) {
+  return refphi::reduce_impl<int64_t, phi::funcs::ProdFunctor>(static_cast<const int64_t*>(in), rank, dims, naxes, axes,
+                                                       reduce_all != 0, static_cast<int64_t*>(out));
+}

@@ -1,0 +1,166 @@
+"""ctypes binding of libb200phi.so (the C ABI in include/b200phi.h).
+
+This is the *second* driver of the C ABI next to the phi adapter
+(adapter/phi_b200_kernels.cu): tests and bench.py call the library the same way a
+cgo/JNI/ctypes host would.  There is no CPU fallback anywhere in this package:
+if the shared library is missing or a tensor is not on a CUDA device the call
+raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200phi.so")
+
+MAX_RANK = 9
+MAX_ARITY = 3
+
+# phi::DataType values (paddle/phi/common/data_type.h:42-85)
+UNDEFINED, BOOL, UINT8, INT8, INT16, INT32, INT64 = 0, 1, 2, 3, 5, 7, 9
+FLOAT32, FLOAT64, FLOAT16, BFLOAT16 = 10, 11, 15, 16
+
+SUM, MEAN, MAX, MIN, PROD, ANY, ALL, AMAX, AMIN = range(9)
+ARGMAX, ARGMIN = 0, 1
+ADD, SUBTRACT, MULTIPLY, DIVIDE, MAXIMUM, MINIMUM = range(6)
+ACT_NONE, ACT_RELU, ACT_SCALE, ACT_GELU, ACT_SIGMOID, ACT_TANH = range(6)
+
+STATUS_NAMES = {
+    0: "OK",
+    1: "INVALID_ARGUMENT",
+    2: "UNSUPPORTED",
+    3: "CUDA_ERROR",
+    4: "WORKSPACE_TOO_SMALL",
+    5: "NCCL_ERROR",
+}
+
+
+class ReduceDesc(C.Structure):
+    _fields_ = [
+        ("op", C.c_int32),
+        ("in_dtype", C.c_int32),
+        ("out_dtype", C.c_int32),
+        ("rank", C.c_int32),
+        ("dims", C.c_int64 * MAX_RANK),
+        ("naxes", C.c_int32),
+        ("axes", C.c_int32 * MAX_RANK),
+        ("reduce_all", C.c_int32),
+        ("x", C.c_void_p),
+        ("out", C.c_void_p),
+        ("workspace", C.c_void_p),
+        ("workspace_bytes", C.c_size_t),
+    ]
+
+
+class ArgReduceDesc(C.Structure):
+    _fields_ = [
+        ("op", C.c_int32),
+        ("in_dtype", C.c_int32),
+        ("index_dtype", C.c_int32),
+        ("rank", C.c_int32),
+        ("dims", C.c_int64 * MAX_RANK),
+        ("axis", C.c_int64),
+        ("flatten", C.c_int32),
+        ("x", C.c_void_p),
+        ("out", C.c_void_p),
+        ("max_out", C.c_void_p),
+    ]
+
+
+class RowStatsDesc(C.Structure):
+    _fields_ = [
+        ("in_dtype", C.c_int32),
+        ("out_dtype", C.c_int32),
+        ("rows", C.c_int64),
+        ("cols", C.c_int64),
+        ("unbiased", C.c_int32),
+        ("x", C.c_void_p),
+        ("mean", C.c_void_p),
+        ("var", C.c_void_p),
+    ]
+
+
+class TensorView(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32),
+        ("dims", C.c_int64 * MAX_RANK),
+        ("data", C.c_void_p),
+    ]
+
+
+class ElementwiseDesc(C.Structure):
+    _fields_ = [
+        ("binary", C.c_int32),
+        ("act", C.c_int32),
+        ("compound", C.c_int32),
+        ("scale", C.c_float),
+        ("dtype", C.c_int32),
+        ("arity", C.c_int32),
+        ("axis", C.c_int32),
+        ("in_", TensorView * MAX_ARITY),
+        ("out_rank", C.c_int32),
+        ("out_dims", C.c_int64 * MAX_RANK),
+        ("out", C.c_void_p),
+        ("intermediate_out", C.c_void_p),
+    ]
+
+
+class B200PhiError(RuntimeError):
+    """A non-zero b200phi_status; mirrors the reference's EnforceNotMet."""
+
+    def __init__(self, status, message):
+        self.status = status
+        super().__init__(f"b200phi {STATUS_NAMES.get(status, status)}: {message}")
+
+
+# every symbol include/b200phi.h declares; tests check the library exports them all
+EXPORTS = [
+    "b200phi_reduce_workspace",
+    "b200phi_reduce",
+    "b200phi_argreduce",
+    "b200phi_rowstats",
+    "b200phi_elementwise",
+    "b200phi_comm_unique_id",
+    "b200phi_comm_init_rank",
+    "b200phi_comm_destroy",
+    "b200phi_sharded_reduce",
+    "b200phi_last_error",
+    "b200phi_version",
+]
+
+_lib = None
+
+
+def lib():
+    """Load libb200phi.so once. Raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C paddle2_b200/csrc`. There is no CPU fallback."
+        )
+    L = C.CDLL(LIB_PATH)
+    L.b200phi_last_error.restype = C.c_char_p
+    L.b200phi_version.restype = C.c_char_p
+    L.b200phi_reduce_workspace.restype = C.c_size_t
+    L.b200phi_reduce_workspace.argtypes = [C.POINTER(ReduceDesc)]
+    L.b200phi_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
+    L.b200phi_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_void_p]
+    L.b200phi_rowstats.argtypes = [C.POINTER(RowStatsDesc), C.c_void_p]
+    L.b200phi_elementwise.argtypes = [C.POINTER(ElementwiseDesc), C.c_void_p]
+    L.b200phi_comm_unique_id.argtypes = [C.c_char_p]
+    L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    L.b200phi_comm_destroy.argtypes = [C.c_void_p]
+    L.b200phi_sharded_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_int64, C.c_void_p, C.c_void_p]
+    for name in ("b200phi_reduce", "b200phi_argreduce", "b200phi_rowstats", "b200phi_elementwise",
+                 "b200phi_comm_unique_id", "b200phi_comm_init_rank", "b200phi_comm_destroy",
+                 "b200phi_sharded_reduce"):
+        getattr(L, name).restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(status):
+    if status != 0:
+        raise B200PhiError(status, lib().b200phi_last_error().decode())

@@ -1,0 +1,141 @@
+// extern "C" surface of libb200phi.so (include/b200phi.h).  Nothing here touches
+// phi or torch types; the host logic is reduce_plan.cc / bcast_plan.cc.
+#include <cuda_runtime.h>
+#include <stdio.h>
+
+#include <mutex>
+#include <string>
+
+#include "../../include/b200phi.h"
+#include "reduce_launch.cuh"
+
+namespace b200phi {
+
+static thread_local std::string g_last_error;
+
+int set_error(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+
+int cuda_status(cudaError_t e) {
+  return set_error(B200PHI_CUDA_ERROR, std::string("CUDA: ") + cudaGetErrorString(e));
+}
+
+// Device properties are immutable: cache per device ordinal.
+int current_sm_count() {
+  static std::mutex mu;
+  static int cache[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 148;
+  }
+  if (dev < 0 || dev >= 64) return 148;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+      cudaGetLastError();
+      n = 148;
+    }
+    cache[dev] = n;
+  }
+  return cache[dev];
+}
+
+int run_reduce(const b200phi_reduce_desc* d, cudaStream_t stream) {
+  ReducePlan plan;
+  std::string err;
+  int rc = plan_reduce(d, default_tunables(current_sm_count()), &plan, &err);
+  if (rc != B200PHI_OK) return set_error(rc, err);
+  if (!d->x || !d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null tensor pointer");
+  if (plan.ws_total_bytes > 0) {
+    if (!d->workspace || d->workspace_bytes < plan.ws_total_bytes) {
+      char buf[160];
+      snprintf(buf, sizeof(buf), "workspace too small: need %zu bytes, got %zu",
+               plan.ws_total_bytes, d->workspace ? d->workspace_bytes : (size_t)0);
+      return set_error(B200PHI_WORKSPACE_TOO_SMALL, buf);
+    }
+    if (reinterpret_cast<uintptr_t>(d->workspace) % 256 != 0)
+      return set_error(B200PHI_INVALID_ARGUMENT, "workspace must be 256-byte aligned");
+  }
+  ReduceArgs a{&plan, d->x, d->out, d->workspace, stream};
+  switch (d->op) {
+    case B200PHI_SUM:
+    case B200PHI_MEAN:
+      rc = launch_sum(a);
+      break;
+    case B200PHI_PROD:
+      rc = launch_prod(a);
+      break;
+    case B200PHI_MAX:
+    case B200PHI_MIN:
+    case B200PHI_AMAX:
+    case B200PHI_AMIN:
+      rc = launch_minmax(a);
+      break;
+    default:
+      rc = launch_logical(a);
+      break;
+  }
+  if (rc == B200PHI_UNSUPPORTED) return set_error(rc, "dtype/op combination not built");
+  return rc;
+}
+
+int run_argreduce(const b200phi_argreduce_desc* d, cudaStream_t stream);
+int run_rowstats(const b200phi_rowstats_desc* d, cudaStream_t stream);
+int run_elementwise(const b200phi_elementwise_desc* d, cudaStream_t stream);
+int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, void* comm,
+                       cudaStream_t stream);
+int comm_unique_id(unsigned char id[128]);
+int comm_init_rank(const unsigned char id[128], int nranks, int rank, void** comm);
+int comm_destroy(void* comm);
+
+}  // namespace b200phi
+
+using namespace b200phi;
+
+extern "C" {
+
+const char* b200phi_last_error(void) { return g_last_error.c_str(); }
+
+const char* b200phi_version(void) { return "b200phi 0.1 sm_100a"; }
+
+size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d) {
+  ReducePlan plan;
+  std::string err;
+  if (plan_reduce(d, default_tunables(current_sm_count()), &plan, &err) != B200PHI_OK) return 0;
+  return plan.ws_total_bytes;
+}
+
+int b200phi_reduce(const b200phi_reduce_desc* d, void* stream) {
+  return run_reduce(d, static_cast<cudaStream_t>(stream));
+}
+
+int b200phi_argreduce(const b200phi_argreduce_desc* d, void* stream) {
+  return run_argreduce(d, static_cast<cudaStream_t>(stream));
+}
+
+int b200phi_rowstats(const b200phi_rowstats_desc* d, void* stream) {
+  return run_rowstats(d, static_cast<cudaStream_t>(stream));
+}
+
+int b200phi_elementwise(const b200phi_elementwise_desc* d, void* stream) {
+  return run_elementwise(d, static_cast<cudaStream_t>(stream));
+}
+
+int b200phi_comm_unique_id(unsigned char id[128]) { return comm_unique_id(id); }
+
+int b200phi_comm_init_rank(const unsigned char id[128], int nranks, int rank, void** comm) {
+  return comm_init_rank(id, nranks, rank, comm);
+}
+
+int b200phi_comm_destroy(void* comm) { return comm_destroy(comm); }
+
+int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count, void* comm,
+                           void* stream) {
+  return run_sharded_reduce(d, global_reduce_count, comm, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,321 @@
+// argmax / argmin for sm_100a.  Replaces ArgCUDAKernel + ComputeFullArg
+// (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:58-145): instead of one scalar
+// strided load per element and a cub::BlockReduce of KeyValuePair<int,T>, rows are
+// streamed with 16-byte loads, indices are 64-bit, and the combine rule
+// "better value, else lower index" is applied at every level so ties are
+// bit-exact with the CPU kernel (Eigen argmax, cpu/arg_min_max_kernel.cc:46-59).
+#include <string>
+
+#include "../../include/b200phi.h"
+#include "prim.cuh"
+#include "reduce_plan.h"
+
+namespace b200phi {
+
+int set_error(int code, const std::string& msg);
+int cuda_status(cudaError_t e);
+int current_sm_count();
+
+template <typename V>
+struct ArgPair {
+  V v;
+  long long i;
+};
+
+// kMax: b replaces a when b.v > a.v, or equal and b.i < a.i.
+template <typename V, bool kMax>
+struct ArgOp {
+  static __device__ __forceinline__ ArgPair<V> identity() {
+    ArgPair<V> p;
+    p.v = kMax ? Limits<V>::lowest() : Limits<V>::highest();
+    p.i = 0;  // an all-identity slice answers 0, like the CPU kernel
+    return p;
+  }
+  static __device__ __forceinline__ bool better(V b, V a) { return kMax ? (b > a) : (b < a); }
+  static __device__ __forceinline__ ArgPair<V> combine(ArgPair<V> a, ArgPair<V> b) {
+    const bool take = better(b.v, a.v) || (b.v == a.v && b.i < a.i);
+    return take ? b : a;
+  }
+  // in-order visit by one thread: strict comparison keeps the first occurrence
+  static __device__ __forceinline__ void visit(ArgPair<V>& a, V v, long long i) {
+    if (better(v, a.v)) {
+      a.v = v;
+      a.i = i;
+    }
+  }
+};
+
+template <typename V>
+__device__ __forceinline__ ArgPair<V> shfl_pair(ArgPair<V> p, int m) {
+  ArgPair<V> r;
+  r.v = __shfl_xor_sync(0xffffffffu, p.v, m);
+  r.i = __shfl_xor_sync(0xffffffffu, p.i, m);
+  return r;
+}
+
+template <typename V, typename Op>
+__device__ __forceinline__ ArgPair<V> warp_arg(ArgPair<V> p) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) p = Op::combine(p, shfl_pair(p, m));
+  return p;
+}
+
+template <typename T>
+struct StoreVal {
+  template <typename V>
+  static __device__ __forceinline__ void put(void* p, long long slot, V v) {
+    reinterpret_cast<T*>(p)[slot] = static_cast<T>(v);
+  }
+};
+template <>
+struct StoreVal<__nv_bfloat16> {
+  static __device__ __forceinline__ void put(void* p, long long slot, float v) {
+    reinterpret_cast<__nv_bfloat16*>(p)[slot] = __float2bfloat16_rn(v);  // exact: v came from bf16
+  }
+};
+template <>
+struct StoreVal<__half> {
+  static __device__ __forceinline__ void put(void* p, long long slot, float v) {
+    reinterpret_cast<__half*>(p)[slot] = __float2half_rn(v);
+  }
+};
+
+template <typename T, typename V>
+__device__ __forceinline__ void store_arg(void* out, int index_dtype, void* val_out, long long slot,
+                                          const ArgPair<V>& p) {
+  if (index_dtype == B200PHI_INT32)
+    reinterpret_cast<int*>(out)[slot] = static_cast<int>(p.i);
+  else
+    reinterpret_cast<long long*>(out)[slot] = p.i;
+  if (val_out) StoreVal<T>::put(val_out, slot, p.v);
+}
+
+// Scan `n` contiguous elements with a group of G threads.
+template <typename T, typename V, typename Op, int G, int U>
+__device__ __forceinline__ ArgPair<V> arg_span(const T* __restrict__ row, long long n, int g) {
+  constexpr int VE = VecOf<T>::kElems;
+  ArgPair<V> best = Op::identity();
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(row);
+  long long head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
+  if (head > n) head = n;
+  const long long nvec = (n - head) / VE;
+  const long long tail0 = head + nvec * VE;
+  if (g < head) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + g)), g);
+  const V16* __restrict__ vp = reinterpret_cast<const V16*>(row + head);
+  long long v = g;
+  for (; v + static_cast<long long>(U - 1) * G < nvec; v += static_cast<long long>(U) * G) {
+    V16 buf[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) buf[u] = ldg_stream16(vp + v + static_cast<long long>(u) * G);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      typename VecOf<T>::U w;
+      w.raw = buf[u];
+      const long long i0 = head + (v + static_cast<long long>(u) * G) * VE;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) Op::visit(best, Cvt<V, T>::to(w.e[e]), i0 + e);
+    }
+  }
+  for (; v < nvec; v += G) {
+    typename VecOf<T>::U w;
+    w.raw = ldg_stream16(vp + v);
+    const long long i0 = head + v * VE;
+#pragma unroll
+    for (int e = 0; e < VE; ++e) Op::visit(best, Cvt<V, T>::to(w.e[e]), i0 + e);
+  }
+  for (long long i = tail0 + g; i < n; i += G) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + i)), i);
+  return best;
+}
+
+// post == 1: [rows, n].  kWarpsPerRow as in row_reduce_kernel.
+template <typename T, typename V, bool kMax, int kWarpsPerRow>
+__global__ void __launch_bounds__(kBlock)
+    arg_row_kernel(const T* __restrict__ x, long long rows, long long n, void* out, int index_dtype,
+                   void* val_out) {
+  using Op = ArgOp<V, kMax>;
+  __shared__ V s_v[kWarps];
+  __shared__ long long s_i[kWarps];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if constexpr (kWarpsPerRow == 1) {
+    for (long long row = static_cast<long long>(blockIdx.x) * kWarps + warp; row < rows;
+         row += static_cast<long long>(gridDim.x) * kWarps) {
+      ArgPair<V> p = arg_span<T, V, Op, 32, 8>(x + row * n, n, lane);
+      p = warp_arg<V, Op>(p);
+      if (lane == 0) store_arg<T, V>(out, index_dtype, val_out, row, p);
+    }
+  } else {
+    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+      ArgPair<V> p = arg_span<T, V, Op, kBlock, 8>(x + row * n, n, threadIdx.x);
+      p = warp_arg<V, Op>(p);
+      __syncthreads();
+      if (lane == 0) {
+        s_v[warp] = p.v;
+        s_i[warp] = p.i;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        ArgPair<V> r;
+        r.v = s_v[0];
+        r.i = s_i[0];
+#pragma unroll
+        for (int w = 1; w < kWarps; ++w) {
+          ArgPair<V> q;
+          q.v = s_v[w];
+          q.i = s_i[w];
+          r = Op::combine(r, q);
+        }
+        store_arg<T, V>(out, index_dtype, val_out, row, r);
+      }
+    }
+  }
+}
+
+// post > 1: [pre, n, post].  Block = TX x TY: tx walks post (contiguous), ty walks n.
+template <typename T, typename V, bool kMax>
+__global__ void __launch_bounds__(kBlock)
+    arg_col_kernel(const T* __restrict__ x, long long n, long long post, int TX, long long tiles,
+                   void* out, int index_dtype, void* val_out) {
+  using Op = ArgOp<V, kMax>;
+  __shared__ V s_v[kBlock];
+  __shared__ long long s_i[kBlock];
+  const int TY = kBlock / TX;
+  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+  const long long o = blockIdx.x / tiles, tile = blockIdx.x % tiles;
+  const long long c = tile * TX + tx;
+  const bool live = c < post;
+  ArgPair<V> best = Op::identity();
+  if (live) {
+    const T* __restrict__ base = x + o * n * post + c;
+    long long r = ty;
+    for (; r + 3LL * TY < n; r += 4LL * TY) {
+      T b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) b[u] = ldg_scalar(base + (r + static_cast<long long>(u) * TY) * post);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) Op::visit(best, Cvt<V, T>::to(b[u]), r + static_cast<long long>(u) * TY);
+    }
+    for (; r < n; r += TY) Op::visit(best, Cvt<V, T>::to(ldg_scalar(base + r * post)), r);
+  }
+  s_v[ty * TX + tx] = best.v;
+  s_i[ty * TX + tx] = best.i;
+  __syncthreads();
+  for (int half = TY >> 1; half > 0; half >>= 1) {
+    if (ty < half) {
+      ArgPair<V> a, b;
+      a.v = s_v[ty * TX + tx];
+      a.i = s_i[ty * TX + tx];
+      b.v = s_v[(ty + half) * TX + tx];
+      b.i = s_i[(ty + half) * TX + tx];
+      a = Op::combine(a, b);
+      s_v[ty * TX + tx] = a.v;
+      s_i[ty * TX + tx] = a.i;
+    }
+    __syncthreads();
+  }
+  if (ty == 0 && live) {
+    ArgPair<V> r;
+    r.v = s_v[tx];
+    r.i = s_i[tx];
+    store_arg<T, V>(out, index_dtype, val_out, o * post + c, r);
+  }
+}
+
+struct ArgGeom {
+  long long pre, n, post;
+};
+
+template <typename T, typename V, bool kMax>
+static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, void* val_out,
+                      cudaStream_t stream) {
+  const int sms = current_sm_count();
+  if (g.post == 1) {
+    const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
+    if (g.pre >= static_cast<long long>(sms) * 16 && row_bytes <= 16384) {
+      long long ctas = (g.pre + kWarps - 1) / kWarps;
+      if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
+      arg_row_kernel<T, V, kMax, 1><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, g.pre, g.n, out, index_dtype, val_out);
+    } else {
+      long long ctas = g.pre > 0x7fffffffLL ? 0x7fffffffLL : g.pre;
+      arg_row_kernel<T, V, kMax, kWarps><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, g.pre, g.n, out, index_dtype, val_out);
+    }
+  } else {
+    int TX = 1;
+    while (TX < g.post && TX < kBlock) TX <<= 1;
+    const long long tiles = (g.post + TX - 1) / TX;
+    const long long blocks = g.pre * tiles;
+    if (blocks > 0x7fffffffLL) return set_error(B200PHI_UNSUPPORTED, "argreduce: output too large");
+    arg_col_kernel<T, V, kMax><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(
+        x, g.n, g.post, TX, tiles, out, index_dtype, val_out);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_status(e);
+  return B200PHI_OK;
+}
+
+template <typename T, typename V>
+static int launch_arg_op(int op, const void* x, const ArgGeom& g, void* out, int index_dtype,
+                         void* val_out, cudaStream_t s) {
+  if (op == B200PHI_ARGMAX)
+    return launch_arg<T, V, true>(static_cast<const T*>(x), g, out, index_dtype, val_out, s);
+  return launch_arg<T, V, false>(static_cast<const T*>(x), g, out, index_dtype, val_out, s);
+}
+
+int run_argreduce(const b200phi_argreduce_desc* d, cudaStream_t stream) {
+  if (!d) return set_error(B200PHI_INVALID_ARGUMENT, "null descriptor");
+  if (d->op != B200PHI_ARGMAX && d->op != B200PHI_ARGMIN)
+    return set_error(B200PHI_INVALID_ARGUMENT, "unknown arg op");
+  if (d->rank < 0 || d->rank > B200PHI_MAX_RANK)
+    return set_error(B200PHI_INVALID_ARGUMENT, "rank must be in [0, 9]");
+  int index_dtype = d->index_dtype == B200PHI_UNDEFINED ? B200PHI_INT64 : d->index_dtype;
+  if (index_dtype != B200PHI_INT32 && index_dtype != B200PHI_INT64)
+    return set_error(B200PHI_INVALID_ARGUMENT, "argmax/argmin index dtype must be int32 or int64");
+  long long numel = 1;
+  for (int i = 0; i < d->rank; ++i) {
+    if (d->dims[i] < 0) return set_error(B200PHI_INVALID_ARGUMENT, "negative extent");
+    numel *= d->dims[i];
+  }
+  if (numel <= 0)
+    return set_error(B200PHI_INVALID_ARGUMENT, "argmin/argmax input numel must > 0, bug got 0");
+  if (!d->x || !d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null tensor pointer");
+  ArgGeom g;
+  if (d->flatten || d->rank == 0) {
+    g.pre = 1;
+    g.n = numel;
+    g.post = 1;
+  } else {
+    long long axis = d->axis;
+    if (axis < -d->rank || axis >= d->rank)
+      return set_error(B200PHI_INVALID_ARGUMENT, "argmax/argmin axis out of range");
+    if (axis < 0) axis += d->rank;
+    g.pre = g.post = 1;
+    for (int i = 0; i < axis; ++i) g.pre *= d->dims[i];
+    g.n = d->dims[axis];
+    for (int i = static_cast<int>(axis) + 1; i < d->rank; ++i) g.post *= d->dims[i];
+  }
+  if (index_dtype == B200PHI_INT32 && g.n > 0x7fffffffLL)
+    return set_error(B200PHI_INVALID_ARGUMENT, "int32 indices need the reduced extent <= INT_MAX");
+  switch (d->in_dtype) {
+    case B200PHI_FLOAT32:
+      return launch_arg_op<float, float>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_FLOAT64:
+      return launch_arg_op<double, double>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_BFLOAT16:
+      return launch_arg_op<__nv_bfloat16, float>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_FLOAT16:
+      return launch_arg_op<__half, float>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_INT64:
+      return launch_arg_op<long long, long long>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_INT32:
+      return launch_arg_op<int32_t, int32_t>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_INT16:
+      return launch_arg_op<int16_t, int32_t>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    case B200PHI_UINT8:
+      return launch_arg_op<uint8_t, int32_t>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);
+    default:
+      return set_error(B200PHI_UNSUPPORTED, "argmax/argmin: dtype not built");
+  }
+}
+
+}  // namespace b200phi

@@ -1,0 +1,470 @@
+// n-ary broadcast / elementwise engine with a fused unary epilogue, sm_100a.
+// Replaces VectorizedBroadcastKernel (broadcast_function.h:284-435),
+// VectorizedElementwiseKernel (elementwise_base.h:690-722) and the 2018-era
+// FusedElemwiseAndActBroadcast{1,2}CUDAKernel (elementwise_op_function.h:203-350,
+// grid = n = 64 CTAs for config C2).
+//
+// bcast_rows_kernel: the output is viewed as [rows, inner] with `inner` the
+// innermost merged dim.  A CTA owns one chunk of one row; the per-input base
+// offset of the row is unravelled once per CTA (not per element), then the inner
+// loop is pure 16-byte loads -> functor -> 16-byte streaming stores.  An input
+// that is broadcast along `inner` is read once per row and splatted.
+// bcast_generic_kernel: per-element unravel, for outputs whose innermost merged
+// dim is tiny (e.g. [10,3,1,4] + [10,1,12,1]).
+#include <string>
+
+#include "../../include/b200phi.h"
+#include "bcast_plan.h"
+#include "prim.cuh"
+
+namespace b200phi {
+
+int set_error(int code, const std::string& msg);
+int cuda_status(cudaError_t e);
+
+// ---- compute type ------------------------------------------------------------------
+template <typename T>
+struct ComputeT {
+  using type = T;
+};
+template <>
+struct ComputeT<__nv_bfloat16> {
+  using type = float;
+};
+template <>
+struct ComputeT<__half> {
+  using type = float;
+};
+template <>
+struct ComputeT<int16_t> {
+  using type = int;
+};
+template <>
+struct ComputeT<int8_t> {
+  using type = int;
+};
+template <>
+struct ComputeT<uint8_t> {
+  using type = int;
+};
+template <>
+struct ComputeT<Bool8> {
+  using type = int;
+};
+
+template <typename T, typename C>
+__device__ __forceinline__ T from_compute(C v) {
+  return static_cast<T>(v);
+}
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_compute<__nv_bfloat16, float>(float v) {
+  return __float2bfloat16_rn(v);
+}
+template <>
+__device__ __forceinline__ __half from_compute<__half, float>(float v) {
+  return __float2half_rn(v);
+}
+template <>
+__device__ __forceinline__ Bool8 from_compute<Bool8, int>(int v) {
+  Bool8 b;
+  b.v = v != 0 ? 1 : 0;
+  return b;
+}
+
+// ---- functors --------------------------------------------------------------------------
+template <typename C>
+__device__ __forceinline__ C binary_apply(int op, C a, C b) {
+  switch (op) {
+    case B200PHI_ADD:
+      return a + b;
+    case B200PHI_SUBTRACT:
+      return a - b;
+    case B200PHI_MULTIPLY:
+      return a * b;
+    case B200PHI_DIVIDE:
+      if constexpr (std::numeric_limits<C>::is_integer) {
+        return b == C(0) ? C(0) : a / b;
+      } else {
+        return a / b;
+      }
+    case B200PHI_MAXIMUM:
+      return a > b ? a : b;
+    default:
+      return a < b ? a : b;
+  }
+}
+
+template <typename C>
+__device__ __forceinline__ C unary_apply(int act, C v, float scale) {
+  if constexpr (std::numeric_limits<C>::is_integer) {
+    return act == B200PHI_ACT_RELU ? (v > C(0) ? v : C(0)) : v;
+  } else {
+    switch (act) {
+      case B200PHI_ACT_RELU:
+        return v > C(0) ? v : C(0);
+      case B200PHI_ACT_SCALE:
+        return v * static_cast<C>(scale);
+      case B200PHI_ACT_GELU:
+        return C(0.5) * v * (C(1) + erf(v * C(0.70710678118654752440)));
+      case B200PHI_ACT_SIGMOID:
+        return C(1) / (C(1) + exp(-v));
+      case B200PHI_ACT_TANH:
+        return tanh(v);
+      default:
+        return v;
+    }
+  }
+}
+
+// compile-time functor for the hot combinations
+template <int kBinary, int kAct>
+struct StaticF {
+  static constexpr bool kInter = false;  // never asked for save_intermediate_out
+  template <typename C>
+  __device__ __forceinline__ C pre(C a, C b, C c, int arity) const {
+    return binary_apply<C>(kBinary, a, b);
+  }
+  template <typename C>
+  __device__ __forceinline__ C post(C t) const {
+    return unary_apply<C>(kAct, t, 0.f);
+  }
+};
+
+// everything else: functor ids are kernel arguments (uniform branches)
+struct RuntimeF {
+  static constexpr bool kInter = true;
+  int binary, act, compound;
+  float scale;
+  template <typename C>
+  __device__ __forceinline__ C pre(C a, C b, C c, int arity) const {
+    if (arity == 1) return a;
+    if (compound) return binary_apply<C>(binary, a, unary_apply<C>(act, b, scale));
+    C t = binary_apply<C>(binary, a, b);
+    if (arity == 3) t = binary_apply<C>(binary, t, c);
+    return t;
+  }
+  template <typename C>
+  __device__ __forceinline__ C post(C t) const {
+    return compound ? t : unary_apply<C>(act, t, scale);
+  }
+};
+
+// ---- kernels ----------------------------------------------------------------------------
+template <int Arity>
+struct RowsParams {
+  const void* in[Arity];
+  void* out;
+  void* inter;  // optional second output: pre() result (save_intermediate_out)
+  int nouter;
+  long long oext[B200PHI_MAX_RANK];
+  long long ostride[Arity][B200PHI_MAX_RANK];
+  long long inner;
+  int istride[Arity];  // 0 or 1
+  long long chunk_v;   // 16-byte vectors per chunk
+  long long chunks;    // chunks per row
+};
+
+template <typename T, typename F, int Arity>
+__global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p, F f) {
+  using C = typename ComputeT<T>::type;
+  constexpr int VE = VecOf<T>::kElems;
+  constexpr int U = 4;
+  const long long row = blockIdx.x / p.chunks, chunk = blockIdx.x % p.chunks;
+
+  // per-row base offsets (uniform over the CTA)
+  const T* src[Arity];
+  {
+    long long off[Arity];
+#pragma unroll
+    for (int i = 0; i < Arity; ++i) off[i] = 0;
+    long long idx = row;
+    for (int k = p.nouter - 1; k >= 0; --k) {
+      const long long e = p.oext[k];
+      const long long q = idx / e, rem = idx - q * e;
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) off[i] += rem * p.ostride[i][k];
+      idx = q;
+    }
+#pragma unroll
+    for (int i = 0; i < Arity; ++i) src[i] = static_cast<const T*>(p.in[i]) + off[i];
+  }
+  T* __restrict__ dst = static_cast<T*>(p.out) + row * p.inner;
+  T* __restrict__ dst2 = nullptr;
+  if constexpr (F::kInter) dst2 = p.inter ? static_cast<T*>(p.inter) + row * p.inner : nullptr;
+
+  C splat[Arity];
+  bool aligned = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) &&
+                 (!dst2 || reinterpret_cast<uintptr_t>(dst2) % 16 == 0);
+#pragma unroll
+  for (int i = 0; i < Arity; ++i) {
+    splat[i] = C(0);
+    if (p.istride[i] == 0) {
+      splat[i] = Cvt<C, T>::to(ldg_scalar(src[i]));
+    } else {
+      aligned = aligned && (reinterpret_cast<uintptr_t>(src[i]) % 16 == 0);
+    }
+  }
+
+  const long long nvec_row = p.inner / VE;
+  const long long v0 = chunk * p.chunk_v;
+  const bool last_chunk = (chunk == p.chunks - 1);
+
+  if (aligned) {
+    long long v1 = v0 + p.chunk_v;
+    if (v1 > nvec_row) v1 = nvec_row;
+    for (long long vb = v0 + threadIdx.x; vb < v1; vb += static_cast<long long>(U) * kBlock) {
+      V16 raw[Arity][U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long v = vb + static_cast<long long>(u) * kBlock;
+        if (v < v1) {
+#pragma unroll
+          for (int i = 0; i < Arity; ++i)
+            if (p.istride[i]) raw[i][u] = ldg_stream16(reinterpret_cast<const V16*>(src[i]) + v);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long v = vb + static_cast<long long>(u) * kBlock;
+        if (v < v1) {
+          typename VecOf<T>::U w[Arity], o, o2;
+#pragma unroll
+          for (int i = 0; i < Arity; ++i)
+            if (p.istride[i]) w[i].raw = raw[i][u];
+#pragma unroll
+          for (int e = 0; e < VE; ++e) {
+            C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+            for (int i = 0; i < Arity; ++i) a[i] = p.istride[i] ? Cvt<C, T>::to(w[i].e[e]) : splat[i];
+            const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
+            o.e[e] = from_compute<T, C>(f.template post<C>(t));
+            if constexpr (F::kInter) o2.e[e] = from_compute<T, C>(t);
+          }
+          stg_stream16(reinterpret_cast<V16*>(dst) + v, o.raw);
+          if constexpr (F::kInter) {
+            if (dst2) stg_stream16(reinterpret_cast<V16*>(dst2) + v, o2.raw);
+          }
+        }
+      }
+    }
+    if (last_chunk) {
+      for (long long i = nvec_row * VE + threadIdx.x; i < p.inner; i += kBlock) {
+        C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+        for (int k = 0; k < Arity; ++k)
+          a[k] = p.istride[k] ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
+        const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
+        dst[i] = from_compute<T, C>(f.template post<C>(t));
+        if (dst2) dst2[i] = from_compute<T, C>(t);
+      }
+    }
+  } else {
+    const long long e0 = v0 * VE;
+    long long e1 = last_chunk ? p.inner : (v0 + p.chunk_v) * VE;
+    if (e1 > p.inner) e1 = p.inner;
+    for (long long i = e0 + threadIdx.x; i < e1; i += kBlock) {
+      C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+      for (int k = 0; k < Arity; ++k)
+        a[k] = p.istride[k] ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
+      const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
+      dst[i] = from_compute<T, C>(f.template post<C>(t));
+      if (dst2) dst2[i] = from_compute<T, C>(t);
+    }
+  }
+}
+
+template <int Arity>
+struct GenericParams {
+  const void* in[Arity];
+  void* out;
+  void* inter;
+  int ndim;
+  long long extent[B200PHI_MAX_RANK];
+  long long stride[Arity][B200PHI_MAX_RANK];
+  long long numel;
+};
+
+template <typename T, typename F, int Arity>
+__global__ void __launch_bounds__(kBlock) bcast_generic_kernel(GenericParams<Arity> p, F f) {
+  using C = typename ComputeT<T>::type;
+  for (long long o = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; o < p.numel;
+       o += static_cast<long long>(gridDim.x) * kBlock) {
+    long long off[Arity];
+#pragma unroll
+    for (int i = 0; i < Arity; ++i) off[i] = 0;
+    long long idx = o;
+    for (int k = p.ndim - 1; k >= 0; --k) {
+      const long long e = p.extent[k];
+      long long q, rem;
+      if ((static_cast<unsigned long long>(idx) | static_cast<unsigned long long>(e)) >> 32) {
+        q = idx / e;
+        rem = idx - q * e;
+      } else {
+        const unsigned qi = static_cast<unsigned>(idx) / static_cast<unsigned>(e);
+        q = qi;
+        rem = static_cast<unsigned>(idx) - qi * static_cast<unsigned>(e);
+      }
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) off[i] += rem * p.stride[i][k];
+      idx = q;
+    }
+    C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+    for (int i = 0; i < Arity; ++i)
+      a[i] = Cvt<C, T>::to(ldg_scalar(static_cast<const T*>(p.in[i]) + off[i]));
+    const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
+    static_cast<T*>(p.out)[o] = from_compute<T, C>(f.template post<C>(t));
+    if (p.inter) static_cast<T*>(p.inter)[o] = from_compute<T, C>(t);
+  }
+}
+
+// ---- launch -----------------------------------------------------------------------------
+template <typename T, typename F, int Arity>
+static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, F f, void* inter,
+                        cudaStream_t stream) {
+  constexpr int VE = VecOf<T>::kElems;
+  if (bp.use_rows_kernel) {
+    RowsParams<Arity> p;
+    for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
+    p.out = d->out;
+    p.inter = inter;
+    p.nouter = bp.ndim - 1;
+    for (int k = 0; k < bp.ndim - 1; ++k) {
+      p.oext[k] = bp.extent[k];
+      for (int i = 0; i < Arity; ++i) p.ostride[i][k] = bp.stride[i][k];
+    }
+    p.inner = bp.inner;
+    for (int i = 0; i < Arity; ++i) p.istride[i] = bp.stride[i][bp.ndim - 1] ? 1 : 0;
+    const long long nvec = (bp.inner + VE - 1) / VE;
+    const long long max_chunk = static_cast<long long>(kBlock) * 8;  // 8 vectors per thread
+    p.chunks = (nvec + max_chunk - 1) / max_chunk;
+    if (p.chunks < 1) p.chunks = 1;
+    p.chunk_v = (nvec + p.chunks - 1) / p.chunks;
+    const long long blocks = bp.rows * p.chunks;
+    if (blocks > 0x7fffffffLL) return set_error(B200PHI_UNSUPPORTED, "elementwise: too many rows");
+    bcast_rows_kernel<T, F, Arity><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(p, f);
+  } else {
+    GenericParams<Arity> p;
+    for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
+    p.out = d->out;
+    p.inter = inter;
+    p.ndim = bp.ndim;
+    for (int k = 0; k < bp.ndim; ++k) {
+      p.extent[k] = bp.extent[k];
+      for (int i = 0; i < Arity; ++i) p.stride[i][k] = bp.stride[i][k];
+    }
+    p.numel = bp.out_numel;
+    long long blocks = (bp.out_numel + kBlock - 1) / kBlock;
+    if (blocks > 148LL * 8 * 64) blocks = 148LL * 8 * 64;
+    bcast_generic_kernel<T, F, Arity><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(p, f);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_status(e);
+  return B200PHI_OK;
+}
+
+template <typename T>
+static int launch_runtime(const b200phi_elementwise_desc* d, const BcastPlan& bp, void* inter,
+                          cudaStream_t s) {
+  RuntimeF f{d->binary, d->act, d->compound, d->scale};
+  switch (d->arity) {
+    case 1:
+      return launch_bcast<T, RuntimeF, 1>(d, bp, f, inter, s);
+    case 2:
+      return launch_bcast<T, RuntimeF, 2>(d, bp, f, inter, s);
+    default:
+      return launch_bcast<T, RuntimeF, 3>(d, bp, f, inter, s);
+  }
+}
+
+// hot = binary op without epilogue, or relu(x + y); two inputs; no second output
+template <typename T>
+static int launch_typed(const b200phi_elementwise_desc* d, const BcastPlan& bp, void* inter,
+                        cudaStream_t s) {
+  if (d->arity == 2 && !inter && d->compound == 0) {
+    if (d->act == B200PHI_ACT_NONE) {
+      switch (d->binary) {
+        case B200PHI_ADD:
+          return launch_bcast<T, StaticF<B200PHI_ADD, 0>, 2>(d, bp, {}, nullptr, s);
+        case B200PHI_SUBTRACT:
+          return launch_bcast<T, StaticF<B200PHI_SUBTRACT, 0>, 2>(d, bp, {}, nullptr, s);
+        case B200PHI_MULTIPLY:
+          return launch_bcast<T, StaticF<B200PHI_MULTIPLY, 0>, 2>(d, bp, {}, nullptr, s);
+        case B200PHI_DIVIDE:
+          return launch_bcast<T, StaticF<B200PHI_DIVIDE, 0>, 2>(d, bp, {}, nullptr, s);
+        case B200PHI_MAXIMUM:
+          return launch_bcast<T, StaticF<B200PHI_MAXIMUM, 0>, 2>(d, bp, {}, nullptr, s);
+        default:
+          return launch_bcast<T, StaticF<B200PHI_MINIMUM, 0>, 2>(d, bp, {}, nullptr, s);
+      }
+    }
+    if (d->act == B200PHI_ACT_RELU && d->binary == B200PHI_ADD)
+      return launch_bcast<T, StaticF<B200PHI_ADD, B200PHI_ACT_RELU>, 2>(d, bp, {}, nullptr, s);
+  }
+  return launch_runtime<T>(d, bp, inter, s);
+}
+
+int run_elementwise(const b200phi_elementwise_desc* d, cudaStream_t stream) {
+  BcastPlan bp;
+  std::string err;
+  int rc = plan_broadcast(d, &bp, &err);
+  if (rc != B200PHI_OK) return set_error(rc, err);
+  if (d->binary < B200PHI_ADD || d->binary > B200PHI_MINIMUM)
+    return set_error(B200PHI_INVALID_ARGUMENT, "unknown binary functor");
+  if (d->act < B200PHI_ACT_NONE || d->act > B200PHI_ACT_TANH)
+    return set_error(B200PHI_INVALID_ARGUMENT, "unknown unary functor");
+  if (d->compound && (d->arity != 2 || d->act == B200PHI_ACT_NONE))
+    return set_error(B200PHI_INVALID_ARGUMENT, "compound == 1 needs two inputs and a unary functor");
+  if (bp.out_numel == 0) return B200PHI_OK;
+  if (!d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null output pointer");
+  for (int i = 0; i < d->arity; ++i)
+    if (!d->in[i].data) return set_error(B200PHI_INVALID_ARGUMENT, "null input pointer");
+
+  void* inter = d->intermediate_out;
+  if (inter && d->compound) {
+    // intermediate = act(in1), shaped like in1: a unary pass over in1 alone
+    b200phi_elementwise_desc u = *d;
+    u.arity = 1;
+    u.compound = 0;
+    u.in[0] = d->in[1];
+    u.out_rank = d->in[1].rank;
+    for (int k = 0; k < d->in[1].rank; ++k) u.out_dims[k] = d->in[1].dims[k];
+    u.out = inter;
+    u.intermediate_out = nullptr;
+    u.axis = -1;
+    rc = run_elementwise(&u, stream);
+    if (rc != B200PHI_OK) return rc;
+    inter = nullptr;
+  }
+  const bool is_float = d->dtype == B200PHI_FLOAT32 || d->dtype == B200PHI_FLOAT64 ||
+                        d->dtype == B200PHI_FLOAT16 || d->dtype == B200PHI_BFLOAT16;
+  if (!is_float && d->act != B200PHI_ACT_NONE && d->act != B200PHI_ACT_RELU)
+    return set_error(B200PHI_UNSUPPORTED, "this unary functor needs a floating-point dtype");
+  switch (d->dtype) {
+    case B200PHI_FLOAT32:
+      return launch_typed<float>(d, bp, inter, stream);
+    case B200PHI_FLOAT64:
+      return launch_typed<double>(d, bp, inter, stream);
+    case B200PHI_BFLOAT16:
+      return launch_typed<__nv_bfloat16>(d, bp, inter, stream);
+    case B200PHI_FLOAT16:
+      return launch_typed<__half>(d, bp, inter, stream);
+    case B200PHI_INT32:
+      return launch_typed<int32_t>(d, bp, inter, stream);
+    case B200PHI_INT64:
+      return launch_typed<long long>(d, bp, inter, stream);
+    case B200PHI_INT16:
+      return launch_runtime<int16_t>(d, bp, inter, stream);
+    case B200PHI_INT8:
+      return launch_runtime<int8_t>(d, bp, inter, stream);
+    case B200PHI_UINT8:
+      return launch_runtime<uint8_t>(d, bp, inter, stream);
+    case B200PHI_BOOL:
+      return launch_runtime<Bool8>(d, bp, inter, stream);
+    default:
+      return set_error(B200PHI_UNSUPPORTED, "elementwise: dtype not built");
+  }
+}
+
+}  // namespace b200phi

@@ -1,0 +1,270 @@
+// Device building blocks shared by the reduce / arg / broadcast kernels.
+// Plays the role of the reference's KPS layer
+// (paddle/phi/kernels/primitive/{compute,datamover,functor}_primitives.h) but is
+// written for sm_100a only: 16-byte streaming loads that bypass L1, xor-shuffle
+// warp combines, and one shared-memory hop per block combine.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <limits>
+
+namespace b200phi {
+
+constexpr int kBlock = 256;  // threads per CTA for every streaming kernel
+constexpr int kWarps = kBlock / 32;
+constexpr int kMaxRank = 9;  // common/ddim.h:71
+
+// bool tensors are bytes; a distinct type keeps the `!= 0` rule in the loader.
+struct Bool8 {
+  uint8_t v;
+};
+
+struct alignas(16) V16 {
+  uint32_t w[4];
+};
+
+// Streaming 16-byte load: read-only path, no L1 allocation (each byte is used once).
+__device__ __forceinline__ V16 ldg_stream16(const void* p) {
+  V16 r;
+  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+      : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3])
+      : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ void stg_stream16(void* p, const V16& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.w[0]),
+               "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3])
+               : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ T ldg_scalar(const T* p) {
+  return __ldg(p);
+}
+template <>
+__device__ __forceinline__ __nv_bfloat16 ldg_scalar(const __nv_bfloat16* p) {
+  unsigned short u = __ldg(reinterpret_cast<const unsigned short*>(p));
+  return __ushort_as_bfloat16(u);
+}
+template <>
+__device__ __forceinline__ __half ldg_scalar(const __half* p) {
+  unsigned short u = __ldg(reinterpret_cast<const unsigned short*>(p));
+  return __ushort_as_half(u);
+}
+template <>
+__device__ __forceinline__ Bool8 ldg_scalar(const Bool8* p) {
+  Bool8 b;
+  b.v = __ldg(reinterpret_cast<const uint8_t*>(p));
+  return b;
+}
+
+// ---- element conversion: storage type -> accumulation type ------------------
+// Mirrors "cast x to out_dtype, then accumulate in MPType"
+// (gpu/reduce.h:48-69, amp_type_traits.h:25-53) without the extra pass.
+template <typename Acc, typename T>
+struct Cvt {
+  static __device__ __forceinline__ Acc to(T v) { return static_cast<Acc>(v); }
+};
+template <typename Acc>
+struct Cvt<Acc, __nv_bfloat16> {
+  static __device__ __forceinline__ Acc to(__nv_bfloat16 v) {
+    return static_cast<Acc>(__bfloat162float(v));
+  }
+};
+template <typename Acc>
+struct Cvt<Acc, __half> {
+  static __device__ __forceinline__ Acc to(__half v) { return static_cast<Acc>(__half2float(v)); }
+};
+template <typename Acc>
+struct Cvt<Acc, Bool8> {
+  static __device__ __forceinline__ Acc to(Bool8 v) { return static_cast<Acc>(v.v != 0 ? 1 : 0); }
+};
+
+// Truthiness used by any/all: the reference casts to bool first (cpu/reduce.h:90-98).
+template <typename T>
+__device__ __forceinline__ int truthy(T v) {
+  return v != static_cast<T>(0) ? 1 : 0;
+}
+template <>
+__device__ __forceinline__ int truthy(__nv_bfloat16 v) {
+  return __bfloat162float(v) != 0.f ? 1 : 0;
+}
+template <>
+__device__ __forceinline__ int truthy(__half v) {
+  return __half2float(v) != 0.f ? 1 : 0;
+}
+template <>
+__device__ __forceinline__ int truthy(Bool8 v) {
+  return v.v != 0 ? 1 : 0;
+}
+
+// ---- reduce operators (functor_primitives.h:140-209) -------------------------
+template <typename Acc>
+struct SumOp {
+  static constexpr bool kLogical = false;
+  static __device__ __forceinline__ Acc identity() { return Acc(0); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return a + b; }
+};
+template <typename Acc>
+struct ProdOp {
+  static constexpr bool kLogical = false;
+  static __device__ __forceinline__ Acc identity() { return Acc(1); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return a * b; }
+};
+template <typename Acc>
+struct Limits {
+  static __device__ __forceinline__ Acc lowest() { return std::numeric_limits<Acc>::lowest(); }
+  static __device__ __forceinline__ Acc highest() { return std::numeric_limits<Acc>::max(); }
+};
+template <>
+struct Limits<float> {
+  static __device__ __forceinline__ float lowest() { return -3.402823466e+38f; }
+  static __device__ __forceinline__ float highest() { return 3.402823466e+38f; }
+};
+template <>
+struct Limits<double> {
+  static __device__ __forceinline__ double lowest() { return -1.7976931348623157e+308; }
+  static __device__ __forceinline__ double highest() { return 1.7976931348623157e+308; }
+};
+template <>
+struct Limits<long long> {
+  static __device__ __forceinline__ long long lowest() { return (-9223372036854775807LL - 1); }
+  static __device__ __forceinline__ long long highest() { return 9223372036854775807LL; }
+};
+template <typename Acc>
+struct MaxOp {  // (b > a) ? b : a, seed lowest()
+  static constexpr bool kLogical = false;
+  static __device__ __forceinline__ Acc identity() { return Limits<Acc>::lowest(); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return (b > a) ? b : a; }
+};
+template <typename Acc>
+struct MinOp {  // (b < a) ? b : a, seed max()
+  static constexpr bool kLogical = false;
+  static __device__ __forceinline__ Acc identity() { return Limits<Acc>::highest(); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return (b < a) ? b : a; }
+};
+template <typename Acc>
+struct AnyOp {
+  static constexpr bool kLogical = true;
+  static __device__ __forceinline__ Acc identity() { return Acc(0); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return a | b; }
+};
+template <typename Acc>
+struct AllOp {
+  static constexpr bool kLogical = true;
+  static __device__ __forceinline__ Acc identity() { return Acc(1); }
+  static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return a & b; }
+};
+
+// Load one element as the accumulation type, honouring the any/all truthiness rule.
+template <typename Acc, typename Op, typename T>
+__device__ __forceinline__ Acc load_as(T v) {
+  if constexpr (Op::kLogical) {
+    return static_cast<Acc>(truthy(v));
+  } else {
+    return Cvt<Acc, T>::to(v);
+  }
+}
+
+// ---- 16-byte vector of T ------------------------------------------------------
+template <typename T>
+struct VecOf {
+  static constexpr int kElems = 16 / sizeof(T);
+  union U {
+    V16 raw;
+    T e[kElems];
+    __device__ U() {}
+  };
+};
+
+// Fold a 16-byte vector into kLanes independent accumulators (shorter add chains).
+template <typename Acc, typename Op, typename T, int kLanes>
+__device__ __forceinline__ void fold_vec(const V16& raw, Acc (&acc)[kLanes]) {
+  typename VecOf<T>::U u;
+  u.raw = raw;
+#pragma unroll
+  for (int e = 0; e < VecOf<T>::kElems; ++e) {
+    acc[e % kLanes] = Op::combine(acc[e % kLanes], load_as<Acc, Op>(u.e[e]));
+  }
+}
+
+// ---- warp / block combines ------------------------------------------------------
+template <typename Acc>
+__device__ __forceinline__ Acc shfl_xor(Acc v, int m) {
+  return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+template <typename Acc, typename Op>
+__device__ __forceinline__ Acc warp_combine(Acc v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v = Op::combine(v, shfl_xor(v, m));
+  return v;
+}
+
+// All kBlock threads call; result valid in every thread. `smem` holds kWarps Acc.
+template <typename Acc, typename Op>
+__device__ __forceinline__ Acc block_combine(Acc v, Acc* smem) {
+  v = warp_combine<Acc, Op>(v);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();  // smem may still be read by the previous round
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  Acc r = smem[0];
+#pragma unroll
+  for (int w = 1; w < kWarps; ++w) r = Op::combine(r, smem[w]);
+  return r;
+}
+
+// ---- typed result store -----------------------------------------------------------
+struct Epilogue {
+  void* out;
+  int out_dtype;    // b200phi_dtype
+  int is_mean;      // divide by count before the store (reduce_function.h:686-688)
+  long long count;  // reduce_num
+};
+
+template <typename Acc>
+__device__ __forceinline__ void store_result(const Epilogue& ep, long long idx, Acc v) {
+  if (ep.is_mean) v = v / static_cast<Acc>(ep.count);
+  switch (ep.out_dtype) {
+    case 1:  // BOOL
+      reinterpret_cast<uint8_t*>(ep.out)[idx] = (v != Acc(0)) ? 1 : 0;
+      break;
+    case 2:
+      reinterpret_cast<uint8_t*>(ep.out)[idx] = static_cast<uint8_t>(v);
+      break;
+    case 3:
+      reinterpret_cast<int8_t*>(ep.out)[idx] = static_cast<int8_t>(v);
+      break;
+    case 5:
+      reinterpret_cast<int16_t*>(ep.out)[idx] = static_cast<int16_t>(v);
+      break;
+    case 7:
+      reinterpret_cast<int32_t*>(ep.out)[idx] = static_cast<int32_t>(v);
+      break;
+    case 9:
+      reinterpret_cast<long long*>(ep.out)[idx] = static_cast<long long>(v);
+      break;
+    case 10:
+      reinterpret_cast<float*>(ep.out)[idx] = static_cast<float>(v);
+      break;
+    case 11:
+      reinterpret_cast<double*>(ep.out)[idx] = static_cast<double>(v);
+      break;
+    case 15:
+      reinterpret_cast<__half*>(ep.out)[idx] = __float2half_rn(static_cast<float>(v));
+      break;
+    case 16:
+      reinterpret_cast<__nv_bfloat16*>(ep.out)[idx] = __float2bfloat16_rn(static_cast<float>(v));
+      break;
+    default:
+      break;
+  }
+}
+
+}  // namespace b200phi

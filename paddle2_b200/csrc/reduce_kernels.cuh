@@ -1,0 +1,327 @@
+// Reduction kernels for sm_100a.  Four shapes of work after the host has merged
+// the dims (reduce_plan.h):
+//   row_reduce_kernel    [rows, cols] -> [rows]       contiguous axis reduced   (replaces ReduceAnyKernel
+//                                                     in its kReduceLastDim mode, reduce_function.h:573-699)
+//   row_split_kernel     same, few very long rows: the row is cut across CTAs and the last CTA to
+//                        finish combines the partials (replaces CubTensorReduce :938-1039 and the
+//                        Eigen detour for numel > INT32_MAX, kps/reduce_kernel.cu:196-243)
+//   col_reduce_kernel    [outer, R, inner] -> [outer, inner]  (replaces ReduceHigherDimKernel :706-788
+//                        and its second pass; one launch, last-block finalise)
+//   generic_reduce_kernel  any alternating keep/reduce pattern up to rank 9 (kReduceAny mode)
+// All index math is 64-bit: a 2^31-element shard is an ordinary input.
+#pragma once
+
+#include "prim.cuh"
+
+namespace b200phi {
+
+constexpr int kFoldLanes = 4;  // independent accumulators per thread
+
+template <typename Acc, typename Op>
+__device__ __forceinline__ Acc fold_lanes(Acc (&a)[kFoldLanes]) {
+  return Op::combine(Op::combine(a[0], a[1]), Op::combine(a[2], a[3]));
+}
+
+// Consume as many batches of UU strided 16-byte vectors as fit: all UU loads are
+// issued before the first use so UU requests per thread are in flight.
+template <typename T, typename Acc, typename Op, int G, int UU>
+__device__ __forceinline__ void span_step(const V16* __restrict__ vp, long long& v, long long nvec,
+                                          Acc (&acc)[kFoldLanes]) {
+  for (; v + static_cast<long long>(UU - 1) * G < nvec; v += static_cast<long long>(UU) * G) {
+    V16 buf[UU];
+#pragma unroll
+    for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(vp + v + static_cast<long long>(u) * G);
+#pragma unroll
+    for (int u = 0; u < UU; ++u) fold_vec<Acc, Op, T, kFoldLanes>(buf[u], acc);
+  }
+}
+
+// Reduce `cols` contiguous elements starting at `row` with a group of G threads
+// (g = index in group). Handles any element alignment: scalar head up to the
+// first 16-byte boundary, 16-byte vectors, scalar tail.
+template <typename T, typename Acc, typename Op, int G, int U>
+__device__ __forceinline__ Acc reduce_span(const T* __restrict__ row, long long cols, int g) {
+  constexpr int VE = VecOf<T>::kElems;
+  Acc acc[kFoldLanes];
+#pragma unroll
+  for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(row);
+  long long head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
+  if (head > cols) head = cols;
+  const long long nvec = (cols - head) / VE;
+  const long long tail0 = head + nvec * VE;
+
+  if (g < head) acc[0] = Op::combine(acc[0], load_as<Acc, Op>(ldg_scalar(row + g)));
+
+  const V16* __restrict__ vp = reinterpret_cast<const V16*>(row + head);
+  long long v = g;
+  span_step<T, Acc, Op, G, U>(vp, v, nvec, acc);
+  if constexpr (U > 4) span_step<T, Acc, Op, G, 4>(vp, v, nvec, acc);
+  if constexpr (U > 2) span_step<T, Acc, Op, G, 2>(vp, v, nvec, acc);
+  if constexpr (U > 1) span_step<T, Acc, Op, G, 1>(vp, v, nvec, acc);
+  for (long long i = tail0 + g; i < cols; i += G)
+    acc[1] = Op::combine(acc[1], load_as<Acc, Op>(ldg_scalar(row + i)));
+  return fold_lanes<Acc, Op>(acc);
+}
+
+// kWarpsPerRow == 1: one warp per row, no block barrier at all.
+// kWarpsPerRow == kWarps: the CTA works on one row at a time.
+template <typename T, typename Acc, typename Op, int kWarpsPerRow, int U>
+__global__ void __launch_bounds__(kBlock)
+    row_reduce_kernel(const T* __restrict__ x, long long rows, long long cols, Epilogue ep) {
+  __shared__ Acc smem[kWarps];
+  constexpr int kRowsPerCta = kWarps / kWarpsPerRow;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if constexpr (kWarpsPerRow == 1) {
+    for (long long row = static_cast<long long>(blockIdx.x) * kRowsPerCta + warp; row < rows;
+         row += static_cast<long long>(gridDim.x) * kRowsPerCta) {
+      Acc v = reduce_span<T, Acc, Op, 32, U>(x + row * cols, cols, lane);
+      v = warp_combine<Acc, Op>(v);
+      if (lane == 0) store_result(ep, row, v);
+    }
+  } else {
+    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+      Acc v = reduce_span<T, Acc, Op, kBlock, U>(x + row * cols, cols, threadIdx.x);
+      v = block_combine<Acc, Op>(v, smem);
+      if (threadIdx.x == 0) store_result(ep, row, v);
+    }
+  }
+}
+
+// Few, very long rows (a full reduction is rows == 1).  grid = (splits, rows).
+// Each CTA reduces one 16-byte-aligned-friendly segment, parks its partial in
+// `partial[row*splits + s]`, takes a ticket; the CTA that draws the last ticket
+// combines the partials in index order (deterministic, no float atomics) and
+// resets the ticket so the workspace can be reused / graph-replayed.
+template <typename T, typename Acc, typename Op, int U>
+__global__ void __launch_bounds__(kBlock)
+    row_split_kernel(const T* __restrict__ x, long long rows, long long cols, long long seg,
+                     Acc* __restrict__ partial, unsigned* __restrict__ tickets, Epilogue ep) {
+  __shared__ Acc smem[kWarps];
+  __shared__ unsigned s_ticket;
+  const long long row = blockIdx.y;
+  const unsigned splits = gridDim.x;
+  const long long c0 = static_cast<long long>(blockIdx.x) * seg;
+  long long len = cols - c0;
+  if (len > seg) len = seg;
+  Acc v = Op::identity();
+  if (len > 0) v = reduce_span<T, Acc, Op, kBlock, U>(x + row * cols + c0, len, threadIdx.x);
+  v = block_combine<Acc, Op>(v, smem);
+  if (threadIdx.x == 0) {
+    partial[row * splits + blockIdx.x] = v;
+    __threadfence();
+    s_ticket = atomicAdd(&tickets[row], 1u);
+  }
+  __syncthreads();
+  if (s_ticket != splits - 1) return;
+  __threadfence();
+  Acc r = Op::identity();
+  for (unsigned s = threadIdx.x; s < splits; s += kBlock)
+    r = Op::combine(r, __ldcg(&partial[row * splits + s]));
+  r = block_combine<Acc, Op>(r, smem);
+  if (threadIdx.x == 0) {
+    store_result(ep, row, r);
+    tickets[row] = 0;
+  }
+}
+
+// One batch of UU row loads (stride `step` rows) for the column this thread owns.
+template <typename T, typename Acc, typename Op, int VE, int UU>
+__device__ __forceinline__ void col_step(const T* __restrict__ base, long long inner, long long& r,
+                                         long long r1, long long step, Acc (&acc)[VE]) {
+  for (; r + (UU - 1) * step < r1; r += UU * step) {
+    if constexpr (VE > 1) {
+      V16 buf[UU];
+#pragma unroll
+      for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(base + (r + u * step) * inner);
+#pragma unroll
+      for (int u = 0; u < UU; ++u) {
+        typename VecOf<T>::U w;
+        w.raw = buf[u];
+#pragma unroll
+        for (int e = 0; e < VE; ++e) acc[e] = Op::combine(acc[e], load_as<Acc, Op>(w.e[e]));
+      }
+    } else {
+      T buf[UU];
+#pragma unroll
+      for (int u = 0; u < UU; ++u) buf[u] = ldg_scalar(base + (r + u * step) * inner);
+#pragma unroll
+      for (int u = 0; u < UU; ++u) acc[0] = Op::combine(acc[0], load_as<Acc, Op>(buf[u]));
+    }
+  }
+}
+
+// [outer, R, inner] -> [outer, inner].  Block = TX x TY (TX*TY == kBlock): tx walks
+// the kept contiguous axis in units of VE elements (VE = 16/sizeof(T) when inner
+// allows 16-byte loads, else 1), ty walks the reduced axis.  grid.x = outer * tiles,
+// grid.y = splits of R.  U row-loads are in flight per thread.
+template <typename T, typename Acc, typename Op, int VE, int U>
+__global__ void __launch_bounds__(kBlock)
+    col_reduce_kernel(const T* __restrict__ x, long long R, long long inner, int TX,
+                      long long tiles, long long rows_per_split, Acc* __restrict__ partial,
+                      unsigned* __restrict__ tickets, Epilogue ep) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Acc* smem = reinterpret_cast<Acc*>(smem_raw);  // [TY][TX][VE]
+  __shared__ unsigned s_ticket;
+  const int TY = kBlock / TX;
+  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+  const long long o = blockIdx.x / tiles, tile = blockIdx.x % tiles;
+  const long long inner_v = inner / VE;  // VE divides inner on the vector path
+  const long long cv = tile * TX + tx;   // column (in vectors) this thread owns
+  const bool live = cv < inner_v;
+  const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_split;
+  long long r1 = r0 + rows_per_split;
+  if (r1 > R) r1 = R;
+  const unsigned splits = gridDim.y;
+
+  Acc acc[VE];
+#pragma unroll
+  for (int e = 0; e < VE; ++e) acc[e] = Op::identity();
+
+  if (live) {
+    const T* __restrict__ base = x + o * R * inner + cv * VE;
+    long long r = r0 + ty;
+    const long long step = TY;
+    col_step<T, Acc, Op, VE, U>(base, inner, r, r1, step, acc);
+    if constexpr (U > 4) col_step<T, Acc, Op, VE, 4>(base, inner, r, r1, step, acc);
+    if constexpr (U > 2) col_step<T, Acc, Op, VE, 2>(base, inner, r, r1, step, acc);
+    if constexpr (U > 1) col_step<T, Acc, Op, VE, 1>(base, inner, r, r1, step, acc);
+  }
+
+  // combine across ty through shared memory (tree over TY, TY is a power of two)
+#pragma unroll
+  for (int e = 0; e < VE; ++e) smem[(ty * TX + tx) * VE + e] = acc[e];
+  __syncthreads();
+  for (int half = TY >> 1; half > 0; half >>= 1) {
+    if (ty < half) {
+#pragma unroll
+      for (int e = 0; e < VE; ++e)
+        smem[(ty * TX + tx) * VE + e] = Op::combine(smem[(ty * TX + tx) * VE + e],
+                                                    smem[((ty + half) * TX + tx) * VE + e]);
+    }
+    __syncthreads();
+  }
+
+  const long long out_base = o * inner + cv * VE;
+  if (splits == 1) {
+    if (ty == 0 && live) {
+#pragma unroll
+      for (int e = 0; e < VE; ++e) store_result(ep, out_base + e, smem[tx * VE + e]);
+    }
+    return;
+  }
+
+  const long long out_numel = static_cast<long long>(gridDim.x / tiles) * inner;
+  if (ty == 0 && live) {
+#pragma unroll
+    for (int e = 0; e < VE; ++e)
+      partial[static_cast<long long>(blockIdx.y) * out_numel + out_base + e] = smem[tx * VE + e];
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_ticket = atomicAdd(&tickets[blockIdx.x], 1u);
+  __syncthreads();
+  if (s_ticket != splits - 1) return;
+  __threadfence();
+
+  // last CTA for this (outer, tile): combine the `splits` partials in index order
+#pragma unroll
+  for (int e = 0; e < VE; ++e) acc[e] = Op::identity();
+  if (live) {
+    for (unsigned s = ty; s < splits; s += TY) {
+#pragma unroll
+      for (int e = 0; e < VE; ++e)
+        acc[e] = Op::combine(acc[e], __ldcg(&partial[s * out_numel + out_base + e]));
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < VE; ++e) smem[(ty * TX + tx) * VE + e] = acc[e];
+  __syncthreads();
+  for (int half = TY >> 1; half > 0; half >>= 1) {
+    if (ty < half) {
+#pragma unroll
+      for (int e = 0; e < VE; ++e)
+        smem[(ty * TX + tx) * VE + e] = Op::combine(smem[(ty * TX + tx) * VE + e],
+                                                    smem[((ty + half) * TX + tx) * VE + e]);
+    }
+    __syncthreads();
+  }
+  if (ty == 0 && live) {
+#pragma unroll
+    for (int e = 0; e < VE; ++e) store_result(ep, out_base + e, smem[tx * VE + e]);
+  }
+  if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
+}
+
+// Arbitrary keep/reduce interleaving (up to 9 merged dims).  The host hands over
+// the kept dims and the reduced dims separately, each with extents and input
+// strides, innermost last (the job of IndexCalculator, index_calculator.h:53-107).
+struct GenericDims {
+  int nkeep, nred;
+  long long keep_extent[kMaxRank], keep_stride[kMaxRank];
+  long long red_extent[kMaxRank], red_stride[kMaxRank];
+  long long out_numel, red_numel;
+};
+
+__device__ __forceinline__ long long unravel(long long idx, int n, const long long* extent,
+                                             const long long* stride) {
+  long long off = 0;
+  for (int d = n - 1; d >= 0; --d) {
+    const long long e = extent[d];
+    long long q, rem;
+    if ((static_cast<unsigned long long>(idx) | static_cast<unsigned long long>(e)) >> 32) {
+      q = idx / e;
+      rem = idx - q * e;
+    } else {
+      const unsigned qi = static_cast<unsigned>(idx) / static_cast<unsigned>(e);
+      q = qi;
+      rem = static_cast<unsigned>(idx) - qi * static_cast<unsigned>(e);
+    }
+    off += rem * stride[d];
+    idx = q;
+  }
+  return off;
+}
+
+// Block = TX x TY.  tx walks outputs (coalesced when the innermost merged dim is
+// kept), ty walks the flattened reduce space (coalesced when it is reduced; the
+// host then picks TX == 1).
+template <typename T, typename Acc, typename Op>
+__global__ void __launch_bounds__(kBlock)
+    generic_reduce_kernel(const T* __restrict__ x, GenericDims gd, int TX, Epilogue ep) {
+  __shared__ Acc smem[kBlock];
+  const int TY = kBlock / TX;
+  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+  const long long o = static_cast<long long>(blockIdx.x) * TX + tx;
+  Acc acc = Op::identity();
+  if (o < gd.out_numel) {
+    const long long base = unravel(o, gd.nkeep, gd.keep_extent, gd.keep_stride);
+    // walk the innermost reduced dim directly, unravel only the outer part
+    const long long in_e = gd.nred > 0 ? gd.red_extent[gd.nred - 1] : 1;
+    const long long in_s = gd.nred > 0 ? gd.red_stride[gd.nred - 1] : 0;
+    const long long outer_n = gd.red_numel / in_e;
+    if (in_e >= TY || outer_n == 1) {
+      for (long long jo = 0; jo < outer_n; ++jo) {
+        const long long ob = base + unravel(jo, gd.nred - 1, gd.red_extent, gd.red_stride);
+        for (long long ji = ty; ji < in_e; ji += TY)
+          acc = Op::combine(acc, load_as<Acc, Op>(ldg_scalar(x + ob + ji * in_s)));
+      }
+    } else {
+      for (long long j = ty; j < gd.red_numel; j += TY) {
+        const long long off = unravel(j, gd.nred, gd.red_extent, gd.red_stride);
+        acc = Op::combine(acc, load_as<Acc, Op>(ldg_scalar(x + base + off)));
+      }
+    }
+  }
+  smem[ty * TX + tx] = acc;
+  __syncthreads();
+  for (int half = TY >> 1; half > 0; half >>= 1) {
+    if (ty < half)
+      smem[ty * TX + tx] = Op::combine(smem[ty * TX + tx], smem[(ty + half) * TX + tx]);
+    __syncthreads();
+  }
+  if (ty == 0 && o < gd.out_numel) store_result(ep, o, smem[tx]);
+}
+
+}  // namespace b200phi

@@ -1,0 +1,286 @@
+// See reduce_plan.h.  Host-only; compiled by g++ (unit tests) and nvcc (library).
+#include "reduce_plan.h"
+
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <algorithm>
+
+namespace b200phi {
+
+size_t dtype_size(int dtype) {
+  switch (dtype) {
+    case B200PHI_BOOL:
+    case B200PHI_UINT8:
+    case B200PHI_INT8:
+      return 1;
+    case B200PHI_INT16:
+    case B200PHI_FLOAT16:
+    case B200PHI_BFLOAT16:
+      return 2;
+    case B200PHI_INT32:
+    case B200PHI_FLOAT32:
+      return 4;
+    case B200PHI_INT64:
+    case B200PHI_FLOAT64:
+      return 8;
+    default:
+      return 0;
+  }
+}
+
+bool dtype_known(int dtype) { return dtype_size(dtype) != 0; }
+
+bool dtype_is_float(int dtype) {
+  return dtype == B200PHI_FLOAT32 || dtype == B200PHI_FLOAT64 || dtype == B200PHI_FLOAT16 ||
+         dtype == B200PHI_BFLOAT16;
+}
+
+static long long env_ll(const char* name, long long dflt) {
+  const char* s = getenv(name);
+  if (!s || !*s) return dflt;
+  return atoll(s);
+}
+
+Tunables default_tunables(int sm_count) {
+  Tunables t;
+  t.sm_count = sm_count > 0 ? sm_count : 148;
+  t.row_warp_max_bytes = env_ll("B200PHI_ROW_WARP_MAX_BYTES", 16384);
+  t.ctas_per_sm = static_cast<int>(env_ll("B200PHI_CTAS_PER_SM", 8));
+  t.force_kind = static_cast<int>(env_ll("B200PHI_FORCE_KIND", -1));
+  return t;
+}
+
+static long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
+static long long round_up(long long a, long long b) { return ceil_div(a, b) * b; }
+static int pow2_ceil(long long v) {
+  int p = 1;
+  while (p < v && p < (1 << 30)) p <<= 1;
+  return p;
+}
+
+static int fail(std::string* err, int code, const std::string& msg) {
+  if (err) *err = msg;
+  return code;
+}
+
+int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, std::string* err) {
+  char buf[256];
+  if (!d) return fail(err, B200PHI_INVALID_ARGUMENT, "null descriptor");
+  *p = ReducePlan();
+  if (d->op < B200PHI_SUM || d->op > B200PHI_AMIN)
+    return fail(err, B200PHI_INVALID_ARGUMENT, "unknown reduce op");
+  if (!dtype_known(d->in_dtype)) return fail(err, B200PHI_UNSUPPORTED, "unsupported input dtype");
+  if (d->rank < 0 || d->rank > B200PHI_MAX_RANK)
+    return fail(err, B200PHI_INVALID_ARGUMENT, "rank must be in [0, 9]");
+  if (d->naxes < 0 || d->naxes > B200PHI_MAX_RANK)
+    return fail(err, B200PHI_INVALID_ARGUMENT, "naxes must be in [0, 9]");
+
+  const bool logical = d->op == B200PHI_ANY || d->op == B200PHI_ALL;
+  int out_dtype = d->out_dtype;
+  if (out_dtype == B200PHI_UNDEFINED) out_dtype = logical ? B200PHI_BOOL : d->in_dtype;
+  if (!dtype_known(out_dtype)) return fail(err, B200PHI_UNSUPPORTED, "unsupported output dtype");
+  if (logical && out_dtype != B200PHI_BOOL)
+    return fail(err, B200PHI_INVALID_ARGUMENT, "any/all write BOOL");
+  if (!logical && out_dtype == B200PHI_BOOL && d->in_dtype != B200PHI_BOOL)
+    return fail(err, B200PHI_UNSUPPORTED, "BOOL output needs any/all or a BOOL input");
+  if ((out_dtype == B200PHI_FLOAT16 || out_dtype == B200PHI_BFLOAT16) && out_dtype != d->in_dtype)
+    return fail(err, B200PHI_UNSUPPORTED,
+                "16-bit float output from a different input dtype is not built");
+
+  const bool sum_like = d->op == B200PHI_SUM || d->op == B200PHI_MEAN;
+  if (!sum_like && !logical && out_dtype != d->in_dtype)
+    return fail(err, B200PHI_UNSUPPORTED, "max/min/prod keep the input dtype");
+
+  p->op = d->op;
+  p->in_dtype = d->in_dtype;
+  p->out_dtype = out_dtype;
+  if (logical)
+    p->acc = 3;
+  else if (out_dtype == B200PHI_FLOAT64)
+    p->acc = 1;
+  else if (dtype_is_float(out_dtype))
+    p->acc = 0;
+  else
+    p->acc = 2;
+  const size_t acc_size = (p->acc == 0 || p->acc == 3) ? 4 : 8;
+
+  // ---- numel, emptiness (reduce_function.h:1052-1055) -------------------------
+  long long numel = 1;
+  for (int i = 0; i < d->rank; ++i) {
+    if (d->dims[i] < 0) return fail(err, B200PHI_INVALID_ARGUMENT, "negative extent");
+    numel *= d->dims[i];
+  }
+  if (numel == 0)
+    return fail(err, B200PHI_INVALID_ARGUMENT, "Tensor need be reduced must not empty.");
+  p->in_numel = numel;
+
+  // ---- which axes are reduced (reduce_function.h:100-123, kernel_utils.h:405-416)
+  bool red[B200PHI_MAX_RANK] = {false};
+  bool all = d->reduce_all != 0 || d->naxes == 0 || d->rank == 0;
+  if (!all) {
+    for (int i = 0; i < d->naxes; ++i) {
+      int a = d->axes[i];
+      if (a < -d->rank || a >= d->rank) {
+        snprintf(buf, sizeof(buf),
+                 "The reduce dim index %d should be in the range [ -dimension(X), dimension(X) ) "
+                 "which dimension = %d. But received dim index = %d.",
+                 i, d->rank, a);
+        return fail(err, B200PHI_INVALID_ARGUMENT, buf);
+      }
+      if (a < 0) a += d->rank;
+      red[a] = true;
+    }
+  } else {
+    for (int i = 0; i < d->rank; ++i) red[i] = true;
+  }
+
+  // ---- drop extent-1 dims, merge neighbours with the same role -------------------
+  long long ext[B200PHI_MAX_RANK];
+  bool isred[B200PHI_MAX_RANK];
+  int m = 0;
+  for (int i = 0; i < d->rank; ++i) {
+    if (d->dims[i] == 1) continue;
+    if (m > 0 && isred[m - 1] == red[i]) {
+      ext[m - 1] *= d->dims[i];
+    } else {
+      ext[m] = d->dims[i];
+      isred[m] = red[i];
+      ++m;
+    }
+  }
+  long long stride[B200PHI_MAX_RANK];
+  long long s = 1;
+  for (int i = m - 1; i >= 0; --i) {
+    stride[i] = s;
+    s *= ext[i];
+  }
+  long long red_numel = 1, out_numel = 1;
+  p->nkeep = p->nred = 0;
+  for (int i = 0; i < m; ++i) {
+    if (isred[i]) {
+      p->red_extent[p->nred] = ext[i];
+      p->red_stride[p->nred++] = stride[i];
+      red_numel *= ext[i];
+    } else {
+      p->keep_extent[p->nkeep] = ext[i];
+      p->keep_stride[p->nkeep++] = stride[i];
+      out_numel *= ext[i];
+    }
+  }
+  p->red_numel = red_numel;
+  p->out_numel = out_numel;
+
+  const size_t esize = dtype_size(d->in_dtype);
+  const int VE = static_cast<int>(16 / esize);
+  const long long want_ctas = static_cast<long long>(t.sm_count) * t.ctas_per_sm;
+
+  // ---- kind ---------------------------------------------------------------------
+  int kind = kGeneric;
+  if (red_numel > 1) {
+    if (m == 1) {  // [cols] all reduced
+      kind = kRowBlock;
+      p->rows = 1;
+      p->cols = ext[0];
+    } else if (m == 2 && !isred[0] && isred[1]) {
+      kind = kRowBlock;
+      p->rows = ext[0];
+      p->cols = ext[1];
+    } else if (m == 2 && isred[0] && !isred[1]) {
+      kind = kCol;
+      p->outer = 1;
+      p->R = ext[0];
+      p->inner = ext[1];
+    } else if (m == 3 && !isred[0] && isred[1] && !isred[2]) {
+      kind = kCol;
+      p->outer = ext[0];
+      p->R = ext[1];
+      p->inner = ext[2];
+    }
+  }
+  if (kind == kCol && p->R < 16) kind = kGeneric;
+
+  if (kind == kRowBlock) {
+    const long long row_bytes = p->cols * static_cast<long long>(esize);
+    if (p->rows >= static_cast<long long>(t.sm_count) * 16 && row_bytes <= t.row_warp_max_bytes) {
+      kind = kRowWarp;
+    } else if (p->rows < static_cast<long long>(t.sm_count) * 2) {
+      long long splits = std::min(ceil_div(want_ctas, p->rows), row_bytes / 32768);
+      splits = std::min<long long>(splits, 65535);
+      if (splits > 1) {
+        long long seg = round_up(ceil_div(p->cols, splits), static_cast<long long>(VE) * 32);
+        splits = ceil_div(p->cols, seg);
+        if (splits > 1) {
+          kind = kRowSplit;
+          p->seg = seg;
+          p->splits = static_cast<int>(splits);
+        }
+      }
+    }
+    if (t.force_kind == kRowWarp || t.force_kind == kRowBlock) {
+      if (kind != kRowSplit) kind = t.force_kind;
+    }
+  }
+  p->kind = kind;
+
+  // ---- geometry -----------------------------------------------------------------
+  p->splits = (kind == kRowSplit) ? p->splits : 1;
+  switch (kind) {
+    case kRowWarp: {
+      long long ctas = ceil_div(p->rows, 8);
+      p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, want_ctas * 64));
+      p->grid_y = 1;
+      break;
+    }
+    case kRowBlock:
+      p->grid_x = static_cast<unsigned>(std::min<long long>(p->rows, 0x7fffffffLL));
+      p->grid_y = 1;
+      break;
+    case kRowSplit:
+      p->grid_x = static_cast<unsigned>(p->splits);
+      p->grid_y = static_cast<unsigned>(p->rows);
+      p->ws_partial_bytes = static_cast<size_t>(p->rows) * p->splits * acc_size;
+      p->ws_ticket_bytes = static_cast<size_t>(p->rows) * 4;
+      break;
+    case kCol: {
+      const bool vec_ok =
+          VE > 1 && (p->inner % VE == 0) && (reinterpret_cast<uintptr_t>(d->x) % 16 == 0);
+      p->vec = vec_ok ? VE : 1;
+      const long long inner_v = p->inner / p->vec;
+      p->TX = std::min(256, pow2_ceil(inner_v));
+      const int TY = 256 / p->TX;
+      p->tiles = ceil_div(inner_v, p->TX);
+      const long long bxy = p->outer * p->tiles;
+      if (bxy > 0x7fffffffLL) return fail(err, B200PHI_UNSUPPORTED, "output too large for col plan");
+      long long max_splits = std::max<long long>(1, p->R / (static_cast<long long>(TY) * 8));
+      long long splits = std::min(std::max<long long>(1, ceil_div(want_ctas, bxy)), max_splits);
+      splits = std::min<long long>(splits, 65535);
+      p->rows_per_split = round_up(ceil_div(p->R, splits), TY);
+      splits = ceil_div(p->R, p->rows_per_split);
+      p->splits = static_cast<int>(splits);
+      p->grid_x = static_cast<unsigned>(bxy);
+      p->grid_y = static_cast<unsigned>(splits);
+      if (splits > 1) {
+        p->ws_partial_bytes = static_cast<size_t>(splits) * out_numel * acc_size;
+        p->ws_ticket_bytes = static_cast<size_t>(bxy) * 4;
+      }
+      break;
+    }
+    default: {  // kGeneric
+      const bool inner_reduced = m > 0 && isred[m - 1];
+      int TY = std::min(256, pow2_ceil(red_numel));
+      if (!inner_reduced) TY = std::min(TY, 8);
+      p->TX = 256 / TY;
+      const long long gx = ceil_div(out_numel, p->TX);
+      if (gx > 0x7fffffffLL) return fail(err, B200PHI_UNSUPPORTED, "output too large");
+      p->grid_x = static_cast<unsigned>(gx);
+      p->grid_y = 1;
+      break;
+    }
+  }
+  p->ws_partial_bytes = static_cast<size_t>(round_up(static_cast<long long>(p->ws_partial_bytes), 256));
+  p->ws_total_bytes = p->ws_partial_bytes + p->ws_ticket_bytes;
+  return B200PHI_OK;
+}
+
+}  // namespace b200phi

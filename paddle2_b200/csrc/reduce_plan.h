@@ -1,0 +1,73 @@
+// Host-side planning for reductions: axis canonicalisation, dim merging and the
+// choice of kernel + launch geometry.  Pure C++ (no CUDA types) so the same code
+// is unit-tested on a CPU-only box.
+//
+// Re-states, for one device family, what the reference spreads over
+//   details::GetReduceDim            reduce_function.h:100-123   (negative axes, range check)
+//   recompute_reduce_all             kernel_utils.h:405-416
+//   ReduceConfig::SetReduceDim       reduce_function.h:301-383   (merge adjacent dims)
+//   ReduceConfig::SetReduceType      reduce_function.h:410-431   (LastDim / HigherDim / Any)
+//   ReduceConfig::SetBlockDim*       reduce_function.h:434-561   (geometry)
+// but sizes grids for 148 SMs and never narrows an extent to 32 bits.
+#pragma once
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/b200phi.h"
+
+namespace b200phi {
+
+enum ReduceKind {
+  kRowWarp = 0,   // [rows, cols], one warp per row
+  kRowBlock = 1,  // [rows, cols], one CTA per row
+  kRowSplit = 2,  // [rows, cols], several CTAs per row + last-block finalise
+  kCol = 3,       // [outer, R, inner]
+  kGeneric = 4    // anything else (also the reduce_num == 1 cast/copy)
+};
+
+struct ReducePlan {
+  int kind;
+  int op;         // b200phi_reduce_op with MEAN/AMAX/AMIN kept as given
+  int in_dtype;
+  int out_dtype;  // resolved (never UNDEFINED)
+  int acc;        // 0 float, 1 double, 2 int64, 3 logical(int)
+  long long in_numel, out_numel, red_numel;
+  // row kinds
+  long long rows, cols, seg;
+  // col kind
+  long long outer, R, inner, tiles, rows_per_split;
+  int vec;  // elements per 16-byte vector on the col vector path, else 1
+  int TX;
+  // generic kind
+  int nkeep, nred;
+  long long keep_extent[B200PHI_MAX_RANK], keep_stride[B200PHI_MAX_RANK];
+  long long red_extent[B200PHI_MAX_RANK], red_stride[B200PHI_MAX_RANK];
+  // launch
+  unsigned grid_x, grid_y;
+  int splits;
+  size_t ws_partial_bytes;  // first region of the workspace
+  size_t ws_ticket_bytes;   // second region (256-byte aligned start)
+  size_t ws_total_bytes;
+};
+
+size_t dtype_size(int dtype);
+bool dtype_known(int dtype);
+bool dtype_is_float(int dtype);
+
+// Tunables (read once from the environment; see DESIGN.md "knobs").
+struct Tunables {
+  int sm_count;             // multiprocessors of the current device (148 on B200)
+  long long row_warp_max_bytes;  // rows up to this many bytes go one-warp-per-row
+  int ctas_per_sm;          // resident CTAs per SM the split heuristics aim for
+  int force_kind;           // -1, or a ReduceKind to force where legal (testing)
+};
+Tunables default_tunables(int sm_count);
+
+// Fills *plan. Returns B200PHI_OK or a status with *err set.
+int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* plan,
+                std::string* err);
+
+}  // namespace b200phi

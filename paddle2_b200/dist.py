@@ -1,0 +1,123 @@
+"""Sharded global reduce over the GPUs of one box: one process per GPU.
+
+Config C5: a tensor too large for one GPU is split along axis 0 into contiguous
+row blocks; each rank reduces its block locally and the [C]-sized partials are
+combined by an allreduce over NVLink issued on the same CUDA stream.  This is the
+reference's `paddle.sum(local, axis=0)` + `paddle.distributed.all_reduce`
+(process_group_nccl.cc:267-298) / Partial->Replicate reshard
+(p_to_r_reshard_function.cc:67) as ONE C-ABI call, b200phi_sharded_reduce.
+
+torch.distributed is only the rendezvous: it carries the 128-byte NCCL unique id
+from rank 0 to the others (what CommContextManager does over its TCPStore,
+comm_context_manager.cc:75) and the row counts.  The data path never goes through
+torch collectives.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib as L
+from . import ops as _ops
+
+
+def partition_rows(total_rows, world_size, rank):
+    """Contiguous row block of `rank`: (start, count).  Blocks differ by at most one
+    row and cover [0, total_rows) exactly (the layout Shard(0) gives a DistTensor)."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad rank/world_size")
+    base, extra = divmod(total_rows, world_size)
+    start = rank * base + (rank if rank < extra else extra)
+    return start, base + (1 if rank < extra else 0)
+
+
+def exchange_unique_id(make_id, group=None):
+    """Rank 0 calls make_id() -> bytes(128); every rank returns those bytes."""
+    rank = dist.get_rank(group)
+    box = [make_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    uid = box[0]
+    if not isinstance(uid, (bytes, bytearray)) or len(uid) != 128:
+        raise RuntimeError("unique id rendezvous failed")
+    return bytes(uid)
+
+
+def global_count(local_rows, group=None):
+    """Sum of the ranks' row counts (the divisor of a sharded mean)."""
+    t = torch.tensor([int(local_rows)], dtype=torch.int64)
+    backend = dist.get_backend(group)
+    if backend == "nccl":
+        t = t.cuda()
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return int(t.item())
+
+
+class ShardedReducer:
+    """Owns one NCCL communicator created through the C ABI (b200phi_comm_*)."""
+
+    def __init__(self, group=None):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed must be initialised (it is the rendezvous)")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        lib = L.lib()
+        self.comm = None
+        if self.world == 1:
+            return  # single GPU: no communicator, no collective (north star)
+
+        def make_id():
+            buf = C.create_string_buffer(128)
+            L.check(lib.b200phi_comm_unique_id(buf))
+            return buf.raw
+
+        uid = exchange_unique_id(make_id, group)
+        comm = C.c_void_p()
+        L.check(lib.b200phi_comm_init_rank(uid, self.world, self.rank, C.byref(comm)))
+        self.comm = comm
+
+    def close(self):
+        if getattr(self, "comm", None):
+            L.check(L.lib().b200phi_comm_destroy(self.comm))
+            self.comm = None
+
+    def reduce(self, op, x_local, global_rows=None, out=None, workspace=None):
+        """Reduce the row-sharded tensor over axis 0; every rank gets the result.
+        `op` is a b200phi reduce op id (L.SUM, L.MEAN, L.MAX, ...)."""
+        _ops._require_cuda(x_local)
+        x = x_local.contiguous()
+        if x.dim() < 1:
+            raise ValueError("sharded reduce needs rank >= 1")
+        out_dtype = _ops._sum_out_dtype(x.dtype, None) if op == L.SUM else x.dtype
+        if op in (L.ANY, L.ALL):
+            out_dtype = torch.bool
+        if out is None:
+            out = torch.empty(x.shape[1:], dtype=out_dtype, device=x.device)
+        d = L.ReduceDesc()
+        d.op = op
+        d.in_dtype = _ops._phi_dtype(x.dtype)
+        d.out_dtype = _ops._phi_dtype(out.dtype)
+        d.rank = x.dim()
+        for i, s in enumerate(x.shape):
+            d.dims[i] = s
+        d.naxes = 1
+        d.axes[0] = 0
+        d.reduce_all = 0
+        d.x = x.data_ptr()
+        d.out = out.data_ptr()
+        lib = L.lib()
+        with torch.cuda.device(x.device):
+            ws_bytes = lib.b200phi_reduce_workspace(C.byref(d))
+            if ws_bytes:
+                if workspace is None or workspace.numel() < ws_bytes:
+                    workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+                d.workspace = workspace.data_ptr()
+                d.workspace_bytes = workspace.numel()
+            if global_rows is None:
+                global_rows = global_count(x.shape[0], self.group) if op == L.MEAN else 0
+            stream = C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            L.check(lib.b200phi_sharded_reduce(C.byref(d), int(global_rows), self.comm, stream))
+        return out
+
+    def sum(self, x_local, **kw):  # noqa: A003
+        return self.reduce(L.SUM, x_local, **kw)

@@ -1,0 +1,476 @@
+"""paddle.* look-alikes for the hot path, on torch CUDA tensors, through the C ABI.
+
+Mirrors the reference's Python entry points (argument names, defaults, dtype and
+shape rules) so the parity tests read like the reference's own:
+
+  sum   python/paddle/tensor/math.py:1475-1625     add   math.py:682
+  max   math.py:2870   min math.py:3029   prod math.py:4779   any math.py:5119
+  mean  python/paddle/tensor/stat.py:45            var   stat.py:141-198
+  argmax python/paddle/tensor/search.py:175
+
+torch is only the owner of device memory and streams here (torch.empty,
+torch.cuda.current_stream); every value is computed by libb200phi.so.  Shape and
+dtype inference that Paddle runs before the kernel (InferMeta) is re-stated in
+_reduce_out_shape / _sum_out_dtype / broadcast_shape with citations.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+_T2P = {
+    torch.bool: L.BOOL,
+    torch.uint8: L.UINT8,
+    torch.int8: L.INT8,
+    torch.int16: L.INT16,
+    torch.int32: L.INT32,
+    torch.int64: L.INT64,
+    torch.float32: L.FLOAT32,
+    torch.float64: L.FLOAT64,
+    torch.float16: L.FLOAT16,
+    torch.bfloat16: L.BFLOAT16,
+}
+_NAME2T = {
+    "bool": torch.bool, "uint8": torch.uint8, "int8": torch.int8, "int16": torch.int16,
+    "int32": torch.int32, "int64": torch.int64, "float32": torch.float32,
+    "float64": torch.float64, "float16": torch.float16, "bfloat16": torch.bfloat16,
+}
+
+
+def _to_torch_dtype(dtype):
+    if dtype is None or isinstance(dtype, torch.dtype):
+        return dtype
+    if isinstance(dtype, str) and dtype in _NAME2T:
+        return _NAME2T[dtype]
+    raise TypeError(f"unsupported dtype {dtype!r}")
+
+
+def _phi_dtype(t):
+    try:
+        return _T2P[t]
+    except KeyError:
+        raise TypeError(f"dtype {t} is not supported by the b200phi path") from None
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if not isinstance(t, torch.Tensor):
+            raise TypeError("expected a torch.Tensor holding device memory")
+        if not t.is_cuda:
+            raise RuntimeError(
+                "b200phi has no CPU path: tensors must live on a CUDA device "
+                "(the reference's CPU kernels are only used as the test oracle)")
+
+
+def _stream_ptr(x):
+    return C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+
+
+def _norm_axes(axis, rank):
+    """axis argument -> (sorted unique non-negative axes, reduce_all).
+    ReduceInferDim, paddle/phi/infermeta/unary.cc:3631-3700."""
+    if axis is None:
+        return list(range(rank)), True
+    if isinstance(axis, int):
+        axis = [axis]
+    axis = list(axis)
+    if len(axis) == 0:
+        return list(range(rank)), True
+    lo, hi = (-rank, rank) if rank > 0 else (-1, 1)
+    out = set()
+    for a in axis:
+        if not (lo <= a < hi):
+            raise ValueError(
+                f"The reduce dim index should be in the range [-dimension(X), dimension(X)) "
+                f"which dimension = {rank}, but received dim index = {a}.")
+        out.add(a + rank if a < 0 else a)
+    if rank == 0:
+        return [], True
+    return sorted(out), len(out) == rank
+
+
+def _reduce_out_shape(shape, axes, reduce_all, keepdim):
+    rank = len(shape)
+    if reduce_all:
+        return [1] * rank if keepdim else []
+    if keepdim:
+        return [1 if i in axes else s for i, s in enumerate(shape)]
+    return [s for i, s in enumerate(shape) if i not in axes]
+
+
+def _reduce(op, x, axis, keepdim, out_dtype, out=None):
+    _require_cuda(x)
+    x = x.contiguous()  # PrepareData/Trans2Contiguous does this before phi kernels
+    rank = x.dim()
+    axes, reduce_all = _norm_axes(axis, rank)
+    out_shape = _reduce_out_shape(list(x.shape), axes, reduce_all, keepdim)
+    if out is None:
+        out = torch.empty(out_shape, dtype=out_dtype, device=x.device)
+    else:  # caller-provided result storage (the phi contract: `DenseTensor* out`)
+        _require_cuda(out)
+        if list(out.shape) != out_shape or out.dtype != out_dtype or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous {out_dtype} tensor of shape {out_shape}")
+    d = L.ReduceDesc()
+    d.op = op
+    d.in_dtype = _phi_dtype(x.dtype)
+    d.out_dtype = _phi_dtype(out_dtype)
+    d.rank = rank
+    for i, s in enumerate(x.shape):
+        d.dims[i] = s
+    d.naxes = 0 if reduce_all else len(axes)
+    for i, a in enumerate(axes if not reduce_all else []):
+        d.axes[i] = a
+    d.reduce_all = 1 if reduce_all else 0
+    d.x = x.data_ptr()
+    d.out = out.data_ptr()
+    lib = L.lib()
+    with torch.cuda.device(x.device):
+        ws_bytes = lib.b200phi_reduce_workspace(C.byref(d))
+        ws = None
+        if ws_bytes:
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)  # dev_ctx.Alloc stand-in
+            d.workspace = ws.data_ptr()
+            d.workspace_bytes = ws_bytes
+        L.check(lib.b200phi_reduce(C.byref(d), _stream_ptr(x)))
+    return out
+
+
+def _sum_out_dtype(x_dtype, dtype):
+    """SumRawInferMeta, paddle/phi/infermeta/unary.cc:4698-4707."""
+    if dtype is not None:
+        return dtype
+    if x_dtype in (torch.bool, torch.int32, torch.int64):
+        return torch.int64
+    return x_dtype
+
+
+def sum(x, axis=None, dtype=None, keepdim=False, out=None):  # noqa: A001 - paddle name
+    return _reduce(L.SUM, x, axis, keepdim, _sum_out_dtype(x.dtype, _to_torch_dtype(dtype)), out)
+
+
+def mean(x, axis=None, keepdim=False):
+    return _reduce(L.MEAN, x, axis, keepdim, x.dtype)
+
+
+def max(x, axis=None, keepdim=False, out=None):  # noqa: A001
+    return _reduce(L.MAX, x, axis, keepdim, x.dtype, out)
+
+
+def min(x, axis=None, keepdim=False, out=None):  # noqa: A001
+    return _reduce(L.MIN, x, axis, keepdim, x.dtype, out)
+
+
+def amax(x, axis=None, keepdim=False):
+    return _reduce(L.AMAX, x, axis, keepdim, x.dtype)
+
+
+def amin(x, axis=None, keepdim=False):
+    return _reduce(L.AMIN, x, axis, keepdim, x.dtype)
+
+
+def prod(x, axis=None, keepdim=False, dtype=None):
+    dtype = _to_torch_dtype(dtype)
+    if dtype is not None and dtype != x.dtype:
+        # math.py:4779+: prod casts x first when dtype is given
+        x = cast(x, dtype)
+    return _reduce(L.PROD, x, axis, keepdim, x.dtype)
+
+
+def any(x, axis=None, keepdim=False):  # noqa: A001
+    return _reduce(L.ANY, x, axis, keepdim, torch.bool)
+
+
+def all(x, axis=None, keepdim=False):  # noqa: A001
+    return _reduce(L.ALL, x, axis, keepdim, torch.bool)
+
+
+def cast(x, dtype):
+    """phi::Cast for the dtypes the reduce engine reads: a reduce with
+    reduce_num == 1 is the reference's own elementwise shortcut
+    (reduce_function.h:1087-1092)."""
+    dtype = _to_torch_dtype(dtype)
+    _require_cuda(x)
+    x = x.contiguous()
+    out = torch.empty(x.shape, dtype=dtype, device=x.device)
+    if x.numel() == 0:
+        return out
+    d = L.ReduceDesc()
+    d.op = L.SUM
+    d.in_dtype = _phi_dtype(x.dtype)
+    d.out_dtype = _phi_dtype(dtype)
+    d.rank = 2
+    d.dims[0] = x.numel()
+    d.dims[1] = 1
+    d.naxes = 1
+    d.axes[0] = 1
+    d.x = x.data_ptr()
+    d.out = out.data_ptr()
+    with torch.cuda.device(x.device):
+        L.check(L.lib().b200phi_reduce(C.byref(d), _stream_ptr(x)))
+    return out
+
+
+# --------------------------------------------------------------------------- arg
+
+
+def _arg(op, x, axis, keepdim, dtype, want_value=False):
+    _require_cuda(x)
+    x = x.contiguous()
+    dtype = _to_torch_dtype(dtype)
+    if dtype not in (torch.int32, torch.int64):
+        # search.py:175+: "dtype" must be int32 or int64 (None is rejected too)
+        raise ValueError("the value of 'dtype' in argmax/argmin must be int32 or int64")
+    if x.numel() == 0:
+        raise ValueError("argmin/argmax input numel must > 0")
+    rank = x.dim()
+    flatten = axis is None
+    if flatten:
+        ax = 0
+        out_shape = [1] * rank if keepdim else []
+    else:
+        if not isinstance(axis, int):
+            raise TypeError("The type of 'axis' must be int or None in argmax/argmin")
+        lo, hi = (-rank, rank) if rank > 0 else (-1, 1)
+        if not (lo <= axis < hi):
+            raise ValueError(f"'axis' must be in [-{rank}, {rank}), but received {axis}")
+        ax = axis + rank if axis < 0 else axis
+        if rank == 0:
+            out_shape = []
+        elif keepdim:
+            out_shape = [1 if i == ax else s for i, s in enumerate(x.shape)]
+        else:
+            out_shape = [s for i, s in enumerate(x.shape) if i != ax]
+    # ArgMinMaxInferMeta (unary.cc:257-360): int32 needs the reduced extent <= INT_MAX
+    extent = x.numel() if flatten else (x.shape[ax] if rank else 1)
+    if dtype == torch.int32 and extent > 2**31 - 1:
+        raise ValueError("argmax/argmin with int32 indices needs the reduced extent <= INT_MAX")
+    out = torch.empty(out_shape, dtype=dtype, device=x.device)
+    val = torch.empty(out_shape, dtype=x.dtype, device=x.device) if want_value else None
+    d = L.ArgReduceDesc()
+    d.op = op
+    d.in_dtype = _phi_dtype(x.dtype)
+    d.index_dtype = _phi_dtype(dtype)
+    d.rank = rank
+    for i, s in enumerate(x.shape):
+        d.dims[i] = s
+    d.axis = ax
+    d.flatten = 1 if flatten else 0
+    d.x = x.data_ptr()
+    d.out = out.data_ptr()
+    d.max_out = val.data_ptr() if want_value else None
+    with torch.cuda.device(x.device):
+        L.check(L.lib().b200phi_argreduce(C.byref(d), _stream_ptr(x)))
+    return (out, val) if want_value else out
+
+
+def argmax(x, axis=None, keepdim=False, dtype="int64"):
+    return _arg(L.ARGMAX, x, axis, keepdim, dtype)
+
+
+def argmin(x, axis=None, keepdim=False, dtype="int64"):
+    return _arg(L.ARGMIN, x, axis, keepdim, dtype)
+
+
+def argmax_with_value(x, axis=None, keepdim=False, dtype="int64"):
+    """One pass over x for both paddle.argmax and paddle.max (config C3)."""
+    return _arg(L.ARGMAX, x, axis, keepdim, dtype, want_value=True)
+
+
+def argmin_with_value(x, axis=None, keepdim=False, dtype="int64"):
+    return _arg(L.ARGMIN, x, axis, keepdim, dtype, want_value=True)
+
+
+# --------------------------------------------------------------------- row stats
+
+
+def row_mean_var(x, unbiased=True, out_dtype=None):
+    """mean and variance over the last axis in a single read of x (config C4)."""
+    _require_cuda(x)
+    x = x.contiguous()
+    if x.dim() < 1:
+        raise ValueError("row_mean_var needs rank >= 1")
+    cols = x.shape[-1]
+    rows = x.numel() // cols if cols else 0
+    out_dtype = _to_torch_dtype(out_dtype) or x.dtype
+    m = torch.empty(x.shape[:-1], dtype=out_dtype, device=x.device)
+    v = torch.empty(x.shape[:-1], dtype=out_dtype, device=x.device)
+    d = L.RowStatsDesc()
+    d.in_dtype = _phi_dtype(x.dtype)
+    d.out_dtype = _phi_dtype(out_dtype)
+    d.rows = rows
+    d.cols = cols
+    d.unbiased = 1 if unbiased else 0
+    d.x = x.data_ptr()
+    d.mean = m.data_ptr()
+    d.var = v.data_ptr()
+    with torch.cuda.device(x.device):
+        L.check(L.lib().b200phi_rowstats(C.byref(d), _stream_ptr(x)))
+    return m, v
+
+
+def var(x, axis=None, unbiased=True, keepdim=False):
+    """paddle.var (stat.py:141-198).  The last-axis case is one fused kernel; any
+    other axis set runs the reference's own composite (mean -> subtract -> square
+    -> sum -> divide) on the b200phi reduce and broadcast kernels."""
+    _require_cuda(x)
+    rank = x.dim()
+    axes, reduce_all = _norm_axes(axis, rank)
+    if x.dtype in (torch.float32, torch.float64, torch.float16, torch.bfloat16) and rank >= 1 \
+            and not reduce_all and axes == [rank - 1]:
+        _, v = row_mean_var(x, unbiased=unbiased)
+        return v.unsqueeze(-1) if keepdim else v
+    u = mean(x, axis, keepdim=True)
+    diff = subtract(x, u)
+    sq = multiply(diff, diff)
+    ssum = sum(sq, axis, keepdim=keepdim)
+    n = 1
+    for a in (range(rank) if reduce_all else axes):
+        n *= x.shape[a]
+    if unbiased:
+        n = n - 1 if n > 1 else 1  # stat.py:193-196: where(n > 1, n - 1, 1)
+    return scale(ssum, 1.0 / n)
+
+
+# ------------------------------------------------------------------- elementwise
+
+
+def broadcast_shape(xs, ys, axis=-1):
+    """Output dims of a binary op: paddle/phi/infermeta/binary.cc:1665-1740 with
+    funcs::GetBroadcastDimsArrays (common_shape.h:35-92)."""
+    xs, ys = list(xs), list(ys)
+    if len(xs) == len(ys) and axis not in (-1, 0):
+        raise ValueError("axis should be -1 or 0 while the dimension of tensor X == tensor Y")
+    max_dim = len(xs) if len(xs) >= len(ys) else len(ys)
+    if axis < -1 - max_dim or axis > max_dim:
+        raise ValueError(f"The axis range must be [{-max_dim - 1}, {max_dim}], but axis is {axis}.")
+    ax = abs(len(xs) - len(ys)) + axis + 1 if axis < 0 else axis
+    if len(xs) >= len(ys):
+        big, small, small_is_y = xs, ys, True
+    else:
+        big, small, small_is_y = ys, xs, False
+    if ax + len(small) > max_dim:
+        raise ValueError("Broadcast dimension mismatch: axis places the smaller operand out of range")
+    padded = [1] * ax + small + [1] * (max_dim - ax - len(small))
+    out = []
+    for a, b in zip(big, padded):
+        if not (a == b or a <= 1 or b <= 1):
+            x_, y_ = (big, padded) if small_is_y else (padded, big)
+            raise ValueError(
+                f"Broadcast dimension mismatch. Operands could not be broadcast together with "
+                f"the shape of X = {x_} and the shape of Y = {y_}.")
+        out.append(0 if (a == 0 or b == 0) else (a if a > b else b))
+    return out
+
+
+def _elementwise(binary, ins, act=L.ACT_NONE, compound=0, scale_v=0.0, axis=-1,
+                 want_intermediate=False):
+    _require_cuda(*ins)
+    ins = [t.contiguous() for t in ins]
+    dt = ins[0].dtype
+    for t in ins[1:]:
+        if t.dtype != dt:
+            raise TypeError("b200phi elementwise: all inputs must share one dtype "
+                            "(type promotion happens above the kernel in Paddle)")
+    if len(ins) == 1:
+        out_shape = list(ins[0].shape)
+    else:
+        out_shape = broadcast_shape(ins[0].shape, ins[1].shape, axis)
+        for t in ins[2:]:
+            out_shape = broadcast_shape(out_shape, t.shape, -1)
+    out = torch.empty(out_shape, dtype=dt, device=ins[0].device)
+    inter = torch.empty(out_shape if compound == 0 else list(ins[1].shape), dtype=dt,
+                        device=ins[0].device) if want_intermediate else None
+    d = L.ElementwiseDesc()
+    d.binary = binary
+    d.act = act
+    d.compound = compound
+    d.scale = scale_v
+    d.dtype = _phi_dtype(dt)
+    d.arity = len(ins)
+    d.axis = axis
+    for i, t in enumerate(ins):
+        d.in_[i].rank = t.dim()
+        for j, s in enumerate(t.shape):
+            d.in_[i].dims[j] = s
+        d.in_[i].data = t.data_ptr()
+    d.out_rank = len(out_shape)
+    for j, s in enumerate(out_shape):
+        d.out_dims[j] = s
+    d.out = out.data_ptr()
+    d.intermediate_out = inter.data_ptr() if want_intermediate else None
+    if out.numel() > 0:
+        with torch.cuda.device(out.device):
+            L.check(L.lib().b200phi_elementwise(C.byref(d), _stream_ptr(out)))
+    return (out, inter) if want_intermediate else out
+
+
+def add(x, y, axis=-1):
+    return _elementwise(L.ADD, [x, y], axis=axis)
+
+
+def subtract(x, y, axis=-1):
+    return _elementwise(L.SUBTRACT, [x, y], axis=axis)
+
+
+def multiply(x, y, axis=-1):
+    return _elementwise(L.MULTIPLY, [x, y], axis=axis)
+
+
+def divide(x, y, axis=-1):
+    return _elementwise(L.DIVIDE, [x, y], axis=axis)
+
+
+def maximum(x, y, axis=-1):
+    return _elementwise(L.MAXIMUM, [x, y], axis=axis)
+
+
+def minimum(x, y, axis=-1):
+    return _elementwise(L.MINIMUM, [x, y], axis=axis)
+
+
+def add_n3(a, b, c):
+    """Ternary broadcast add, the shape of test_ternary_broadcast.cu:96-120."""
+    return _elementwise(L.ADD, [a, b, c])
+
+
+def relu(x):
+    return _elementwise(L.ADD, [x], act=L.ACT_RELU)
+
+
+def scale(x, s):
+    return _elementwise(L.ADD, [x], act=L.ACT_SCALE, scale_v=float(s))
+
+
+_BINARY_NAMES = {"elementwise_add": L.ADD, "elementwise_sub": L.SUBTRACT,
+                 "elementwise_mul": L.MULTIPLY}
+_UNARY_NAMES = {"relu": L.ACT_RELU, "scale": L.ACT_SCALE, "gelu": L.ACT_GELU,
+                "sigmoid": L.ACT_SIGMOID, "tanh": L.ACT_TANH}
+
+
+def fused_elemwise_activation(x, y, functor_list, axis=-1, scale=0.0,  # noqa: A002
+                              save_intermediate_out=False):
+    """fused_elemwise_activation / fused_elemwise_add_activation
+    (fused_ops.yaml:349-357; RunFunctors, fused_elemwise_activation_functor.h:388-458).
+    functor_list = [outer, inner]:
+      ["relu", "elementwise_add"]  -> out = relu(x + y),   intermediate = x + y
+      ["elementwise_add", "relu"]  -> out = x + relu(y),   intermediate = relu(y)
+    """
+    if len(functor_list) != 2:
+        raise ValueError("functor_list must hold exactly two functor names")
+    f0, f1 = functor_list
+    if f0 in _UNARY_NAMES and f1 in _BINARY_NAMES:
+        compound, act, binary = 0, _UNARY_NAMES[f0], _BINARY_NAMES[f1]
+    elif f0 in _BINARY_NAMES and f1 in _UNARY_NAMES:
+        compound, act, binary = 1, _UNARY_NAMES[f1], _BINARY_NAMES[f0]
+    else:
+        raise ValueError(f"{functor_list} is not a (unary, binary) or (binary, unary) pair")
+    return _elementwise(binary, [x, y], act=act, compound=compound, scale_v=float(scale),
+                        axis=axis, want_intermediate=save_intermediate_out)
+
+
+def fused_elemwise_add_activation(x, y, functor_list, axis=-1, scale=0.0,  # noqa: A002
+                                  save_intermediate_out=False):
+    if "elementwise_add" not in functor_list:
+        raise ValueError("fused_elemwise_add_activation needs elementwise_add in functor_list")
+    return fused_elemwise_activation(x, y, functor_list, axis, scale, save_intermediate_out)

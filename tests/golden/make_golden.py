@@ -1,0 +1,88 @@
+"""Generates tests/golden/phi_ref_golden.npz from the REFERENCE build of the oracle
+(oracle/_ref/libphi_ref.so: the reference's own functors + vendored Eigen, compiled
+from /root/reference by oracle/Makefile).  Run in the build container only:
+
+    make -C oracle ref && python tests/golden/make_golden.py
+
+The fixture holds, for every case of tests/cases.py, the input(s) and the output
+the reference arithmetic produced, plus the literal answers of the reference's
+docstring examples.  The GPU box has no /root/reference; it checks against this file.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import cases  # noqa: E402
+from oracle import pyoracle as O  # noqa: E402
+
+
+def main():
+    assert O.have_ref(), "build oracle/_ref first (make -C oracle ref)"
+    store = {}
+    for i, (op, dt, shape, axis, keepdim, _src) in enumerate(cases.REDUCE_CASES):
+        rng = np.random.default_rng(123 + i)
+        kind = "logical" if op in ("any", "all") else ("prod" if op == "prod" else "uniform")
+        x = cases.make_input(rng, dt, shape, kind)
+        store[f"reduce_{i}_x"] = x
+        store[f"reduce_{i}_y"] = O.reduce(op, x, axis, keepdim, impl="ref")
+    for i, (idt, odt, shape, axis, keepdim, _src) in enumerate(cases.SUM_DTYPE_CASES):
+        rng = np.random.default_rng(1000 + i)
+        x = cases.make_input(rng, idt, shape)
+        store[f"sumdt_{i}_x"] = x
+        if np.dtype(odt) in (np.dtype(np.float32), np.dtype(np.float64), np.dtype(np.int32),
+                             np.dtype(np.int64)):
+            store[f"sumdt_{i}_y"] = O.reduce("sum", x, axis, keepdim, out_dtype=odt, impl="ref")
+    for i, (op, dt, shape, axis, keepdim, idt, _src) in enumerate(cases.ARG_CASES):
+        rng = np.random.default_rng(2000 + i)
+        x = (1000 * rng.random(shape)).astype(dt)  # test_arg_min_max_op.py:38
+        store[f"arg_{i}_x"] = x
+        store[f"arg_{i}_y"] = O.argreduce(op, x, axis, keepdim, np.dtype(idt), impl="ref")
+    for i, (xs, ys, axis, _src) in enumerate(cases.ADD_CASES):
+        rng = np.random.default_rng(3000 + i)
+        x = cases.make_input(rng, "float32", xs, "signed")
+        y = cases.make_input(rng, "float32", ys, "signed")
+        store[f"add_{i}_x"], store[f"add_{i}_y"] = x, y
+        store[f"add_{i}_z"] = O.elementwise("add", [x, y], axis=axis, impl="ref")
+    k = 0
+    for (xs, ys, axis, _src) in cases.FUSED_SHAPES:
+        for fl in cases.FUSED_FUNCTOR_LISTS:
+            rng = np.random.default_rng(4000 + k)
+            x = cases.make_input(rng, "float32", xs, "signed")
+            y = cases.make_input(rng, "float32", ys, "signed")
+            binary, act, compound = parse_functor_list(fl)
+            out, inter = O.elementwise(binary, [x, y], act=act, compound=compound, scale=0.1,
+                                       axis=axis, want_intermediate=True, impl="ref")
+            store[f"fused_{k}_x"], store[f"fused_{k}_y"] = x, y
+            store[f"fused_{k}_out"], store[f"fused_{k}_inter"] = out, inter
+            k += 1
+    # ternary broadcast (test/cpp/phi/kernels/test_ternary_broadcast.cu:96-120), scaled down
+    rng = np.random.default_rng(5000)
+    a = rng.random((1, 64, 112)).astype(np.float32)
+    b = rng.random((1, 64, 1)).astype(np.float32)
+    c = rng.random((1, 1, 112)).astype(np.float32)
+    store["ternary_a"], store["ternary_b"], store["ternary_c"] = a, b, c
+    store["ternary_out"] = O.elementwise("add", [a, b, c], impl="ref")
+    # row variance (test_variance_layer.py: np.var(ddof=1) oracle; composite stat.py:184-197)
+    x = np.random.default_rng(6000).random((64, 1000)).astype(np.float32)
+    store["var_x"] = x
+    store["var_y"] = O.var_composite(x, axis=-1, unbiased=True, impl="ref")
+    store["mean_y"] = O.reduce("mean", x, [-1], impl="ref")
+    np.savez_compressed(os.path.join(HERE, "phi_ref_golden.npz"), **store)
+    print("wrote", len(store), "arrays")
+
+
+def parse_functor_list(fl):
+    binary_names = {"elementwise_add": "add", "elementwise_mul": "multiply", "elementwise_sub": "subtract"}
+    if fl[0] in binary_names:
+        return binary_names[fl[0]], fl[1], 1
+    return binary_names[fl[1]], fl[0], 0
+
+
+if __name__ == "__main__":
+    main()

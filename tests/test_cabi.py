@@ -1,0 +1,135 @@
+"""The C-ABI library loads on a CPU-only box, exports every symbol include/b200phi.h
+declares, and its host-side planning (no kernel launch) reports errors the way the
+reference does.  No compute calls here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200phi.h")).read()
+    return sorted(set(re.findall(r"B200PHI_API\s+[\w\s\*]+?\b(b200phi_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_expected_surface():
+    from paddle2_b200 import _lib
+    assert _declared_symbols() == sorted(_lib.EXPORTS)
+
+
+def test_library_exports_every_declared_symbol():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    for name in _declared_symbols():
+        assert hasattr(lib, name), name
+    assert b"sm_100a" in lib.b200phi_version()
+
+
+def test_struct_layout_matches_header():
+    """ctypes mirrors of the POD descriptors must have the C sizes (checked by compiling
+    a tiny C program against the header)."""
+    import subprocess
+    import tempfile
+    from paddle2_b200 import _lib
+    src = r'''
+#include <stdio.h>
+#include "b200phi.h"
+int main(void){printf("%zu %zu %zu %zu %zu\n", sizeof(b200phi_reduce_desc), sizeof(b200phi_argreduce_desc),
+ sizeof(b200phi_rowstats_desc), sizeof(b200phi_tensor_view), sizeof(b200phi_elementwise_desc)); return 0;}
+'''
+    with tempfile.TemporaryDirectory() as td:
+        c = os.path.join(td, "s.c")
+        open(c, "w").write(src)
+        exe = os.path.join(td, "s")
+        subprocess.run(["/usr/bin/gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe], check=True)
+        sizes = [int(v) for v in subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()]
+    assert sizes == [C.sizeof(_lib.ReduceDesc), C.sizeof(_lib.ArgReduceDesc), C.sizeof(_lib.RowStatsDesc),
+                     C.sizeof(_lib.TensorView), C.sizeof(_lib.ElementwiseDesc)]
+
+
+def _reduce_desc(dims, axes, op=0, in_dtype=10, out_dtype=0, reduce_all=0):
+    from paddle2_b200 import _lib
+    d = _lib.ReduceDesc()
+    d.op, d.in_dtype, d.out_dtype, d.rank = op, in_dtype, out_dtype, len(dims)
+    for i, s in enumerate(dims):
+        d.dims[i] = s
+    d.naxes = len(axes)
+    for i, a in enumerate(axes):
+        d.axes[i] = a
+    d.reduce_all = reduce_all
+    return d
+
+
+def test_planner_errors_match_reference_messages():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    # empty tensor: reduce_function.h:1052-1055
+    d = _reduce_desc([0, 3], [0])
+    assert lib.b200phi_reduce(C.byref(d), None) == 1
+    assert b"Tensor need be reduced must not empty." in lib.b200phi_last_error()
+    # axis out of range: reduce_function.h:112-118
+    d = _reduce_desc([2, 3], [2])
+    assert lib.b200phi_reduce(C.byref(d), None) == 1
+    assert b"should be in the range" in lib.b200phi_last_error()
+    # unknown dtype / unsupported pair
+    d = _reduce_desc([2, 3], [1], in_dtype=12)
+    assert lib.b200phi_reduce(C.byref(d), None) == 2
+    d = _reduce_desc([2, 3], [1], op=2, in_dtype=10, out_dtype=11)  # max keeps the dtype
+    assert lib.b200phi_reduce(C.byref(d), None) == 2
+    with pytest.raises(_lib.B200PhiError):
+        _lib.check(1)
+
+
+def test_workspace_query_is_pure_host_logic():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    # C1: row reduce, no scratch
+    assert lib.b200phi_reduce_workspace(C.byref(_reduce_desc([32, 1024, 4096], [2]))) == 0
+    # C5: axis-0 reduce of [524288, 4096] splits rows across CTAs -> partials + tickets
+    ws = lib.b200phi_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0])))
+    assert ws > 4096 * 4 and ws % 4 == 0
+    # full reduction of 2^31 elements (the numel > INT32_MAX regime, kps/reduce_kernel.cu:196)
+    ws = lib.b200phi_reduce_workspace(C.byref(_reduce_desc([2 ** 31], [0])))
+    assert 0 < ws < (1 << 20)
+
+
+def test_elementwise_plan_errors():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    d = _lib.ElementwiseDesc()
+    d.binary, d.act, d.dtype, d.arity, d.axis = 0, 0, 10, 2, -1
+    d.in_[0].rank = 2
+    d.in_[0].dims[0], d.in_[0].dims[1] = 2, 3
+    d.in_[1].rank = 2
+    d.in_[1].dims[0], d.in_[1].dims[1] = 2, 4
+    d.out_rank = 2
+    d.out_dims[0], d.out_dims[1] = 2, 4
+    assert lib.b200phi_elementwise(C.byref(d), None) == 1
+    assert b"Broadcast dimension mismatch" in lib.b200phi_last_error()
+
+
+def test_no_cpu_fallback():
+    """The product path refuses host tensors instead of silently computing on the CPU."""
+    import torch
+    import paddle2_b200 as pb
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        pb.sum(torch.ones(4, 4))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        pb.add(torch.ones(4), torch.ones(4))
+
+
+def test_product_code_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under paddle2_b200/ may reference it."""
+    bad = []
+    for base, _dirs, files in os.walk(os.path.join(ROOT, "paddle2_b200")):
+        if "build" in base.split(os.sep):
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")) or f == "Makefile":
+                text = open(os.path.join(base, f), errors="ignore").read()
+                if "pyoracle" in text or "phi_oracle" in text or "libphi_ref" in text:
+                    bad.append(os.path.join(base, f))
+    assert not bad, bad

@@ -1,0 +1,59 @@
+"""Two-rank NCCL run of the sharded reduce (skipped unless >= 2 GPUs are visible):
+one process per GPU, local reduce + allreduce in one C-ABI call."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, ret):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import pyoracle as O
+        from paddle2_b200 import _lib as L
+        from paddle2_b200.dist import ShardedReducer, partition_rows
+        total_rows, cols = 40003, 1024
+        full = np.random.default_rng(123).random((total_rows, cols)).astype(np.float32)
+        start, count = partition_rows(total_rows, world, rank)
+        x = torch.from_numpy(full[start:start + count]).cuda()
+        red = ShardedReducer()
+        got = red.sum(x).cpu().numpy()
+        np.testing.assert_allclose(got, O.reduce("sum", full, [0]), rtol=1e-5)
+        got = red.reduce(L.MAX, x).cpu().numpy()
+        assert np.array_equal(got, O.reduce("max", full, [0]))
+        got = red.reduce(L.MEAN, x).cpu().numpy()
+        np.testing.assert_allclose(got, O.reduce("mean", full, [0]), rtol=1e-5)
+        torch.cuda.synchronize()
+        red.close()
+        ret[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_nccl_sharded_sum():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
+    assert dict(ret) == {0: "ok", 1: "ok"}

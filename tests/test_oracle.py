@@ -1,0 +1,177 @@
+"""Pins the oracle (oracle/phi_oracle.c, the plain-C port) before anything trusts it:
+  * against the committed golden vectors that the REFERENCE build produced
+    (tests/golden/phi_ref_golden.npz, generator tests/golden/make_golden.py),
+  * against the reference build itself when oracle/_ref/libphi_ref.so is present
+    (it is built here from /root/reference and travels to the GPU box),
+  * against the literal answers in the reference's docstrings.
+Bit-exact for every dtype, floating point included: the port restates Eigen's
+accumulation order."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_ref_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(GOLDEN)
+
+
+@pytest.mark.parametrize("i", range(len(cases.REDUCE_CASES)))
+def test_reduce_port_matches_golden(oracle, golden, i):
+    op, dt, shape, axis, keepdim, src = cases.REDUCE_CASES[i]
+    x = golden[f"reduce_{i}_x"]
+    want = golden[f"reduce_{i}_y"]
+    got = oracle.reduce(op, x, axis, keepdim)
+    assert got.shape == want.shape and got.dtype == want.dtype, src
+    assert np.array_equal(got, want), src
+
+
+@pytest.mark.parametrize("i", range(len(cases.SUM_DTYPE_CASES)))
+def test_sum_dtype_port(oracle, golden, i):
+    idt, odt, shape, axis, keepdim, src = cases.SUM_DTYPE_CASES[i]
+    x = golden[f"sumdt_{i}_x"]
+    got = oracle.reduce("sum", x, axis, keepdim, out_dtype=odt)
+    if f"sumdt_{i}_y" in golden.files:
+        assert np.array_equal(got, golden[f"sumdt_{i}_y"]), src
+    else:  # narrow integer outputs: the reference casts, then accumulates in that type
+        want = x.astype(odt).sum(axis=tuple(axis) if axis is not None else None, dtype=odt,
+                                 keepdims=keepdim)
+        assert np.array_equal(got, want), src
+
+
+@pytest.mark.parametrize("i", range(len(cases.ARG_CASES)))
+def test_arg_port_matches_golden(oracle, golden, i):
+    op, dt, shape, axis, keepdim, idt, src = cases.ARG_CASES[i]
+    x = golden[f"arg_{i}_x"]
+    want = golden[f"arg_{i}_y"]
+    got = oracle.argreduce(op, x, axis, keepdim, np.dtype(idt))
+    assert got.dtype == want.dtype and got.shape == want.shape, src
+    assert np.array_equal(got, want), src
+    # and numpy agrees (the reference tests' own oracle, test_arg_min_max_op.py:40-50)
+    npf = np.argmax if op == "argmax" else np.argmin
+    ref = npf(x) if axis is None else npf(x, axis=axis)
+    assert np.array_equal(got.reshape(np.shape(ref)), ref), src
+
+
+@pytest.mark.parametrize("i", range(len(cases.ADD_CASES)))
+def test_add_port_matches_golden(oracle, golden, i):
+    xs, ys, axis, src = cases.ADD_CASES[i]
+    got = oracle.elementwise("add", [golden[f"add_{i}_x"], golden[f"add_{i}_y"]], axis=axis)
+    assert np.array_equal(got, golden[f"add_{i}_z"]), src
+
+
+def test_fused_port_matches_golden(oracle, golden):
+    from golden.make_golden import parse_functor_list
+    k = 0
+    for (xs, ys, axis, src) in cases.FUSED_SHAPES:
+        for fl in cases.FUSED_FUNCTOR_LISTS:
+            binary, act, compound = parse_functor_list(fl)
+            out, inter = oracle.elementwise(binary, [golden[f"fused_{k}_x"], golden[f"fused_{k}_y"]],
+                                            act=act, compound=compound, scale=0.1, axis=axis,
+                                            want_intermediate=True)
+            np.testing.assert_allclose(out, golden[f"fused_{k}_out"], rtol=1e-6, atol=1e-7,
+                                       err_msg=f"{src} {fl}")
+            np.testing.assert_allclose(inter, golden[f"fused_{k}_inter"], rtol=1e-6, atol=1e-7)
+            k += 1
+
+
+def test_ternary_and_var_port(oracle, golden):
+    out = oracle.elementwise("add", [golden["ternary_a"], golden["ternary_b"], golden["ternary_c"]])
+    assert np.array_equal(out, golden["ternary_out"])
+    mean, var = oracle.rowstats_f32(golden["var_x"], unbiased=True)
+    assert np.array_equal(var, golden["var_y"])
+    assert np.array_equal(mean, golden["mean_y"])
+    # the reference test's own oracle: numpy variance with ddof=1 (test_variance_layer.py)
+    np.testing.assert_allclose(var, np.var(golden["var_x"].astype(np.float64), axis=-1, ddof=1),
+                               rtol=1e-4)
+
+
+def test_docstring_examples(oracle):
+    """Literal answers in python/paddle/tensor/math.py (sum :1475-1567, max :2870-2987)
+    and search.py (argmax)."""
+    x = np.array([[0.2, 0.3, 0.5, 0.9], [0.1, 0.2, 0.6, 0.7]], dtype=np.float32)
+    np.testing.assert_allclose(oracle.reduce("sum", x, None), 3.5, rtol=1e-6)
+    np.testing.assert_allclose(oracle.reduce("sum", x, [0]), [0.3, 0.5, 1.1, 1.6], rtol=1e-6)
+    np.testing.assert_allclose(oracle.reduce("sum", x, [-1]), [1.9, 1.6], rtol=1e-6)
+    np.testing.assert_allclose(oracle.reduce("sum", x, [-1], keepdim=True), [[1.9], [1.6]], rtol=1e-6)
+    y = np.array([[[1, 2], [3, 4]], [[5, 6], [7, 8]]], dtype=np.float32)
+    np.testing.assert_allclose(oracle.reduce("sum", y, [1, 2]), [10, 26])
+    np.testing.assert_allclose(oracle.reduce("sum", y, [0, 1]), [16, 20])
+    b = np.array([[True, True, True, True], [False, False, False, False]])
+    assert oracle.reduce("sum", b, None, out_dtype=np.int64) == 4
+    assert np.array_equal(oracle.reduce("sum", b, [0], out_dtype=np.int64), [1, 1, 1, 1])
+    assert np.array_equal(oracle.reduce("sum", b, [1], out_dtype=np.int64), [4, 0])
+    np.testing.assert_allclose(oracle.reduce("max", x, None), 0.9)
+    np.testing.assert_allclose(oracle.reduce("max", x, [0]), [0.2, 0.3, 0.6, 0.9])
+    np.testing.assert_allclose(oracle.reduce("max", x, [-1]), [0.9, 0.7])
+    a = np.array([[5, 8, 9, 5], [0, 0, 1, 7], [6, 9, 2, 4]], dtype=np.float32)
+    assert oracle.argreduce("argmax", a, None) == 2
+    assert np.array_equal(oracle.argreduce("argmax", a, 0), [2, 2, 0, 1])
+    assert np.array_equal(oracle.argreduce("argmax", a, -1), [2, 3, 1])
+    assert np.array_equal(oracle.argreduce("argmin", a, -1), [0, 0, 2])
+
+
+def test_tie_break_and_identity_rows(oracle):
+    """SURVEY.md probe P7: lowest index on ties; an all-lowest() row answers 0."""
+    i64 = np.iinfo(np.int64)
+    x = np.array([[1, 3, 3, 2], [i64.min] * 4, [5, 1, 5, 5]], dtype=np.int64)
+    assert np.array_equal(oracle.argreduce("argmax", x, 1), [1, 0, 0])
+    y = np.array([[i64.max] * 4, [2, 1, 1, 3]], dtype=np.int64)
+    assert np.array_equal(oracle.argreduce("argmin", y, 1), [0, 1])
+
+
+def test_errors(oracle):
+    with pytest.raises(ValueError):
+        oracle.reduce("sum", np.zeros((0, 3), np.float32), [0])  # "must not empty"
+    with pytest.raises(ValueError):
+        oracle.elementwise("add", [np.zeros((2, 3), np.float32), np.zeros((2, 4), np.float32)])
+
+
+# ---- against the reference build itself, on fresh random inputs -----------------------------
+def _need_ref(oracle):
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref/libphi_ref.so not built (needs /root/reference)")
+
+
+@pytest.mark.parametrize("shape,axis", [
+    ((5, 6, 10), [0]), ((5, 6, 10), [-1]), ((32, 4096), [-1]), ((3, 100000), [1]),
+    ((100000,), None), ((2, 4, 3, 5, 6, 10), [2, 4]), ((2, 5, 3, 2, 2, 3, 4, 2), (1, 3, 4)),
+    ((5, 6, 10), [0, 2]), ((20000, 16), [0]), ((7, 33, 9), [1]), ((100, 1, 1), [1, 2]),
+])
+def test_port_equals_reference_build_reduce(oracle, shape, axis):
+    _need_ref(oracle)
+    rng = np.random.default_rng(123)
+    for dt in (np.float32, np.float64, np.int32, np.int64):
+        x = (rng.random(shape) * (10 if np.issubdtype(dt, np.integer) else 1)).astype(dt)
+        for op in ("sum", "mean", "max", "min", "prod"):
+            if op == "mean" and np.issubdtype(dt, np.integer):
+                continue
+            a = oracle.reduce(op, x, axis, impl="port")
+            b = oracle.reduce(op, x, axis, impl="ref")
+            assert np.array_equal(a, b), (shape, axis, dt, op)
+    xb = rng.integers(0, 2, size=shape).astype(np.bool_)
+    for op in ("any", "all"):
+        assert np.array_equal(oracle.reduce(op, xb, axis), oracle.reduce(op, xb, axis, impl="ref"))
+
+
+def test_port_equals_reference_build_arg_and_elementwise(oracle):
+    _need_ref(oracle)
+    rng = np.random.default_rng(7)
+    for shape, axis in [((3, 4, 5), 0), ((3, 4), 1), ((3, 4, 5), None), ((64, 257), 1)]:
+        for dt in (np.float32, np.float64, np.int32, np.int64):
+            x = (rng.random(shape) * 4).astype(dt)  # few distinct ints: ties
+            for op in ("argmax", "argmin"):
+                assert np.array_equal(oracle.argreduce(op, x, axis),
+                                      oracle.argreduce(op, x, axis, impl="ref"))
+    for xs, ys, ax, _ in cases.ADD_CASES:
+        for dt in (np.float32, np.float64, np.int32, np.int64):
+            x = (rng.random(xs) * 5 - 2).astype(dt)
+            y = (rng.random(ys) * 5 - 2).astype(dt)
+            for b in ("add", "subtract", "multiply", "maximum", "minimum"):
+                assert np.array_equal(oracle.elementwise(b, [x, y], axis=ax),
+                                      oracle.elementwise(b, [x, y], axis=ax, impl="ref"))
