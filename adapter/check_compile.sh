@@ -1,0 +1,12 @@
+#!/bin/sh
+# Compile-check of the adapter against the reference headers (needs /root/reference).
+# It proves the signatures and PD_REGISTER_KERNEL registrations type-check; linking needs libphi.
+set -e
+REF=${REF:-/root/reference}
+HERE=$(cd "$(dirname "$0")" && pwd)
+OUT=${OUT:-/tmp/phi_b200_kernels.o}
+/usr/local/cuda/bin/nvcc -std=c++17 -gencode arch=compute_100a,code=sm_100a -DPADDLE_WITH_CUDA -DEIGEN_USE_GPU \
+  --expt-relaxed-constexpr --expt-extended-lambda -w \
+  -I"$HERE/shim" -I"$HERE/../include" -I"$REF" -I"$REF/third_party/eigen3" \
+  -c "$HERE/phi_b200_kernels.cu" -o "$OUT"
+echo "adapter compiles: $OUT"

@@ -1,0 +1,277 @@
+// Drop-in adapter: the phi kernel bodies for the reduce / argmax / elementwise family,
+// implemented on libb200phi.so's C ABI (include/b200phi.h), registered under the
+// reference's own kernel names and signatures.  This is the ONLY translation unit
+// that sees phi types; it is compiled inside a Paddle build in place of
+//   paddle/phi/kernels/kps/reduce_kernel.cu            (SumRaw/MeanRaw/Max/MinRaw/Prod/AnyRaw/AllRaw/AMaxRaw/AMinRaw)
+//   paddle/phi/kernels/legacy/kps/reduce_max_kernel.cu (MaxRaw)
+//   paddle/phi/kernels/gpu/arg_min_max_kernel.cu       (ArgMax/ArgMin)
+//   paddle/phi/kernels/kps/elementwise_kernel.cu + legacy/kps/elementwise_kernel.cu (Add..Minimum, *Raw)
+//   paddle/phi/kernels/fusion/gpu/fused_elemwise_activation_kernel.cu
+// (those files are globbed by paddle/phi/kernels/CMakeLists.txt:33-34, so swapping the
+// file swaps the kernel).  Here it is compile-checked against the
+// reference headers (tests/test_adapter_compile.py); it cannot be linked without libphi.
+//
+// Contract kept: signatures of reduce_sum_kernel.h:22-37 etc.; out's dims/dtype come
+// from InferMeta; storage from dev_ctx.Alloc; scratch from a local DenseTensor + Alloc
+// (freed stream-safely by the context allocator); everything enqueued on
+// dev_ctx.stream(); errors raised as EnforceNotMet via PADDLE_THROW.
+#include <vector>
+
+#include "b200phi.h"
+#include "paddle/phi/backends/gpu/gpu_context.h"
+#include "paddle/phi/common/int_array.h"
+#include "paddle/phi/common/scalar.h"
+#include "paddle/phi/core/dense_tensor.h"
+#include "paddle/phi/core/kernel_registry.h"
+
+namespace phi {
+namespace b200 {
+
+inline void Check(int status) {
+  if (status != B200PHI_OK) {
+    PADDLE_THROW(common::errors::InvalidArgument("%s", b200phi_last_error()));
+  }
+}
+
+inline void FillDims(const DenseTensor& t, int32_t* rank, int64_t* dims) {
+  *rank = t.dims().size();
+  for (int i = 0; i < *rank; ++i) dims[i] = t.dims()[i];
+}
+
+template <typename Context>
+void Reduce(const Context& dev_ctx, int op, const DenseTensor& x, const std::vector<int64_t>& dims,
+            bool reduce_all, DenseTensor* out) {
+  // out->dtype() was fixed by InferMeta (e.g. int32 -> int64 for sum, BOOL for any/all)
+  dev_ctx.Alloc(out, out->dtype());
+  b200phi_reduce_desc d = {};
+  d.op = op;
+  d.in_dtype = static_cast<int>(x.dtype());
+  d.out_dtype = static_cast<int>(out->dtype());
+  FillDims(x, &d.rank, d.dims);
+  d.naxes = static_cast<int>(dims.size());
+  for (int i = 0; i < d.naxes && i < B200PHI_MAX_RANK; ++i) d.axes[i] = static_cast<int>(dims[i]);
+  d.reduce_all = reduce_all ? 1 : 0;
+  d.x = x.data();
+  d.out = out->data();
+  DenseTensor scratch;
+  const size_t ws = b200phi_reduce_workspace(&d);
+  if (ws > 0) {
+    scratch.Resize({static_cast<int64_t>(ws)});
+    d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+    d.workspace_bytes = ws;
+  }
+  Check(b200phi_reduce(&d, dev_ctx.stream()));
+}
+
+template <typename Context>
+void Arg(const Context& dev_ctx, int op, const DenseTensor& x, const Scalar& axis, bool flatten,
+         DataType dtype, DenseTensor* out) {
+  const DataType idx = (dtype == DataType::UNDEFINED) ? DataType::INT64 : dtype;
+  dev_ctx.Alloc(out, idx);
+  b200phi_argreduce_desc d = {};
+  d.op = op;
+  d.in_dtype = static_cast<int>(x.dtype());
+  d.index_dtype = static_cast<int>(idx);
+  FillDims(x, &d.rank, d.dims);
+  d.axis = axis.to<int64_t>();
+  d.flatten = flatten ? 1 : 0;
+  d.x = x.data();
+  d.out = out->data();
+  Check(b200phi_argreduce(&d, dev_ctx.stream()));
+}
+
+template <typename Context>
+void Elementwise(const Context& dev_ctx, int binary, int act, int compound, float scale,
+                 const DenseTensor& x, const DenseTensor& y, int axis, DenseTensor* out,
+                 DenseTensor* intermediate) {
+  dev_ctx.Alloc(out, x.dtype());
+  b200phi_elementwise_desc d = {};
+  d.binary = binary;
+  d.act = act;
+  d.compound = compound;
+  d.scale = scale;
+  d.dtype = static_cast<int>(x.dtype());
+  d.arity = 2;
+  d.axis = axis;
+  FillDims(x, &d.in[0].rank, d.in[0].dims);
+  d.in[0].data = x.data();
+  FillDims(y, &d.in[1].rank, d.in[1].dims);
+  d.in[1].data = y.data();
+  FillDims(*out, &d.out_rank, d.out_dims);
+  d.out = out->data();
+  if (intermediate != nullptr) {
+    dev_ctx.Alloc(intermediate, x.dtype());
+    d.intermediate_out = intermediate->data();
+  }
+  Check(b200phi_elementwise(&d, dev_ctx.stream()));
+}
+
+}  // namespace b200
+
+// ---- reductions: signatures of kps/reduce_kernel.cu:35-133,185-271 --------------------------
+template <typename T, typename Context>
+void SumRawKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+                  bool reduce_all, DataType out_dtype, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_SUM, x, dims.GetData(), reduce_all, out);
+}
+template <typename T, typename Context>
+void MeanRawKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+                   bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_MEAN, x, dims.GetData(), reduce_all, out);
+}
+template <typename T, typename Context>
+void MaxRawKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+                  bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_MAX, x, dims.GetData(), reduce_all, out);
+}
+template <typename T, typename Context>
+void MaxKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+               DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_MAX, x, dims.GetData(), false, out);
+}
+template <typename T, typename Context>
+void MinRawKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+                  bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_MIN, x, dims.GetData(), reduce_all, out);
+}
+template <typename T, typename Context>
+void AMaxRawKernel(const Context& dev_ctx, const DenseTensor& x, const std::vector<int64_t>& dims,
+                   bool keep_dim, bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_AMAX, x, dims, reduce_all, out);
+}
+template <typename T, typename Context>
+void AMinRawKernel(const Context& dev_ctx, const DenseTensor& x, const std::vector<int64_t>& dims,
+                   bool keep_dim, bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_AMIN, x, dims, reduce_all, out);
+}
+template <typename T, typename Context>
+void ProdKernel(const Context& dev_ctx, const DenseTensor& x, const IntArray& dims, bool keep_dim,
+                bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_PROD, x, dims.GetData(), reduce_all, out);
+}
+template <typename T, typename Context>
+void AnyRawKernel(const Context& dev_ctx, const DenseTensor& x, const std::vector<int64_t>& dims,
+                  bool keep_dim, bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_ANY, x, dims, reduce_all, out);
+}
+template <typename T, typename Context>
+void AllRawKernel(const Context& dev_ctx, const DenseTensor& x, const std::vector<int64_t>& dims,
+                  bool keep_dim, bool reduce_all, DenseTensor* out) {
+  b200::Reduce(dev_ctx, B200PHI_ALL, x, dims, reduce_all, out);
+}
+
+// ---- argmax / argmin: arg_min_max_kernel.h:22-38 ---------------------------------------------
+template <typename T, typename Context>
+void ArgMaxKernel(const Context& dev_ctx, const DenseTensor& x, const Scalar& axis, bool keepdims,
+                  bool flatten, DataType dtype, DenseTensor* out) {
+  b200::Arg(dev_ctx, B200PHI_ARGMAX, x, axis, flatten, dtype, out);
+}
+template <typename T, typename Context>
+void ArgMinKernel(const Context& dev_ctx, const DenseTensor& x, const Scalar& axis, bool keepdims,
+                  bool flatten, DataType dtype, DenseTensor* out) {
+  b200::Arg(dev_ctx, B200PHI_ARGMIN, x, axis, flatten, dtype, out);
+}
+
+// ---- elementwise: impl/elementwise_kernel_impl.h:50-62 (DEFINE_CUDA_ELEMENTWISE_OP) ----------
+#define B200_DEFINE_ELEMENTWISE(Name, BinaryId)                                               \
+  template <typename T, typename Context>                                                     \
+  void Name##RawKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,    \
+                       int axis, DenseTensor* out) {                                          \
+    b200::Elementwise(dev_ctx, BinaryId, B200PHI_ACT_NONE, 0, 0.f, x, y, axis, out, nullptr); \
+  }                                                                                           \
+  template <typename T, typename Context>                                                     \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,       \
+                    DenseTensor* out) {                                                       \
+    b200::Elementwise(dev_ctx, BinaryId, B200PHI_ACT_NONE, 0, 0.f, x, y, -1, out, nullptr);   \
+  }
+B200_DEFINE_ELEMENTWISE(Add, B200PHI_ADD)
+B200_DEFINE_ELEMENTWISE(Subtract, B200PHI_SUBTRACT)
+B200_DEFINE_ELEMENTWISE(Multiply, B200PHI_MULTIPLY)
+B200_DEFINE_ELEMENTWISE(Divide, B200PHI_DIVIDE)
+B200_DEFINE_ELEMENTWISE(Maximum, B200PHI_MAXIMUM)
+B200_DEFINE_ELEMENTWISE(Minimum, B200PHI_MINIMUM)
+
+// ---- fused add + activation: impl/fused_elemwise_activation_kernel_impl.h:202-222 ----------------
+template <typename T, typename Context>
+void FusedElemwiseAddActivationKernel(const Context& dev_ctx, const DenseTensor& x,
+                                      const DenseTensor& y,
+                                      const std::vector<std::string>& functor_list, int axis,
+                                      float scale, bool save_intermediate_out, DenseTensor* out,
+                                      DenseTensor* intermediate_out) {
+  PADDLE_ENFORCE_EQ(functor_list.size(), 2UL,
+                    common::errors::InvalidArgument("functor_list must hold two functors"));
+  auto unary_id = [](const std::string& s) -> int {
+    if (s == "relu") return B200PHI_ACT_RELU;
+    if (s == "scale") return B200PHI_ACT_SCALE;
+    if (s == "gelu") return B200PHI_ACT_GELU;
+    if (s == "sigmoid") return B200PHI_ACT_SIGMOID;
+    if (s == "tanh") return B200PHI_ACT_TANH;
+    return -1;
+  };
+  int compound = 0, act = -1;
+  if (functor_list[1] == "elementwise_add") {         // Unary(Binary(x, y))
+    act = unary_id(functor_list[0]);
+  } else if (functor_list[0] == "elementwise_add") {  // Binary(x, Unary(y))
+    act = unary_id(functor_list[1]);
+    compound = 1;
+  }
+  PADDLE_ENFORCE_GE(act, 0, common::errors::InvalidArgument(
+                                "%s, %s is not a supported functor pair", functor_list[0], functor_list[1]));
+  b200::Elementwise(dev_ctx, B200PHI_ADD, act, compound, scale, x, y, axis, out,
+                    save_intermediate_out ? intermediate_out : nullptr);
+}
+
+}  // namespace phi
+
+// ---- registrations: same names, backend GPU (KPS folds into GPU, backend.h:140-148) ------------
+// dtype lists follow kps/reduce_kernel.cu:302-410 and reduce_sum_kernel.cc:60-77 minus the
+// complex types, which this library does not implement ("what stays").
+using float16 = phi::dtype::float16;
+using bfloat16 = phi::dtype::bfloat16;
+
+PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, phi::SumRawKernel, bool, float, double, float16,
+                   bfloat16, int16_t, int, int64_t, uint8_t, int8_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(mean_raw, GPU, ALL_LAYOUT, phi::MeanRawKernel, float, double, bool, float16,
+                   bfloat16, int, int64_t) {}
+PD_REGISTER_KERNEL(max_raw, GPU, ALL_LAYOUT, phi::MaxRawKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(max, GPU, ALL_LAYOUT, phi::MaxKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(min_raw, GPU, ALL_LAYOUT, phi::MinRawKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(amax_raw, GPU, ALL_LAYOUT, phi::AMaxRawKernel, float, double, int, int64_t) {}
+PD_REGISTER_KERNEL(amin_raw, GPU, ALL_LAYOUT, phi::AMinRawKernel, float, double, int, int64_t) {}
+PD_REGISTER_KERNEL(prod, GPU, ALL_LAYOUT, phi::ProdKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(any_raw, GPU, ALL_LAYOUT, phi::AnyRawKernel, float, double, int, int64_t, bool) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::BOOL);
+}
+PD_REGISTER_KERNEL(all_raw, GPU, ALL_LAYOUT, phi::AllRawKernel, float, double, int, int64_t, bool) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::BOOL);
+}
+PD_REGISTER_KERNEL(argmax, GPU, ALL_LAYOUT, phi::ArgMaxKernel, float16, bfloat16, float, double,
+                   int32_t, int64_t, int16_t, uint8_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(argmin, GPU, ALL_LAYOUT, phi::ArgMinKernel, float16, bfloat16, float, double,
+                   int32_t, int64_t, int16_t, uint8_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(add, GPU, ALL_LAYOUT, phi::AddKernel, float, double, int16_t, int, bool, uint8_t,
+                   int8_t, int64_t, float16, bfloat16) {}
+PD_REGISTER_KERNEL(add_raw, GPU, ALL_LAYOUT, phi::AddRawKernel, float, double, int16_t, int, bool,
+                   uint8_t, int8_t, int64_t, float16, bfloat16) {}
+PD_REGISTER_KERNEL(subtract, GPU, ALL_LAYOUT, phi::SubtractKernel, float, double, int16_t, int,
+                   int64_t, float16, bfloat16) {}
+PD_REGISTER_KERNEL(multiply, GPU, ALL_LAYOUT, phi::MultiplyKernel, float, double, int, int64_t, bool,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(divide, GPU, ALL_LAYOUT, phi::DivideKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(maximum, GPU, ALL_LAYOUT, phi::MaximumKernel, float, double, int, int64_t,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(minimum, GPU, ALL_LAYOUT, phi::MinimumKernel, float, double, int, int64_t,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(fused_elemwise_add_activation, GPU, ALL_LAYOUT,
+                   phi::FusedElemwiseAddActivationKernel, float, double, float16) {}
