@@ -42,46 +42,58 @@ def env_int(name, default):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock + throttle reasons during the timed region, read in-process through NVML
+    (the same counters `nvidia-smi --query-gpu=clocks.sm,clocks_event_reasons.*` prints;
+    spawning nvidia-smi next to a 30 ms timed region perturbs it)."""
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, period=0.01):
         super().__init__(daemon=True)
         self.gpu = gpu_index
-        self.samples = []
+        self.period = period
+        self.sm = []
+        self.reasons = set()
+        self.smax = None
         self.stop_flag = threading.Event()
+        self.h = None
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = gpu_index
+            if vis:
+                try:
+                    idx = int(vis.split(",")[gpu_index])
+                except (ValueError, IndexError):
+                    idx = gpu_index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
 
     def run(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        names = [("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                 ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                 ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                 ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap)]
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.gpu)], capture_output=True, text=True, timeout=5).stdout
-                f = [v.strip() for v in out.strip().split(",")]
-                if len(f) >= 8:
-                    self.samples.append(f)
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for n, bit in names:
+                    if mask & bit:
+                        self.reasons.add(n)
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(self.period)
 
     def summary(self):
-        sm = []
-        reasons = set()
-        smax = None
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for f in self.samples:
-            try:
-                sm.append(float(f[1]))
-                smax = float(f[2])
-            except ValueError:
-                continue
-            for n, v in zip(names, f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.smax,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml"}
 
 
 def measured_peak():
@@ -229,29 +241,81 @@ def time_steps(torch, fn, steps, warmup, dist=None):
 
 
 def other_configs(torch, pb):
-    """Kernel-only GB/s of C1-C4 (parity cases, reported for context; inputs > L2)."""
+    """Kernel-only GB/s of C1-C4 (parity cases, reported for context; inputs > L2).
+    Descriptors and outputs are prepared once and the C ABI is called back to back, so the
+    figure is the kernel's, not the Python wrapper's."""
+    import ctypes as C
+    from paddle2_b200 import _lib as L
+    lib = L.lib()
     res = {}
 
-    def t(fn, nbytes, iters=10, warm=3):
+    def t(fn, nbytes, iters=20, warm=5):
         s = time_steps(torch, fn, iters, warm)
         return round(nbytes / (s / iters) / 1e9, 1)
 
+    def stream():
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
     x = torch.rand(32, 1024, 4096, device="cuda")
-    res["C1_sum_fp32_32x1024x4096_lastaxis"] = t(lambda: pb.sum(x, axis=-1), 537001984)
-    del x
-    x = torch.rand(256, 64, 112, 112, device="cuda")
-    y = torch.rand(64, 1, 1, device="cuda")
-    res["C2_add_relu_fp32_256x64x112x112"] = t(
-        lambda: pb.fused_elemwise_add_activation(x, y, ["relu", "elementwise_add"]), 1644167424)
-    del x, y
+    out = torch.empty(32, 1024, device="cuda")
+    d = L.ReduceDesc()
+    d.op, d.in_dtype, d.out_dtype, d.rank = L.SUM, L.FLOAT32, L.FLOAT32, 3
+    d.dims[0], d.dims[1], d.dims[2] = 32, 1024, 4096
+    d.naxes = 1
+    d.axes[0] = 2
+    d.x, d.out = x.data_ptr(), out.data_ptr()
+    res["C1_sum_fp32_32x1024x4096_lastaxis"] = t(lambda: L.check(lib.b200phi_reduce(C.byref(d), stream())), 537001984)
+    assert torch.allclose(out, x.sum(-1), rtol=1e-4)
+    del x, out
+
+    x = torch.rand(256, 64, 112, 112, device="cuda") * 2 - 1
+    y = torch.rand(64, 1, 1, device="cuda") * 2 - 1
+    out = torch.empty_like(x)
+    e = L.ElementwiseDesc()
+    e.binary, e.act, e.compound, e.dtype, e.arity, e.axis = L.ADD, L.ACT_RELU, 0, L.FLOAT32, 2, -1
+    for i, tt in enumerate((x, y)):
+        e.in_[i].rank = tt.dim()
+        for j, sz in enumerate(tt.shape):
+            e.in_[i].dims[j] = sz
+        e.in_[i].data = tt.data_ptr()
+    e.out_rank = 4
+    for j, sz in enumerate(x.shape):
+        e.out_dims[j] = sz
+    e.out = out.data_ptr()
+    res["C2_add_relu_fp32_256x64x112x112"] = t(lambda: L.check(lib.b200phi_elementwise(C.byref(e), stream())), 1644167424)
+    assert torch.equal(out[3], torch.relu(x[3] + y))
+    del x, y, out
+
+    def arg_desc(xt, idx, val):
+        a = L.ArgReduceDesc()
+        a.op, a.in_dtype, a.index_dtype, a.rank = L.ARGMAX, pb.ops._phi_dtype(xt.dtype), L.INT64, 2
+        a.dims[0], a.dims[1] = xt.shape
+        a.axis = 1
+        a.x, a.out, a.max_out = xt.data_ptr(), idx.data_ptr(), val.data_ptr()
+        return a
+
     x = torch.randint(-(2 ** 40), 2 ** 40, (8192, 32000), device="cuda", dtype=torch.int64)
-    res["C3a_argmax+max_int64_8192x32000"] = t(lambda: pb.argmax_with_value(x, axis=-1), 2097283072)
+    idx = torch.empty(8192, device="cuda", dtype=torch.int64)
+    val = torch.empty(8192, device="cuda", dtype=torch.int64)
+    a = arg_desc(x, idx, val)
+    res["C3a_argmax+max_int64_8192x32000"] = t(lambda: L.check(lib.b200phi_argreduce(C.byref(a), stream())), 2097283072)
+    assert torch.equal(val, x.max(1).values)
     del x
     x = torch.randn(8192, 32000, device="cuda").bfloat16()
-    res["C3b_argmax+max_bf16_8192x32000"] = t(lambda: pb.argmax_with_value(x, axis=-1), 524369920)
+    val = torch.empty(8192, device="cuda", dtype=torch.bfloat16)
+    a = arg_desc(x, idx, val)
+    res["C3b_argmax+max_bf16_8192x32000"] = t(lambda: L.check(lib.b200phi_argreduce(C.byref(a), stream())), 524369920)
+    assert torch.equal(val, x.max(1).values)
     del x
+
     x = torch.randn(16384, 8192, device="cuda").bfloat16()
-    res["C4_row_mean_var_bf16_16384x8192"] = t(lambda: pb.row_mean_var(x), 268500992)
+    m = torch.empty(16384, device="cuda", dtype=torch.bfloat16)
+    v = torch.empty(16384, device="cuda", dtype=torch.bfloat16)
+    r = L.RowStatsDesc()
+    r.in_dtype, r.out_dtype, r.rows, r.cols, r.unbiased = L.BFLOAT16, L.BFLOAT16, 16384, 8192, 1
+    r.x, r.mean, r.var = x.data_ptr(), m.data_ptr(), v.data_ptr()
+    res["C4_row_mean_var_bf16_16384x8192"] = t(lambda: L.check(lib.b200phi_rowstats(C.byref(r), stream())), 268500992)
+    assert torch.allclose(v.float(), x.float().var(1), rtol=2e-2)
     del x
     torch.cuda.empty_cache()
     return res

@@ -164,12 +164,19 @@ struct RowsParams {
   long long chunks;    // chunks per row
 };
 
-template <typename T, typename F, int Arity>
+// kMask >= 0: bit i set <=> input i is streamed along the row (stride 1), clear <=> it is
+// one value per row (stride 0); known at compile time so only streamed inputs get load
+// buffers (with a run-time flag every input got one and the kernel needed 113 registers,
+// i.e. 2 CTAs per SM).  kMask == -1: decided at run time (the RuntimeF / ternary path).
+template <typename T, typename F, int Arity, int kMask, int U>
 __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p, F f) {
   using C = typename ComputeT<T>::type;
   constexpr int VE = VecOf<T>::kElems;
-  constexpr int U = 4;
   const long long row = blockIdx.x / p.chunks, chunk = blockIdx.x % p.chunks;
+  auto streamed = [&](int i) -> bool {
+    if constexpr (kMask >= 0) return (kMask >> i) & 1;
+    return p.istride[i] != 0;
+  };
 
   // per-row base offsets (uniform over the CTA)
   const T* src[Arity];
@@ -180,7 +187,15 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
     long long idx = row;
     for (int k = p.nouter - 1; k >= 0; --k) {
       const long long e = p.oext[k];
-      const long long q = idx / e, rem = idx - q * e;
+      long long q, rem;
+      if ((static_cast<unsigned long long>(idx) | static_cast<unsigned long long>(e)) >> 32) {
+        q = idx / e;
+        rem = idx - q * e;
+      } else {
+        const unsigned qi = static_cast<unsigned>(idx) / static_cast<unsigned>(e);
+        q = qi;
+        rem = static_cast<unsigned>(idx) - qi * static_cast<unsigned>(e);
+      }
 #pragma unroll
       for (int i = 0; i < Arity; ++i) off[i] += rem * p.ostride[i][k];
       idx = q;
@@ -198,7 +213,7 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
 #pragma unroll
   for (int i = 0; i < Arity; ++i) {
     splat[i] = C(0);
-    if (p.istride[i] == 0) {
+    if (!streamed(i)) {
       splat[i] = Cvt<C, T>::to(ldg_scalar(src[i]));
     } else {
       aligned = aligned && (reinterpret_cast<uintptr_t>(src[i]) % 16 == 0);
@@ -220,7 +235,7 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
         if (v < v1) {
 #pragma unroll
           for (int i = 0; i < Arity; ++i)
-            if (p.istride[i]) raw[i][u] = ldg_stream16(reinterpret_cast<const V16*>(src[i]) + v);
+            if (streamed(i)) raw[i][u] = ldg_stream16(reinterpret_cast<const V16*>(src[i]) + v);
         }
       }
 #pragma unroll
@@ -230,12 +245,12 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
           typename VecOf<T>::U w[Arity], o, o2;
 #pragma unroll
           for (int i = 0; i < Arity; ++i)
-            if (p.istride[i]) w[i].raw = raw[i][u];
+            if (streamed(i)) w[i].raw = raw[i][u];
 #pragma unroll
           for (int e = 0; e < VE; ++e) {
             C a[3] = {C(0), C(0), C(0)};
 #pragma unroll
-            for (int i = 0; i < Arity; ++i) a[i] = p.istride[i] ? Cvt<C, T>::to(w[i].e[e]) : splat[i];
+            for (int i = 0; i < Arity; ++i) a[i] = streamed(i) ? Cvt<C, T>::to(w[i].e[e]) : splat[i];
             const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
             o.e[e] = from_compute<T, C>(f.template post<C>(t));
             if constexpr (F::kInter) o2.e[e] = from_compute<T, C>(t);
@@ -252,7 +267,7 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
         C a[3] = {C(0), C(0), C(0)};
 #pragma unroll
         for (int k = 0; k < Arity; ++k)
-          a[k] = p.istride[k] ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
+          a[k] = streamed(k) ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
         const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
         dst[i] = from_compute<T, C>(f.template post<C>(t));
         if (dst2) dst2[i] = from_compute<T, C>(t);
@@ -266,7 +281,7 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
       C a[3] = {C(0), C(0), C(0)};
 #pragma unroll
       for (int k = 0; k < Arity; ++k)
-        a[k] = p.istride[k] ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
+        a[k] = streamed(k) ? Cvt<C, T>::to(ldg_scalar(src[k] + i)) : splat[k];
       const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
       dst[i] = from_compute<T, C>(f.template post<C>(t));
       if (dst2) dst2[i] = from_compute<T, C>(t);
@@ -324,6 +339,7 @@ template <typename T, typename F, int Arity>
 static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, F f, void* inter,
                         cudaStream_t stream) {
   constexpr int VE = VecOf<T>::kElems;
+  constexpr bool kStaticMask = !F::kInter && Arity == 2;
   if (bp.use_rows_kernel) {
     RowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
@@ -336,6 +352,8 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
     }
     p.inner = bp.inner;
     for (int i = 0; i < Arity; ++i) p.istride[i] = bp.stride[i][bp.ndim - 1] ? 1 : 0;
+    int mask = 0;
+    for (int i = 0; i < Arity; ++i) mask |= p.istride[i] << i;
     const long long nvec = (bp.inner + VE - 1) / VE;
     const long long max_chunk = static_cast<long long>(kBlock) * 8;  // 8 vectors per thread
     p.chunks = (nvec + max_chunk - 1) / max_chunk;
@@ -343,7 +361,20 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
     p.chunk_v = (nvec + p.chunks - 1) / p.chunks;
     const long long blocks = bp.rows * p.chunks;
     if (blocks > 0x7fffffffLL) return set_error(B200PHI_UNSUPPORTED, "elementwise: too many rows");
-    bcast_rows_kernel<T, F, Arity><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(p, f);
+    const unsigned g = static_cast<unsigned>(blocks);
+    if constexpr (kStaticMask) {
+      // two-input hot functors: the stream/splat pattern is a template argument
+      if (mask == 1)
+        bcast_rows_kernel<T, F, Arity, 1, 8><<<g, kBlock, 0, stream>>>(p, f);
+      else if (mask == 2)
+        bcast_rows_kernel<T, F, Arity, 2, 8><<<g, kBlock, 0, stream>>>(p, f);
+      else if (mask == 3)
+        bcast_rows_kernel<T, F, Arity, 3, 4><<<g, kBlock, 0, stream>>>(p, f);
+      else
+        bcast_rows_kernel<T, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
+    } else {
+      bcast_rows_kernel<T, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
+    }
   } else {
     GenericParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;

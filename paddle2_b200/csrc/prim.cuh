@@ -220,51 +220,151 @@ __device__ __forceinline__ Acc block_combine(Acc v, Acc* smem) {
   return r;
 }
 
+// Barrier over the G threads of one group.  G == kBlock is the plain CTA barrier (immediate
+// id 0); smaller groups use named barrier 1 + group (a register id costs a few us per 100 us
+// of short-lived CTAs, so the whole-CTA case must not go through it).
+template <int G>
+__device__ __forceinline__ void group_barrier() {
+  if constexpr (G == kBlock) {
+    __syncthreads();
+  } else {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + static_cast<int>(threadIdx.x) / G), "r"(G) : "memory");
+  }
+}
+
+// Combine across a group of G threads (G = 32, 64, 128 or 256; groups are G-aligned slices of
+// the CTA).  Warps of one group meet on a named barrier (id 1 + group), so groups never wait
+// for each other.  `smem` holds kWarps Acc.  Result valid in every thread of the group.
+template <typename Acc, typename Op, int G>
+__device__ __forceinline__ Acc group_combine(Acc v, Acc* smem) {
+  v = warp_combine<Acc, Op>(v);
+  if constexpr (G > 32) {
+    constexpr int kW = G / 32;
+    const int warp = threadIdx.x >> 5, grp = threadIdx.x / G;
+    if ((threadIdx.x & 31) == 0) smem[warp] = v;
+    group_barrier<G>();
+    Acc r = smem[grp * kW];
+#pragma unroll
+    for (int w = 1; w < kW; ++w) r = Op::combine(r, smem[grp * kW + w]);
+    group_barrier<G>();  // smem reusable
+    v = r;
+  }
+  return v;
+}
+
+// Same, but only the group's thread 0 needs the result, and `smem` holds 2*kWarps Acc used
+// alternately (`parity` flips per call) so ONE named barrier per call is enough.
+template <typename Acc, typename Op, int G>
+__device__ __forceinline__ Acc group_combine_leader(Acc v, Acc* smem, int parity) {
+  v = warp_combine<Acc, Op>(v);
+  if constexpr (G > 32) {
+    constexpr int kW = G / 32;
+    const int warp = threadIdx.x >> 5, grp = threadIdx.x / G;
+    Acc* buf = smem + parity * kWarps;
+    if ((threadIdx.x & 31) == 0) buf[warp] = v;
+    group_barrier<G>();
+    if (threadIdx.x % G == 0) {
+      Acc r = buf[grp * kW];
+#pragma unroll
+      for (int w = 1; w < kW; ++w) r = Op::combine(r, buf[grp * kW + w]);
+      v = r;
+    }
+  }
+  return v;
+}
+
 // ---- typed result store -----------------------------------------------------------
 struct Epilogue {
   void* out;
   int out_dtype;    // b200phi_dtype
   int is_mean;      // divide by count before the store (reduce_function.h:686-688)
-  long long count;  // reduce_num
+  long long count;  // reduce_num, also pre-converted on the host: an I2F.S64 + RCP chain in
+  float count_f;    // every CTA's epilogue cost ~10% on config C1
+  double count_d;
 };
 
+inline Epilogue make_epilogue(void* out, int out_dtype, bool is_mean, long long count) {
+  Epilogue ep;
+  ep.out = out;
+  ep.out_dtype = out_dtype;
+  ep.is_mean = is_mean ? 1 : 0;
+  ep.count = count;
+  ep.count_f = static_cast<float>(count);
+  ep.count_d = static_cast<double>(count);
+  return ep;
+}
+
 template <typename Acc>
-__device__ __forceinline__ void store_result(const Epilogue& ep, long long idx, Acc v) {
-  if (ep.is_mean) v = v / static_cast<Acc>(ep.count);
-  switch (ep.out_dtype) {
+struct EpiTraits;
+template <>
+struct EpiTraits<float> {
+  static constexpr int kNative = 10;
+  static __device__ __forceinline__ float count(const Epilogue& ep) { return ep.count_f; }
+};
+template <>
+struct EpiTraits<double> {
+  static constexpr int kNative = 11;
+  static __device__ __forceinline__ double count(const Epilogue& ep) { return ep.count_d; }
+};
+template <>
+struct EpiTraits<long long> {
+  static constexpr int kNative = 9;
+  static __device__ __forceinline__ long long count(const Epilogue& ep) { return ep.count; }
+};
+template <>
+struct EpiTraits<int> {
+  static constexpr int kNative = 7;
+  static __device__ __forceinline__ int count(const Epilogue& ep) { return static_cast<int>(ep.count); }
+};
+
+// Every other output dtype: out of line, so the hot path stays a compare and a store
+// (inlined, the compiler folded it into one jump table that every CTA's leader walked).
+template <typename Acc>
+__device__ __noinline__ void store_result_slow(void* out, int out_dtype, long long idx, Acc v) {
+  switch (out_dtype) {
     case 1:  // BOOL
-      reinterpret_cast<uint8_t*>(ep.out)[idx] = (v != Acc(0)) ? 1 : 0;
+      reinterpret_cast<uint8_t*>(out)[idx] = (v != Acc(0)) ? 1 : 0;
       break;
     case 2:
-      reinterpret_cast<uint8_t*>(ep.out)[idx] = static_cast<uint8_t>(v);
+      reinterpret_cast<uint8_t*>(out)[idx] = static_cast<uint8_t>(v);
       break;
     case 3:
-      reinterpret_cast<int8_t*>(ep.out)[idx] = static_cast<int8_t>(v);
+      reinterpret_cast<int8_t*>(out)[idx] = static_cast<int8_t>(v);
       break;
     case 5:
-      reinterpret_cast<int16_t*>(ep.out)[idx] = static_cast<int16_t>(v);
+      reinterpret_cast<int16_t*>(out)[idx] = static_cast<int16_t>(v);
       break;
     case 7:
-      reinterpret_cast<int32_t*>(ep.out)[idx] = static_cast<int32_t>(v);
+      reinterpret_cast<int32_t*>(out)[idx] = static_cast<int32_t>(v);
       break;
     case 9:
-      reinterpret_cast<long long*>(ep.out)[idx] = static_cast<long long>(v);
+      reinterpret_cast<long long*>(out)[idx] = static_cast<long long>(v);
       break;
     case 10:
-      reinterpret_cast<float*>(ep.out)[idx] = static_cast<float>(v);
+      reinterpret_cast<float*>(out)[idx] = static_cast<float>(v);
       break;
     case 11:
-      reinterpret_cast<double*>(ep.out)[idx] = static_cast<double>(v);
+      reinterpret_cast<double*>(out)[idx] = static_cast<double>(v);
       break;
     case 15:
-      reinterpret_cast<__half*>(ep.out)[idx] = __float2half_rn(static_cast<float>(v));
+      reinterpret_cast<__half*>(out)[idx] = __float2half_rn(static_cast<float>(v));
       break;
     case 16:
-      reinterpret_cast<__nv_bfloat16*>(ep.out)[idx] = __float2bfloat16_rn(static_cast<float>(v));
+      reinterpret_cast<__nv_bfloat16*>(out)[idx] = __float2bfloat16_rn(static_cast<float>(v));
       break;
     default:
       break;
   }
+}
+
+template <typename Acc>
+__device__ __forceinline__ void store_result(const Epilogue& ep, long long idx, Acc v) {
+  if (ep.is_mean) v = v / EpiTraits<Acc>::count(ep);
+  if (ep.out_dtype == EpiTraits<Acc>::kNative) {
+    reinterpret_cast<Acc*>(ep.out)[idx] = v;
+    return;
+  }
+  store_result_slow<Acc>(ep.out, ep.out_dtype, idx, v);
 }
 
 }  // namespace b200phi

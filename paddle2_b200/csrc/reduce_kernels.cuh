@@ -65,27 +65,44 @@ __device__ __forceinline__ Acc reduce_span(const T* __restrict__ row, long long 
   return fold_lanes<Acc, Op>(acc);
 }
 
-// kWarpsPerRow == 1: one warp per row, no block barrier at all.
-// kWarpsPerRow == kWarps: the CTA works on one row at a time.
-template <typename T, typename Acc, typename Op, int kWarpsPerRow, int U>
+// Every row starts on a 16-byte boundary and holds a whole number of vectors (checked on the
+// host): no head/tail peel, no per-row address inspection.
+template <typename T, typename Acc, typename Op, int G, int U>
+__device__ __forceinline__ Acc reduce_span_aligned(const T* __restrict__ row, long long nvec, int g) {
+  Acc acc[kFoldLanes];
+#pragma unroll
+  for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+  const V16* __restrict__ vp = reinterpret_cast<const V16*>(row);
+  long long v = g;
+  span_step<T, Acc, Op, G, U>(vp, v, nvec, acc);
+  if constexpr (U > 4) span_step<T, Acc, Op, G, 4>(vp, v, nvec, acc);
+  if constexpr (U > 2) span_step<T, Acc, Op, G, 2>(vp, v, nvec, acc);
+  if constexpr (U > 1) span_step<T, Acc, Op, G, 1>(vp, v, nvec, acc);
+  return fold_lanes<Acc, Op>(acc);
+}
+
+// G threads per row (G = 32: a warp per row, no barrier at all; 64/128: sub-CTA groups on
+// named barriers; 256: the CTA works on one row).  Measured on C1 (16 KiB rows): G = 256 with
+// one row per CTA reads 7.09 TB/s, G = 32 reads 6.74 TB/s (profiles/r01_microbench.md).
+template <typename T, typename Acc, typename Op, int G, int U, bool kAligned>
 __global__ void __launch_bounds__(kBlock)
     row_reduce_kernel(const T* __restrict__ x, long long rows, long long cols, Epilogue ep) {
-  __shared__ Acc smem[kWarps];
-  constexpr int kRowsPerCta = kWarps / kWarpsPerRow;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if constexpr (kWarpsPerRow == 1) {
-    for (long long row = static_cast<long long>(blockIdx.x) * kRowsPerCta + warp; row < rows;
-         row += static_cast<long long>(gridDim.x) * kRowsPerCta) {
-      Acc v = reduce_span<T, Acc, Op, 32, U>(x + row * cols, cols, lane);
-      v = warp_combine<Acc, Op>(v);
-      if (lane == 0) store_result(ep, row, v);
+  __shared__ Acc smem[2 * kWarps];
+  constexpr int kRowsPerCta = kBlock / G;
+  constexpr int VE = VecOf<T>::kElems;
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
+  int parity = 0;
+  for (long long row = static_cast<long long>(blockIdx.x) * kRowsPerCta + grp; row < rows;
+       row += static_cast<long long>(gridDim.x) * kRowsPerCta) {
+    Acc v;
+    if constexpr (kAligned) {
+      v = reduce_span_aligned<T, Acc, Op, G, U>(x + row * cols, cols / VE, g);
+    } else {
+      v = reduce_span<T, Acc, Op, G, U>(x + row * cols, cols, g);
     }
-  } else {
-    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-      Acc v = reduce_span<T, Acc, Op, kBlock, U>(x + row * cols, cols, threadIdx.x);
-      v = block_combine<Acc, Op>(v, smem);
-      if (threadIdx.x == 0) store_result(ep, row, v);
-    }
+    v = group_combine_leader<Acc, Op, G>(v, smem, parity);
+    parity ^= 1;
+    if (g == 0) store_result(ep, row, v);
   }
 }
 
@@ -126,15 +143,19 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
-// One batch of UU row loads (stride `step` rows) for the column this thread owns.
+// Batches of UU row loads for the column this thread owns.  The address advances by
+// pointer increments with a precomputed byte stride: a fresh 64-bit multiply per load makes
+// ptxas interleave address math with the loads and only ~2 stay in flight (measured:
+// 6.3 TB/s vs 7.3 TB/s on config C5, profiles/r01_col_reduce.md).
 template <typename T, typename Acc, typename Op, int VE, int UU>
-__device__ __forceinline__ void col_step(const T* __restrict__ base, long long inner, long long& r,
-                                         long long r1, long long step, Acc (&acc)[VE]) {
-  for (; r + (UU - 1) * step < r1; r += UU * step) {
+__device__ __forceinline__ void col_step(const unsigned char* __restrict__& p, size_t stride_bytes,
+                                         long long& left, Acc (&acc)[VE]) {
+  for (; left >= UU; left -= UU) {
     if constexpr (VE > 1) {
       V16 buf[UU];
 #pragma unroll
-      for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(base + (r + u * step) * inner);
+      for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(p + u * stride_bytes);
+      p += UU * stride_bytes;
 #pragma unroll
       for (int u = 0; u < UU; ++u) {
         typename VecOf<T>::U w;
@@ -145,7 +166,8 @@ __device__ __forceinline__ void col_step(const T* __restrict__ base, long long i
     } else {
       T buf[UU];
 #pragma unroll
-      for (int u = 0; u < UU; ++u) buf[u] = ldg_scalar(base + (r + u * step) * inner);
+      for (int u = 0; u < UU; ++u) buf[u] = ldg_scalar(reinterpret_cast<const T*>(p + u * stride_bytes));
+      p += UU * stride_bytes;
 #pragma unroll
       for (int u = 0; u < UU; ++u) acc[0] = Op::combine(acc[0], load_as<Acc, Op>(buf[u]));
     }
@@ -179,14 +201,15 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
   for (int e = 0; e < VE; ++e) acc[e] = Op::identity();
 
-  if (live) {
-    const T* __restrict__ base = x + o * R * inner + cv * VE;
-    long long r = r0 + ty;
-    const long long step = TY;
-    col_step<T, Acc, Op, VE, U>(base, inner, r, r1, step, acc);
-    if constexpr (U > 4) col_step<T, Acc, Op, VE, 4>(base, inner, r, r1, step, acc);
-    if constexpr (U > 2) col_step<T, Acc, Op, VE, 2>(base, inner, r, r1, step, acc);
-    if constexpr (U > 1) col_step<T, Acc, Op, VE, 1>(base, inner, r, r1, step, acc);
+  if (live && r0 + ty < r1) {
+    const unsigned char* __restrict__ p =
+        reinterpret_cast<const unsigned char*>(x + (o * R + r0 + ty) * inner + cv * VE);
+    const size_t stride_bytes = static_cast<size_t>(TY) * inner * sizeof(T);
+    long long left = (r1 - r0 - ty + TY - 1) / TY;  // rows this thread visits
+    col_step<T, Acc, Op, VE, U>(p, stride_bytes, left, acc);
+    if constexpr (U > 4) col_step<T, Acc, Op, VE, 4>(p, stride_bytes, left, acc);
+    if constexpr (U > 2) col_step<T, Acc, Op, VE, 2>(p, stride_bytes, left, acc);
+    if constexpr (U > 1) col_step<T, Acc, Op, VE, 1>(p, stride_bytes, left, acc);
   }
 
   // combine across ty through shared memory (tree over TY, TY is a power of two)
@@ -225,14 +248,29 @@ __global__ void __launch_bounds__(kBlock)
   if (s_ticket != splits - 1) return;
   __threadfence();
 
-  // last CTA for this (outer, tile): combine the `splits` partials in index order
+  // last CTA for this (outer, tile): combine the `splits` partials in index order.
+  // Loads are issued in batches of 8 before the first use: the partials sit in L2 and a
+  // dependent chain of `splits` loads would put their latencies end to end.
 #pragma unroll
   for (int e = 0; e < VE; ++e) acc[e] = Op::identity();
   if (live) {
-    for (unsigned s = ty; s < splits; s += TY) {
+    unsigned s = ty;
+    for (; s + 7u * TY < splits; s += 8u * TY) {
+      Acc b[8][VE];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int e = 0; e < VE; ++e)
+          b[u][e] = __ldcg(&partial[static_cast<long long>(s + u * TY) * out_numel + out_base + e]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int e = 0; e < VE; ++e) acc[e] = Op::combine(acc[e], b[u][e]);
+    }
+    for (; s < splits; s += TY) {
 #pragma unroll
       for (int e = 0; e < VE; ++e)
-        acc[e] = Op::combine(acc[e], __ldcg(&partial[s * out_numel + out_base + e]));
+        acc[e] = Op::combine(acc[e], __ldcg(&partial[static_cast<long long>(s) * out_numel + out_base + e]));
     }
   }
 #pragma unroll

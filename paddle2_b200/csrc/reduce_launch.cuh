@@ -20,11 +20,7 @@ template <typename T, typename Acc, typename Op>
 int launch_reduce_typed(const ReduceArgs& a) {
   const ReducePlan& p = *a.plan;
   const T* x = static_cast<const T*>(a.x);
-  Epilogue ep;
-  ep.out = a.out;
-  ep.out_dtype = p.out_dtype;
-  ep.is_mean = (p.op == B200PHI_MEAN) ? 1 : 0;
-  ep.count = p.red_numel;
+  const Epilogue ep = make_epilogue(a.out, p.out_dtype, p.op == B200PHI_MEAN, p.red_numel);
   Acc* partial = static_cast<Acc*>(a.ws);
   unsigned* tickets =
       reinterpret_cast<unsigned*>(static_cast<unsigned char*>(a.ws) + p.ws_partial_bytes);
@@ -35,11 +31,23 @@ int launch_reduce_typed(const ReduceArgs& a) {
   }
   switch (p.kind) {
     case kRowWarp:
-      row_reduce_kernel<T, Acc, Op, 1, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, p.cols, ep);
-      break;
     case kRowBlock:
-      row_reduce_kernel<T, Acc, Op, kWarps, 8>
-          <<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, p.cols, ep);
+#define B200PHI_ROW(GG)                                                                        \
+  if (p.aligned)                                                                               \
+    row_reduce_kernel<T, Acc, Op, GG, 8, true><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, p.cols, ep); \
+  else                                                                                         \
+    row_reduce_kernel<T, Acc, Op, GG, 8, false><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, p.cols, ep);
+      switch (p.G) {
+        case 32:
+          B200PHI_ROW(32) break;
+        case 64:
+          B200PHI_ROW(64) break;
+        case 128:
+          B200PHI_ROW(128) break;
+        default:
+          B200PHI_ROW(256) break;
+      }
+#undef B200PHI_ROW
       break;
     case kRowSplit:
       row_split_kernel<T, Acc, Op, 8><<<dim3(p.grid_x, p.grid_y), kBlock, 0, a.stream>>>(

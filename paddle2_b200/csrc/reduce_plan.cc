@@ -45,8 +45,8 @@ static long long env_ll(const char* name, long long dflt) {
 Tunables default_tunables(int sm_count) {
   Tunables t;
   t.sm_count = sm_count > 0 ? sm_count : 148;
-  t.row_warp_max_bytes = env_ll("B200PHI_ROW_WARP_MAX_BYTES", 16384);
-  t.ctas_per_sm = static_cast<int>(env_ll("B200PHI_CTAS_PER_SM", 8));
+  t.row_bytes_per_thread = env_ll("B200PHI_ROW_BYTES_PER_THREAD", 64);
+  t.ctas_per_sm = static_cast<int>(env_ll("B200PHI_CTAS_PER_SM", 4));  // measured: profiles/r01_microbench.md
   t.force_kind = static_cast<int>(env_ll("B200PHI_FORCE_KIND", -1));
   return t;
 }
@@ -202,9 +202,14 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
 
   if (kind == kRowBlock) {
     const long long row_bytes = p->cols * static_cast<long long>(esize);
-    if (p->rows >= static_cast<long long>(t.sm_count) * 16 && row_bytes <= t.row_warp_max_bytes) {
-      kind = kRowWarp;
-    } else if (p->rows < static_cast<long long>(t.sm_count) * 2) {
+    // threads per row: each thread should own about 4 16-byte vectors of the row
+    int G = pow2_ceil(ceil_div(row_bytes, std::max<long long>(16, t.row_bytes_per_thread)));
+    G = std::min(256, std::max(32, G));
+    if (t.force_kind == kRowWarp) G = 32;
+    if (t.force_kind == kRowBlock) G = 256;
+    p->G = G;
+    p->aligned = (reinterpret_cast<uintptr_t>(d->x) % 16 == 0 && row_bytes % 16 == 0) ? 1 : 0;
+    if (p->rows < static_cast<long long>(t.sm_count) * 2) {
       long long splits = std::min(ceil_div(want_ctas, p->rows), row_bytes / 32768);
       splits = std::min<long long>(splits, 65535);
       if (splits > 1) {
@@ -217,25 +222,20 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         }
       }
     }
-    if (t.force_kind == kRowWarp || t.force_kind == kRowBlock) {
-      if (kind != kRowSplit) kind = t.force_kind;
-    }
+    if (kind != kRowSplit) kind = (G == 256) ? kRowBlock : kRowWarp;
   }
   p->kind = kind;
 
   // ---- geometry -----------------------------------------------------------------
   p->splits = (kind == kRowSplit) ? p->splits : 1;
   switch (kind) {
-    case kRowWarp: {
-      long long ctas = ceil_div(p->rows, 8);
-      p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, want_ctas * 64));
+    case kRowWarp:
+    case kRowBlock: {
+      const long long ctas = ceil_div(p->rows, 256 / p->G);
+      p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, 0x7fffffffLL));
       p->grid_y = 1;
       break;
     }
-    case kRowBlock:
-      p->grid_x = static_cast<unsigned>(std::min<long long>(p->rows, 0x7fffffffLL));
-      p->grid_y = 1;
-      break;
     case kRowSplit:
       p->grid_x = static_cast<unsigned>(p->splits);
       p->grid_y = static_cast<unsigned>(p->rows);

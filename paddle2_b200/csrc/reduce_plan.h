@@ -21,8 +21,8 @@
 namespace b200phi {
 
 enum ReduceKind {
-  kRowWarp = 0,   // [rows, cols], one warp per row
-  kRowBlock = 1,  // [rows, cols], one CTA per row
+  kRowWarp = 0,   // [rows, cols], G < 256 threads per row (several rows per CTA)
+  kRowBlock = 1,  // [rows, cols], one CTA (G = 256) per row
   kRowSplit = 2,  // [rows, cols], several CTAs per row + last-block finalise
   kCol = 3,       // [outer, R, inner]
   kGeneric = 4    // anything else (also the reduce_num == 1 cast/copy)
@@ -37,6 +37,8 @@ struct ReducePlan {
   long long in_numel, out_numel, red_numel;
   // row kinds
   long long rows, cols, seg;
+  int G;  // threads per row: 32, 64, 128 or 256
+  int aligned;  // every row starts 16-byte aligned and is a whole number of 16-byte vectors
   // col kind
   long long outer, R, inner, tiles, rows_per_split;
   int vec;  // elements per 16-byte vector on the col vector path, else 1
@@ -60,7 +62,7 @@ bool dtype_is_float(int dtype);
 // Tunables (read once from the environment; see DESIGN.md "knobs").
 struct Tunables {
   int sm_count;             // multiprocessors of the current device (148 on B200)
-  long long row_warp_max_bytes;  // rows up to this many bytes go one-warp-per-row
+  long long row_bytes_per_thread;  // a row gets ~row_bytes / this many threads (pow2, 32..256)
   int ctas_per_sm;          // resident CTAs per SM the split heuristics aim for
   int force_kind;           // -1, or a ReduceKind to force where legal (testing)
 };

@@ -1,0 +1,128 @@
+// C++ driver of the C ABI (no Python, no torch): times b200phi_* calls on the five configs
+// with cudaMalloc'd buffers and CUDA events.  Cross-checks bench.py's numbers.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/abi_bench tools/abi_bench.cu -Iinclude -Lpaddle2_b200 -lb200phi -Xlinker -rpath -Xlinker '$ORIGIN/../paddle2_b200'
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "b200phi.h"
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1);} } while (0)
+#define OK(x) do { int rc = (x); if (rc) { printf("b200phi status %d: %s (line %d)\n", rc, b200phi_last_error(), __LINE__); exit(1);} } while (0)
+
+__global__ void fill_random(unsigned* x, long long n, unsigned seed, unsigned mask, unsigned orv) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    unsigned long long z = (unsigned long long)i * 0x9E3779B97F4A7C15ull + seed;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+    x[i] = ((unsigned)(z >> 32) & mask) | orv;
+  }
+}
+
+template <typename F> float time_it(F fn, int iters) {
+  for (int i = 0; i < 5; ++i) fn();
+  CK(cudaDeviceSynchronize());
+  cudaEvent_t a, b;
+  cudaEventCreate(&a); cudaEventCreate(&b);
+  cudaEventRecord(a);
+  for (int i = 0; i < iters; ++i) fn();
+  cudaEventRecord(b);
+  CK(cudaEventSynchronize(b));
+  float ms; cudaEventElapsedTime(&ms, a, b);
+  return ms / iters;
+}
+
+static void* dalloc(size_t bytes, unsigned mask, unsigned orv) {
+  void* p; CK(cudaMalloc(&p, bytes));
+  fill_random<<<148 * 8, 256>>>((unsigned*)p, (long long)(bytes / 4), 123u, mask, orv);
+  CK(cudaDeviceSynchronize());
+  return p;
+}
+
+int main(int argc, char** argv) {
+  const char* only = argc > 1 ? argv[1] : "";
+  printf("%s\n", b200phi_version());
+  const unsigned F01_MASK = 0x007fffff, F01_OR = 0x3f000000;  // floats in [0.5, 1)
+  if (!*only || strstr(only, "C1")) {
+    float* x = (float*)dalloc((size_t)32 * 1024 * 4096 * 4, F01_MASK, F01_OR);
+    float* out; CK(cudaMalloc(&out, 32 * 1024 * 4));
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_SUM; d.in_dtype = d.out_dtype = B200PHI_FLOAT32; d.rank = 3;
+    d.dims[0] = 32; d.dims[1] = 1024; d.dims[2] = 4096; d.naxes = 1; d.axes[0] = 2; d.x = x; d.out = out;
+    float ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+    printf("C1 sum fp32 [32,1024,4096] axis -1      %8.2f us  %7.1f GB/s\n", ms * 1e3, 537001984.0 / ms / 1e6);
+    cudaFree(x); cudaFree(out);
+  }
+  if (!*only || strstr(only, "C2")) {
+    const size_t n = (size_t)256 * 64 * 112 * 112;
+    float* x = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
+    float* y = (float*)dalloc(64 * 4, 0x807fffff, 0x3f000000);
+    float* out; CK(cudaMalloc(&out, n * 4));
+    b200phi_elementwise_desc e = {};
+    e.binary = B200PHI_ADD; e.act = B200PHI_ACT_RELU; e.dtype = B200PHI_FLOAT32; e.arity = 2; e.axis = -1;
+    e.in[0].rank = 4; e.in[0].dims[0] = 256; e.in[0].dims[1] = 64; e.in[0].dims[2] = 112; e.in[0].dims[3] = 112; e.in[0].data = x;
+    e.in[1].rank = 3; e.in[1].dims[0] = 64; e.in[1].dims[1] = 1; e.in[1].dims[2] = 1; e.in[1].data = y;
+    e.out_rank = 4; memcpy(e.out_dims, e.in[0].dims, sizeof(e.out_dims)); e.out = out;
+    float ms = time_it([&] { OK(b200phi_elementwise(&e, 0)); }, 20);
+    printf("C2 relu(x+y) fp32 [256,64,112,112]+[64,1,1] %8.2f us  %7.1f GB/s\n", ms * 1e3, 1644167424.0 / ms / 1e6);
+    cudaFree(x); cudaFree(y); cudaFree(out);
+  }
+  if (!*only || strstr(only, "C3")) {
+    const size_t n = (size_t)8192 * 32000;
+    void* x = dalloc(n * 8, 0xffffffff, 0);
+    long long *idx, *val; CK(cudaMalloc(&idx, 8192 * 8)); CK(cudaMalloc(&val, 8192 * 8));
+    b200phi_argreduce_desc a = {};
+    a.op = B200PHI_ARGMAX; a.in_dtype = B200PHI_INT64; a.index_dtype = B200PHI_INT64; a.rank = 2;
+    a.dims[0] = 8192; a.dims[1] = 32000; a.axis = 1; a.x = x; a.out = idx; a.max_out = val;
+    float ms = time_it([&] { OK(b200phi_argreduce(&a, 0)); }, 20);
+    printf("C3a argmax+max int64 [8192,32000]        %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097283072.0 / ms / 1e6);
+    a.in_dtype = B200PHI_BFLOAT16;   // reuse the buffer as bf16 bits; mask NaN/Inf exponents is not needed for timing
+    ms = time_it([&] { OK(b200phi_argreduce(&a, 0)); }, 20);
+    printf("C3b argmax+max bf16 [8192,32000]         %8.2f us  %7.1f GB/s\n", ms * 1e3, 524369920.0 / ms / 1e6);
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_MAX; d.in_dtype = d.out_dtype = B200PHI_INT64; d.rank = 2; d.dims[0] = 8192; d.dims[1] = 32000;
+    d.naxes = 1; d.axes[0] = 1; d.x = x; d.out = val;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+    printf("C3a max alone int64 [8192,32000]         %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097217536.0 / ms / 1e6);
+    cudaFree(x); cudaFree(idx); cudaFree(val);
+  }
+  if (!*only || strstr(only, "C4")) {
+    const size_t n = (size_t)16384 * 8192;
+    void* x = dalloc(n * 2, 0x3f7f3f7f, 0x3c003c00);  // bf16 pairs of moderate magnitude
+    void *m, *v; CK(cudaMalloc(&m, 16384 * 2)); CK(cudaMalloc(&v, 16384 * 2));
+    b200phi_rowstats_desc r = {};
+    r.in_dtype = r.out_dtype = B200PHI_BFLOAT16; r.rows = 16384; r.cols = 8192; r.unbiased = 1; r.x = x; r.mean = m; r.var = v;
+    float ms = time_it([&] { OK(b200phi_rowstats(&r, 0)); }, 20);
+    printf("C4 row mean+var bf16 [16384,8192]        %8.2f us  %7.1f GB/s\n", ms * 1e3, 268500992.0 / ms / 1e6);
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_MEAN; d.in_dtype = d.out_dtype = B200PHI_BFLOAT16; d.rank = 2; d.dims[0] = 16384; d.dims[1] = 8192;
+    d.naxes = 1; d.axes[0] = 1; d.x = x; d.out = m;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+    printf("C4 mean alone bf16 [16384,8192]          %8.2f us  %7.1f GB/s\n", ms * 1e3, 268468224.0 / ms / 1e6);
+    cudaFree(x); cudaFree(m); cudaFree(v);
+  }
+  if (!*only || strstr(only, "C5")) {
+    const long long R = 524288, C = 4096;
+    float* x = (float*)dalloc((size_t)R * C * 4, F01_MASK, F01_OR);
+    float* out; CK(cudaMalloc(&out, C * 4));
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_SUM; d.in_dtype = d.out_dtype = B200PHI_FLOAT32; d.rank = 2; d.dims[0] = R; d.dims[1] = C;
+    d.naxes = 1; d.axes[0] = 0; d.x = x; d.out = out;
+    size_t ws = b200phi_reduce_workspace(&d);
+    void* w; CK(cudaMalloc(&w, ws ? ws : 256));
+    d.workspace = w; d.workspace_bytes = ws;
+    float ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 10);
+    printf("C5 sum fp32 [524288,4096] axis 0 (ws %zu B)  %8.2f us  %7.1f GB/s\n", ws, ms * 1e3, 8589950976.0 / ms / 1e6);
+    d.naxes = 0; d.reduce_all = 1;
+    ws = b200phi_reduce_workspace(&d); d.workspace_bytes = ws;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 10);
+    printf("   full reduce of the same 2^31 floats        %8.2f us  %7.1f GB/s\n", ms * 1e3, 8589934596.0 / ms / 1e6);
+    d.naxes = 1; d.axes[0] = 1; d.reduce_all = 0; d.workspace_bytes = 0; d.workspace = nullptr;
+    float* out2; CK(cudaMalloc(&out2, R * 4)); d.out = out2;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 10);
+    printf("   row sums of the same tensor (axis 1)       %8.2f us  %7.1f GB/s\n", ms * 1e3, (8589934592.0 + R * 4) / ms / 1e6);
+    cudaFree(x); cudaFree(out); cudaFree(w); cudaFree(out2);
+  }
+  printf("done\n");
+  return 0;
+}
