@@ -117,6 +117,19 @@ B200PHI_API size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d);
  * is fused into the load. */
 B200PHI_API int b200phi_reduce(const b200phi_reduce_desc* d, void* stream);
 
+/* No counterpart in the reference.  The same column (leading-axis) reduce as
+ * b200phi_reduce, for hosts that cannot hand over a workspace because they may not, or
+ * cannot, allocate device memory where the call is made: a C/Go service linking this
+ * library with no device allocator of its own, a server whose memory plan is frozen before
+ * the first request, a callback that must not take the allocator lock.  The scratch is a
+ * fixed B200PHI_NOALLOC_SCRATCH_BYTES array inside the library (every device that loads the
+ * library holds it until exit); d->workspace is ignored.  A reduce that needs more scratch is
+ * refused with B200PHI_WORKSPACE_TOO_SMALL.  The first call on a device resolves the
+ * array's address and should be made before any stream capture on that device.  All calls
+ * on a device share the array: calls that overlap on the GPU race, keep them on one stream. */
+#define B200PHI_NOALLOC_SCRATCH_BYTES (4u << 20)
+B200PHI_API int b200phi_reduce_noalloc(const b200phi_reduce_desc* d, void* stream);
+
 /* ------------------------------------------------------------------------ */
 /* argmax / argmin                                                          */
 /* ------------------------------------------------------------------------ */

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libb200phi.so")
 
 MAX_RANK = 9
 MAX_ARITY = 3
+NOALLOC_SCRATCH_BYTES = 4 << 20  # B200PHI_NOALLOC_SCRATCH_BYTES
 
 # phi::DataType values (paddle/phi/common/data_type.h:42-85)
 UNDEFINED, BOOL, UINT8, INT8, INT16, INT32, INT64 = 0, 1, 2, 3, 5, 7, 9
@@ -116,6 +117,7 @@ class B200PhiError(RuntimeError):
 EXPORTS = [
     "b200phi_reduce_workspace",
     "b200phi_reduce",
+    "b200phi_reduce_noalloc",
     "b200phi_argreduce",
     "b200phi_rowstats",
     "b200phi_elementwise",
@@ -146,6 +148,8 @@ def lib():
     L.b200phi_reduce_workspace.restype = C.c_size_t
     L.b200phi_reduce_workspace.argtypes = [C.POINTER(ReduceDesc)]
     L.b200phi_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
+    L.b200phi_reduce_noalloc.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
+    L.b200phi_reduce_noalloc.restype = C.c_int
     L.b200phi_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_void_p]
     L.b200phi_rowstats.argtypes = [C.POINTER(RowStatsDesc), C.c_void_p]
     L.b200phi_elementwise.argtypes = [C.POINTER(ElementwiseDesc), C.c_void_p]
