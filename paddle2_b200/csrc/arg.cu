@@ -90,83 +90,149 @@ __device__ __forceinline__ void store_arg(void* out, int index_dtype, void* val_
   if (val_out) StoreVal<T>::put(val_out, slot, p.v);
 }
 
-// Scan `n` contiguous elements with a group of G threads.
-template <typename T, typename V, typename Op, int G, int U>
+// Extreme value of one 16-byte vector: a short tree instead of VE dependent compare/select
+// steps (the per-element chain made config C3b latency-bound at 5.1 TB/s).  16-bit floats use
+// the packed min/max instructions on the raw pairs.
+template <typename T, typename V, bool kMax>
+struct VecExtreme {
+  static __device__ __forceinline__ V of(const V16& raw) {
+    typename VecOf<T>::U w;
+    w.raw = raw;
+    V m[VecOf<T>::kElems];
+#pragma unroll
+    for (int e = 0; e < VecOf<T>::kElems; ++e) m[e] = Cvt<V, T>::to(w.e[e]);
+#pragma unroll
+    for (int half = VecOf<T>::kElems / 2; half > 0; half >>= 1)
+#pragma unroll
+      for (int e = 0; e < half; ++e) m[e] = ArgOp<V, kMax>::better(m[e + half], m[e]) ? m[e + half] : m[e];
+    return m[0];
+  }
+};
+template <bool kMax>
+struct VecExtreme<__nv_bfloat16, float, kMax> {
+  static __device__ __forceinline__ float of(const V16& raw) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+    __nv_bfloat162 a = kMax ? __hmax2(h[0], h[1]) : __hmin2(h[0], h[1]);
+    __nv_bfloat162 b = kMax ? __hmax2(h[2], h[3]) : __hmin2(h[2], h[3]);
+    a = kMax ? __hmax2(a, b) : __hmin2(a, b);
+    const float lo = __low2float(a), hi = __high2float(a);
+    return kMax ? fmaxf(lo, hi) : fminf(lo, hi);
+  }
+};
+template <bool kMax>
+struct VecExtreme<__half, float, kMax> {
+  static __device__ __forceinline__ float of(const V16& raw) {
+    const __half2* h = reinterpret_cast<const __half2*>(&raw);
+    __half2 a = kMax ? __hmax2(h[0], h[1]) : __hmin2(h[0], h[1]);
+    __half2 b = kMax ? __hmax2(h[2], h[3]) : __hmin2(h[2], h[3]);
+    a = kMax ? __hmax2(a, b) : __hmin2(a, b);
+    const float lo = __low2float(a), hi = __high2float(a);
+    return kMax ? fmaxf(lo, hi) : fminf(lo, hi);
+  }
+};
+
+// Visit one vector whose first element has index i0.  Only when the vector's extreme beats
+// the thread's best (rare after the first few vectors) is the position inside it looked up;
+// scanning downwards leaves the LOWEST matching position.
+template <typename T, typename V, bool kMax>
+__device__ __forceinline__ void visit_vec(ArgPair<V>& best, const V16& raw, long long i0) {
+  const V vm = VecExtreme<T, V, kMax>::of(raw);
+  if (ArgOp<V, kMax>::better(vm, best.v)) {
+    typename VecOf<T>::U w;
+    w.raw = raw;
+    int first = 0;
+#pragma unroll
+    for (int e = VecOf<T>::kElems - 1; e >= 0; --e)
+      if (Cvt<V, T>::to(w.e[e]) == vm) first = e;
+    best.v = vm;
+    best.i = i0 + first;
+  }
+}
+
+// Batches of UU strided vectors, all loads issued before the first visit.  The caller
+// cascades UU = 8, 4, 2, 1 so the remainder of a row never degenerates into one load at a time
+// (a 62.5 KiB bf16 row left up to 7 serial loads per thread: 5.8 TB/s on C3b).
+template <typename T, typename V, bool kMax, int G, int UU>
+__device__ __forceinline__ void arg_step(ArgPair<V>& best, const V16* __restrict__ vp, long long& v,
+                                         long long nvec, long long head) {
+  constexpr int VE = VecOf<T>::kElems;
+  for (; v + static_cast<long long>(UU - 1) * G < nvec; v += static_cast<long long>(UU) * G) {
+    V16 buf[UU];
+#pragma unroll
+    for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(vp + v + static_cast<long long>(u) * G);
+#pragma unroll
+    for (int u = 0; u < UU; ++u)
+      visit_vec<T, V, kMax>(best, buf[u], head + (v + static_cast<long long>(u) * G) * VE);
+  }
+}
+
+// Scan `n` contiguous elements with a group of G threads.  kAligned: the row starts on a
+// 16-byte boundary and is a whole number of vectors (no head / tail).
+template <typename T, typename V, bool kMax, int G, int U, bool kAligned>
 __device__ __forceinline__ ArgPair<V> arg_span(const T* __restrict__ row, long long n, int g) {
+  using Op = ArgOp<V, kMax>;
   constexpr int VE = VecOf<T>::kElems;
   ArgPair<V> best = Op::identity();
-  const uintptr_t addr = reinterpret_cast<uintptr_t>(row);
-  long long head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
-  if (head > n) head = n;
+  long long head = 0;
+  if constexpr (!kAligned) {
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(row);
+    head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
+    if (head > n) head = n;
+    if (g < head) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + g)), g);
+  }
   const long long nvec = (n - head) / VE;
   const long long tail0 = head + nvec * VE;
-  if (g < head) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + g)), g);
   const V16* __restrict__ vp = reinterpret_cast<const V16*>(row + head);
   long long v = g;
-  for (; v + static_cast<long long>(U - 1) * G < nvec; v += static_cast<long long>(U) * G) {
-    V16 buf[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) buf[u] = ldg_stream16(vp + v + static_cast<long long>(u) * G);
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      typename VecOf<T>::U w;
-      w.raw = buf[u];
-      const long long i0 = head + (v + static_cast<long long>(u) * G) * VE;
-#pragma unroll
-      for (int e = 0; e < VE; ++e) Op::visit(best, Cvt<V, T>::to(w.e[e]), i0 + e);
-    }
+  arg_step<T, V, kMax, G, U>(best, vp, v, nvec, head);
+  if constexpr (U > 4) arg_step<T, V, kMax, G, 4>(best, vp, v, nvec, head);
+  if constexpr (U > 2) arg_step<T, V, kMax, G, 2>(best, vp, v, nvec, head);
+  if constexpr (U > 1) arg_step<T, V, kMax, G, 1>(best, vp, v, nvec, head);
+  if constexpr (!kAligned) {
+    for (long long i = tail0 + g; i < n; i += G) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + i)), i);
   }
-  for (; v < nvec; v += G) {
-    typename VecOf<T>::U w;
-    w.raw = ldg_stream16(vp + v);
-    const long long i0 = head + v * VE;
-#pragma unroll
-    for (int e = 0; e < VE; ++e) Op::visit(best, Cvt<V, T>::to(w.e[e]), i0 + e);
-  }
-  for (long long i = tail0 + g; i < n; i += G) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + i)), i);
   return best;
 }
 
-// post == 1: [rows, n].  kWarpsPerRow as in row_reduce_kernel.
-template <typename T, typename V, bool kMax, int kWarpsPerRow>
+// post == 1: [rows, n], G threads per row (as in row_reduce_kernel).
+template <typename T, typename V, bool kMax, int G, bool kAligned>
 __global__ void __launch_bounds__(kBlock)
     arg_row_kernel(const T* __restrict__ x, long long rows, long long n, void* out, int index_dtype,
                    void* val_out) {
   using Op = ArgOp<V, kMax>;
-  __shared__ V s_v[kWarps];
-  __shared__ long long s_i[kWarps];
+  __shared__ V s_v[2 * kWarps];
+  __shared__ long long s_i[2 * kWarps];
+  constexpr int kRowsPerCta = kBlock / G;
+  constexpr int kW = G / 32;
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if constexpr (kWarpsPerRow == 1) {
-    for (long long row = static_cast<long long>(blockIdx.x) * kWarps + warp; row < rows;
-         row += static_cast<long long>(gridDim.x) * kWarps) {
-      ArgPair<V> p = arg_span<T, V, Op, 32, 8>(x + row * n, n, lane);
-      p = warp_arg<V, Op>(p);
-      if (lane == 0) store_arg<T, V>(out, index_dtype, val_out, row, p);
-    }
-  } else {
-    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-      ArgPair<V> p = arg_span<T, V, Op, kBlock, 8>(x + row * n, n, threadIdx.x);
-      p = warp_arg<V, Op>(p);
-      __syncthreads();
+  int parity = 0;
+  for (long long row = static_cast<long long>(blockIdx.x) * kRowsPerCta + grp; row < rows;
+       row += static_cast<long long>(gridDim.x) * kRowsPerCta) {
+    ArgPair<V> p = arg_span<T, V, kMax, G, 8, kAligned>(x + row * n, n, g);
+    p = warp_arg<V, Op>(p);
+    if constexpr (G > 32) {
+      V* bv = s_v + parity * kWarps;
+      long long* bi = s_i + parity * kWarps;
+      parity ^= 1;
       if (lane == 0) {
-        s_v[warp] = p.v;
-        s_i[warp] = p.i;
+        bv[warp] = p.v;
+        bi[warp] = p.i;
       }
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        ArgPair<V> r;
-        r.v = s_v[0];
-        r.i = s_i[0];
+      group_barrier<G>();
+      if (g == 0) {
+        p.v = bv[grp * kW];
+        p.i = bi[grp * kW];
 #pragma unroll
-        for (int w = 1; w < kWarps; ++w) {
+        for (int w = 1; w < kW; ++w) {
           ArgPair<V> q;
-          q.v = s_v[w];
-          q.i = s_i[w];
-          r = Op::combine(r, q);
+          q.v = bv[grp * kW + w];
+          q.i = bi[grp * kW + w];
+          p = Op::combine(p, q);
         }
-        store_arg<T, V>(out, index_dtype, val_out, row, r);
       }
     }
+    if (g == 0) store_arg<T, V>(out, index_dtype, val_out, row, p);
   }
 }
 
@@ -227,19 +293,30 @@ struct ArgGeom {
 template <typename T, typename V, bool kMax>
 static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, void* val_out,
                       cudaStream_t stream) {
-  const int sms = current_sm_count();
   if (g.post == 1) {
     const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
-    if (g.pre >= static_cast<long long>(sms) * 16 && row_bytes <= 16384) {
-      long long ctas = (g.pre + kWarps - 1) / kWarps;
-      if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
-      arg_row_kernel<T, V, kMax, 1><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, g.pre, g.n, out, index_dtype, val_out);
-    } else {
-      long long ctas = g.pre > 0x7fffffffLL ? 0x7fffffffLL : g.pre;
-      arg_row_kernel<T, V, kMax, kWarps><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, g.pre, g.n, out, index_dtype, val_out);
+    int G = 32;
+    while (G < 256 && static_cast<long long>(G) * 64 < row_bytes) G <<= 1;
+    const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
+    long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);
+    if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
+    const unsigned grid = static_cast<unsigned>(ctas);
+#define B200PHI_ARG_ROW(GG)                                                                          \
+  if (aligned)                                                                                       \
+    arg_row_kernel<T, V, kMax, GG, true><<<grid, kBlock, 0, stream>>>(x, g.pre, g.n, out, index_dtype, val_out); \
+  else                                                                                               \
+    arg_row_kernel<T, V, kMax, GG, false><<<grid, kBlock, 0, stream>>>(x, g.pre, g.n, out, index_dtype, val_out);
+    switch (G) {
+      case 32:
+        B200PHI_ARG_ROW(32) break;
+      case 64:
+        B200PHI_ARG_ROW(64) break;
+      case 128:
+        B200PHI_ARG_ROW(128) break;
+      default:
+        B200PHI_ARG_ROW(256) break;
     }
+#undef B200PHI_ARG_ROW
   } else {
     int TX = 1;
     while (TX < g.post && TX < kBlock) TX <<= 1;

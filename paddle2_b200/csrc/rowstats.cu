@@ -6,10 +6,13 @@
 // 16-byte streaming loads, the mean is formed, and sum((x-mean)^2) is taken from
 // the same registers.  Rows that do not fit the register tile take the same two
 // steps with the second pass served from L2.
+#include <stdlib.h>
+
 #include <string>
 
 #include "../../include/b200phi.h"
 #include "prim.cuh"
+#include "tma.cuh"
 
 namespace b200phi {
 
@@ -48,14 +51,18 @@ __device__ __forceinline__ void put_stat(void* p, int dtype, long long i, double
 template <typename T, typename Acc, int G, int NV>
 __global__ void __launch_bounds__(kBlock)
     rowstats_reg_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
-                        void* mean_out, void* var_out, int out_dtype) {
+                        Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
-  __shared__ Acc smem[kWarps];
-  const int g = threadIdx.x % G;
+  constexpr int kW = G / 32;
+  // [combine 0|1][parity][warp]: alternating parity per row leaves one barrier per combine
+  __shared__ Acc smem[2][2][kWarps];
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long rows_per_cta = kBlock / G;
   const long long nvec = cols / VE;
-  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + threadIdx.x / G;
-       row < rows; row += static_cast<long long>(gridDim.x) * rows_per_cta) {
+  int parity = 0;
+  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + grp; row < rows;
+       row += static_cast<long long>(gridDim.x) * rows_per_cta) {
     const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + row * cols);
     V16 buf[NV];
 #pragma unroll
@@ -67,25 +74,47 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) fold_vec<Acc, SumOp<Acc>, T, 4>(buf[k], s);
+      if (v < nvec) {
+        Acc val[VE];
+        unpack_vec<T, Acc>(buf[k], val);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) s[e % 4] += val[e];
+      }
     }
-    Acc sum = group_sum<Acc, G>((s[0] + s[1]) + (s[2] + s[3]), smem);
-    const Acc mean = sum / static_cast<Acc>(cols);
+    Acc sum = warp_combine<Acc, SumOp<Acc>>((s[0] + s[1]) + (s[2] + s[3]));
+    if constexpr (G > 32) {
+      if (lane == 0) smem[0][parity][warp] = sum;
+      group_barrier<G>();
+      sum = smem[0][parity][grp * kW];
+#pragma unroll
+      for (int w = 1; w < kW; ++w) sum += smem[0][parity][grp * kW + w];
+    }
+    const Acc mean = sum / cols_acc;
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const long long v = g + static_cast<long long>(k) * G;
       if (v < nvec) {
-        typename VecOf<T>::U w;
-        w.raw = buf[k];
+        Acc val[VE];
+        unpack_vec<T, Acc>(buf[k], val);
 #pragma unroll
         for (int e = 0; e < VE; ++e) {
-          const Acc dlt = Cvt<Acc, T>::to(w.e[e]) - mean;
+          const Acc dlt = val[e] - mean;
           q[e % 4] += dlt * dlt;
         }
       }
     }
-    Acc ss = group_sum<Acc, G>((q[0] + q[1]) + (q[2] + q[3]), smem);
+    Acc ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    if constexpr (G > 32) {
+      if (lane == 0) smem[1][parity][warp] = ss;
+      group_barrier<G>();
+      if (g == 0) {
+        ss = smem[1][parity][grp * kW];
+#pragma unroll
+        for (int w = 1; w < kW; ++w) ss += smem[1][parity][grp * kW + w];
+      }
+    }
+    parity ^= 1;
     if (g == 0) {
       if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
       if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
@@ -98,7 +127,7 @@ __global__ void __launch_bounds__(kBlock)
 template <typename T, typename Acc>
 __global__ void __launch_bounds__(kBlock)
     rowstats_sweep_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
-                          void* mean_out, void* var_out, int out_dtype) {
+                          Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
   __shared__ Acc smem[kWarps];
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
@@ -125,7 +154,7 @@ __global__ void __launch_bounds__(kBlock)
     }
     for (long long i = tail0 + threadIdx.x; i < cols; i += kBlock) s[1] += Cvt<Acc, T>::to(ldg_scalar(r + i));
     const Acc sum = block_combine<Acc, SumOp<Acc>>((s[0] + s[1]) + (s[2] + s[3]), smem);
-    const Acc mean = sum / static_cast<Acc>(cols);
+    const Acc mean = sum / cols_acc;
 
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
     if (threadIdx.x < head) {
@@ -153,6 +182,150 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Persistent CTAs with a ring of whole rows in shared memory, filled by one producer thread
+// with bulk asynchronous copies (TMA) while the 256 consumer threads take mean and
+// sum((x-mean)^2) of earlier rows out of the ring: the next rows are always in flight, so the
+// two block combines per row no longer leave the memory system idle (the register kernel above
+// is latency-bound between rows: 5.2 TB/s on config C4).
+// Requirements (host-checked): row_bytes % 16 == 0, x 16-byte aligned, stages * row_bytes fits.
+// NV > 0: the row has at most kBlock*NV vectors and each consumer keeps its share as unpacked
+// accumulation-type values in registers (one conversion, one shared-memory read per element;
+// the stage is handed back to the producer before any arithmetic).  NV == 0: any row that fits
+// a stage; both passes read shared memory.
+template <typename T, typename Acc, int NV, bool kExact>
+__global__ void __launch_bounds__(kBlock + 32)
+    rowstats_tma_kernel(const T* __restrict__ x, long long rows, long long cols, int stages, Acc denom,
+                        Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
+  extern __shared__ __align__(128) unsigned char ring[];
+  constexpr int VE = VecOf<T>::kElems;
+  const uint32_t row_bytes = static_cast<uint32_t>(cols * sizeof(T));
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + static_cast<size_t>(stages) * row_bytes);
+  uint64_t* empty = full + stages;
+  __shared__ Acc s_part[2][kWarps];
+  const long long my_rows = (rows > blockIdx.x) ? (rows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (threadIdx.x >= kBlock) {  // producer warp
+    if (threadIdx.x == kBlock) {
+      for (long long k = 0; k < my_rows; ++k) {
+        const int s = static_cast<int>(k % stages);
+        const uint32_t phase = static_cast<uint32_t>((k / stages) & 1);
+        if (k >= stages) mbar_wait(&empty[s], phase ^ 1u);
+        const long long row = blockIdx.x + k * static_cast<long long>(gridDim.x);
+        mbar_arrive_expect_tx(&full[s], row_bytes);
+        bulk_load(ring + static_cast<size_t>(s) * row_bytes, x + row * cols, row_bytes, &full[s]);
+      }
+    }
+    return;
+  }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = static_cast<int>(cols / VE);
+  for (long long k = 0; k < my_rows; ++k) {
+    const int s = static_cast<int>(k % stages);
+    const uint32_t phase = static_cast<uint32_t>((k / stages) & 1);
+    mbar_wait(&full[s], phase);
+    const V16* __restrict__ sv = reinterpret_cast<const V16*>(ring + static_cast<size_t>(s) * row_bytes);
+    Acc sum, ss;
+    Acc mean;
+    if constexpr (NV > 0) {
+      Acc val[NV * VE];
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int v = threadIdx.x + j * kBlock;
+        if (kExact || v < nvec) {  // kExact: the row is exactly kBlock*NV vectors, no predicates
+          unpack_vec<T, Acc>(sv[v], &val[j * VE]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < VE; ++e) val[j * VE + e] = Acc(0);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);  // the row now lives in registers
+      Acc a[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+#pragma unroll
+      for (int i = 0; i < NV * VE; ++i) a[i % 4] += val[i];
+      sum = warp_combine<Acc, SumOp<Acc>>((a[0] + a[1]) + (a[2] + a[3]));
+      if (lane == 0) s_part[0][warp] = sum;
+      consumer_barrier<kBlock>();
+      sum = s_part[0][0];
+#pragma unroll
+      for (int w = 1; w < kWarps; ++w) sum += s_part[0][w];
+      mean = sum / cols_acc;  // cols converted once on the host: I2F.S64 per row was the hottest line
+      Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        if (kExact || threadIdx.x + j * kBlock < nvec) {
+#pragma unroll
+          for (int e = 0; e < VE; ++e) {
+            const Acc dlt = val[j * VE + e] - mean;
+            q[e % 4] += dlt * dlt;
+          }
+        }
+      }
+      ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    } else {
+      Acc a[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+      for (int v = threadIdx.x; v < nvec; v += kBlock) fold_vec<Acc, SumOp<Acc>, T, 4>(sv[v], a);
+      sum = warp_combine<Acc, SumOp<Acc>>((a[0] + a[1]) + (a[2] + a[3]));
+      if (lane == 0) s_part[0][warp] = sum;
+      consumer_barrier<kBlock>();
+      sum = s_part[0][0];
+#pragma unroll
+      for (int w = 1; w < kWarps; ++w) sum += s_part[0][w];
+      mean = sum / cols_acc;
+      Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+      for (int v = threadIdx.x; v < nvec; v += kBlock) {
+        Acc val[VE];
+        unpack_vec<T, Acc>(sv[v], val);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          const Acc dlt = val[e] - mean;
+          q[e % 4] += dlt * dlt;
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    }
+    if (lane == 0) s_part[1][warp] = ss;
+    consumer_barrier<kBlock>();  // also orders this row's reads of s_part[0] before the next row's writes
+    if (threadIdx.x == 0) {
+      ss = s_part[1][0];
+#pragma unroll
+      for (int w = 1; w < kWarps; ++w) ss += s_part[1][w];
+      const long long row = blockIdx.x + k * static_cast<long long>(gridDim.x);
+      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
+      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+    }
+  }
+}
+
+template <typename T, typename Acc, int NV, bool kExact>
+static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int out_dtype, Acc denom,
+                               int stages, size_t smem, long long ctas, cudaStream_t stream) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    cudaError_t ea = cudaFuncSetAttribute(rowstats_tma_kernel<T, Acc, NV, kExact>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (ea != cudaSuccess) return cuda_status(ea);
+    attr_set[dev] = true;
+  }
+  rowstats_tma_kernel<T, Acc, NV, kExact><<<static_cast<unsigned>(ctas), kBlock + 32, smem, stream>>>(
+      x, d->rows, d->cols, stages, denom, static_cast<Acc>(d->cols), d->mean, d->var, out_dtype);
+  return B200PHI_OK;
+}
+
 template <typename T, typename Acc>
 static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaStream_t stream) {
   constexpr int VE = VecOf<T>::kElems;
@@ -163,20 +336,51 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   const bool aligned = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (n % VE == 0);
   const long long nvec = n / VE;
   const int sms = current_sm_count();
+  const long long row_bytes = n * static_cast<long long>(sizeof(T));
+  // The TMA ring was measured at 4.1 TB/s on C4 against 5.2 TB/s for the register kernel
+  // (instruction-issue bound: profiles/r01_rowstats_tma.md); it stays available for study.
+  static const bool no_tma = getenv("B200PHI_ROWSTATS_TMA") == nullptr;
+  static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   if (aligned && nvec <= 32 * 8 && d->rows >= static_cast<long long>(sms) * 16) {
     long long ctas = (d->rows + kWarps - 1) / kWarps;
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 32, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-        x, d->rows, n, denom, d->mean, d->var, out_dtype);
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+  } else if (aligned && !no_tma && row_bytes >= 4096 && row_bytes <= 98304) {
+    // ring of whole rows: 2..6 stages, as many CTAs per SM as 200 KiB of shared memory allow
+    int stages = static_cast<int>((192 * 1024) / row_bytes);
+    stages = stages > 12 ? 4 : (stages >= 8 ? 4 : (stages >= 6 ? 3 : 2));
+    const size_t smem = static_cast<size_t>(stages) * row_bytes + 2 * stages * sizeof(uint64_t);
+    int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 4) per_sm = 4;
+    long long ctas = static_cast<long long>(sms) * per_sm;
+    if (ctas > d->rows) ctas = d->rows;
+    int rc;
+    if (nvec == kBlock * 4)
+      rc = launch_rowstats_tma<T, Acc, 4, true>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    else if (nvec == kBlock * 2)
+      rc = launch_rowstats_tma<T, Acc, 2, true>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    else if (nvec <= kBlock * 2)
+      rc = launch_rowstats_tma<T, Acc, 2, false>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    else if (nvec <= kBlock * 4)
+      rc = launch_rowstats_tma<T, Acc, 4, false>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    else
+      rc = launch_rowstats_tma<T, Acc, 0, false>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    if (rc != B200PHI_OK) return rc;
+  } else if (aligned && nvec <= 256 * 4 && force_g == 256) {
+    long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
+    rowstats_reg_kernel<T, Acc, 256, 4><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (aligned && nvec <= 128 * 8) {
     long long ctas = (d->rows + 1) / 2;
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-        x, d->rows, n, denom, d->mean, d->var, out_dtype);
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else {
     long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
     rowstats_sweep_kernel<T, Acc><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-        x, d->rows, n, denom, d->mean, d->var, out_dtype);
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);

@@ -74,16 +74,22 @@ int main(int argc, char** argv) {
     b200phi_argreduce_desc a = {};
     a.op = B200PHI_ARGMAX; a.in_dtype = B200PHI_INT64; a.index_dtype = B200PHI_INT64; a.rank = 2;
     a.dims[0] = 8192; a.dims[1] = 32000; a.axis = 1; a.x = x; a.out = idx; a.max_out = val;
-    float ms = time_it([&] { OK(b200phi_argreduce(&a, 0)); }, 20);
-    printf("C3a argmax+max int64 [8192,32000]        %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097283072.0 / ms / 1e6);
+    float ms = 0;
+    const bool only_b = strstr(only, "C3b") != nullptr;
+    if (!only_b) {
+      ms = time_it([&] { OK(b200phi_argreduce(&a, 0)); }, 20);
+      printf("C3a argmax+max int64 [8192,32000]        %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097283072.0 / ms / 1e6);
+    }
     a.in_dtype = B200PHI_BFLOAT16;   // reuse the buffer as bf16 bits; mask NaN/Inf exponents is not needed for timing
     ms = time_it([&] { OK(b200phi_argreduce(&a, 0)); }, 20);
     printf("C3b argmax+max bf16 [8192,32000]         %8.2f us  %7.1f GB/s\n", ms * 1e3, 524369920.0 / ms / 1e6);
-    b200phi_reduce_desc d = {};
-    d.op = B200PHI_MAX; d.in_dtype = d.out_dtype = B200PHI_INT64; d.rank = 2; d.dims[0] = 8192; d.dims[1] = 32000;
-    d.naxes = 1; d.axes[0] = 1; d.x = x; d.out = val;
-    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
-    printf("C3a max alone int64 [8192,32000]         %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097217536.0 / ms / 1e6);
+    if (!only_b) {
+      b200phi_reduce_desc d = {};
+      d.op = B200PHI_MAX; d.in_dtype = d.out_dtype = B200PHI_INT64; d.rank = 2; d.dims[0] = 8192; d.dims[1] = 32000;
+      d.naxes = 1; d.axes[0] = 1; d.x = x; d.out = val;
+      ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+      printf("C3a max alone int64 [8192,32000]         %8.2f us  %7.1f GB/s\n", ms * 1e3, 2097217536.0 / ms / 1e6);
+    }
     cudaFree(x); cudaFree(idx); cudaFree(val);
   }
   if (!*only || strstr(only, "C4")) {
