@@ -4,6 +4,8 @@
 // streamed with 16-byte loads, indices are 64-bit, and the combine rule
 // "better value, else lower index" is applied at every level so ties are
 // bit-exact with the CPU kernel (Eigen argmax, cpu/arg_min_max_kernel.cc:46-59).
+#include <stdlib.h>
+
 #include <string>
 
 #include "../../include/b200phi.h"
@@ -297,6 +299,8 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
     int G = 32;
     while (G < 256 && static_cast<long long>(G) * 64 < row_bytes) G <<= 1;
+    static const int force_g = getenv("B200PHI_ARG_G") ? atoi(getenv("B200PHI_ARG_G")) : 0;
+    if (force_g == 32 || force_g == 64 || force_g == 128 || force_g == 256) G = force_g;
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
     long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
