@@ -250,11 +250,38 @@ def other_configs(torch, pb):
     res = {}
 
     def t(fn, nbytes, iters=20, warm=5):
-        s = time_steps(torch, fn, iters, warm)
+        """`iters` back-to-back launches replayed from a CUDA graph: at 40-100 us per kernel the
+        Python/ctypes call (~30 us) would otherwise be what is measured."""
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        try:
+            side = torch.cuda.Stream()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                nonlocal_cur.value = side.cuda_stream
+                with torch.cuda.graph(graph, stream=side):
+                    for _ in range(iters):
+                        fn()
+            nonlocal_cur.value = torch.cuda.current_stream().cuda_stream
+            graph.replay()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            s = e0.elapsed_time(e1) / 1e3
+        except Exception:
+            nonlocal_cur.value = torch.cuda.current_stream().cuda_stream
+            torch.cuda.synchronize()
+            s = time_steps(torch, fn, iters, 0)
         return round(nbytes / (s / iters) / 1e9, 1)
 
+    nonlocal_cur = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
     def stream():
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return nonlocal_cur
 
     x = torch.rand(32, 1024, 4096, device="cuda")
     out = torch.empty(32, 1024, device="cuda")
@@ -362,9 +389,35 @@ def run_gpu_arm(args):
     d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
     comm = reducer.comm if reducer is not None else None
 
+    # N > 1: ncclAllReduce on the reduce's stream by default.  B200PHI_COLLECTIVE=p2p selects the
+    # fused kernel (local reduce + exchange over NVLink peer memory in one launch); measured at
+    # N=2 it is 1.212 ms/step against 1.204 for the NCCL route (profiles/r01_multigpu.md), so
+    # the faster one is the default
+    p2p = None
+    collective = "none (single GPU)"
+    if multi:
+        collective = "ncclAllReduce after the local reduce (b200phi_sharded_reduce)"
+        if os.environ.get("B200PHI_COLLECTIVE", "nccl") == "p2p":
+            try:
+                from paddle2_b200.dist import P2PReducer
+                p2p = P2PReducer(max_out_numel=COLS, max_tiles=64)
+                collective = "fused in the reduce kernel over NVLink peer memory (b200phi_sharded_reduce_p2p)"
+            except Exception as exc:  # e.g. CUDA IPC not permitted in this container
+                p2p = None
+                collective += f" [p2p unavailable: {str(exc)[:80]}]"
+        ok = torch.tensor([1 if p2p is not None else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            p2p = None
+    state = {"epoch": 0}
+
     def step():
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        L.check(lib.b200phi_sharded_reduce(C.byref(d), 0, comm, stream))
+        if p2p is not None:
+            p2p.epoch += 1
+            L.check(lib.b200phi_sharded_reduce_p2p(C.byref(d), 0, C.byref(p2p.g), p2p.epoch, stream))
+        else:
+            L.check(lib.b200phi_sharded_reduce(C.byref(d), 0, comm, stream))
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
@@ -380,6 +433,10 @@ def run_gpu_arm(args):
     ms_per_step = secs / args.steps * 1e3
     value = ALGO_BYTES * world / (secs / args.steps) / 1e9
 
+    if p2p is not None:  # the fused exchange must agree with the NCCL route on the same shards
+        ref = reducer.sum(x)
+        torch.cuda.synchronize()
+        assert torch.allclose(out, ref, rtol=1e-6), "fused p2p result differs from the NCCL route"
     # correctness of what was timed: column sums against an fp64 torch reduction of a slab + full
     chk = x[:8192].double().sum(0)
     got_slab = pb.sum(x[:8192], axis=0).double()
@@ -436,6 +493,8 @@ def run_gpu_arm(args):
            "host_buffer": f"[{host_rows},{COLS}] pinned fp32, streamed {reps}x per step in 16384-row chunks"}
     del xh
 
+    if p2p is not None:
+        p2p.close()
     if rank != 0:
         if multi:
             dist.barrier()
@@ -475,7 +534,8 @@ def run_gpu_arm(args):
         "config": {"workload": "C5 global paddle.sum fp32 axis=0, [524288,4096] per GPU (8 GiB), "
                                "row-sharded, local reduce + ncclAllReduce of the [4096] partial",
                    "l2": "inputs (8 GiB per GPU) are far larger than the 126 MB L2; no flush needed",
-                   "parallelism": f"rows sharded over {world} GPU(s), one process per GPU"},
+                   "parallelism": f"rows sharded over {world} GPU(s), one process per GPU",
+                   "collective": collective},
         "clocks": sampler.summary() if sampler else None,
         "e2e": e2e, "gpu_launches": args.steps,
         "roofline": roofline, "cpu_baseline": cpu_baseline,

@@ -265,6 +265,37 @@ B200PHI_API int b200phi_comm_destroy(void* comm);
 B200PHI_API int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count,
                            void* comm, void* stream);
 
+/* ---- fused variant: local reduce + exchange over NVLink peer memory in ONE kernel ---- */
+
+/* Replaces the same reference pair as b200phi_sharded_reduce
+ * (SumKernel + ProcessGroupNCCL::AllReduce, process_group_nccl.cc:267-298), without a
+ * collective library on the path: the thread block that finishes an output tile writes it
+ * into every peer's buffer (CUDA IPC mapping), publishes an epoch flag and combines the
+ * ranks' slots in rank order, so every rank ends with identical bits.
+ * Set-up (once): every rank allocates b200phi_p2p_buffer_bytes(...) with b200phi_p2p_alloc,
+ * exchanges the 64-byte handles with its rendezvous, maps the peers' buffers with
+ * b200phi_p2p_open and fills base[r] (base[rank] = its own pointer).
+ * Per call: the same epoch on every rank, starting at 1 and growing by 1; calls of one
+ * group must be issued in the same order on every rank; the kernels of all ranks must be
+ * able to run at the same time (one GPU per rank).  Covers the vectorised column reduce
+ * (leading axis sharded) for fp32 sum/mean/max/min, bf16/fp64/int64 sum; anything else
+ * returns B200PHI_UNSUPPORTED and b200phi_sharded_reduce is the route. */
+typedef struct {
+  int32_t nranks;        /* 1..8 */
+  int32_t rank;
+  void* base[8];         /* base[r]: rank r's buffer as mapped into this process */
+  int64_t max_out_numel; /* output elements the buffers were sized for */
+  int64_t max_tiles;     /* output tiles (thread blocks along the kept axis) they were sized for */
+} b200phi_p2p_group;
+
+B200PHI_API size_t b200phi_p2p_buffer_bytes(int nranks, int64_t max_out_numel, int64_t max_tiles);
+B200PHI_API int b200phi_p2p_alloc(size_t bytes, void** ptr, unsigned char handle[64]);
+B200PHI_API int b200phi_p2p_open(const unsigned char handle[64], void** ptr);
+B200PHI_API int b200phi_p2p_close(void* ptr);
+B200PHI_API int b200phi_p2p_free(void* ptr);
+B200PHI_API int b200phi_sharded_reduce_p2p(const b200phi_reduce_desc* d, int64_t global_reduce_count,
+                                           const b200phi_p2p_group* g, uint32_t epoch, void* stream);
+
 /* ------------------------------------------------------------------------ */
 
 /* Message of the last non-zero status returned on this host thread. */

@@ -105,6 +105,16 @@ class ElementwiseDesc(C.Structure):
     ]
 
 
+class P2PGroup(C.Structure):
+    _fields_ = [
+        ("nranks", C.c_int32),
+        ("rank", C.c_int32),
+        ("base", C.c_void_p * 8),
+        ("max_out_numel", C.c_int64),
+        ("max_tiles", C.c_int64),
+    ]
+
+
 class B200PhiError(RuntimeError):
     """A non-zero b200phi_status; mirrors the reference's EnforceNotMet."""
 
@@ -125,6 +135,12 @@ EXPORTS = [
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
     "b200phi_sharded_reduce",
+    "b200phi_p2p_buffer_bytes",
+    "b200phi_p2p_alloc",
+    "b200phi_p2p_open",
+    "b200phi_p2p_close",
+    "b200phi_p2p_free",
+    "b200phi_sharded_reduce_p2p",
     "b200phi_last_error",
     "b200phi_version",
 ]
@@ -157,6 +173,17 @@ def lib():
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]
     L.b200phi_sharded_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_int64, C.c_void_p, C.c_void_p]
+    L.b200phi_p2p_buffer_bytes.restype = C.c_size_t
+    L.b200phi_p2p_buffer_bytes.argtypes = [C.c_int, C.c_int64, C.c_int64]
+    L.b200phi_p2p_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
+    L.b200phi_p2p_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.b200phi_p2p_close.argtypes = [C.c_void_p]
+    L.b200phi_p2p_free.argtypes = [C.c_void_p]
+    L.b200phi_sharded_reduce_p2p.argtypes = [C.POINTER(ReduceDesc), C.c_int64, C.POINTER(P2PGroup),
+                                             C.c_uint32, C.c_void_p]
+    for name in ("b200phi_p2p_alloc", "b200phi_p2p_open", "b200phi_p2p_close", "b200phi_p2p_free",
+                 "b200phi_sharded_reduce_p2p"):
+        getattr(L, name).restype = C.c_int
     for name in ("b200phi_reduce", "b200phi_argreduce", "b200phi_rowstats", "b200phi_elementwise",
                  "b200phi_comm_unique_id", "b200phi_comm_init_rank", "b200phi_comm_destroy",
                  "b200phi_sharded_reduce"):

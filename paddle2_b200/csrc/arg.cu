@@ -297,8 +297,10 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
                       cudaStream_t stream) {
   if (g.post == 1) {
     const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
+    // threads per row: about 32 vectors per thread (measured on C3b, 4000 vectors per row:
+    // G=128 reads 6.2 TB/s, G=256 6.0, G=64 and 32 5.7)
     int G = 32;
-    while (G < 256 && static_cast<long long>(G) * 64 < row_bytes) G <<= 1;
+    while (G < 256 && static_cast<long long>(G) * 512 < row_bytes) G <<= 1;
     static const int force_g = getenv("B200PHI_ARG_G") ? atoi(getenv("B200PHI_ARG_G")) : 0;
     if (force_g == 32 || force_g == 64 || force_g == 128 || force_g == 256) G = force_g;
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;

@@ -121,3 +121,86 @@ class ShardedReducer:
 
     def sum(self, x_local, **kw):  # noqa: A003
         return self.reduce(L.SUM, x_local, **kw)
+
+
+class P2PReducer:
+    """Fused sharded reduce: local column reduce + exchange over NVLink peer memory in one
+    kernel per rank (b200phi_sharded_reduce_p2p).  torch.distributed only carries the 64-byte
+    CUDA IPC handles at set-up; the data path is the kernel's own peer loads/stores."""
+
+    def __init__(self, max_out_numel, max_tiles=4096, group=None):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed must be initialised (it is the rendezvous)")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        if self.world > 8:
+            raise ValueError("the fused exchange covers one NVSwitch box: at most 8 ranks")
+        lib = L.lib()
+        self.lib = lib
+        self.max_out, self.max_tiles = int(max_out_numel), int(max_tiles)
+        nbytes = lib.b200phi_p2p_buffer_bytes(self.world, self.max_out, self.max_tiles)
+        own = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        L.check(lib.b200phi_p2p_alloc(nbytes, C.byref(own), handle))
+        self.own = own
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self.peers = []
+        g = L.P2PGroup()
+        g.nranks, g.rank = self.world, self.rank
+        g.max_out_numel, g.max_tiles = self.max_out, self.max_tiles
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                g.base[r] = own.value
+            else:
+                p = C.c_void_p()
+                L.check(lib.b200phi_p2p_open(h, C.byref(p)))
+                self.peers.append(p)
+                g.base[r] = p.value
+        self.g = g
+        self.epoch = 0
+        dist.barrier(group=group)  # every rank has mapped every buffer before the first kernel
+
+    def close(self):
+        if getattr(self, "own", None) is None:
+            return
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        for p in self.peers:
+            self.lib.b200phi_p2p_close(p)
+        self.lib.b200phi_p2p_free(self.own)
+        self.own, self.peers = None, []
+
+    def reduce(self, op, x_local, global_rows=0, out=None, workspace=None):
+        _ops._require_cuda(x_local)
+        x = x_local.contiguous()
+        out_dtype = _ops._sum_out_dtype(x.dtype, None) if op == L.SUM else x.dtype
+        if out is None:
+            out = torch.empty(x.shape[1:], dtype=out_dtype, device=x.device)
+        d = L.ReduceDesc()
+        d.op = op
+        d.in_dtype = _ops._phi_dtype(x.dtype)
+        d.out_dtype = _ops._phi_dtype(out.dtype)
+        d.rank = x.dim()
+        for i, s in enumerate(x.shape):
+            d.dims[i] = s
+        d.naxes = 1
+        d.axes[0] = 0
+        d.x = x.data_ptr()
+        d.out = out.data_ptr()
+        with torch.cuda.device(x.device):
+            ws_bytes = self.lib.b200phi_reduce_workspace(C.byref(d))
+            if ws_bytes:
+                if workspace is None or workspace.numel() < ws_bytes:
+                    workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+                d.workspace = workspace.data_ptr()
+                d.workspace_bytes = workspace.numel()
+            self.epoch += 1
+            stream = C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            L.check(self.lib.b200phi_sharded_reduce_p2p(C.byref(d), int(global_rows), C.byref(self.g),
+                                                        self.epoch, stream))
+        return out
+
+    def sum(self, x_local, **kw):  # noqa: A003
+        return self.reduce(L.SUM, x_local, **kw)

@@ -46,6 +46,23 @@ def _worker(rank, world, port, ret):
         got = red.reduce(L.MEAN, x).cpu().numpy()
         G.assert_reduce_close(got, O.reduce("mean", full, [0]), full, [0], "mean", G.FP32_RTOL)
         torch.cuda.synchronize()
+        # the fused variant: one kernel per rank, exchange over peer memory, no NCCL
+        from paddle2_b200.dist import P2PReducer
+        p2p = P2PReducer(max_out_numel=cols, max_tiles=64)
+        nccl_sum = red.sum(x)
+        for _ in range(3):                       # epochs 1..3: slots alternate by parity
+            fused = p2p.sum(x)
+            torch.cuda.synchronize()
+            np.testing.assert_allclose(fused.cpu().numpy(), nccl_sum.cpu().numpy(), rtol=1e-6)
+        G.assert_reduce_close(fused.cpu().numpy(), O.reduce("sum", full, [0]), full, [0], "sum", G.FP32_RTOL)
+        assert np.array_equal(p2p.reduce(L.MAX, x).cpu().numpy(), O.reduce("max", full, [0]))
+        fm = p2p.reduce(L.MEAN, x, global_rows=total_rows).cpu().numpy()
+        G.assert_reduce_close(fm, O.reduce("mean", full, [0]), full, [0], "mean", G.FP32_RTOL)
+        # every rank must hold the same bits: compare through a gloo all_gather
+        gathered = [None] * world
+        dist.all_gather_object(gathered, fused.cpu().numpy().tobytes())
+        assert all(b == gathered[0] for b in gathered)
+        p2p.close()
         red.close()
         ret[rank] = "ok"
     finally:
