@@ -122,6 +122,123 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Asynchronous-copy staging (LDGSTS): a persistent CTA owns rows blockIdx.x, +gridDim.x, ...;
+// every thread copies ITS OWN NV vectors of the rows ahead into a private slot of a shared-memory
+// ring with cp.async and later reads back only what it copied itself, so no barrier or mbarrier
+// guards the data: cp.async.wait_group is enough.  kStages-1 rows per CTA are always in flight
+// while the current row is unpacked ONCE into registers and both passes run from there.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <typename T, typename Acc, int NV, int kStages>
+__global__ void __launch_bounds__(kBlock)
+    rowstats_async_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+                          Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
+  extern __shared__ __align__(128) unsigned char ring[];  // [kStages][NV][kBlock] V16
+  __shared__ Acc part[2][2][kWarps];
+  constexpr int VE = VecOf<T>::kElems;
+  V16* stage = reinterpret_cast<V16*>(ring);
+  const int nvec = static_cast<int>(cols / VE);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long my_rows = (rows > blockIdx.x) ? (rows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  auto issue = [&](long long k) {
+    if (k < my_rows) {
+      const V16* src = reinterpret_cast<const V16*>(x + (blockIdx.x + k * static_cast<long long>(gridDim.x)) * cols);
+      V16* dst = stage + static_cast<size_t>(k % kStages) * (NV * kBlock);
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int v = threadIdx.x + j * kBlock;
+        if (v < nvec) cp_async16(dst + v, src + v);
+      }
+    }
+    cp_async_commit();  // always: keeps the group count uniform
+  };
+
+#pragma unroll
+  for (int s = 0; s < kStages - 1; ++s) issue(s);
+  int parity = 0;
+  for (long long k = 0; k < my_rows; ++k) {
+    issue(k + kStages - 1);
+    cp_async_wait<kStages - 1>();  // row k's copies (this thread's own) have landed
+    const V16* cur = stage + static_cast<size_t>(k % kStages) * (NV * kBlock);
+    Acc val[NV * VE];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = threadIdx.x + j * kBlock;
+      if (v < nvec) {
+        unpack_vec<T, Acc>(cur[v], &val[j * VE]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < VE; ++e) val[j * VE + e] = Acc(0);
+      }
+    }
+    Acc a[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+#pragma unroll
+    for (int i = 0; i < NV * VE; ++i) a[i % 4] += val[i];
+    Acc sum = warp_combine<Acc, SumOp<Acc>>((a[0] + a[1]) + (a[2] + a[3]));
+    if (lane == 0) part[0][parity][warp] = sum;
+    __syncthreads();
+    sum = part[0][parity][0];
+#pragma unroll
+    for (int w = 1; w < kWarps; ++w) sum += part[0][parity][w];
+    const Acc mean = sum / cols_acc;
+    Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      if (threadIdx.x + j * kBlock < nvec) {
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          const Acc dlt = val[j * VE + e] - mean;
+          q[e % 4] += dlt * dlt;
+        }
+      }
+    }
+    Acc ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    if (lane == 0) part[1][parity][warp] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      ss = part[1][parity][0];
+#pragma unroll
+      for (int w = 1; w < kWarps; ++w) ss += part[1][parity][w];
+      const long long row = blockIdx.x + k * static_cast<long long>(gridDim.x);
+      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
+      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+    }
+    parity ^= 1;
+  }
+  cp_async_wait<0>();
+}
+
+template <typename T, typename Acc, int NV, int kStages>
+static int launch_rowstats_async(const T* x, const b200phi_rowstats_desc* d, int out_dtype, Acc denom,
+                                 int sms, cudaStream_t stream) {
+  const size_t smem = static_cast<size_t>(kStages) * NV * kBlock * sizeof(V16);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    cudaError_t ea = cudaFuncSetAttribute(rowstats_async_kernel<T, Acc, NV, kStages>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (ea != cudaSuccess) return cuda_status(ea);
+    attr_set[dev] = true;
+  }
+  int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
+  if (per_sm > 6) per_sm = 6;
+  if (per_sm < 1) per_sm = 1;
+  long long ctas = static_cast<long long>(sms) * per_sm;
+  if (ctas > d->rows) ctas = d->rows;
+  rowstats_async_kernel<T, Acc, NV, kStages><<<static_cast<unsigned>(ctas), kBlock, smem, stream>>>(
+      x, d->rows, d->cols, denom, static_cast<Acc>(d->cols), d->mean, d->var, out_dtype);
+  return B200PHI_OK;
+}
+
 // Any cols / alignment: one CTA per row, two sweeps (the second is an L2 hit for
 // rows up to tens of MB).
 template <typename T, typename Acc>
@@ -340,6 +457,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   // The TMA ring was measured at 4.1 TB/s on C4 against 5.2 TB/s for the register kernel
   // (instruction-issue bound: profiles/r01_rowstats_tma.md); it stays available for study.
   static const bool no_tma = getenv("B200PHI_ROWSTATS_TMA") == nullptr;
+  static const bool no_async = getenv("B200PHI_ROWSTATS_NO_ASYNC") != nullptr;
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   if (aligned && nvec <= 32 * 8 && d->rows >= static_cast<long long>(sms) * 16) {
     long long ctas = (d->rows + kWarps - 1) / kWarps;
@@ -367,6 +485,11 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
       rc = launch_rowstats_tma<T, Acc, 4, false>(x, d, out_dtype, denom, stages, smem, ctas, stream);
     else
       rc = launch_rowstats_tma<T, Acc, 0, false>(x, d, out_dtype, denom, stages, smem, ctas, stream);
+    if (rc != B200PHI_OK) return rc;
+  } else if (aligned && force_g == 0 && !no_async && sizeof(T) <= 4 && nvec > 128 * 2 && nvec <= 256 * 4) {
+    // 4..16 KiB rows: asynchronous-copy ring, 2 rows per CTA in flight behind the one in registers
+    int rc = (nvec <= 256 * 2) ? launch_rowstats_async<T, Acc, 2, 3>(x, d, out_dtype, denom, sms, stream)
+                               : launch_rowstats_async<T, Acc, 4, 3>(x, d, out_dtype, denom, sms, stream);
     if (rc != B200PHI_OK) return rc;
   } else if (aligned && nvec <= 256 * 4 && force_g == 256) {
     long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;

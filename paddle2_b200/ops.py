@@ -364,7 +364,7 @@ def broadcast_shape(xs, ys, axis=-1):
 
 
 def _elementwise(binary, ins, act=L.ACT_NONE, compound=0, scale_v=0.0, axis=-1,
-                 want_intermediate=False):
+                 want_intermediate=False, out_shape=None):
     _require_cuda(*ins)
     ins = [t.contiguous() for t in ins]
     dt = ins[0].dtype
@@ -372,7 +372,9 @@ def _elementwise(binary, ins, act=L.ACT_NONE, compound=0, scale_v=0.0, axis=-1,
         if t.dtype != dt:
             raise TypeError("b200phi elementwise: all inputs must share one dtype "
                             "(type promotion happens above the kernel in Paddle)")
-    if len(ins) == 1:
+    if out_shape is not None:
+        out_shape = list(out_shape)  # a unary op broadcast into a larger shape (reduce_grad.h:30-42)
+    elif len(ins) == 1:
         out_shape = list(ins[0].shape)
     else:
         out_shape = broadcast_shape(ins[0].shape, ins[1].shape, axis)
