@@ -28,6 +28,11 @@ _port = None
 _ref = None
 
 
+def _c(x, dtype=None):
+    """C-contiguous array that keeps 0-D arrays 0-D (np.ascontiguousarray would make them 1-D)."""
+    return np.require(np.asarray(x, dtype=dtype), requirements=["C"])
+
+
 def build():
     """Compile the port (and, where /root/reference exists, the reference build)."""
     import subprocess
@@ -56,13 +61,13 @@ def ref():
 
 def bf16_bits_to_f32(bits):
     """uint16 bf16 bit patterns -> float32 (exact)."""
-    bits = np.ascontiguousarray(bits, dtype=np.uint16)
+    bits = _c(bits, dtype=np.uint16)
     return (bits.astype(np.uint32) << 16).view(np.float32)
 
 
 def f32_to_bf16_bits(x):
     """float32 -> bf16 bit patterns, round-to-nearest-even."""
-    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    u = _c(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
     r = ((u >> 16) & 1) + 0x7FFF
     return ((u + r) >> 16).astype(np.uint16)
 
@@ -98,7 +103,7 @@ def sum_out_dtype(x_dtype, dtype=None):
 
 def reduce(op, x, axis=None, keepdim=False, out_dtype=None, impl="port"):
     """Reduce like phi::Reduce<CPUContext> does. impl: 'port' or 'ref'."""
-    x = np.ascontiguousarray(x)
+    x = _c(x)
     rank = x.ndim
     axes, reduce_all = _axes_list(axis, rank)
     logical = op in ("any", "all")
@@ -119,7 +124,7 @@ def reduce(op, x, axis=None, keepdim=False, out_dtype=None, impl="port"):
     xin = x.astype(out_dtype) if x.dtype != out_dtype else x
     if logical:
         xin = (x != 0)
-    xin = np.ascontiguousarray(xin)
+    xin = _c(xin)
     names = {np.dtype(np.float32): "float", np.dtype(np.float64): "double",
              np.dtype(np.int32): "int32", np.dtype(np.int64): "int64", np.dtype(np.bool_): "bool"}
     opname = {"amax": "max", "amin": "min"}.get(op, op)
@@ -134,7 +139,7 @@ def reduce(op, x, axis=None, keepdim=False, out_dtype=None, impl="port"):
 
 def argreduce(op, x, axis=None, keepdim=False, dtype=np.int64, impl="port"):
     """argmax/argmin like the CPU kernel (Eigen argmax(axis).cast<Tout>())."""
-    x = np.ascontiguousarray(x)
+    x = _c(x)
     rank = x.ndim
     flatten = axis is None
     ax = 0 if flatten else (axis + rank if axis < 0 else axis)
@@ -190,7 +195,7 @@ def broadcast_out_shape(xs, ys, axis=-1):
 def elementwise(binary, ins, act=None, compound=0, scale=0.0, axis=-1, want_intermediate=False,
                 impl="port"):
     """out = act(binary(x, y[, z])) (compound 0) or binary(x, act(y)) (compound 1)."""
-    ins = [np.ascontiguousarray(t) for t in ins]
+    ins = [_c(t) for t in ins]
     dt = ins[0].dtype
     if len(ins) == 1:
         out_shape, pads = list(ins[0].shape), [list(ins[0].shape)]
@@ -231,7 +236,7 @@ def elementwise(binary, ins, act=None, compound=0, scale=0.0, axis=-1, want_inte
 
 def rowstats_f32(x, unbiased=True):
     """(mean, var) over the last axis of a float32 array: paddle.var's composite in fp32."""
-    x = np.ascontiguousarray(x, dtype=np.float32)
+    x = _c(x, dtype=np.float32)
     cols = x.shape[-1]
     rows = x.size // cols
     mean = np.empty(x.shape[:-1], dtype=np.float32)
@@ -247,7 +252,7 @@ def rowstats_f32(x, unbiased=True):
 def var_composite(x, axis=None, unbiased=True, keepdim=False, impl="port"):
     """paddle.var as the reference composes it (stat.py:184-197), every step through
     the oracle's reduce / elementwise, in x's own dtype (fp32 / fp64)."""
-    x = np.ascontiguousarray(x)
+    x = _c(x)
     u = reduce("mean", x, axis, keepdim=True, impl=impl)
     d = elementwise("subtract", [x, u], impl=impl)
     sq = elementwise("multiply", [d, d], impl=impl)
@@ -261,7 +266,7 @@ def var_composite(x, axis=None, unbiased=True, keepdim=False, impl="port"):
 
 def sum_axis0_f32_mt(x, threads):
     """bench.py only: axis-0 sum of a [rows, cols] fp32 array on `threads` host threads."""
-    x = np.ascontiguousarray(x, dtype=np.float32)
+    x = _c(x, dtype=np.float32)
     rows, cols = x.shape
     out = np.empty(cols, dtype=np.float32)
     rc = port().phi_oracle_sum_axis0_f32_mt(C.c_int64(rows), C.c_int64(cols),

@@ -13,7 +13,7 @@ FP16_RTOL = 1e-2
 
 
 def to_dev(x):
-    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    return torch.from_numpy(np.array(x, order="C")).cuda()   # keeps 0-D arrays 0-D
 
 
 def to_np(t):
