@@ -108,6 +108,32 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Short rows (softmax / classifier widths: a few to ~128 elements): G = 1, 2, 4, 8 or 16 lanes
+// per row, 32/G rows per warp, scalar loads (consecutive rows are contiguous, so a warp still
+// reads one contiguous span and L1 serves the strided revisits), xor-shuffle combine inside the
+// G-lane group.  A full warp per 40-byte row would leave 22 of 32 lanes idle.
+template <typename T, typename Acc, typename Op, int G>
+__global__ void __launch_bounds__(kBlock)
+    row_small_kernel(const T* __restrict__ x, long long rows, int cols, Epilogue ep) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G;
+  constexpr int kRowsPerWarp = 32 / G;
+  // the loop condition is warp-uniform: every lane takes part in the shuffles
+  for (long long wbase = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kRowsPerWarp; wbase < rows;
+       wbase += static_cast<long long>(gridDim.x) * kWarps * kRowsPerWarp) {
+    const long long row = wbase + lane / G;
+    const bool valid = row < rows;
+    Acc acc = Op::identity();
+    if (valid) {
+      const T* __restrict__ r = x + row * cols;
+      for (int i = g; i < cols; i += G) acc = Op::combine(acc, load_as<Acc, Op>(r[i]));
+    }
+#pragma unroll
+    for (int m = G >> 1; m > 0; m >>= 1) acc = Op::combine(acc, shfl_xor(acc, m));
+    if (valid && g == 0) store_result(ep, row, acc);
+  }
+}
+
 // Few, very long rows (a full reduction is rows == 1).  grid = (splits, rows).
 // Each CTA reduces one 16-byte-aligned-friendly segment, parks its partial in
 // `partial[row*splits + s]`, takes a ticket; the CTA that draws the last ticket

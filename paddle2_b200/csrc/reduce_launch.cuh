@@ -49,6 +49,27 @@ int launch_reduce_typed(const ReduceArgs& a) {
       }
 #undef B200PHI_ROW
       break;
+    case kRowSmall: {
+      const int c = static_cast<int>(p.cols);
+      switch (p.G) {
+        case 1:
+          row_small_kernel<T, Acc, Op, 1><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          break;
+        case 2:
+          row_small_kernel<T, Acc, Op, 2><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          break;
+        case 4:
+          row_small_kernel<T, Acc, Op, 4><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          break;
+        case 8:
+          row_small_kernel<T, Acc, Op, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          break;
+        default:
+          row_small_kernel<T, Acc, Op, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          break;
+      }
+      break;
+    }
     case kRowSplit:
       row_split_kernel<T, Acc, Op, 8><<<dim3(p.grid_x, p.grid_y), kBlock, 0, a.stream>>>(
           x, p.rows, p.cols, p.seg, partial, tickets, ep);

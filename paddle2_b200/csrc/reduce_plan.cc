@@ -223,6 +223,12 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       }
     }
     if (kind != kRowSplit) kind = (G == 256) ? kRowBlock : kRowWarp;
+    // short rows: fewer than 32 lanes per row (about 8 elements per lane)
+    if (kind == kRowWarp && p->cols <= 128 && p->rows >= 64 && t.force_kind < 0) {
+      int g = pow2_ceil(ceil_div(p->cols, 8));
+      p->G = std::min(16, std::max(1, g));
+      kind = kRowSmall;
+    }
   }
   p->kind = kind;
 
@@ -230,7 +236,8 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   p->splits = (kind == kRowSplit) ? p->splits : 1;
   switch (kind) {
     case kRowWarp:
-    case kRowBlock: {
+    case kRowBlock:
+    case kRowSmall: {
       const long long ctas = ceil_div(p->rows, 256 / p->G);
       p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, 0x7fffffffLL));
       p->grid_y = 1;

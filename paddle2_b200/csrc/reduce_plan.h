@@ -25,7 +25,8 @@ enum ReduceKind {
   kRowBlock = 1,  // [rows, cols], one CTA (G = 256) per row
   kRowSplit = 2,  // [rows, cols], several CTAs per row + last-block finalise
   kCol = 3,       // [outer, R, inner]
-  kGeneric = 4    // anything else (also the reduce_num == 1 cast/copy)
+  kGeneric = 4,   // anything else (also the reduce_num == 1 cast/copy)
+  kRowSmall = 5   // [rows, cols] with short rows: G < 32 lanes per row
 };
 
 struct ReducePlan {

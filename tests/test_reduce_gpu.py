@@ -53,7 +53,11 @@ def test_sum_default_promotion(oracle):
 
 # every kernel kind and its boundaries: (shape, axis)
 KIND_SHAPES = [
-    ((3000, 10), [1]),          # warp-per-row, tiny rows (scalar path)
+    ((3000, 10), [1]),          # short rows: 2 lanes per row
+    ((100000, 3), [1]),         # short rows: 1 lane per row
+    ((5000, 100), [1]),         # short rows: 16 lanes per row
+    ((70, 128), [1]),           # short rows, partial last warp
+    ((40, 5), [1]),             # fewer than 64 rows: warp per row
     ((2400, 1027), [1]),        # warp-per-row, misaligned rows (head/tail peel)
     ((4096, 4096), [1]),        # warp-per-row, 16 KiB rows (C1 shape class)
     ((512, 20000), [1]),        # CTA-per-row
