@@ -240,6 +240,95 @@ typedef struct {
 B200PHI_API int b200phi_elementwise(const b200phi_elementwise_desc* d, void* stream);
 
 /* ------------------------------------------------------------------------ */
+/* Functor plug-ins on the broadcast engine          */
+/* ------------------------------------------------------------------------ */
+
+/* The other clients of funcs::BroadcastKernel / funcs::ElementwiseKernel: one launch,
+ * same broadcasting rules and the same [rows, inner] walk as b200phi_elementwise, but the
+ * output dtype may differ from the input dtype (compare / logical write BOOL) and the
+ * functor may take three operands.  in[] dtype is in_dtype for every operand. */
+typedef enum {
+  /* out BOOL; funcs/compare_functors.h:20-60 (kps/compare_kernel.cu).  EQUAL on floating
+   * point is the reference's tolerant form: |a-b| < 1e-8 unless either is inf (then ==)
+   * or NaN (then false). */
+  B200PHI_MAP_EQUAL = 0,
+  B200PHI_MAP_NOT_EQUAL = 1,
+  B200PHI_MAP_LESS_THAN = 2,
+  B200PHI_MAP_LESS_EQUAL = 3,
+  B200PHI_MAP_GREATER_THAN = 4,
+  B200PHI_MAP_GREATER_EQUAL = 5,
+  /* out BOOL, operands by truthiness; funcs/logical_functor.h:20-42 (kps/logical_kernel.cu) */
+  B200PHI_MAP_LOGICAL_AND = 16,
+  B200PHI_MAP_LOGICAL_OR = 17,
+  B200PHI_MAP_LOGICAL_XOR = 18,
+  B200PHI_MAP_LOGICAL_NOT = 19, /* arity 1 */
+  /* integer and bool dtypes, out = in dtype; funcs/bitwise_functors.h:20-48
+   * (kps/bitwise_kernel.cu); on BOOL they are the logical forms, NOT is !a */
+  B200PHI_MAP_BITWISE_AND = 32,
+  B200PHI_MAP_BITWISE_OR = 33,
+  B200PHI_MAP_BITWISE_XOR = 34,
+  B200PHI_MAP_BITWISE_NOT = 35, /* arity 1 */
+  /* three operands, out = in dtype: the functors the backward kernels feed to the
+   * broadcast engine (funcs/elementwise_functor.h:173-179, 478-531; gpu/reduce_kernel.cu:74-119) */
+  B200PHI_MAP_EQUAL_MUL = 48,  /* in2 * T(EQUAL(in0, in1))   max_grad / min_grad: (x, out, dout) */
+  B200PHI_MAP_MAX_GRAD_X = 49, /* in2 * T(in0 >  in1)        (x, y, dout) */
+  B200PHI_MAP_MAX_GRAD_Y = 50, /* in2 * T(in0 <= in1) */
+  B200PHI_MAP_MIN_GRAD_X = 51, /* in2 * T(in0 <  in1) */
+  B200PHI_MAP_MIN_GRAD_Y = 52, /* in2 * T(in0 >= in1) */
+  B200PHI_MAP_DIV_GRAD_Y = 53, /* -in0 * ((in1 / in2) / in2)  (dout, out, y) */
+  /* two operands, out = in dtype */
+  B200PHI_MAP_EQUAL_T = 56,    /* T(EQUAL(in0, in1)): the mask amax_grad / amin_grad count */
+  B200PHI_MAP_SUB_EXP = 57,    /* exp(in0 - in1): logsumexp's second pass (gpu/logsumexp_kernel.cu:64-67) */
+  /* one operand, floating point, computed in fp32 for 16-bit dtypes (MPType); the Cuda*Functor
+   * forms of funcs/activation_functor.h driven through ElementwiseKernel by
+   * gpu/activation_kernel.cu.  p0 / p1 are the functor's attributes. */
+  B200PHI_MAP_EXP = 64,
+  B200PHI_MAP_LOG = 65,
+  B200PHI_MAP_SQRT = 66,
+  B200PHI_MAP_RSQRT = 67,
+  B200PHI_MAP_SQUARE = 68,
+  B200PHI_MAP_RECIPROCAL = 69,
+  B200PHI_MAP_SIN = 70,
+  B200PHI_MAP_COS = 71,
+  B200PHI_MAP_TANH = 72,
+  B200PHI_MAP_SIGMOID = 73,
+  B200PHI_MAP_SILU = 74,
+  B200PHI_MAP_LEAKY_RELU = 75, /* p0 = alpha */
+  B200PHI_MAP_ELU = 76,        /* p0 = alpha */
+  B200PHI_MAP_SOFTPLUS = 77,   /* p0 = beta, p1 = threshold */
+  B200PHI_MAP_FLOOR = 78,
+  B200PHI_MAP_CEIL = 79,
+  B200PHI_MAP_EXPM1 = 80,
+  B200PHI_MAP_LOG1P = 81,
+  B200PHI_MAP_LOG2 = 82,
+  B200PHI_MAP_LOG10 = 83,
+  B200PHI_MAP_RELU6 = 84,        /* p0 = threshold */
+  B200PHI_MAP_HARD_SIGMOID = 85, /* p0 = slope, p1 = offset */
+  B200PHI_MAP_SWISH = 86,        /* p0 = beta */
+  B200PHI_MAP_MISH = 87,         /* p0 = threshold */
+  B200PHI_MAP_SOFTSIGN = 88,
+  B200PHI_MAP_LOG_SIGMOID = 89,
+  B200PHI_MAP_ABS = 90,          /* gpu/abs_kernel.cu; integer dtypes allowed */
+  B200PHI_MAP_POW_ABS = 91,      /* |x|^p0: p_norm's UnsignedPowFunctor (gpu/p_norm_kernel.cu:43-52) */
+  B200PHI_MAP_RELU = 92          /* CudaReluFunctor: x > 0 ? x : 0 */
+} b200phi_map_op;
+
+typedef struct {
+  int32_t op;        /* b200phi_map_op */
+  int32_t in_dtype;  /* every operand */
+  int32_t out_dtype; /* UNDEFINED => what the op implies; otherwise it must be that */
+  int32_t arity;     /* must be the op's operand count */
+  int32_t axis;      /* as in b200phi_elementwise_desc */
+  float p0, p1;      /* functor attributes */
+  b200phi_tensor_view in[B200PHI_MAX_ARITY];
+  int32_t out_rank;
+  int64_t out_dims[B200PHI_MAX_RANK];
+  void* out;
+} b200phi_map_desc;
+
+B200PHI_API int b200phi_map(const b200phi_map_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------ */
 /* Sharded reduction: local reduce + allreduce of the partial               */
 /* ------------------------------------------------------------------------ */
 

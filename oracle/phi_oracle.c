@@ -551,3 +551,177 @@ EXPORT int phi_oracle_sum_axis0_f32_mt(int64_t rows, int64_t cols, const float* 
   }
   return 0;
 }
+
+/* ---- functor plug-ins on the broadcast engine (b200phi_map) ------------------------------- */
+/* Op ids follow b200phi_map_op (include/b200phi.h).  Restated from
+ *   funcs/compare_functors.h:20-60   funcs/logical_functor.h:20-42   funcs/bitwise_functors.h:20-48
+ *   funcs/elementwise_functor.h:173-179 (DivGradY), :478-531 (Max/MinGrad X/Y)
+ *   gpu/reduce_kernel.cu:74-119 (min/max grad = Equal then Multiply)
+ *   funcs/activation_functor.h (one formula per functor, quoted at each case)
+ *   gpu/p_norm_kernel.cu:43-52 (UnsignedPowFunctor) */
+static int equal_f32(float a, float b) {
+  if (isinf(a) || isinf(b)) return a == b;
+  if (isnan(a) || isnan(b)) return 0;
+  return fabs((double)(a - b)) < 1e-8;
+}
+static int equal_f64(double a, double b) {
+  if (isinf((float)a) || isinf((float)b)) return a == b;
+  if (isnan((float)a) || isnan((float)b)) return 0;
+  return fabs(a - b) < 1e-8;
+}
+#define MAP_ACT(T, SUF, NAME)                                                                     \
+  static T NAME(int op, T x, float p0, float p1) {                                                \
+    const T one = 1, zero = 0;                                                                    \
+    switch (op) {                                                                                 \
+      case 64: return exp##SUF(x);                                                                \
+      case 65: return log##SUF(x);                                                                \
+      case 66: return sqrt##SUF(x);                                                               \
+      case 67: return one / sqrt##SUF(x);                                                         \
+      case 68: return x * x;                                                                      \
+      case 69: return one / x;                                                                    \
+      case 70: return sin##SUF(x);                                                                \
+      case 71: return cos##SUF(x);                                                                \
+      case 72: return tanh##SUF(x);                                                               \
+      case 73: return one / (one + exp##SUF(-x));                         /* sigmoid */            \
+      case 74: return x / (one + exp##SUF(-x));                           /* silu */               \
+      case 75: return x > zero ? x : (T)p0 * x;                           /* leaky_relu */         \
+      case 76: return x > zero ? x : (T)p0 * (exp##SUF(x) - one);         /* elu */                \
+      case 77: { T xb = x * (T)p0;                                        /* softplus */           \
+                 return xb > (T)p1 ? x : log##SUF(one + exp##SUF(xb)) / (T)p0; }                  \
+      case 78: return floor##SUF(x);                                                              \
+      case 79: return ceil##SUF(x);                                                               \
+      case 80: return expm1##SUF(x);                                                              \
+      case 81: return log##SUF(one + x);                                  /* log1p: log(1 + x) */  \
+      case 82: return log2##SUF(x);                                                               \
+      case 83: return log10##SUF(x);                                                              \
+      case 84: return x <= zero ? zero : (x < (T)p0 ? x : (T)p0);         /* relu6 */              \
+      case 85: { T t = x * (T)p0 + (T)p1; T hi = t > zero ? t : zero;     /* hard_sigmoid */       \
+                 return hi < one ? hi : one; }                                                    \
+      case 86: return x / (one + exp##SUF(-(T)p0 * x));                   /* swish */              \
+      case 87: { T sp = x > (T)p0 ? x : log##SUF(one + exp##SUF(x));      /* mish */               \
+                 return x * tanh##SUF(sp); }                                                      \
+      case 88: return x / (one + (x > -x ? x : -x));                      /* softsign */           \
+      case 89: { T t = x > zero ? zero : -x;                              /* log_sigmoid */        \
+                 return -t - log##SUF(exp##SUF(-t) + exp##SUF(-x - t)); }                         \
+      case 90: return x < zero ? -x : x;                                                          \
+      case 91: return pow##SUF(x < zero ? -x : x, (T)p0);                 /* |x|^p */              \
+      case 92: return x > zero ? x : zero;                                                        \
+      default: return x;                                                                          \
+    }                                                                                             \
+  }
+MAP_ACT(float, f, map_act_f32)
+MAP_ACT(double, , map_act_f64)
+
+static int map_op_arity(int op) {
+  if (op == 19 || op == 35 || op >= 64) return 1;
+  return (op >= 48 && op <= 53) ? 3 : 2;
+}
+
+/* in_dims[i*9 + k]: operand i padded to out_rank.  in_dtype: BOOL, UINT8, INT8, INT16, INT32,
+ * INT64, F32, F64.  out: BOOL bytes for op < 32, else in_dtype. */
+EXPORT int phi_oracle_map(int op, int in_dtype, float p0, float p1, int arity, int out_rank,
+                          const int64_t* out_dims, const int64_t* in_dims, const void* const* ins,
+                          void* out) {
+  if (arity != map_op_arity(op) || out_rank < 0 || out_rank > 9) return 1;
+  const int flt = is_float_dt(in_dtype);
+  if (op >= 32 && op <= 35 && flt) return 2;
+  if ((op == 57 || (op >= 64 && op != 90 && op != 92)) && !flt) return 2;
+  int64_t numel = 1;
+  for (int i = 0; i < out_rank; ++i) numel *= out_dims[i];
+  for (int i = 0; i < arity; ++i)
+    for (int k = 0; k < out_rank; ++k) {
+      const int64_t a = in_dims[i * 9 + k];
+      if (a != out_dims[k] && a != 1) return 1;
+    }
+  int64_t idx[9] = {0};
+  for (int64_t n = 0; n < numel; ++n) {
+    int64_t off[3] = {0, 0, 0};
+    for (int i = 0; i < arity; ++i)
+      for (int k = 0; k < out_rank; ++k) {
+        const int64_t e = in_dims[i * 9 + k];
+        off[i] = off[i] * e + (e == 1 ? 0 : idx[k]);
+      }
+    if (flt) {
+      /* operands in their own precision */
+      double a = load_as_double(ins[0], in_dtype, off[0]);
+      double b = arity > 1 ? load_as_double(ins[1], in_dtype, off[1]) : 0;
+      double c = arity > 2 ? load_as_double(ins[2], in_dtype, off[2]) : 0;
+      const int f32 = in_dtype == DT_F32;
+      const int eq = f32 ? equal_f32((float)a, (float)b) : equal_f64(a, b);
+      int bres = -1;
+      double r = 0;
+      switch (op) {
+        case 0: bres = eq; break;
+        case 1: bres = !eq; break;
+        case 2: bres = a < b; break;
+        case 3: bres = a <= b; break;
+        case 4: bres = a > b; break;
+        case 5: bres = a >= b; break;
+        case 16: bres = (a != 0) && (b != 0); break;
+        case 17: bres = (a != 0) || (b != 0); break;
+        case 18: bres = (a != 0) != (b != 0); break;
+        case 19: bres = !(a != 0); break;
+        case 48: r = f32 ? (double)((float)c * (float)eq) : c * (double)eq; break;
+        case 49: r = f32 ? (double)((float)c * (float)(a > b)) : c * (double)(a > b); break;
+        case 50: r = f32 ? (double)((float)c * (float)(a <= b)) : c * (double)(a <= b); break;
+        case 51: r = f32 ? (double)((float)c * (float)(a < b)) : c * (double)(a < b); break;
+        case 52: r = f32 ? (double)((float)c * (float)(a >= b)) : c * (double)(a >= b); break;
+        case 53:
+          if (f32) { float fa = (float)a, fb = (float)b, fc = (float)c; r = -fa * ((fb / fc) / fc); }
+          else r = -a * ((b / c) / c);
+          break;
+        case 56: r = eq; break;
+        case 57: r = f32 ? (double)expf((float)a - (float)b) : exp(a - b); break;
+        default:
+          r = f32 ? (double)map_act_f32(op, (float)a, p0, p1) : map_act_f64(op, a, p0, p1);
+          break;
+      }
+      if (bres >= 0) ((uint8_t*)out)[n] = (uint8_t)bres;
+      else if (f32) ((float*)out)[n] = (float)r;
+      else ((double*)out)[n] = r;
+    } else {
+      int64_t a = load_as_i64(ins[0], in_dtype, off[0]);
+      int64_t b = arity > 1 ? load_as_i64(ins[1], in_dtype, off[1]) : 0;
+      int64_t c = arity > 2 ? load_as_i64(ins[2], in_dtype, off[2]) : 0;
+      int bres = -1;
+      int64_t r = 0;
+      switch (op) {
+        case 0: bres = a == b; break;
+        case 1: bres = a != b; break;
+        case 2: bres = a < b; break;
+        case 3: bres = a <= b; break;
+        case 4: bres = a > b; break;
+        case 5: bres = a >= b; break;
+        case 16: bres = (a != 0) && (b != 0); break;
+        case 17: bres = (a != 0) || (b != 0); break;
+        case 18: bres = (a != 0) != (b != 0); break;
+        case 19: bres = !(a != 0); break;
+        case 32: r = a & b; break;
+        case 33: r = a | b; break;
+        case 34: r = a ^ b; break;
+        case 35: r = in_dtype == DT_BOOL ? !a : ~a; break;
+        case 48: r = c * (a == b); break;
+        case 49: r = c * (a > b); break;
+        case 50: r = c * (a <= b); break;
+        case 51: r = c * (a < b); break;
+        case 52: r = c * (a >= b); break;
+        case 53: r = c == 0 ? 0 : -a * ((b / c) / c); break;
+        case 56: r = a == b; break;
+        case 90: r = a < 0 ? -a : a; break;
+        case 92: r = a > 0 ? a : 0; break;
+        default: return 2;
+      }
+      if (bres >= 0) ((uint8_t*)out)[n] = (uint8_t)bres;
+      else switch (in_dtype) {
+        case DT_BOOL: ((uint8_t*)out)[n] = r != 0; break;
+        case DT_UINT8: ((uint8_t*)out)[n] = (uint8_t)r; break;
+        case DT_INT8: ((int8_t*)out)[n] = (int8_t)r; break;
+        case DT_INT16: ((int16_t*)out)[n] = (int16_t)r; break;
+        case DT_INT32: ((int32_t*)out)[n] = (int32_t)r; break;
+        default: ((int64_t*)out)[n] = r; break;
+      }
+    }
+    for (int k = out_rank - 1; k >= 0; --k) { if (++idx[k] < out_dims[k]) break; idx[k] = 0; }
+  }
+  return 0;
+}

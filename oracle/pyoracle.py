@@ -234,6 +234,74 @@ def elementwise(binary, ins, act=None, compound=0, scale=0.0, axis=-1, want_inte
     return (out, inter) if want_intermediate else out
 
 
+MAP_OPS = {
+    "equal": 0, "not_equal": 1, "less_than": 2, "less_equal": 3, "greater_than": 4,
+    "greater_equal": 5,
+    "logical_and": 16, "logical_or": 17, "logical_xor": 18, "logical_not": 19,
+    "bitwise_and": 32, "bitwise_or": 33, "bitwise_xor": 34, "bitwise_not": 35,
+    "equal_mul": 48, "max_grad_x": 49, "max_grad_y": 50, "min_grad_x": 51, "min_grad_y": 52,
+    "div_grad_y": 53, "equal_t": 56, "sub_exp": 57,
+    "exp": 64, "log": 65, "sqrt": 66, "rsqrt": 67, "square": 68, "reciprocal": 69, "sin": 70,
+    "cos": 71, "tanh": 72, "sigmoid": 73, "silu": 74, "leaky_relu": 75, "elu": 76,
+    "softplus": 77, "floor": 78, "ceil": 79, "expm1": 80, "log1p": 81, "log2": 82, "log10": 83,
+    "relu6": 84, "hard_sigmoid": 85, "swish": 86, "mish": 87, "softsign": 88,
+    "log_sigmoid": 89, "abs": 90, "pow_abs": 91, "relu": 92,
+}
+_REF_NAMES = {np.dtype(np.float32): "float", np.dtype(np.float64): "double",
+              np.dtype(np.int32): "int32", np.dtype(np.int64): "int64",
+              np.dtype(np.int16): "int16", np.dtype(np.int8): "int8",
+              np.dtype(np.uint8): "uint8", np.dtype(np.bool_): "bool"}
+
+
+def map_arity(op):
+    if op in (19, 35) or op >= 64:
+        return 1
+    return 3 if 48 <= op <= 53 else 2
+
+
+def map(name, ins, p0=0.0, p1=0.0, axis=-1, impl="port"):  # noqa: A001
+    """One functor plug-in of b200phi_map on numpy operands (compare / logical / bitwise /
+    backward functors / activations).  impl="ref" runs the reference's own functors."""
+    op = MAP_OPS[name]
+    ins = [_c(t) for t in ins]
+    if len(ins) != map_arity(op):
+        raise ValueError(f"{name} takes {map_arity(op)} operand(s)")
+    dt = ins[0].dtype
+    if len(ins) == 1:
+        out_shape, pads = list(ins[0].shape), [list(ins[0].shape)]
+    else:
+        out_shape, xp, yp = broadcast_out_shape(ins[0].shape, ins[1].shape, axis)
+        pads = [xp, yp]
+        for t in ins[2:]:
+            prev = out_shape
+            out_shape, _, zp = broadcast_out_shape(prev, t.shape, -1)
+            pads = [_padded_dims(p, len(out_shape), len(out_shape) - len(p)) for p in pads] + [zp]
+    R = len(out_shape)
+    out = np.empty(out_shape, dtype=np.bool_ if op < 32 else dt)
+    od = (C.c_int64 * 9)(*out_shape)
+    ptrs = (C.c_void_p * 3)(*[t.ctypes.data for t in ins] + [None] * (3 - len(ins)))
+    if impl == "port":
+        flat = (C.c_int64 * 27)()
+        for i, p in enumerate(pads):
+            for k, s in enumerate(p):
+                flat[i * 9 + k] = s
+        rc = port().phi_oracle_map(op, _NP2DT[dt], C.c_float(p0), C.c_float(p1), len(ins), R, od,
+                                   flat, ptrs, out.ctypes.data_as(C.c_void_p))
+    elif op >= 64:
+        fn = getattr(ref(), f"phi_ref_act_{_REF_NAMES[dt]}")
+        rc = fn(op, C.c_float(p0), C.c_float(p1), ins[0].ctypes.data_as(C.c_void_p),
+                out.ctypes.data_as(C.c_void_p), C.c_int64(ins[0].size))
+    else:
+        rows = [(C.c_int64 * 9)(*p) for p in pads]
+        rowptrs = (C.POINTER(C.c_int64) * 3)(*[C.cast(r, C.POINTER(C.c_int64)) for r in rows] +
+                                             [None] * (3 - len(rows)))
+        fn = getattr(ref(), f"phi_ref_map_{_REF_NAMES[dt]}")
+        rc = fn(op, R, od, rowptrs, ptrs, out.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise ValueError(f"oracle map status {rc} for {name} on {dt}")
+    return out
+
+
 def rowstats_f32(x, unbiased=True):
     """(mean, var) over the last axis of a float32 array: paddle.var's composite in fp32."""
     x = _c(x, dtype=np.float32)

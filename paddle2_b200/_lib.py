@@ -25,6 +25,32 @@ ARGMAX, ARGMIN = 0, 1
 ADD, SUBTRACT, MULTIPLY, DIVIDE, MAXIMUM, MINIMUM = range(6)
 ACT_NONE, ACT_RELU, ACT_SCALE, ACT_GELU, ACT_SIGMOID, ACT_TANH = range(6)
 
+# b200phi_map_op
+MAP_OPS = {
+    "equal": 0, "not_equal": 1, "less_than": 2, "less_equal": 3, "greater_than": 4,
+    "greater_equal": 5,
+    "logical_and": 16, "logical_or": 17, "logical_xor": 18, "logical_not": 19,
+    "bitwise_and": 32, "bitwise_or": 33, "bitwise_xor": 34, "bitwise_not": 35,
+    "equal_mul": 48, "max_grad_x": 49, "max_grad_y": 50, "min_grad_x": 51, "min_grad_y": 52,
+    "div_grad_y": 53, "equal_t": 56, "sub_exp": 57,
+    "exp": 64, "log": 65, "sqrt": 66, "rsqrt": 67, "square": 68, "reciprocal": 69, "sin": 70,
+    "cos": 71, "tanh": 72, "sigmoid": 73, "silu": 74, "leaky_relu": 75, "elu": 76,
+    "softplus": 77, "floor": 78, "ceil": 79, "expm1": 80, "log1p": 81, "log2": 82, "log10": 83,
+    "relu6": 84, "hard_sigmoid": 85, "swish": 86, "mish": 87, "softsign": 88,
+    "log_sigmoid": 89, "abs": 90, "pow_abs": 91, "relu": 92,
+}
+
+
+def map_arity(op):
+    """Operand count of a b200phi_map_op (include/b200phi.h)."""
+    if op in (19, 35) or op >= 64:
+        return 1
+    return 3 if 48 <= op <= 53 else 2
+
+
+def map_out_is_bool(op):
+    return op < 32
+
 STATUS_NAMES = {
     0: "OK",
     1: "INVALID_ARGUMENT",
@@ -105,6 +131,22 @@ class ElementwiseDesc(C.Structure):
     ]
 
 
+class MapDesc(C.Structure):
+    _fields_ = [
+        ("op", C.c_int32),
+        ("in_dtype", C.c_int32),
+        ("out_dtype", C.c_int32),
+        ("arity", C.c_int32),
+        ("axis", C.c_int32),
+        ("p0", C.c_float),
+        ("p1", C.c_float),
+        ("in_", TensorView * MAX_ARITY),
+        ("out_rank", C.c_int32),
+        ("out_dims", C.c_int64 * MAX_RANK),
+        ("out", C.c_void_p),
+    ]
+
+
 class P2PGroup(C.Structure):
     _fields_ = [
         ("nranks", C.c_int32),
@@ -131,6 +173,7 @@ EXPORTS = [
     "b200phi_argreduce",
     "b200phi_rowstats",
     "b200phi_elementwise",
+    "b200phi_map",
     "b200phi_comm_unique_id",
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
@@ -169,6 +212,8 @@ def lib():
     L.b200phi_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_void_p]
     L.b200phi_rowstats.argtypes = [C.POINTER(RowStatsDesc), C.c_void_p]
     L.b200phi_elementwise.argtypes = [C.POINTER(ElementwiseDesc), C.c_void_p]
+    L.b200phi_map.argtypes = [C.POINTER(MapDesc), C.c_void_p]
+    L.b200phi_map.restype = C.c_int
     L.b200phi_comm_unique_id.argtypes = [C.c_char_p]
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]

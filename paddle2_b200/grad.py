@@ -87,3 +87,93 @@ def multiply_grad(x, y, out_grad, axis=-1):
     y_axis = axis if len(y.shape) <= len(x.shape) else -1
     x_axis = axis if len(x.shape) < len(y.shape) else -1
     return _reduce_to(gx, x.shape, x_axis), _reduce_to(gy, y.shape, y_axis)
+
+
+def _minmax_grad(x, out, out_grad, axis):
+    o, _ = _keepdim_view(out, list(x.shape), axis)
+    g, _ = _keepdim_view(out_grad, list(x.shape), axis)
+    return ops._map("equal_mul", [x, o, g])
+
+
+def max_grad(x, out, out_grad, axis=None, keepdim=False):
+    """d/dx of paddle.max: out_grad * T(Equal(x, out)) with out and out_grad broadcast over the
+    reduced dims.  The reference runs BroadcastKernel(EqualFunctor) into a temporary, then
+    MultiplyKernel (ReduceMaxGradKernel, gpu/reduce_kernel.cu:144-187); here it is one ternary
+    launch, no temporary.  Every position that ties with the max receives the full gradient."""
+    return _minmax_grad(x, out, out_grad, axis)
+
+
+def min_grad(x, out, out_grad, axis=None, keepdim=False):
+    """ReduceMinGradKernel, gpu/reduce_kernel.cu:74-119: same form as max_grad."""
+    return _minmax_grad(x, out, out_grad, axis)
+
+
+def _aminmax_grad(x, out, out_grad, axis):
+    o, _ = _keepdim_view(out, list(x.shape), axis)
+    g, _ = _keepdim_view(out_grad, list(x.shape), axis)
+    rank = len(x.shape)
+    axes, reduce_all = ops._norm_axes(axis, rank)
+    dims = list(range(rank)) if reduce_all else list(axes)
+    mask = ops._map("equal_t", [x, o])
+    count = ops.sum(mask, axis=dims, keepdim=True, dtype=x.dtype) if dims else mask
+    share = ops.divide(g, count.reshape(list(g.shape)))
+    return ops._map("equal_mul", [x, o, share])
+
+
+def amax_grad(x, out, out_grad, axis=None, keepdim=False):
+    """d/dx of paddle.amax: the gradient is shared evenly between the positions that tie with
+    the max: (out_grad * eq) / sum(eq) (ReduceCudaAMaxAMinGrad,
+    gpu/reduce_amin_amax_common.h:28-107).  out_grad / sum(eq) is formed on the small tensor
+    first, which gives the same quotient at the ties and 0 elsewhere."""
+    return _aminmax_grad(x, out, out_grad, axis)
+
+
+def amin_grad(x, out, out_grad, axis=None, keepdim=False):
+    return _aminmax_grad(x, out, out_grad, axis)
+
+
+def _bcast_axis(a, b, axis):
+    return axis if len(b.shape) < len(a.shape) else -1
+
+
+def divide_grad(x, y, out, out_grad, axis=-1):
+    """dx = sum(dout / y), dy = sum(-dout * ((out / y) / y)) over the broadcast dims
+    (DivGradXFunctor / DivGradYFunctor, funcs/elementwise_functor.h:157-179;
+    ElementwiseDivGrad, gpu/elementwise_grad.h)."""
+    gx = ops.divide(out_grad, y, axis=_bcast_axis(out_grad, y, axis))
+    gy = ops._map("div_grad_y", [out_grad, out, _align(y, out.shape, x.shape, axis)])
+    y_axis = axis if len(y.shape) <= len(x.shape) else -1
+    x_axis = axis if len(x.shape) < len(y.shape) else -1
+    return _reduce_to(gx, x.shape, x_axis), _reduce_to(gy, y.shape, y_axis)
+
+
+def _align(t, out_shape, other_shape, axis):
+    """View the lower-rank operand with 1s so that numpy-style (right-aligned) broadcasting
+    places it where the legacy `axis` attribute would (common_shape.h:35-92)."""
+    r = len(out_shape)
+    if len(t.shape) == r:
+        return t
+    off = r - len(t.shape) if axis < 0 else axis
+    dims = [1] * off + list(t.shape) + [1] * (r - off - len(t.shape))
+    return t.contiguous().reshape(dims)
+
+
+def _select_grad(name_x, name_y, x, y, out_grad, axis):
+    shape = list(out_grad.shape)
+    xa, ya = _align(x, shape, y.shape, axis), _align(y, shape, x.shape, axis)
+    gx = ops._map(name_x, [xa, ya, out_grad])
+    gy = ops._map(name_y, [xa, ya, out_grad])
+    y_axis = axis if len(y.shape) <= len(x.shape) else -1
+    x_axis = axis if len(x.shape) < len(y.shape) else -1
+    return _reduce_to(gx, x.shape, x_axis), _reduce_to(gy, y.shape, y_axis)
+
+
+def maximum_grad(x, y, out_grad, axis=-1):
+    """dx = dout * (x > y), dy = dout * (x <= y), summed over the broadcast dims
+    (MaxGradXFunctor / MaxGradYFunctor, funcs/elementwise_functor.h:478-490)."""
+    return _select_grad("max_grad_x", "max_grad_y", x, y, out_grad, axis)
+
+
+def minimum_grad(x, y, out_grad, axis=-1):
+    """dx = dout * (x < y), dy = dout * (x >= y) (MinGradXFunctor / MinGradYFunctor, :513-524)."""
+    return _select_grad("min_grad_x", "min_grad_y", x, y, out_grad, axis)

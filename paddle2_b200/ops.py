@@ -344,7 +344,7 @@ def broadcast_shape(xs, ys, axis=-1):
     max_dim = len(xs) if len(xs) >= len(ys) else len(ys)
     if axis < -1 - max_dim or axis > max_dim:
         raise ValueError(f"The axis range must be [{-max_dim - 1}, {max_dim}], but axis is {axis}.")
-    ax = abs(len(xs) - len(ys)) + axis + 1 if axis < 0 else axis
+    ax = (len(xs) - len(ys) if len(xs) >= len(ys) else len(ys) - len(xs)) + axis + 1 if axis < 0 else axis
     if len(xs) >= len(ys):
         big, small, small_is_y = xs, ys, True
     else:
@@ -476,3 +476,132 @@ def fused_elemwise_add_activation(x, y, functor_list, axis=-1, scale=0.0,  # noq
     if "elementwise_add" not in functor_list:
         raise ValueError("fused_elemwise_add_activation needs elementwise_add in functor_list")
     return fused_elemwise_activation(x, y, functor_list, axis, scale, save_intermediate_out)
+
+
+# ------------------------------------------------------------------- functor plug-ins (map)
+
+
+def _map(name, ins, p0=0.0, p1=0.0, axis=-1, out_shape=None):
+    """One b200phi_map launch: compare / logical / bitwise / backward / activation functors on
+    the broadcast engine (kps/compare_kernel.cu, kps/logical_kernel.cu, kps/bitwise_kernel.cu,
+    gpu/activation_kernel.cu, gpu/elementwise_grad.h, gpu/reduce_kernel.cu:74-119)."""
+    op = L.MAP_OPS[name]
+    if len(ins) != L.map_arity(op):
+        raise ValueError(f"{name} takes {L.map_arity(op)} operand(s)")
+    _require_cuda(*ins)
+    ins = [t.contiguous() for t in ins]
+    dt = ins[0].dtype
+    for t in ins[1:]:
+        if t.dtype != dt:
+            raise TypeError("b200phi map: all operands must share one dtype")
+    if out_shape is not None:
+        out_shape = list(out_shape)
+    elif len(ins) == 1:
+        out_shape = list(ins[0].shape)
+    else:
+        out_shape = broadcast_shape(ins[0].shape, ins[1].shape, axis)
+        for t in ins[2:]:
+            out_shape = broadcast_shape(out_shape, t.shape, -1)
+    out = torch.empty(out_shape, dtype=torch.bool if L.map_out_is_bool(op) else dt,
+                      device=ins[0].device)
+    d = L.MapDesc()
+    d.op = op
+    d.in_dtype = _phi_dtype(dt)
+    d.out_dtype = L.UNDEFINED
+    d.arity = len(ins)
+    d.axis = axis
+    d.p0, d.p1 = float(p0), float(p1)
+    for i, t in enumerate(ins):
+        d.in_[i].rank = t.dim()
+        for j, s in enumerate(t.shape):
+            d.in_[i].dims[j] = s
+        d.in_[i].data = t.data_ptr()
+    d.out_rank = len(out_shape)
+    for j, s in enumerate(out_shape):
+        d.out_dims[j] = s
+    d.out = out.data_ptr()
+    if out.numel() > 0:
+        with torch.cuda.device(out.device):
+            L.check(L.lib().b200phi_map(C.byref(d), _stream_ptr(out)))
+    return out
+
+
+def _binary_map(name):
+    def f(x, y, axis=-1):
+        return _map(name, [x, y], axis=axis)
+    f.__name__ = name
+    f.__doc__ = f"paddle.{name}(x, y) through b200phi_map."
+    return f
+
+
+def _unary_map(name):
+    def f(x):
+        return _map(name, [x])
+    f.__name__ = name
+    f.__doc__ = f"paddle.{name}(x) through b200phi_map."
+    return f
+
+
+equal = _binary_map("equal")
+not_equal = _binary_map("not_equal")
+less_than = _binary_map("less_than")
+less_equal = _binary_map("less_equal")
+greater_than = _binary_map("greater_than")
+greater_equal = _binary_map("greater_equal")
+logical_and = _binary_map("logical_and")
+logical_or = _binary_map("logical_or")
+logical_xor = _binary_map("logical_xor")
+logical_not = _unary_map("logical_not")
+bitwise_and = _binary_map("bitwise_and")
+bitwise_or = _binary_map("bitwise_or")
+bitwise_xor = _binary_map("bitwise_xor")
+bitwise_not = _unary_map("bitwise_not")
+
+exp = _unary_map("exp")
+log = _unary_map("log")
+sqrt = _unary_map("sqrt")
+rsqrt = _unary_map("rsqrt")
+square = _unary_map("square")
+reciprocal = _unary_map("reciprocal")
+sin = _unary_map("sin")
+cos = _unary_map("cos")
+tanh = _unary_map("tanh")
+sigmoid = _unary_map("sigmoid")
+silu = _unary_map("silu")
+floor = _unary_map("floor")
+ceil = _unary_map("ceil")
+expm1 = _unary_map("expm1")
+log1p = _unary_map("log1p")
+log2 = _unary_map("log2")
+log10 = _unary_map("log10")
+softsign = _unary_map("softsign")
+log_sigmoid = _unary_map("log_sigmoid")
+abs = _unary_map("abs")  # noqa: A001 - paddle name
+
+
+def leaky_relu(x, negative_slope=0.01):
+    return _map("leaky_relu", [x], p0=negative_slope)
+
+
+def elu(x, alpha=1.0):
+    return _map("elu", [x], p0=alpha)
+
+
+def softplus(x, beta=1.0, threshold=20.0):
+    return _map("softplus", [x], p0=beta, p1=threshold)
+
+
+def relu6(x, threshold=6.0):
+    return _map("relu6", [x], p0=threshold)
+
+
+def hardsigmoid(x, slope=0.1666667, offset=0.5):
+    return _map("hard_sigmoid", [x], p0=slope, p1=offset)
+
+
+def swish(x, beta=1.0):
+    return _map("swish", [x], p0=beta)
+
+
+def mish(x, threshold=20.0):
+    return _map("mish", [x], p0=threshold)

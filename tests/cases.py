@@ -177,3 +177,70 @@ def make_input(rng, dtype, shape, kind="uniform"):
     if kind == "signed":
         return (rng.random(shape) * 2 - 1).astype(dt)
     return rng.random(shape).astype(dt)
+
+
+# ---- functor plug-ins (b200phi_map) ------------------------------------------------------
+# (x_shape, y_shape, source): the broadcast matrix of test_logical_op.py:45-60, which
+# test_bitwise_op.py:57-116 and test_compare_op.py:317-465 repeat in part
+MAP_SHAPES = [
+    ([2, 3, 4, 5], [4, 5], "test_logical_op.py:45"),
+    ([2, 3, 4, 5], [4, 1], "test_logical_op.py:46"),
+    ([2, 3, 4, 5], [1, 4, 1], "test_logical_op.py:47"),
+    ([2, 3, 4, 5], [3, 4, 1], "test_logical_op.py:48"),
+    ([2, 3, 1, 5], [3, 1, 1], "test_logical_op.py:49"),
+    ([4, 1], [2, 3, 4, 5], "test_logical_op.py:50"),
+    ([1, 4, 1], [2, 3, 4, 5], "test_logical_op.py:51"),
+    ([3, 4, 1], [2, 3, 4, 5], "test_logical_op.py:52"),
+    ([3, 1, 1], [2, 3, 1, 5], "test_logical_op.py:53"),
+    ([4, 5], [2, 3, 4, 5], "test_logical_op.py:54"),
+    ([1, 4, 5], [2, 3, 1, 5], "test_logical_op.py:55"),
+    ([10, 7], [10, 7], "test_logical_op.py:56"),
+    ([1, 1, 4, 5], [2, 3, 1, 5], "test_logical_op.py:57"),
+    ([], [], "test_logical_op.py:58"),
+    ([2, 3, 4, 5], [], "test_logical_op.py:59"),
+    ([], [2, 3, 4, 5], "test_logical_op.py:60"),
+    ([1, 2, 1, 3], [1, 2, 3], "test_compare_op.py:317-319"),
+    ([5], [3, 1], "test_compare_op.py:356-357"),
+    ([3, 1], [1], "test_compare_op.py:446-447"),
+]
+MAP_ERROR_SHAPES = [
+    ([2, 3, 4, 5], [3, 4], "test_logical_op.py:64"),
+    ([2, 3, 4, 5], [4, 3], "test_logical_op.py:65"),
+]
+COMPARE_OPS = ["equal", "not_equal", "less_than", "less_equal", "greater_than", "greater_equal"]
+LOGICAL_OPS = ["logical_and", "logical_or", "logical_xor"]
+BITWISE_OPS = ["bitwise_and", "bitwise_or", "bitwise_xor"]
+MAP_INT_DTYPES = ["bool", "uint8", "int8", "int16", "int32", "int64"]
+MAP_ALL_DTYPES = MAP_INT_DTYPES + ["float32", "float64"]
+
+# (name, p0, p1, domain): attributes are the defaults of python/paddle/nn/functional/activation.py
+# or the values test_activation_op.py sets; domain "pos" keeps log/sqrt arguments positive
+ACTIVATIONS = [
+    ("exp", 0, 0, "any"), ("log", 0, 0, "pos"), ("sqrt", 0, 0, "pos"), ("rsqrt", 0, 0, "pos"),
+    ("square", 0, 0, "any"), ("reciprocal", 0, 0, "pos"), ("sin", 0, 0, "any"),
+    ("cos", 0, 0, "any"), ("tanh", 0, 0, "any"), ("sigmoid", 0, 0, "any"), ("silu", 0, 0, "any"),
+    ("leaky_relu", 0.02, 0, "any"), ("elu", 1.0, 0, "any"), ("softplus", 2.0, 15.0, "any"),
+    ("floor", 0, 0, "any"), ("ceil", 0, 0, "any"), ("expm1", 0, 0, "any"), ("log1p", 0, 0, "pos"),
+    ("log2", 0, 0, "pos"), ("log10", 0, 0, "pos"), ("relu6", 6.0, 0, "wide"),
+    ("hard_sigmoid", 0.2, 0.5, "wide"), ("swish", 1.0, 0, "any"), ("mish", 20.0, 0, "any"),
+    ("softsign", 0, 0, "any"), ("log_sigmoid", 0, 0, "any"), ("abs", 0, 0, "any"),
+    ("pow_abs", 2.5, 0, "any"), ("relu", 0, 0, "any"),
+]
+ACT_SHAPES = [[11, 17], [], [10, 12], [3, 1000], [4097]]  # test_activation_op.py:96,548,5283 + vector paths
+
+
+def map_operand(rng, dtype, shape, domain="any"):
+    dt = np.dtype(dtype)
+    if dt == np.bool_:
+        return rng.integers(0, 2, size=shape).astype(np.bool_)
+    if dt == np.uint8:
+        return rng.integers(0, 100, size=shape).astype(dt)
+    if np.issubdtype(dt, np.integer):
+        return rng.integers(-100, 100, size=shape).astype(dt)  # test_bitwise_op.py:61-62
+    if domain == "pos":
+        return (rng.random(shape) * 3 + 0.1).astype(dt)
+    if domain == "wide":
+        return (rng.random(shape) * 16 - 8).astype(dt)
+    # few distinct values so that compare ops see ties
+    return (np.round(rng.random(shape) * 8 - 4, 1)).astype(dt) if domain == "ties" \
+        else (rng.random(shape) * 4 - 2).astype(dt)

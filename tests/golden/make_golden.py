@@ -73,6 +73,30 @@ def main():
     store["var_x"] = x
     store["var_y"] = O.var_composite(x, axis=-1, unbiased=True, impl="ref")
     store["mean_y"] = O.reduce("mean", x, [-1], impl="ref")
+    # functor plug-ins (b200phi_map): the reference's own compare / logical / bitwise / backward
+    # functors over the broadcast matrix of test_logical_op.py:45-60, its CPU activation functors
+    for i, (xs, ys, _src) in enumerate(cases.MAP_SHAPES):
+        for dt in ("float32", "int32", "bool"):
+            rng = np.random.default_rng(7000 + i)
+            x = cases.map_operand(rng, dt, xs, "ties")
+            y = cases.map_operand(rng, dt, ys, "ties")
+            store[f"map_{i}_{dt}_x"], store[f"map_{i}_{dt}_y"] = x, y
+            for name in cases.COMPARE_OPS + cases.LOGICAL_OPS:
+                store[f"map_{i}_{dt}_{name}"] = O.map(name, [x, y], impl="ref")
+            if dt != "float32":
+                for name in cases.BITWISE_OPS:
+                    store[f"map_{i}_{dt}_{name}"] = O.map(name, [x, y], impl="ref")
+    rng = np.random.default_rng(7100)
+    x = cases.map_operand(rng, "float32", [6, 5, 40], "ties")
+    y = cases.map_operand(rng, "float32", [6, 1, 40], "ties")
+    g = cases.map_operand(rng, "float32", [6, 5, 40])
+    store["mapgrad_x"], store["mapgrad_y"], store["mapgrad_g"] = x, y, g
+    for name in ("equal_mul", "max_grad_x", "max_grad_y", "min_grad_x", "min_grad_y", "div_grad_y"):
+        store[f"mapgrad_{name}"] = O.map(name, [x, y, g], impl="ref")
+    for name, p0, p1, dom in cases.ACTIVATIONS:
+        x = cases.map_operand(np.random.default_rng(7200), "float32", [11, 17], dom)
+        store[f"act_{name}_x"] = x
+        store[f"act_{name}_y"] = O.map(name, [x], p0, p1, impl="ref")
     np.savez_compressed(os.path.join(HERE, "phi_ref_golden.npz"), **store)
     print("wrote", len(store), "arrays")
 

@@ -175,3 +175,49 @@ def test_port_equals_reference_build_arg_and_elementwise(oracle):
             for b in ("add", "subtract", "multiply", "maximum", "minimum"):
                 assert np.array_equal(oracle.elementwise(b, [x, y], axis=ax),
                                       oracle.elementwise(b, [x, y], axis=ax, impl="ref"))
+
+
+# ---- functor plug-ins (b200phi_map) ---------------------------------------------------------
+@pytest.mark.parametrize("i", range(len(cases.MAP_SHAPES)))
+def test_map_port_matches_golden(oracle, golden, i):
+    """compare / logical / bitwise: the port is bit-identical to the reference's functors."""
+    _xs, _ys, src = cases.MAP_SHAPES[i]
+    for dt in ("float32", "int32", "bool"):
+        x, y = golden[f"map_{i}_{dt}_x"], golden[f"map_{i}_{dt}_y"]
+        names = cases.COMPARE_OPS + cases.LOGICAL_OPS + ([] if dt == "float32" else cases.BITWISE_OPS)
+        for name in names:
+            want = golden[f"map_{i}_{dt}_{name}"]
+            got = oracle.map(name, [x, y])
+            assert got.dtype == want.dtype and got.shape == want.shape, (src, name, dt)
+            assert np.array_equal(got, want), (src, name, dt)
+
+
+def test_map_grad_and_activation_port(oracle, golden):
+    x, y, g = golden["mapgrad_x"], golden["mapgrad_y"], golden["mapgrad_g"]
+    for name in ("equal_mul", "max_grad_x", "max_grad_y", "min_grad_x", "min_grad_y", "div_grad_y"):
+        assert np.array_equal(oracle.map(name, [x, y, g]), golden[f"mapgrad_{name}"]), name
+    for name, p0, p1, _dom in cases.ACTIVATIONS:
+        got = oracle.map(name, [golden[f"act_{name}_x"]], p0, p1)
+        # libm here, Eigen's packet math in the reference: a few ulp apart on transcendentals
+        np.testing.assert_allclose(got, golden[f"act_{name}_y"], rtol=2e-6, atol=1e-7, err_msg=name)
+
+
+def test_map_equal_is_the_tolerant_form(oracle):
+    """EqualFunctor on floats (compare_functors.h:34-48): |a-b| < 1e-8, inf by ==, NaN never."""
+    a = np.array([1e-9, 0.0, np.inf, np.inf, np.nan, 1.0, 1.0], dtype=np.float32)
+    b = np.array([2e-9, 9e-9, np.inf, -np.inf, np.nan, 1.0, np.nextafter(np.float32(1), np.float32(2))],
+                 dtype=np.float32)
+    assert oracle.map("equal", [a, b]).tolist() == [True, True, True, False, False, True, False]
+    assert oracle.map("not_equal", [a, b]).tolist() == [False, False, False, True, True, False, True]
+    if oracle.have_ref():
+        assert np.array_equal(oracle.map("equal", [a, b], impl="ref"), oracle.map("equal", [a, b]))
+
+
+def test_map_errors(oracle):
+    for xs, ys, _src in cases.MAP_ERROR_SHAPES:
+        with pytest.raises(ValueError):
+            oracle.map("logical_and", [np.zeros(xs, np.bool_), np.zeros(ys, np.bool_)])
+    with pytest.raises(ValueError):
+        oracle.map("bitwise_and", [np.zeros(3, np.float32), np.zeros(3, np.float32)])
+    with pytest.raises(ValueError):
+        oracle.map("exp", [np.zeros(3, np.int32)])

@@ -129,6 +129,64 @@ int main(int argc, char** argv) {
     printf("   row sums of the same tensor (axis 1)       %8.2f us  %7.1f GB/s\n", ms * 1e3, (8589934592.0 + R * 4) / ms / 1e6);
     cudaFree(x); cudaFree(out); cudaFree(w); cudaFree(out2);
   }
+  if (strstr(only, "M")) {  // functor plug-ins (b200phi_map); not part of the default run
+    const size_t n = (size_t)256 * 64 * 112 * 112;
+    float* x = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
+    float* y = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
+    float* out; CK(cudaMalloc(&out, n * 4));
+    auto view = [](b200phi_tensor_view* v, const void* data, int rank, long long a, long long b, long long c, long long e) {
+      v->rank = rank; v->dims[0] = a; v->dims[1] = b; v->dims[2] = c; v->dims[3] = e; v->data = data;
+    };
+    b200phi_map_desc m = {};
+    m.in_dtype = B200PHI_FLOAT32; m.axis = -1; m.out_rank = 4;
+    m.out_dims[0] = 256; m.out_dims[1] = 64; m.out_dims[2] = 112; m.out_dims[3] = 112; m.out = out;
+    view(&m.in[0], x, 4, 256, 64, 112, 112);
+    // unary
+    struct { int op; const char* name; } un[] = {{B200PHI_MAP_RELU, "relu"}, {B200PHI_MAP_SILU, "silu"},
+                                                  {B200PHI_MAP_EXP, "exp"}, {B200PHI_MAP_TANH, "tanh"}};
+    for (auto& u : un) {
+      m.op = u.op; m.arity = 1;
+      float ms = time_it([&] { OK(b200phi_map(&m, 0)); }, 20);
+      printf("M1 %-6s fp32 [256,64,112,112]              %8.2f us  %7.1f GB/s\n", u.name, ms * 1e3, 2.0 * n * 4 / ms / 1e6);
+    }
+    // compare, same shape and channel broadcast: 2 (or 1) fp32 reads, 1 byte written per element
+    m.op = B200PHI_MAP_LESS_THAN; m.arity = 2;
+    view(&m.in[1], y, 4, 256, 64, 112, 112);
+    float ms = time_it([&] { OK(b200phi_map(&m, 0)); }, 20);
+    printf("M2 less_than fp32 same shape -> bool          %8.2f us  %7.1f GB/s\n", ms * 1e3, 9.0 * n / ms / 1e6);
+    view(&m.in[1], y, 3, 64, 1, 1, 0);
+    ms = time_it([&] { OK(b200phi_map(&m, 0)); }, 20);
+    printf("M2 less_than fp32 [..]<[64,1,1] -> bool       %8.2f us  %7.1f GB/s\n", ms * 1e3, 5.0 * n / ms / 1e6);
+    m.op = B200PHI_MAP_EQUAL;
+    ms = time_it([&] { OK(b200phi_map(&m, 0)); }, 20);
+    printf("M2 equal fp32 [..]==[64,1,1] -> bool          %8.2f us  %7.1f GB/s\n", ms * 1e3, 5.0 * n / ms / 1e6);
+    // max_grad over the last axis of [8192, 32000] bf16 / fp32: x streamed, out and dout per row
+    for (int pass = 0; pass < 2; ++pass) {
+      const int dt = pass ? B200PHI_FLOAT32 : B200PHI_BFLOAT16;
+      const size_t es = pass ? 4 : 2;
+      const size_t nn = (size_t)8192 * (pass ? 16000 : 32000);
+      b200phi_map_desc g = {};
+      g.op = B200PHI_MAP_EQUAL_MUL; g.in_dtype = dt; g.arity = 3; g.axis = -1; g.out_rank = 2;
+      g.out_dims[0] = 8192; g.out_dims[1] = (long long)(nn / 8192); g.out = out;
+      view(&g.in[0], x, 2, 8192, (long long)(nn / 8192), 0, 0);
+      view(&g.in[1], y, 2, 8192, 1, 0, 0);
+      view(&g.in[2], y + 65536, 2, 8192, 1, 0, 0);
+      ms = time_it([&] { OK(b200phi_map(&g, 0)); }, 20);
+      printf("M3 max_grad %s [8192,%zu] axis -1          %8.2f us  %7.1f GB/s\n", pass ? "fp32" : "bf16", nn / 8192,
+             ms * 1e3, 2.0 * nn * es / ms / 1e6);
+    }
+    {  // max_grad over axis 0 of [32768, 4096] fp32: all three operands streamed along the row
+      b200phi_map_desc g = {};
+      g.op = B200PHI_MAP_EQUAL_MUL; g.in_dtype = B200PHI_FLOAT32; g.arity = 3; g.axis = -1; g.out_rank = 2;
+      g.out_dims[0] = 32768; g.out_dims[1] = 4096; g.out = out;
+      view(&g.in[0], x, 2, 32768, 4096, 0, 0);
+      view(&g.in[1], y, 1, 4096, 0, 0, 0);
+      view(&g.in[2], y + 4096, 1, 4096, 0, 0, 0);
+      ms = time_it([&] { OK(b200phi_map(&g, 0)); }, 20);
+      printf("M3 max_grad fp32 [32768,4096] axis 0          %8.2f us  %7.1f GB/s\n", ms * 1e3, 2.0 * 32768 * 4096 * 4 / ms / 1e6);
+    }
+    cudaFree(x); cudaFree(y); cudaFree(out);
+  }
   printf("done\n");
   return 0;
 }
