@@ -1,0 +1,307 @@
+// Drop-in adapter, second translation unit: the phi kernels that are functor plug-ins on the
+// broadcast engine, implemented on b200phi_map / b200phi_reduce and
+// registered under the reference's kernel names and signatures.  Compiled inside a Paddle build
+// in place of
+//   paddle/phi/kernels/kps/compare_kernel.cu            (less_than ... not_equal)
+//   paddle/phi/kernels/kps/logical_kernel.cu            (logical_and/or/xor/not)
+//   paddle/phi/kernels/kps/bitwise_kernel.cu            (bitwise_and/or/xor/not)
+//   paddle/phi/kernels/gpu/activation_kernel.cu         (the activations listed below)
+//   paddle/phi/kernels/gpu/reduce_kernel.cu:74-187      (ReduceMax/MinGradKernel)
+//   paddle/phi/kernels/gpu/elementwise_grad_kernel.cu   (Maximum/MinimumGradKernel)
+// Compile-checked against the reference headers (adapter/check_compile.sh).
+#include <vector>
+
+#include "b200phi.h"
+#include "paddle/phi/backends/gpu/gpu_context.h"
+#include "paddle/phi/common/int_array.h"
+#include "paddle/phi/core/dense_tensor.h"
+#include "paddle/phi/core/kernel_registry.h"
+
+namespace phi {
+namespace b200 {
+
+inline void CheckMap(int status) {
+  if (status != B200PHI_OK) {
+    PADDLE_THROW(common::errors::InvalidArgument("%s", b200phi_last_error()));
+  }
+}
+
+inline void View(const DenseTensor& t, b200phi_tensor_view* v) {
+  v->rank = t.dims().size();
+  for (int i = 0; i < v->rank; ++i) v->dims[i] = t.dims()[i];
+  v->data = t.data();
+}
+
+// x's dims with the reduced ones set to 1: how ReduceGrad views out and out_grad
+// (gpu/reduce_kernel.cu:84-101)
+inline void KeepDimView(const DenseTensor& t, const DenseTensor& x, const std::vector<int64_t>& dims,
+                        bool reduce_all, b200phi_tensor_view* v) {
+  const int rank = x.dims().size();
+  v->rank = rank;
+  for (int i = 0; i < rank; ++i) v->dims[i] = x.dims()[i];
+  if (reduce_all || dims.empty() || static_cast<int>(dims.size()) == rank) {
+    for (int i = 0; i < rank; ++i) v->dims[i] = 1;
+  } else {
+    for (int64_t a : dims) v->dims[a < 0 ? a + rank : a] = 1;
+  }
+  v->data = t.data();
+}
+
+// One b200phi_map launch; out's dims come from InferMeta, its dtype from the registration
+// (BOOL for compare / logical) or from x.
+template <typename Context>
+void Map(const Context& dev_ctx, int op, const std::vector<const DenseTensor*>& ins, int axis,
+         float p0, float p1, DenseTensor* out) {
+  const bool to_bool = op < B200PHI_MAP_BITWISE_AND;
+  dev_ctx.Alloc(out, to_bool ? DataType::BOOL : ins[0]->dtype());
+  b200phi_map_desc d = {};
+  d.op = op;
+  d.in_dtype = static_cast<int>(ins[0]->dtype());
+  d.out_dtype = B200PHI_UNDEFINED;
+  d.arity = static_cast<int>(ins.size());
+  d.axis = axis;
+  d.p0 = p0;
+  d.p1 = p1;
+  for (size_t i = 0; i < ins.size(); ++i) View(*ins[i], &d.in[i]);
+  d.out_rank = out->dims().size();
+  for (int i = 0; i < d.out_rank; ++i) d.out_dims[i] = out->dims()[i];
+  d.out = out->data();
+  CheckMap(b200phi_map(&d, dev_ctx.stream()));
+}
+
+template <typename Context>
+void MinMaxGrad(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                const DenseTensor& out_grad, const std::vector<int64_t>& dims, bool reduce_all,
+                DenseTensor* x_grad) {
+  dev_ctx.Alloc(x_grad, x.dtype());
+  b200phi_map_desc d = {};
+  d.op = B200PHI_MAP_EQUAL_MUL;  // dout * T(Equal(x, out)): one launch, no equal_out temporary
+  d.in_dtype = static_cast<int>(x.dtype());
+  d.arity = 3;
+  d.axis = -1;
+  View(x, &d.in[0]);
+  KeepDimView(out, x, dims, reduce_all, &d.in[1]);
+  KeepDimView(out_grad, x, dims, reduce_all, &d.in[2]);
+  d.out_rank = x.dims().size();
+  for (int i = 0; i < d.out_rank; ++i) d.out_dims[i] = x.dims()[i];
+  d.out = x_grad->data();
+  CheckMap(b200phi_map(&d, dev_ctx.stream()));
+}
+
+// dx (or dy) of maximum / minimum: the ternary functor, then -- when the operand was
+// broadcast -- a sum over the broadcast dims (funcs::GetReduceDim; gpu/elementwise_grad.h:173+).
+template <typename Context>
+void SelectGrad(const Context& dev_ctx, int op, const DenseTensor& x, const DenseTensor& y,
+                const DenseTensor& dout, const DenseTensor& like, DenseTensor* grad) {
+  if (grad == nullptr) return;
+  if (like.dims() == dout.dims()) {
+    grad->Resize(dout.dims());
+    Map(dev_ctx, op, {&x, &y, &dout}, -1, 0.f, 0.f, grad);
+    return;
+  }
+  DenseTensor full;
+  full.Resize(dout.dims());
+  Map(dev_ctx, op, {&x, &y, &dout}, -1, 0.f, 0.f, &full);
+  // dims of dout that `like` does not have, or has as 1
+  const int r = dout.dims().size(), lr = like.dims().size(), off = r - lr;
+  b200phi_reduce_desc d = {};
+  d.op = B200PHI_SUM;
+  d.in_dtype = d.out_dtype = static_cast<int>(full.dtype());
+  d.rank = r;
+  for (int i = 0; i < r; ++i) {
+    d.dims[i] = dout.dims()[i];
+    if (i < off || (like.dims()[i - off] == 1 && dout.dims()[i] != 1)) d.axes[d.naxes++] = i;
+  }
+  dev_ctx.Alloc(grad, like.dtype());
+  d.x = full.data();
+  d.out = grad->data();
+  DenseTensor scratch;
+  const size_t ws = b200phi_reduce_workspace(&d);
+  if (ws > 0) {
+    scratch.Resize({static_cast<int64_t>(ws)});
+    d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+    d.workspace_bytes = ws;
+  }
+  CheckMap(b200phi_reduce(&d, dev_ctx.stream()));
+}
+
+}  // namespace b200
+
+// ---- compare: compare_kernel.h:20-33 -----------------------------------------------------------
+#define B200_DEFINE_COMPARE(Name, OpId)                                                   \
+  template <typename T, typename Context>                                                 \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,   \
+                    DenseTensor* out) {                                                   \
+    b200::Map(dev_ctx, OpId, {&x, &y}, -1, 0.f, 0.f, out);                                \
+  }
+B200_DEFINE_COMPARE(LessThan, B200PHI_MAP_LESS_THAN)
+B200_DEFINE_COMPARE(LessEqual, B200PHI_MAP_LESS_EQUAL)
+B200_DEFINE_COMPARE(GreaterThan, B200PHI_MAP_GREATER_THAN)
+B200_DEFINE_COMPARE(GreaterEqual, B200PHI_MAP_GREATER_EQUAL)
+B200_DEFINE_COMPARE(Equal, B200PHI_MAP_EQUAL)
+B200_DEFINE_COMPARE(NotEqual, B200PHI_MAP_NOT_EQUAL)
+// ---- logical: logical_kernel.h:21-36 -------------------------------------------------------------
+B200_DEFINE_COMPARE(LogicalAnd, B200PHI_MAP_LOGICAL_AND)
+B200_DEFINE_COMPARE(LogicalOr, B200PHI_MAP_LOGICAL_OR)
+B200_DEFINE_COMPARE(LogicalXor, B200PHI_MAP_LOGICAL_XOR)
+// ---- bitwise: bitwise_kernel.h:21-42 -------------------------------------------------------------
+B200_DEFINE_COMPARE(BitwiseAnd, B200PHI_MAP_BITWISE_AND)
+B200_DEFINE_COMPARE(BitwiseOr, B200PHI_MAP_BITWISE_OR)
+B200_DEFINE_COMPARE(BitwiseXor, B200PHI_MAP_BITWISE_XOR)
+
+template <typename T, typename Context>
+void LogicalNotKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::Map(dev_ctx, B200PHI_MAP_LOGICAL_NOT, {&x}, -1, 0.f, 0.f, out);
+}
+template <typename T, typename Context>
+void BitwiseNotKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::Map(dev_ctx, B200PHI_MAP_BITWISE_NOT, {&x}, -1, 0.f, 0.f, out);
+}
+
+// ---- activations: activation_kernel.h:23-110 -----------------------------------------------------
+#define B200_DEFINE_ACT(Name, OpId)                                                       \
+  template <typename T, typename Context>                                                 \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {     \
+    b200::Map(dev_ctx, OpId, {&x}, -1, 0.f, 0.f, out);                                    \
+  }
+#define B200_DEFINE_ACT_1(Name, OpId)                                                     \
+  template <typename T, typename Context>                                                 \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, float a, DenseTensor* out) { \
+    b200::Map(dev_ctx, OpId, {&x}, -1, a, 0.f, out);                                      \
+  }
+#define B200_DEFINE_ACT_2(Name, OpId)                                                     \
+  template <typename T, typename Context>                                                 \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, float a, float b,       \
+                    DenseTensor* out) {                                                   \
+    b200::Map(dev_ctx, OpId, {&x}, -1, a, b, out);                                        \
+  }
+B200_DEFINE_ACT(Exp, B200PHI_MAP_EXP)
+B200_DEFINE_ACT(Log, B200PHI_MAP_LOG)
+B200_DEFINE_ACT(Sqrt, B200PHI_MAP_SQRT)
+B200_DEFINE_ACT(Rsqrt, B200PHI_MAP_RSQRT)
+B200_DEFINE_ACT(Square, B200PHI_MAP_SQUARE)
+B200_DEFINE_ACT(Reciprocal, B200PHI_MAP_RECIPROCAL)
+B200_DEFINE_ACT(Sin, B200PHI_MAP_SIN)
+B200_DEFINE_ACT(Cos, B200PHI_MAP_COS)
+B200_DEFINE_ACT(Tanh, B200PHI_MAP_TANH)
+B200_DEFINE_ACT(Sigmoid, B200PHI_MAP_SIGMOID)
+B200_DEFINE_ACT(Silu, B200PHI_MAP_SILU)
+B200_DEFINE_ACT(Floor, B200PHI_MAP_FLOOR)
+B200_DEFINE_ACT(Ceil, B200PHI_MAP_CEIL)
+B200_DEFINE_ACT(Expm1, B200PHI_MAP_EXPM1)
+B200_DEFINE_ACT(Log1p, B200PHI_MAP_LOG1P)
+B200_DEFINE_ACT(Log2, B200PHI_MAP_LOG2)
+B200_DEFINE_ACT(Log10, B200PHI_MAP_LOG10)
+B200_DEFINE_ACT(Softsign, B200PHI_MAP_SOFTSIGN)
+B200_DEFINE_ACT(LogSigmoid, B200PHI_MAP_LOG_SIGMOID)
+B200_DEFINE_ACT(Relu, B200PHI_MAP_RELU)
+B200_DEFINE_ACT_1(LeakyRelu, B200PHI_MAP_LEAKY_RELU)
+B200_DEFINE_ACT_1(Elu, B200PHI_MAP_ELU)
+B200_DEFINE_ACT_1(Mish, B200PHI_MAP_MISH)
+B200_DEFINE_ACT_2(Softplus, B200PHI_MAP_SOFTPLUS)
+B200_DEFINE_ACT_2(HardSigmoid, B200PHI_MAP_HARD_SIGMOID)
+
+template <typename T, typename Context>
+void Relu6Kernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::Map(dev_ctx, B200PHI_MAP_RELU6, {&x}, -1, 6.0f, 0.f, out);  // activation_kernel.cu: threshold 6
+}
+template <typename T, typename Context>
+void SwishKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::Map(dev_ctx, B200PHI_MAP_SWISH, {&x}, -1, 1.0f, 0.f, out);  // beta 1
+}
+
+// ---- backward: reduce_max_grad_kernel.h:22-30, elementwise_grad_kernel.h:38-52 -----------------
+template <typename T, typename Context>
+void ReduceMaxGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                         const DenseTensor& out_grad, const IntArray& dims, bool keep_dim,
+                         bool reduce_all, DenseTensor* x_grad) {
+  b200::MinMaxGrad(dev_ctx, x, out, out_grad, dims.GetData(), reduce_all, x_grad);
+}
+template <typename T, typename Context>
+void ReduceMinGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                         const DenseTensor& out_grad, const IntArray& dims, bool keep_dim,
+                         bool reduce_all, DenseTensor* x_grad) {
+  b200::MinMaxGrad(dev_ctx, x, out, out_grad, dims.GetData(), reduce_all, x_grad);
+}
+template <typename T, typename Context>
+void MaximumGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                       const DenseTensor& dout, DenseTensor* dx, DenseTensor* dy) {
+  b200::SelectGrad(dev_ctx, B200PHI_MAP_MAX_GRAD_X, x, y, dout, x, dx);
+  b200::SelectGrad(dev_ctx, B200PHI_MAP_MAX_GRAD_Y, x, y, dout, y, dy);
+}
+template <typename T, typename Context>
+void MinimumGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                       const DenseTensor& dout, DenseTensor* dx, DenseTensor* dy) {
+  b200::SelectGrad(dev_ctx, B200PHI_MAP_MIN_GRAD_X, x, y, dout, x, dx);
+  b200::SelectGrad(dev_ctx, B200PHI_MAP_MIN_GRAD_Y, x, y, dout, y, dy);
+}
+
+}  // namespace phi
+
+using float16 = phi::dtype::float16;
+using bfloat16 = phi::dtype::bfloat16;
+
+// dtype lists: kps/compare_kernel.cu:146-165, kps/logical_kernel.cu, kps/bitwise_kernel.cu,
+// gpu/activation_kernel.cu:205-330, minus complex (not implemented by this library)
+#define B200_REGISTER_COMPARE(name, func)                                                        \
+  PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, phi::func##Kernel, bool, int, uint8_t, int8_t,       \
+                     int16_t, int64_t, float, double, float16, bfloat16) {                       \
+    kernel->OutputAt(0).SetDataType(phi::DataType::BOOL);                                        \
+  }
+B200_REGISTER_COMPARE(less_than, LessThan)
+B200_REGISTER_COMPARE(less_equal, LessEqual)
+B200_REGISTER_COMPARE(greater_than, GreaterThan)
+B200_REGISTER_COMPARE(greater_equal, GreaterEqual)
+B200_REGISTER_COMPARE(equal, Equal)
+B200_REGISTER_COMPARE(not_equal, NotEqual)
+B200_REGISTER_COMPARE(logical_and, LogicalAnd)
+B200_REGISTER_COMPARE(logical_or, LogicalOr)
+B200_REGISTER_COMPARE(logical_xor, LogicalXor)
+B200_REGISTER_COMPARE(logical_not, LogicalNot)
+
+#define B200_REGISTER_BITWISE(name, func)                                                        \
+  PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, phi::func##Kernel, bool, uint8_t, int8_t, int16_t,   \
+                     int, int64_t) {}
+B200_REGISTER_BITWISE(bitwise_and, BitwiseAnd)
+B200_REGISTER_BITWISE(bitwise_or, BitwiseOr)
+B200_REGISTER_BITWISE(bitwise_xor, BitwiseXor)
+B200_REGISTER_BITWISE(bitwise_not, BitwiseNot)
+
+#define B200_REGISTER_ACT(name, func) \
+  PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, phi::func##Kernel, float, double, float16, bfloat16) {}
+B200_REGISTER_ACT(exp, Exp)
+B200_REGISTER_ACT(log, Log)
+B200_REGISTER_ACT(sqrt, Sqrt)
+B200_REGISTER_ACT(rsqrt, Rsqrt)
+B200_REGISTER_ACT(square, Square)
+B200_REGISTER_ACT(reciprocal, Reciprocal)
+B200_REGISTER_ACT(sin, Sin)
+B200_REGISTER_ACT(cos, Cos)
+B200_REGISTER_ACT(tanh, Tanh)
+B200_REGISTER_ACT(sigmoid, Sigmoid)
+B200_REGISTER_ACT(silu, Silu)
+B200_REGISTER_ACT(floor, Floor)
+B200_REGISTER_ACT(ceil, Ceil)
+B200_REGISTER_ACT(expm1, Expm1)
+B200_REGISTER_ACT(log1p, Log1p)
+B200_REGISTER_ACT(log2, Log2)
+B200_REGISTER_ACT(log10, Log10)
+B200_REGISTER_ACT(softsign, Softsign)
+B200_REGISTER_ACT(logsigmoid, LogSigmoid)
+B200_REGISTER_ACT(relu, Relu)
+B200_REGISTER_ACT(leaky_relu, LeakyRelu)
+B200_REGISTER_ACT(elu, Elu)
+B200_REGISTER_ACT(mish, Mish)
+B200_REGISTER_ACT(softplus, Softplus)
+B200_REGISTER_ACT(hardsigmoid, HardSigmoid)
+B200_REGISTER_ACT(relu6, Relu6)
+B200_REGISTER_ACT(swish, Swish)
+
+PD_REGISTER_KERNEL(max_grad, GPU, ALL_LAYOUT, phi::ReduceMaxGradKernel, float, double, int, int64_t,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(min_grad, GPU, ALL_LAYOUT, phi::ReduceMinGradKernel, float, double, int, int64_t,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(maximum_grad, GPU, ALL_LAYOUT, phi::MaximumGradKernel, float, double, int,
+                   int64_t, float16, bfloat16) {}
+PD_REGISTER_KERNEL(minimum_grad, GPU, ALL_LAYOUT, phi::MinimumGradKernel, float, double, int,
+                   int64_t, float16, bfloat16) {}

@@ -299,91 +299,6 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
-// One sweep over the registers for 16-bit inputs: with K = mean of the row's first vector,
-// accumulate S = sum(x-K) and Q = sum((x-K)^2) together, combine both in ONE round and finish
-//   mean = K + S/n,   var = (Q - S*S/n) / denom.
-// One unpack per element instead of two and one barrier per row instead of two.  The shift
-// keeps the subtraction well conditioned (Q/(Q - S*S/n) = 1 + n(K-mean)^2/sum((x-mean)^2), a
-// small number when K is a local mean); results are fp32-accurate to ~1e-5 on ordinary data,
-// far inside the 1e-2 that bf16/fp16 parity asks for.  fp32/fp64 inputs keep the exact
-// two-pass kernel above.
-template <typename T, int G, int NV>
-__global__ void __launch_bounds__(kBlock)
-    rowstats_onepass_kernel(const T* __restrict__ x, long long rows, long long cols, float denom,
-                            float cols_acc, void* mean_out, void* var_out, int out_dtype) {
-  constexpr int VE = VecOf<T>::kElems;
-  constexpr int kW = G / 32;
-  __shared__ float sm_s[2][kWarps], sm_q[2][kWarps];
-  const int g = threadIdx.x % G, grp = threadIdx.x / G;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long rows_per_cta = kBlock / G;
-  const long long nvec = cols / VE;
-  int parity = 0;
-  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + grp; row < rows;
-       row += static_cast<long long>(gridDim.x) * rows_per_cta) {
-    const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + row * cols);
-    V16 buf[NV];
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) buf[k] = ldg_stream16(vp + v);
-    }
-    float K;
-    {
-      float first[VE];
-      unpack_vec<T, float>(*reinterpret_cast<const V16*>(vp), first);  // same address for the group
-      float t = 0.f;
-#pragma unroll
-      for (int e = 0; e < VE; ++e) t += first[e];
-      K = t * (1.0f / VE);
-    }
-    float s[2] = {0.f, 0.f}, q[2] = {0.f, 0.f};
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) {
-        float val[VE];
-        unpack_vec<T, float>(buf[k], val);
-#pragma unroll
-        for (int e = 0; e < VE; ++e) {
-          const float dlt = val[e] - K;
-          s[e & 1] += dlt;
-          q[e & 1] += dlt * dlt;
-        }
-      }
-    }
-    float S = s[0] + s[1], Q = q[0] + q[1];
-#pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
-      S += __shfl_xor_sync(0xffffffffu, S, m);
-      Q += __shfl_xor_sync(0xffffffffu, Q, m);
-    }
-    if constexpr (G > 32) {
-      if (lane == 0) {
-        sm_s[parity][warp] = S;
-        sm_q[parity][warp] = Q;
-      }
-      group_barrier<G>();
-      if (g == 0) {
-        S = sm_s[parity][grp * kW];
-        Q = sm_q[parity][grp * kW];
-#pragma unroll
-        for (int w = 1; w < kW; ++w) {
-          S += sm_s[parity][grp * kW + w];
-          Q += sm_q[parity][grp * kW + w];
-        }
-      }
-      parity ^= 1;
-    }
-    if (g == 0) {
-      const float mean = K + S / cols_acc;
-      const float ss = fmaxf(Q - S * S / cols_acc, 0.f);
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
-    }
-  }
-}
-
 // Persistent CTAs with a ring of whole rows in shared memory, filled by one producer thread
 // with bulk asynchronous copies (TMA) while the 256 consumer threads take mean and
 // sum((x-mean)^2) of earlier rows out of the ring: the next rows are always in flight, so the
@@ -585,16 +500,6 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   } else if (aligned && nvec <= 128 * 8) {
     long long ctas = (d->rows + 1) / 2;
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
-    if constexpr (sizeof(T) == 2) {
-      static const bool onepass = getenv("B200PHI_ROWSTATS_TWOPASS") == nullptr;
-      if (onepass) {
-        rowstats_onepass_kernel<T, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-            x, d->rows, n, static_cast<float>(denom), static_cast<float>(n), d->mean, d->var, out_dtype);
-        cudaError_t e1 = cudaGetLastError();
-        if (e1 != cudaSuccess) return cuda_status(e1);
-        return B200PHI_OK;
-      }
-    }
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else {

@@ -17,10 +17,17 @@ def test_adapter_compiles_against_reference_headers(tmp_path):
     out = tmp_path / "phi_b200_kernels.o"
     env = dict(os.environ, OUT=str(out))
     r = subprocess.run(["sh", os.path.join(ROOT, "adapter", "check_compile.sh")], env=env,
-                       capture_output=True, text=True, timeout=600)
+                       capture_output=True, text=True, timeout=1200)
     assert r.returncode == 0, r.stderr[-2000:]
     assert out.exists() and out.stat().st_size > 0
     # the object must carry the registrars of the reference kernel names it replaces
     syms = subprocess.run(["nm", "-C", str(out)], capture_output=True, text=True).stdout
     for name in ("sum_raw", "mean_raw", "max_raw", "argmax", "add_raw", "fused_elemwise_add_activation"):
         assert f"__reg_phi_kernel_{name}_GPU_ALL_LAYOUT" in syms or name in syms, name
+    # second TU: the functor plug-ins (compare / logical / bitwise / activations / backward)
+    out2 = tmp_path / "phi_b200_kernels_functors.o"
+    assert out2.exists() and out2.stat().st_size > 0
+    syms2 = subprocess.run(["nm", "-C", str(out2)], capture_output=True, text=True).stdout
+    for name in ("less_than", "equal", "logical_and", "bitwise_xor", "silu", "leaky_relu", "max_grad",
+                 "maximum_grad"):
+        assert f"__reg_phi_kernel_{name}_GPU_ALL_LAYOUT" in syms2 or name in syms2, name

@@ -45,3 +45,29 @@ def test_var_other_axes_uses_the_composite(oracle):
         np.testing.assert_allclose(got, want, rtol=1e-4)
     x64 = x.astype(np.float64)
     np.testing.assert_allclose(G.to_np(pb.var(G.to_dev(x64), axis=-1)), np.var(x64, axis=-1, ddof=1), rtol=1e-10)
+
+
+@pytest.mark.parametrize("tdt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("cols", [8192, 4096, 3000])
+def test_16bit_rows_poorly_conditioned(tdt, cols):
+    """Rows whose first vector sits far from the rest, rows with a large mean and a small spread,
+    constant rows: the cases a one-sweep (shifted sum of squares) formulation loses digits on.
+    The kernel is the exact two-sweep form held in registers, so they must be as accurate as any
+    other row; fp32 outputs, float64 numpy as the judge.  (One-sweep variants were measured and
+    dropped: see DESIGN.md, row statistics.)"""
+    rng = np.random.default_rng(cols)
+    rows = 512
+    x = rng.standard_normal((rows, cols)).astype(np.float32)
+    x[0::4, :8] = 1000.0                    # every element of the first vector is a 1000-sigma outlier
+    x[1::4, :8] = -300.0
+    x[2::4, :] = x[2::4, :] * 0.25 + 200.0  # large mean, small spread (K is near the mean: stays one-sweep)
+    x[3::4, 3] = 500.0                      # a single outlier inside the first vector
+    xt = torch.from_numpy(x).to(tdt)
+    x64 = xt.double().numpy()
+    m, v = pb.row_mean_var(xt.cuda(), out_dtype="float32")
+    np.testing.assert_allclose(G.to_np(m), x64.mean(axis=1), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(G.to_np(v), x64.var(axis=1, ddof=1), rtol=1e-4)
+    # constant rows: variance exactly 0, mean exact
+    c = torch.full((64, cols), 3.5, dtype=tdt)
+    m, v = pb.row_mean_var(c.cuda(), out_dtype="float32")
+    assert torch.all(v == 0) and torch.all(m == 3.5)
