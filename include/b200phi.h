@@ -79,7 +79,16 @@ typedef enum {
   B200PHI_ANY = 5,  /* kps::LogicalOrFunctor on (x != 0), out BOOL  */
   B200PHI_ALL = 6,  /* kps::LogicalAndFunctor on (x != 0), out BOOL */
   B200PHI_AMAX = 7, /* same arithmetic as MAX (differs only in grad) */
-  B200PHI_AMIN = 8
+  B200PHI_AMIN = 8,
+  /* Reductions over a transformed element: the TransformOp slot of funcs::ReduceKernel as
+   * p_norm and squared_l2_norm fill it (gpu/p_norm_kernel.cu:26-52,76-95,
+   * gpu/squared_l2_norm_kernel.cu:24-34).  Floating-point dtypes, out dtype = in dtype. */
+  B200PHI_SUM_ABS = 9,        /* sum |x|            p_norm porder 1 */
+  B200PHI_SUM_SQUARE = 10,    /* sum x*x            squared_l2_norm */
+  B200PHI_L2_NORM = 11,       /* sqrt(sum x*x)      p_norm porder 2 */
+  B200PHI_MAX_ABS = 12,       /* max |x|            p_norm porder +inf */
+  B200PHI_MIN_ABS = 13,       /* min |x|            p_norm porder -inf */
+  B200PHI_COUNT_NONZERO = 14  /* sum (x != 0)       p_norm porder 0 (NonzeroFunctor) */
 } b200phi_reduce_op;
 
 /* One reduction call.  Stands in for the argument list of
@@ -178,6 +187,22 @@ typedef struct {
 } b200phi_rowstats_desc;
 
 B200PHI_API int b200phi_rowstats(const b200phi_rowstats_desc* d, void* stream);
+
+/* Row logsumexp: out[r] = log(sum_j exp(x[r][j])) over the last (merged trailing) axes, computed
+ * as max + log(sum exp(x - max)) in one read of x.  Stands in for phi::LogsumexpKernel
+ * (paddle/phi/kernels/gpu/logsumexp_kernel.cu:81-165) when the reduced axes are the trailing
+ * ones (or all of them): the caller flattens x to [rows, cols].  For other axis sets the host
+ * composes max -> exp(x - max) -> sum -> log + max from b200phi_reduce / b200phi_map, which is
+ * the reference's own fallback (:49-78).  fp16/bf16 accumulate in fp32. */
+typedef struct {
+  int32_t dtype; /* FLOAT32, FLOAT64, BFLOAT16, FLOAT16; out has the same dtype */
+  int64_t rows;
+  int64_t cols;
+  const void* x;
+  void* out;     /* [rows] */
+} b200phi_logsumexp_desc;
+
+B200PHI_API int b200phi_logsumexp(const b200phi_logsumexp_desc* d, void* stream);
 
 /* ------------------------------------------------------------------------ */
 /* n-ary broadcast / elementwise engine with fused unary epilogue           */

@@ -302,6 +302,84 @@ def map(name, ins, p0=0.0, p1=0.0, axis=-1, impl="port"):  # noqa: A001
     return out
 
 
+def _pre_n_post(shape, axis, asvector):
+    """GetDims of cpu/p_norm_kernel.cc:25-44."""
+    if asvector or len(shape) == 0:
+        return 1, int(np.prod(shape, dtype=np.int64)), 1
+    axis = axis + len(shape) if axis < 0 else axis
+    pre = int(np.prod(shape[:axis], dtype=np.int64))
+    post = int(np.prod(shape[axis + 1:], dtype=np.int64))
+    return pre, int(shape[axis]), post
+
+
+def p_norm(x, porder=2.0, axis=-1, keepdim=False, asvector=False, impl="port"):
+    """PNormKernel on the CPU (cpu/p_norm_kernel.cc:46-99) over the (pre, n, post) view."""
+    x = _c(x)
+    pre, n, post = _pre_n_post(list(x.shape), axis, asvector)
+    if asvector or x.ndim == 0:
+        out_shape = [1] * x.ndim if keepdim else []
+    else:
+        a = axis + x.ndim if axis < 0 else axis
+        out_shape = [1 if i == a else s for i, s in enumerate(x.shape)] if keepdim else \
+            [s for i, s in enumerate(x.shape) if i != a]
+    if impl == "ref":
+        out = np.empty((pre, post), dtype=x.dtype)
+        fn = getattr(ref(), f"phi_ref_pnorm_{_REF_NAMES[x.dtype]}")
+        rc = fn(x.ctypes.data_as(C.c_void_p), pre, n, post, C.c_float(porder),
+                out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise ValueError(f"oracle p_norm status {rc}")
+        return out.reshape(out_shape)
+    v = x.reshape(pre, n, post)
+    if porder == 0:
+        out = reduce("sum", (v != 0).astype(x.dtype), [1])
+    elif porder == float("inf"):
+        out = reduce("max", np.abs(v), [1])
+    elif porder == float("-inf"):
+        out = reduce("min", np.abs(v), [1])
+    else:
+        s = reduce("sum", map("pow_abs", [v], p0=porder), [1])
+        out = map("pow_abs", [s], p0=1.0 / porder)
+    return np.asarray(out).reshape(out_shape)
+
+
+def squared_l2_norm(x, impl="port"):
+    """input.square().sum() (funcs/squared_l2_norm.h:40-46): a full reduction of the squares."""
+    x = _c(x)
+    if impl == "ref":
+        out = np.empty([1], dtype=x.dtype)
+        fn = getattr(ref(), f"phi_ref_squared_l2_norm_{_REF_NAMES[x.dtype]}")
+        rc = fn(x.ctypes.data_as(C.c_void_p), C.c_int64(x.size), out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise ValueError(f"oracle squared_l2_norm status {rc}")
+        return out
+    return np.asarray(reduce("sum", (x * x).reshape(-1), None)).reshape([1])
+
+
+def logsumexp(x, axis=None, keepdim=False, impl="port"):
+    """LogsumexpFunctor (impl/logsumexp_kernel_impl.h:33-61): max + log(sum(exp(x - max)))."""
+    x = _c(x)
+    axes, reduce_all = _axes_list(axis, x.ndim)
+    out_shape = _out_shape(list(x.shape), axes, reduce_all, keepdim)
+    if impl == "ref":
+        red = list(range(x.ndim)) if reduce_all else sorted(axes)
+        if red != list(range(red[0], red[0] + len(red))) if red else False:
+            raise ValueError("ref logsumexp: adjacent reduced axes only")
+        pre = int(np.prod(x.shape[:red[0]], dtype=np.int64)) if red else 1
+        n = int(np.prod([x.shape[a] for a in red], dtype=np.int64)) if red else 1
+        post = x.size // max(pre * n, 1)
+        out = np.empty((pre, post), dtype=x.dtype)
+        fn = getattr(ref(), f"phi_ref_logsumexp_{_REF_NAMES[x.dtype]}")
+        rc = fn(x.ctypes.data_as(C.c_void_p), pre, n, post, out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise ValueError(f"oracle logsumexp status {rc}")
+        return out.reshape(out_shape)
+    ax = None if reduce_all else axes
+    m = reduce("max", x, ax, keepdim=True)
+    s = reduce("sum", map("sub_exp", [x, np.asarray(m)]), ax, keepdim=True)
+    return (map("log", [np.asarray(s)]) + np.asarray(m)).astype(x.dtype).reshape(out_shape)
+
+
 def rowstats_f32(x, unbiased=True):
     """(mean, var) over the last axis of a float32 array: paddle.var's composite in fp32."""
     x = _c(x, dtype=np.float32)

@@ -21,6 +21,7 @@ UNDEFINED, BOOL, UINT8, INT8, INT16, INT32, INT64 = 0, 1, 2, 3, 5, 7, 9
 FLOAT32, FLOAT64, FLOAT16, BFLOAT16 = 10, 11, 15, 16
 
 SUM, MEAN, MAX, MIN, PROD, ANY, ALL, AMAX, AMIN = range(9)
+SUM_ABS, SUM_SQUARE, L2_NORM, MAX_ABS, MIN_ABS, COUNT_NONZERO = range(9, 15)
 ARGMAX, ARGMIN = 0, 1
 ADD, SUBTRACT, MULTIPLY, DIVIDE, MAXIMUM, MINIMUM = range(6)
 ACT_NONE, ACT_RELU, ACT_SCALE, ACT_GELU, ACT_SIGMOID, ACT_TANH = range(6)
@@ -131,6 +132,16 @@ class ElementwiseDesc(C.Structure):
     ]
 
 
+class LogsumexpDesc(C.Structure):
+    _fields_ = [
+        ("dtype", C.c_int32),
+        ("rows", C.c_int64),
+        ("cols", C.c_int64),
+        ("x", C.c_void_p),
+        ("out", C.c_void_p),
+    ]
+
+
 class MapDesc(C.Structure):
     _fields_ = [
         ("op", C.c_int32),
@@ -174,6 +185,7 @@ EXPORTS = [
     "b200phi_rowstats",
     "b200phi_elementwise",
     "b200phi_map",
+    "b200phi_logsumexp",
     "b200phi_comm_unique_id",
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
@@ -214,6 +226,8 @@ def lib():
     L.b200phi_elementwise.argtypes = [C.POINTER(ElementwiseDesc), C.c_void_p]
     L.b200phi_map.argtypes = [C.POINTER(MapDesc), C.c_void_p]
     L.b200phi_map.restype = C.c_int
+    L.b200phi_logsumexp.argtypes = [C.POINTER(LogsumexpDesc), C.c_void_p]
+    L.b200phi_logsumexp.restype = C.c_int
     L.b200phi_comm_unique_id.argtypes = [C.c_char_p]
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]

@@ -75,8 +75,12 @@ int run_reduce(const b200phi_reduce_desc* d, cudaStream_t stream) {
     case B200PHI_AMIN:
       rc = launch_minmax(a);
       break;
-    default:
+    case B200PHI_ANY:
+    case B200PHI_ALL:
       rc = launch_logical(a);
+      break;
+    default:
+      rc = launch_norm(a);
       break;
   }
   if (rc == B200PHI_UNSUPPORTED) return set_error(rc, "dtype/op combination not built");

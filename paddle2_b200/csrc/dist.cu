@@ -99,6 +99,10 @@ __global__ void __launch_bounds__(kBlock) divide_inplace_f16(__half* p, long lon
 int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, void* comm,
                        cudaStream_t stream) {
   if (!comm) return run_reduce(d, stream);
+  if (d && d->op > B200PHI_AMIN)
+    return set_error(B200PHI_UNSUPPORTED,
+                     "sharded reduce: the norm reductions are not built (reduce locally, then "
+                     "allreduce the partial with SUM / MAX / MIN)");
   NcclApi* a = nccl_api();
   if (!a->ok) return set_error(B200PHI_NCCL_ERROR, a->why);
 

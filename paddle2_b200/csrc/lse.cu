@@ -1,0 +1,229 @@
+// Row logsumexp: out[r] = max_r + log(sum_j exp(x[r][j] - max_r)), one read of x.
+// Replaces the reference's GPU routes (gpu/logsumexp_kernel.cu): a transpose +
+// DispatchLogsumexpWarp when the reduced extent is <= 1024, else the five-launch fallback
+// max -> subtract -> exp-sum -> log -> add (:49-78), i.e. three reads and one write of x.
+//
+// One pass: every thread keeps a running (m, s) with s = sum exp(x - m) over what it has seen.
+// A 16-byte vector is folded with its own max first: when that beats m (rare once the thread
+// has seen a few vectors) s is rescaled by exp(m - vmax), then the VE terms cost one FFMA + one
+// MUFU.EX2 + one FADD each.  Pairs merge as M = max(m_a, m_b), S = s_a e^(m_a-M) + s_b e^(m_b-M):
+// max-combine then sum-combine over the group with the usual shuffles.
+// G threads per row (32..256, ~64 B of the row per thread per step), 8 loads in flight.
+#include <string>
+
+#include "../../include/b200phi.h"
+#include "prim.cuh"
+
+namespace b200phi {
+
+int set_error(int code, const std::string& msg);
+int cuda_status(cudaError_t e);
+
+template <typename A>
+struct LseMath;
+template <>
+struct LseMath<float> {
+  static __device__ __forceinline__ float neg_inf() { return -INFINITY; }
+  // exp(a - b) for finite b, 0 when a = -inf
+  static __device__ __forceinline__ float exp_diff(float a, float b) {
+    return exp2f((a - b) * 1.4426950408889634f);
+  }
+  static __device__ __forceinline__ float log_(float v) { return logf(v); }
+};
+template <>
+struct LseMath<double> {
+  static __device__ __forceinline__ double neg_inf() { return -INFINITY; }
+  static __device__ __forceinline__ double exp_diff(double a, double b) { return exp(a - b); }
+  static __device__ __forceinline__ double log_(double v) { return log(v); }
+};
+
+// max of one 16-byte vector; 16-bit floats use the packed max on the raw pairs
+template <typename T, typename A>
+struct LseVecMax {
+  static __device__ __forceinline__ A of(const V16& raw, const A* val) {
+    A v = val[0];
+#pragma unroll
+    for (int e = 1; e < VecOf<T>::kElems; ++e) v = val[e] > v ? val[e] : v;
+    return v;
+  }
+};
+template <>
+struct LseVecMax<__nv_bfloat16, float> {
+  static __device__ __forceinline__ float of(const V16& raw, const float*) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+    __nv_bfloat162 a = __hmax2(__hmax2(h[0], h[1]), __hmax2(h[2], h[3]));
+    return fmaxf(__low2float(a), __high2float(a));
+  }
+};
+template <>
+struct LseVecMax<__half, float> {
+  static __device__ __forceinline__ float of(const V16& raw, const float*) {
+    const __half2* h = reinterpret_cast<const __half2*>(&raw);
+    __half2 a = __hmax2(__hmax2(h[0], h[1]), __hmax2(h[2], h[3]));
+    return fmaxf(__low2float(a), __high2float(a));
+  }
+};
+
+__device__ __forceinline__ float ex2_approx(float v) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+
+template <typename T, typename A>
+__device__ __forceinline__ void lse_fold_vec(const V16& raw, A& m, A& s) {
+  constexpr int VE = VecOf<T>::kElems;
+  A val[VE];
+  unpack_vec<T, A>(raw, val);
+  const A vmax = LseVecMax<T, A>::of(raw, val);
+  if (vmax > m) {
+    s = s * LseMath<A>::exp_diff(m, vmax);  // m = -inf the first time: s = 0 stays 0
+    m = vmax;
+  }
+  if (m > LseMath<A>::neg_inf()) {  // a vector of -inf only: nothing to add (and -inf - -inf is NaN)
+    if constexpr (sizeof(A) == 4) {
+      // exp(x - m) = 2^(x log2e - m log2e): one FFMA, one MUFU.EX2, one FADD per element
+      const float mb = m * 1.4426950408889634f;
+      float t[2] = {0.f, 0.f};
+#pragma unroll
+      for (int e = 0; e < VE; ++e) t[e & 1] += ex2_approx(fmaf(val[e], 1.4426950408889634f, -mb));
+      s += t[0] + t[1];
+    } else {
+#pragma unroll
+      for (int e = 0; e < VE; ++e) s += LseMath<A>::exp_diff(val[e], m);
+    }
+  }
+}
+
+template <typename T, typename A>
+__device__ __forceinline__ void lse_fold_scalar(T v, A& m, A& s) {
+  const A a = Cvt<A, T>::to(v);
+  if (a > m) {
+    s = s * LseMath<A>::exp_diff(m, a);
+    m = a;
+  }
+  if (m > LseMath<A>::neg_inf()) s += LseMath<A>::exp_diff(a, m);
+}
+
+__device__ __forceinline__ void lse_put(void* p, int dtype, long long i, double v) {
+  switch (dtype) {
+    case B200PHI_FLOAT32:
+      reinterpret_cast<float*>(p)[i] = static_cast<float>(v);
+      break;
+    case B200PHI_FLOAT64:
+      reinterpret_cast<double*>(p)[i] = v;
+      break;
+    case B200PHI_FLOAT16:
+      reinterpret_cast<__half*>(p)[i] = __float2half_rn(static_cast<float>(v));
+      break;
+    default:
+      reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(static_cast<float>(v));
+      break;
+  }
+}
+
+// kAligned: every row starts 16-byte aligned and cols is a multiple of VE.
+template <typename T, typename A, int G, int U, bool kAligned>
+__global__ void __launch_bounds__(kBlock)
+    lse_rows_kernel(const T* __restrict__ x, long long rows, long long cols, void* out, int out_dtype) {
+  constexpr int VE = VecOf<T>::kElems;
+  __shared__ A smem[2 * kWarps];
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
+  const long long rows_per_cta = kBlock / G;
+  // a group's threads share the row, and groups meet on their own named barrier: no padding
+  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + grp; row < rows;
+       row += static_cast<long long>(gridDim.x) * rows_per_cta) {
+    A m = LseMath<A>::neg_inf(), s = A(0);
+    {
+      const T* __restrict__ r = x + row * cols;
+      if constexpr (kAligned) {
+        const V16* __restrict__ vp = reinterpret_cast<const V16*>(r);
+        const long long nvec = cols / VE;
+        for (long long vb = g; vb < nvec; vb += static_cast<long long>(U) * G) {
+          V16 buf[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const long long v = vb + static_cast<long long>(u) * G;
+            if (v < nvec) buf[u] = ldg_stream16(vp + v);
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const long long v = vb + static_cast<long long>(u) * G;
+            if (v < nvec) lse_fold_vec<T, A>(buf[u], m, s);
+          }
+        }
+      } else {
+        for (long long i = g; i < cols; i += G) lse_fold_scalar<T, A>(ldg_scalar(r + i), m, s);
+      }
+    }
+    // merge the group's pairs: max first, then the sums rescaled to it
+    const A M = group_combine<A, MaxOp<A>, G>(m, smem);
+    const A scaled = (m > LseMath<A>::neg_inf()) ? s * LseMath<A>::exp_diff(m, M) : A(0);
+    const A S = group_combine<A, SumOp<A>, G>(scaled, smem + kWarps);
+    if (g == 0) {
+      // all -inf: max = -inf, sum = 0 -> -inf + log(0) = -inf, as the reference's expression gives
+      lse_put(out, out_dtype, row, static_cast<double>(M + LseMath<A>::log_(S)));
+    }
+  }
+}
+
+template <typename T, typename A>
+static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
+  constexpr int VE = VecOf<T>::kElems;
+  const T* x = static_cast<const T*>(d->x);
+  const long long cols = d->cols, rows = d->rows;
+  const bool aligned = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (cols % VE == 0);
+  const long long row_bytes = cols * static_cast<long long>(sizeof(T));
+  int G = 32;
+  while (G < kBlock && static_cast<long long>(G) * 128 < row_bytes) G <<= 1;  // <= ~128 B per thread per step
+  const long long rows_per_cta = kBlock / G;
+  long long ctas = (rows + rows_per_cta - 1) / rows_per_cta;
+  const long long cap = 148LL * 8 * 16;  // grid-stride beyond that
+  if (ctas > cap) ctas = cap;
+  const unsigned gr = static_cast<unsigned>(ctas);
+#define B200PHI_LSE(GG)                                                                              \
+  if (aligned)                                                                                       \
+    lse_rows_kernel<T, A, GG, 8, true><<<gr, kBlock, 0, stream>>>(x, rows, cols, d->out, d->dtype);  \
+  else                                                                                               \
+    lse_rows_kernel<T, A, GG, 8, false><<<gr, kBlock, 0, stream>>>(x, rows, cols, d->out, d->dtype);
+  switch (G) {
+    case 32:
+      B200PHI_LSE(32) break;
+    case 64:
+      B200PHI_LSE(64) break;
+    case 128:
+      B200PHI_LSE(128) break;
+    default:
+      B200PHI_LSE(256) break;
+  }
+#undef B200PHI_LSE
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_status(e);
+  return B200PHI_OK;
+}
+
+int run_logsumexp(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
+  if (!d) return set_error(B200PHI_INVALID_ARGUMENT, "null descriptor");
+  if (d->rows < 0 || d->cols < 0) return set_error(B200PHI_INVALID_ARGUMENT, "negative extent");
+  if (d->rows == 0 || d->cols == 0)
+    return set_error(B200PHI_INVALID_ARGUMENT, "The dims of Input(X) should be greater than 0.");
+  if (!d->x || !d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null tensor pointer");
+  switch (d->dtype) {
+    case B200PHI_FLOAT32:
+      return launch_lse<float, float>(d, stream);
+    case B200PHI_FLOAT64:
+      return launch_lse<double, double>(d, stream);
+    case B200PHI_BFLOAT16:
+      return launch_lse<__nv_bfloat16, float>(d, stream);
+    case B200PHI_FLOAT16:
+      return launch_lse<__half, float>(d, stream);
+    default:
+      return set_error(B200PHI_UNSUPPORTED, "logsumexp: floating-point input only");
+  }
+}
+
+}  // namespace b200phi
+
+extern "C" int b200phi_logsumexp(const b200phi_logsumexp_desc* d, void* stream) {
+  return b200phi::run_logsumexp(d, static_cast<cudaStream_t>(stream));
+}

@@ -161,13 +161,69 @@ struct AllOp {
   static __device__ __forceinline__ Acc combine(Acc a, Acc b) { return a & b; }
 };
 
-// Load one element as the accumulation type, honouring the any/all truthiness rule.
+// Reduce operators that transform each element first -- the TransformOp slot of
+// funcs::ReduceKernel<Tx, Ty, ReduceOp, TransformOp> (reduce_function.h:1047), as p_norm and
+// squared_l2_norm fill it (gpu/p_norm_kernel.cu:26-52,84-95, gpu/squared_l2_norm_kernel.cu:31).
+// The combine stays the base operator's; only the element load changes.
+enum { kPreNone = 0, kPreAbs = 1, kPreSquare = 2, kPreNonzero = 3 };
+template <typename Op>
+struct OpPre {
+  static constexpr int value = kPreNone;
+};
+template <typename Acc>
+struct SumAbsOp : SumOp<Acc> {};
+template <typename Acc>
+struct SumSquareOp : SumOp<Acc> {};
+template <typename Acc>
+struct L2NormOp : SumOp<Acc> {};  // sum of squares, sqrt at the final store
+template <typename Acc>
+struct CountNonzeroOp : SumOp<Acc> {};
+template <typename Acc>
+struct MaxAbsOp : MaxOp<Acc> {};
+template <typename Acc>
+struct MinAbsOp : MinOp<Acc> {};
+template <typename Acc>
+struct OpPre<SumAbsOp<Acc>> {
+  static constexpr int value = kPreAbs;
+};
+template <typename Acc>
+struct OpPre<SumSquareOp<Acc>> {
+  static constexpr int value = kPreSquare;
+};
+template <typename Acc>
+struct OpPre<L2NormOp<Acc>> {
+  static constexpr int value = kPreSquare;
+};
+template <typename Acc>
+struct OpPre<CountNonzeroOp<Acc>> {
+  static constexpr int value = kPreNonzero;
+};
+template <typename Acc>
+struct OpPre<MaxAbsOp<Acc>> {
+  static constexpr int value = kPreAbs;
+};
+template <typename Acc>
+struct OpPre<MinAbsOp<Acc>> {
+  static constexpr int value = kPreAbs;
+};
+
+// Load one element as the accumulation type, honouring the any/all truthiness rule and the
+// operator's element transform.
 template <typename Acc, typename Op, typename T>
 __device__ __forceinline__ Acc load_as(T v) {
   if constexpr (Op::kLogical) {
     return static_cast<Acc>(truthy(v));
   } else {
-    return Cvt<Acc, T>::to(v);
+    const Acc a = Cvt<Acc, T>::to(v);
+    if constexpr (OpPre<Op>::value == kPreAbs) {
+      return a < Acc(0) ? -a : a;
+    } else if constexpr (OpPre<Op>::value == kPreSquare) {
+      return a * a;
+    } else if constexpr (OpPre<Op>::value == kPreNonzero) {
+      return a != Acc(0) ? Acc(1) : Acc(0);
+    } else {
+      return a;
+    }
   }
 }
 
@@ -385,6 +441,22 @@ __device__ __forceinline__ void store_result(const Epilogue& ep, long long idx, 
     return;
   }
   store_result_slow<Acc>(ep.out, ep.out_dtype, idx, v);
+}
+
+// The store every reduce kernel ends with: the operator's own finishing step, if it has one
+// (sqrt for the l2 norm: the second functor of gpu/p_norm_kernel.cu:90-95), then the typed store.
+template <typename Op>
+struct OpPost {
+  static constexpr bool kSqrt = false;
+};
+template <typename Acc>
+struct OpPost<L2NormOp<Acc>> {
+  static constexpr bool kSqrt = true;
+};
+template <typename Op, typename Acc>
+__device__ __forceinline__ void store_final(const Epilogue& ep, long long idx, Acc v) {
+  if constexpr (OpPost<Op>::kSqrt) v = sqrt(v);
+  store_result(ep, idx, v);
 }
 
 }  // namespace b200phi

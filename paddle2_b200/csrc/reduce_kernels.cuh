@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(kBlock)
     }
     v = group_combine_leader<Acc, Op, G>(v, smem, parity);
     parity ^= 1;
-    if (g == 0) store_result(ep, row, v);
+    if (g == 0) store_final<Op>(ep, row, v);
   }
 }
 
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(kBlock)
     }
 #pragma unroll
     for (int m = G >> 1; m > 0; m >>= 1) acc = Op::combine(acc, shfl_xor(acc, m));
-    if (valid && g == 0) store_result(ep, row, acc);
+    if (valid && g == 0) store_final<Op>(ep, row, acc);
   }
 }
 
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kBlock)
     r = Op::combine(r, __ldcg(&partial[row * splits + s]));
   r = block_combine<Acc, Op>(r, smem);
   if (threadIdx.x == 0) {
-    store_result(ep, row, r);
+    store_final<Op>(ep, row, r);
     tickets[row] = 0;
   }
 }
@@ -287,7 +287,7 @@ __device__ __noinline__ void p2p_finish(const P2PArgs g, bool owner, long long o
       for (int e = 0; e < VE; ++e) r[e] = Op::combine(r[e], src[e]);
     }
 #pragma unroll
-    for (int e = 0; e < VE; ++e) store_result(ep, out_base + e, r[e]);
+    for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, r[e]);
   }
 }
 
@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kBlock)
     } else {
       if (ty == 0 && live) {
 #pragma unroll
-        for (int e = 0; e < VE; ++e) store_result(ep, out_base + e, smem[tx * VE + e]);
+        for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
       }
     }
     return;
@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(kBlock)
   } else {
     if (ty == 0 && live) {
 #pragma unroll
-      for (int e = 0; e < VE; ++e) store_result(ep, out_base + e, smem[tx * VE + e]);
+      for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
     }
   }
   if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(kBlock)
       smem[ty * TX + tx] = Op::combine(smem[ty * TX + tx], smem[(ty + half) * TX + tx]);
     __syncthreads();
   }
-  if (ty == 0 && o < gd.out_numel) store_result(ep, o, smem[tx]);
+  if (ty == 0 && o < gd.out_numel) store_final<Op>(ep, o, smem[tx]);
 }
 
 }  // namespace b200phi

@@ -171,5 +171,6 @@ int launch_sum(const ReduceArgs& a);      // SUM, MEAN
 int launch_prod(const ReduceArgs& a);     // PROD
 int launch_minmax(const ReduceArgs& a);   // MAX, MIN, AMAX, AMIN
 int launch_logical(const ReduceArgs& a);  // ANY, ALL
+int launch_norm(const ReduceArgs& a);     // SUM_ABS, SUM_SQUARE, L2_NORM, MAX_ABS, MIN_ABS, COUNT_NONZERO
 
 }  // namespace b200phi

@@ -68,7 +68,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   char buf[256];
   if (!d) return fail(err, B200PHI_INVALID_ARGUMENT, "null descriptor");
   *p = ReducePlan();
-  if (d->op < B200PHI_SUM || d->op > B200PHI_AMIN)
+  if (d->op < B200PHI_SUM || d->op > B200PHI_COUNT_NONZERO)
     return fail(err, B200PHI_INVALID_ARGUMENT, "unknown reduce op");
   if (!dtype_known(d->in_dtype)) return fail(err, B200PHI_UNSUPPORTED, "unsupported input dtype");
   if (d->rank < 0 || d->rank > B200PHI_MAX_RANK)
@@ -91,6 +91,8 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   const bool sum_like = d->op == B200PHI_SUM || d->op == B200PHI_MEAN;
   if (!sum_like && !logical && out_dtype != d->in_dtype)
     return fail(err, B200PHI_UNSUPPORTED, "max/min/prod keep the input dtype");
+  if (d->op >= B200PHI_SUM_ABS && !dtype_is_float(d->in_dtype))
+    return fail(err, B200PHI_UNSUPPORTED, "the norm reductions take floating-point dtypes");
 
   p->op = d->op;
   p->in_dtype = d->in_dtype;

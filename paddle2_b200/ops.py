@@ -605,3 +605,111 @@ def swish(x, beta=1.0):
 
 def mish(x, threshold=20.0):
     return _map("mish", [x], p0=threshold)
+
+
+# ------------------------------------------------------------------- reduce-side plug-ins
+# The remaining clients of funcs::ReduceKernel named in SURVEY.md 8(f) row 2:
+# gpu/{squared_l2_norm, p_norm, mean_all, logsumexp, dist, reduce_as}_kernel.cu and
+# gpu/broadcast_tensors_kernel.cu.
+
+
+def squared_l2_norm(x):
+    """sum(x*x) over everything, shape [1] (SquaredL2NormKernel, gpu/squared_l2_norm_kernel.cu:24-34)."""
+    return _reduce(L.SUM_SQUARE, x, None, False, x.dtype).reshape([1])
+
+
+def p_norm(x, porder=2.0, axis=-1, epsilon=1e-12, keepdim=False, asvector=False):
+    """PNormKernel (gpu/p_norm_kernel.cu:54-96): porder 0 counts non-zeros, +-inf is max/min |x|,
+    otherwise (sum |x|^p)^(1/p) along `axis` (or over everything with asvector).  porder 1 and 2
+    are single launches; any other finite p goes |x|^p -> sum -> ^(1/p), the same three
+    functors the reference applies.  `epsilon` only matters to the backward kernel."""
+    ax = None if asvector else [axis]
+    porder = float(porder)
+    if porder == 0:
+        return _reduce(L.COUNT_NONZERO, x, ax, keepdim, x.dtype)
+    if porder == float("inf"):
+        return _reduce(L.MAX_ABS, x, ax, keepdim, x.dtype)
+    if porder == float("-inf"):
+        return _reduce(L.MIN_ABS, x, ax, keepdim, x.dtype)
+    if porder == 1.0:
+        return _reduce(L.SUM_ABS, x, ax, keepdim, x.dtype)
+    if porder == 2.0:
+        return _reduce(L.L2_NORM, x, ax, keepdim, x.dtype)
+    s = _reduce(L.SUM, _map("pow_abs", [x], p0=porder), ax, keepdim, x.dtype)
+    return _map("pow_abs", [s], p0=1.0 / porder)
+
+
+def mean_all(x):
+    """MeanAllKernel (gpu/mean_all_kernel.cu:27-53): mean over every element, 0-D result."""
+    return _reduce(L.MEAN, x, None, False, x.dtype)
+
+
+def reduce_as(x, target):
+    """ReduceAsKernel (gpu/reduce_as_kernel.cu:24-36): sum x down to target's shape over the dims
+    funcs::GetReduceDims finds (leading extra dims, and dims where target has 1)."""
+    xs, ts = list(x.shape), list(target.shape)
+    off = len(xs) - len(ts)
+    if off < 0:
+        raise ValueError("reduce_as: target has more dims than x")
+    dims = list(range(off)) + [i + off for i, t in enumerate(ts) if t == 1 and xs[i + off] != 1]
+    for i, t in enumerate(ts):
+        if t != 1 and t != xs[i + off]:
+            raise ValueError(f"reduce_as: target dim {i} = {t} does not divide x's shape {xs}")
+    if not dims:
+        return cast(x, x.dtype)
+    return _reduce(L.SUM, x, dims, False, x.dtype).reshape(ts)
+
+
+def dist(x, y, p=2.0):
+    """DistKernel (gpu/dist_kernel.cu): the p-norm of (x - y) over every element, 0-D result."""
+    return p_norm(subtract(x, y), porder=p, asvector=True).reshape([])
+
+
+def broadcast_tensors(inputs):
+    """BroadcastTensorsKernel (gpu/broadcast_tensors_kernel.cu): every input expanded to the common
+    broadcast shape, each through one unary launch of the broadcast engine."""
+    shape = list(inputs[0].shape)
+    for t in inputs[1:]:
+        shape = broadcast_shape(shape, list(t.shape), -1)
+    return [_elementwise(L.ADD, [t], out_shape=shape) for t in inputs]
+
+
+def equal_all(x, y):
+    """EqualAllKernel (kps/compare_kernel.cu:78-103): false when the shapes differ, else
+    all(x == y) as a 0-D bool."""
+    if list(x.shape) != list(y.shape):
+        return torch.zeros([], dtype=torch.bool, device=x.device)
+    if x.numel() == 0:
+        return torch.ones([], dtype=torch.bool, device=x.device)
+    return _reduce(L.ALL, _map("equal", [x, y]), None, False, torch.bool)
+
+
+def logsumexp(x, axis=None, keepdim=False):
+    """paddle.logsumexp (LogsumexpKernel, gpu/logsumexp_kernel.cu:81-165).  Trailing (or all) axes:
+    one launch of the row kernel, one read of x.  Other axis sets: max -> exp(x - max) -> sum ->
+    log + max, the reference's own fallback (:49-78) on the two engines."""
+    _require_cuda(x)
+    x = x.contiguous()
+    rank = x.dim()
+    axes, reduce_all = _norm_axes(axis, rank)
+    out_shape = _reduce_out_shape(list(x.shape), axes, reduce_all, keepdim)
+    if x.numel() == 0:
+        raise L.B200PhiError(1, "The dims of Input(X) should be greater than 0.")
+    red = sorted(range(rank)) if reduce_all else sorted(axes)
+    trailing = reduce_all or red == list(range(rank - len(red), rank))
+    if trailing:
+        cols = 1
+        for a in red:
+            cols *= x.shape[a]
+        rows = x.numel() // cols
+        out = torch.empty(out_shape, dtype=x.dtype, device=x.device)
+        d = L.LogsumexpDesc()
+        d.dtype = _phi_dtype(x.dtype)
+        d.rows, d.cols = rows, cols
+        d.x, d.out = x.data_ptr(), out.data_ptr()
+        with torch.cuda.device(x.device):
+            L.check(L.lib().b200phi_logsumexp(C.byref(d), _stream_ptr(x)))
+        return out
+    m = _reduce(L.MAX, x, red, True, x.dtype)
+    s = _reduce(L.SUM, _map("sub_exp", [x, m]), red, True, x.dtype)
+    return add(_map("log", [s]), m).reshape(out_shape)

@@ -244,3 +244,35 @@ def map_operand(rng, dtype, shape, domain="any"):
     # few distinct values so that compare ops see ties
     return (np.round(rng.random(shape) * 8 - 4, 1)).astype(dt) if domain == "ties" \
         else (rng.random(shape) * 4 - 2).astype(dt)
+
+
+# ---- reduce-side plug-ins ----------------------------------------------------------------
+# (shape, axis, porder, keepdim, asvector, source): test_norm_all.py's p_norm cases + every porder branch
+PNORM_CASES = [
+    ([2, 3, 4, 5], 1, 2.0, False, False, "test_norm_all.py:217-222"),
+    ([3, 20, 3], 2, 2.0, True, False, "test_norm_all.py:266-271"),
+    ([3, 20, 3], 2, float("inf"), True, False, "test_norm_all.py:282-287"),
+    ([3, 20, 3], 2, float("-inf"), True, False, "test_norm_all.py:300-305"),
+    ([3, 20, 3], 2, 0.0, True, False, "test_norm_all.py:318-323"),
+    ([3, 20, 3], -1, 2.0, False, False, "test_norm_all.py:334-339"),
+    ([3, 20, 3], 1, 1.0, False, False, "porder 1"),
+    ([3, 20, 3], 0, 3.0, False, False, "general porder"),
+    ([3, 20, 3], 1, 0.5, True, False, "fractional porder"),
+    ([2, 3, 4, 5], 0, 2.0, False, True, "asvector"),
+    ([64, 1030], -1, 2.0, False, False, "long rows"),
+    ([1030, 64], 0, 1.0, False, False, "columns"),
+]
+# (shape, axis, keepdim, source): test_logsumexp.py
+LOGSUMEXP_CASES = [
+    ([2, 3, 4, 5], [-1], False, "test_logsumexp.py:63-65"),
+    ([], [], False, "test_logsumexp.py:116-117"),
+    ([4, 5, 6], [-1], False, "test_logsumexp.py:122"),
+    ([2, 3, 4, 5], [0, -1], False, "test_logsumexp.py:127"),
+    ([2, 3, 4, 5], [0, 1, 2, 3], False, "test_logsumexp.py:132"),
+    ([2, 3, 4, 5], [-1], True, "keepdim"),
+    ([2, 3, 4, 5], [2, 3], False, "two trailing axes"),
+    ([2, 3, 4, 5], [1], False, "middle axis: composed route"),
+    ([2, 3, 4, 5], [0], True, "leading axis: composed route"),
+    ([37, 1000], [-1], False, "vocabulary-sized rows"),
+    ([5, 4099], [-1], False, "ragged rows (scalar route)"),
+]

@@ -97,6 +97,21 @@ def main():
         x = cases.map_operand(np.random.default_rng(7200), "float32", [11, 17], dom)
         store[f"act_{name}_x"] = x
         store[f"act_{name}_y"] = O.map(name, [x], p0, p1, impl="ref")
+    # reduce-side plug-ins: the Eigen expressions of cpu/p_norm_kernel.cc, squared_l2_norm.h and
+    # phi::LogsumexpFunctor itself (oracle/ref_src/ref_norm.cc)
+    for i, (shape, axis, porder, keepdim, asvector, _src) in enumerate(cases.PNORM_CASES):
+        x = cases.map_operand(np.random.default_rng(8000 + i), "float32", shape)
+        x.reshape(-1)[::7] = 0  # zeros for the porder 0 count
+        store[f"pnorm_{i}_x"] = x
+        store[f"pnorm_{i}_y"] = O.p_norm(x, porder, axis, keepdim, asvector, impl="ref")
+    x = cases.map_operand(np.random.default_rng(8100), "float32", [13, 1001])
+    store["sql2_x"], store["sql2_y"] = x, O.squared_l2_norm(x, impl="ref")
+    for i, (shape, axis, keepdim, _src) in enumerate(cases.LOGSUMEXP_CASES):
+        x = np.random.default_rng(8200 + i).uniform(-1, 1, shape).astype(np.float32)  # test_logsumexp.py:71
+        store[f"lse_{i}_x"] = x
+        axes = [a % max(len(shape), 1) for a in axis]
+        if sorted(axes) == list(range(min(axes), min(axes) + len(axes))) if axes else True:
+            store[f"lse_{i}_y"] = O.logsumexp(x, axis if axis else None, keepdim, impl="ref")
     np.savez_compressed(os.path.join(HERE, "phi_ref_golden.npz"), **store)
     print("wrote", len(store), "arrays")
 

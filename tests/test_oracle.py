@@ -221,3 +221,26 @@ def test_map_errors(oracle):
         oracle.map("bitwise_and", [np.zeros(3, np.float32), np.zeros(3, np.float32)])
     with pytest.raises(ValueError):
         oracle.map("exp", [np.zeros(3, np.int32)])
+
+
+# ---- reduce-side plug-ins ---------------------------------------------------------------------
+def test_norm_and_logsumexp_port_match_golden(oracle, golden):
+    for i, (shape, axis, porder, keepdim, asvector, src) in enumerate(cases.PNORM_CASES):
+        got = oracle.p_norm(golden[f"pnorm_{i}_x"], porder, axis, keepdim, asvector)
+        want = golden[f"pnorm_{i}_y"]
+        assert got.shape == want.shape, src
+        if porder in (0.0, float("inf"), float("-inf")):
+            assert np.array_equal(got, want), src
+        else:
+            np.testing.assert_allclose(got, want, rtol=2e-6, err_msg=src)
+    np.testing.assert_allclose(oracle.squared_l2_norm(golden["sql2_x"]), golden["sql2_y"], rtol=1e-6)
+    for i, (shape, axis, keepdim, src) in enumerate(cases.LOGSUMEXP_CASES):
+        x = golden[f"lse_{i}_x"]
+        got = oracle.logsumexp(x, axis if axis else None, keepdim)
+        if f"lse_{i}_y" in golden.files:
+            assert got.shape == golden[f"lse_{i}_y"].shape, src
+            np.testing.assert_allclose(got, golden[f"lse_{i}_y"], rtol=2e-6, atol=1e-6, err_msg=src)
+        # the reference test's own oracle (test_logsumexp.py:24-32)
+        ax = tuple(axis) if axis else None
+        np.testing.assert_allclose(got, np.log(np.exp(x.astype(np.float64)).sum(axis=ax, keepdims=keepdim)),
+                                   rtol=1e-5, atol=1e-6, err_msg=src)

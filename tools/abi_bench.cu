@@ -187,6 +187,33 @@ int main(int argc, char** argv) {
     }
     cudaFree(x); cudaFree(y); cudaFree(out);
   }
+  if (strstr(only, "L")) {  // reduce-side plug-ins: logsumexp rows and norm reductions
+    const size_t n = (size_t)8192 * 32000;
+    void* x = dalloc(n * 4, 0x40ff40ff, 0x3c003c00);  // as bf16: pairs of moderate magnitude; as fp32: same range
+    void* out; CK(cudaMalloc(&out, 8192 * 8));
+    b200phi_logsumexp_desc l = {};
+    l.rows = 8192; l.cols = 32000; l.x = x; l.out = out;
+    l.dtype = B200PHI_BFLOAT16;
+    float ms = time_it([&] { OK(b200phi_logsumexp(&l, 0)); }, 20);
+    printf("L1 logsumexp bf16 [8192,32000]             %8.2f us  %7.1f GB/s\n", ms * 1e3, (n * 2.0 + 8192 * 2) / ms / 1e6);
+    l.dtype = B200PHI_FLOAT32;
+    ms = time_it([&] { OK(b200phi_logsumexp(&l, 0)); }, 20);
+    printf("L1 logsumexp fp32 [8192,32000]             %8.2f us  %7.1f GB/s\n", ms * 1e3, (n * 4.0 + 8192 * 4) / ms / 1e6);
+    l.dtype = B200PHI_BFLOAT16; l.rows = 16384 * 4; l.cols = 4096;
+    ms = time_it([&] { OK(b200phi_logsumexp(&l, 0)); }, 20);
+    printf("L1 logsumexp bf16 [65536,4096]             %8.2f us  %7.1f GB/s\n", ms * 1e3, (65536.0 * 4096 * 2) / ms / 1e6);
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_L2_NORM; d.in_dtype = d.out_dtype = B200PHI_FLOAT32; d.rank = 2; d.dims[0] = 32768; d.dims[1] = 4096;
+    d.naxes = 1; d.axes[0] = 1; d.x = x; d.out = out;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+    printf("L2 p_norm(2) fp32 [32768,4096] axis -1      %8.2f us  %7.1f GB/s\n", ms * 1e3, 537001984.0 / ms / 1e6);
+    d.op = B200PHI_SUM_SQUARE; d.in_dtype = d.out_dtype = B200PHI_BFLOAT16; d.dims[0] = 65536; d.naxes = 0; d.reduce_all = 1;
+    size_t ws = b200phi_reduce_workspace(&d);
+    void* w; CK(cudaMalloc(&w, ws ? ws : 256)); d.workspace = w; d.workspace_bytes = ws;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 20);
+    printf("L2 squared_l2_norm bf16 2^28 elements       %8.2f us  %7.1f GB/s\n", ms * 1e3, 65536.0 * 4096 * 2 / ms / 1e6);
+    cudaFree(x); cudaFree(out); cudaFree(w);
+  }
   printf("done\n");
   return 0;
 }
