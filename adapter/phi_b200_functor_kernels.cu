@@ -8,6 +8,7 @@
 //   paddle/phi/kernels/gpu/activation_kernel.cu         (the activations listed below)
 //   paddle/phi/kernels/gpu/reduce_kernel.cu:74-187      (ReduceMax/MinGradKernel)
 //   paddle/phi/kernels/gpu/elementwise_grad_kernel.cu   (Maximum/MinimumGradKernel)
+//   paddle/phi/kernels/gpu/{p_norm,squared_l2_norm,mean_all,reduce_as,logsumexp}_kernel.cu
 // Compile-checked against the reference headers (adapter/check_compile.sh).
 #include <vector>
 
@@ -236,6 +237,141 @@ void MinimumGradKernel(const Context& dev_ctx, const DenseTensor& x, const Dense
   b200::SelectGrad(dev_ctx, B200PHI_MAP_MIN_GRAD_Y, x, y, dout, y, dy);
 }
 
+// ---- reduce-side plug-ins: p_norm_kernel.h, squared_l2_norm_kernel.h, mean_all_kernel.h,
+// reduce_as_kernel.h, logsumexp_kernel.h -------------------------------------------------------
+namespace b200 {
+
+template <typename Context>
+void ReduceOp(const Context& dev_ctx, int op, const DenseTensor& x, const std::vector<int64_t>& axes,
+              bool reduce_all, DenseTensor* out) {
+  dev_ctx.Alloc(out, x.dtype());
+  b200phi_reduce_desc d = {};
+  d.op = op;
+  d.in_dtype = d.out_dtype = static_cast<int>(x.dtype());
+  d.rank = x.dims().size();
+  for (int i = 0; i < d.rank; ++i) d.dims[i] = x.dims()[i];
+  d.naxes = reduce_all ? 0 : static_cast<int>(axes.size());
+  for (int i = 0; i < d.naxes; ++i) d.axes[i] = static_cast<int>(axes[i]);
+  d.reduce_all = reduce_all ? 1 : 0;
+  d.x = x.data();
+  d.out = out->data();
+  DenseTensor scratch;
+  const size_t ws = b200phi_reduce_workspace(&d);
+  if (ws > 0) {
+    scratch.Resize({static_cast<int64_t>(ws)});
+    d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+    d.workspace_bytes = ws;
+  }
+  CheckMap(b200phi_reduce(&d, dev_ctx.stream()));
+}
+
+}  // namespace b200
+
+template <typename T, typename Context>
+void PNormKernel(const Context& dev_ctx, const DenseTensor& x, float porder, int axis, float epsilon,
+                 bool keepdim, bool asvector, DenseTensor* out) {
+  const std::vector<int64_t> axes = {axis};
+  if (porder == 0) {
+    b200::ReduceOp(dev_ctx, B200PHI_COUNT_NONZERO, x, axes, asvector, out);
+  } else if (porder == INFINITY) {
+    b200::ReduceOp(dev_ctx, B200PHI_MAX_ABS, x, axes, asvector, out);
+  } else if (porder == -INFINITY) {
+    b200::ReduceOp(dev_ctx, B200PHI_MIN_ABS, x, axes, asvector, out);
+  } else if (porder == 1.0f) {
+    b200::ReduceOp(dev_ctx, B200PHI_SUM_ABS, x, axes, asvector, out);
+  } else if (porder == 2.0f) {
+    b200::ReduceOp(dev_ctx, B200PHI_L2_NORM, x, axes, asvector, out);
+  } else {
+    // |x|^p -> sum -> ^(1/p): the three functors of gpu/p_norm_kernel.cu:84-95
+    DenseTensor powed;
+    powed.Resize(x.dims());
+    b200::Map(dev_ctx, B200PHI_MAP_POW_ABS, {&x}, -1, porder, 0.f, &powed);
+    b200::ReduceOp(dev_ctx, B200PHI_SUM, powed, axes, asvector, out);
+    DenseTensor in_place = *out;
+    b200::Map(dev_ctx, B200PHI_MAP_POW_ABS, {&in_place}, -1, 1.0f / porder, 0.f, out);
+  }
+}
+
+template <typename T, typename Context>
+void SquaredL2NormKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::ReduceOp(dev_ctx, B200PHI_SUM_SQUARE, x, {}, true, out);
+}
+
+template <typename T, typename Context>
+void MeanAllKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
+  b200::ReduceOp(dev_ctx, B200PHI_MEAN, x, {}, true, out);
+}
+
+template <typename T, typename Context>
+void ReduceAsKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& target,
+                    DenseTensor* out) {
+  // funcs::GetReduceDims(x, target): leading extra dims, and dims where target has 1
+  const int xr = x.dims().size(), tr = target.dims().size(), off = xr - tr;
+  std::vector<int64_t> axes;
+  for (int i = 0; i < xr; ++i)
+    if (i < off || (target.dims()[i - off] == 1 && x.dims()[i] != 1)) axes.push_back(i);
+  if (axes.empty()) axes.push_back(0), out->Resize(x.dims());  // degenerate: reduce_num == 1 copies
+  b200::ReduceOp(dev_ctx, B200PHI_SUM, x, axes, false, out);
+}
+
+template <typename T, typename Context>
+void LogsumexpKernel(const Context& dev_ctx, const DenseTensor& x, const std::vector<int>& axis,
+                     bool keepdim, bool reduce_all, DenseTensor* out) {
+  const int rank = x.dims().size();
+  std::vector<bool> red(rank > 0 ? rank : 1, false);
+  if (axis.empty() || reduce_all || static_cast<int>(axis.size()) == rank) {
+    for (int i = 0; i < rank; ++i) red[i] = true;
+  } else {
+    for (int a : axis) red[a < 0 ? a + rank : a] = true;
+  }
+  int first = 0;
+  while (first < rank && !red[first]) ++first;
+  bool trailing = true;
+  for (int i = first; i < rank; ++i) trailing = trailing && red[i];
+  dev_ctx.Alloc(out, x.dtype());
+  if (trailing) {  // one launch, one read of x
+    b200phi_logsumexp_desc d = {};
+    d.dtype = static_cast<int>(x.dtype());
+    d.rows = 1;
+    d.cols = 1;
+    for (int i = 0; i < rank; ++i) (i < first ? d.rows : d.cols) *= x.dims()[i];
+    d.x = x.data();
+    d.out = out->data();
+    b200::CheckMap(b200phi_logsumexp(&d, dev_ctx.stream()));
+    return;
+  }
+  // other axis sets: max -> exp(x - max) -> sum -> log + max (the reference's fallback,
+  // gpu/logsumexp_kernel.cu:49-78) on the two engines
+  std::vector<int64_t> axes;
+  std::vector<int64_t> kept = common::vectorize(x.dims());
+  for (int i = 0; i < rank; ++i)
+    if (red[i]) axes.push_back(i), kept[i] = 1;
+  DenseTensor mx, ex, sm;
+  mx.Resize(common::make_ddim(kept));
+  b200::ReduceOp(dev_ctx, B200PHI_MAX, x, axes, false, &mx);
+  ex.Resize(x.dims());
+  b200::Map(dev_ctx, B200PHI_MAP_SUB_EXP, {&x, &mx}, -1, 0.f, 0.f, &ex);
+  sm.Resize(common::make_ddim(kept));
+  b200::ReduceOp(dev_ctx, B200PHI_SUM, ex, axes, false, &sm);
+  DenseTensor lg;
+  lg.Resize(common::make_ddim(kept));
+  b200::Map(dev_ctx, B200PHI_MAP_LOG, {&sm}, -1, 0.f, 0.f, &lg);
+  const auto out_dims = out->dims();
+  out->Resize(common::make_ddim(kept));
+  b200phi_elementwise_desc e = {};
+  e.binary = B200PHI_ADD;
+  e.dtype = static_cast<int>(x.dtype());
+  e.arity = 2;
+  e.axis = -1;
+  b200::View(lg, &e.in[0]);
+  b200::View(mx, &e.in[1]);
+  e.out_rank = static_cast<int>(kept.size());
+  for (size_t i = 0; i < kept.size(); ++i) e.out_dims[i] = kept[i];
+  e.out = out->data();
+  b200::CheckMap(b200phi_elementwise(&e, dev_ctx.stream()));
+  out->Resize(out_dims);
+}
+
 }  // namespace phi
 
 using float16 = phi::dtype::float16;
@@ -305,3 +441,12 @@ PD_REGISTER_KERNEL(maximum_grad, GPU, ALL_LAYOUT, phi::MaximumGradKernel, float,
                    int64_t, float16, bfloat16) {}
 PD_REGISTER_KERNEL(minimum_grad, GPU, ALL_LAYOUT, phi::MinimumGradKernel, float, double, int,
                    int64_t, float16, bfloat16) {}
+
+PD_REGISTER_KERNEL(p_norm, GPU, ALL_LAYOUT, phi::PNormKernel, float, double, float16, bfloat16) {}
+PD_REGISTER_KERNEL(squared_l2_norm, GPU, ALL_LAYOUT, phi::SquaredL2NormKernel, float, double, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(mean_all, GPU, ALL_LAYOUT, phi::MeanAllKernel, float, double, float16) {}
+PD_REGISTER_KERNEL(reduce_as, GPU, ALL_LAYOUT, phi::ReduceAsKernel, bool, float, double, float16,
+                   bfloat16, int16_t, int, int64_t, uint8_t, int8_t) {}
+PD_REGISTER_KERNEL(logsumexp, GPU, ALL_LAYOUT, phi::LogsumexpKernel, float, double, float16,
+                   bfloat16) {}

@@ -29,5 +29,5 @@ def test_adapter_compiles_against_reference_headers(tmp_path):
     assert out2.exists() and out2.stat().st_size > 0
     syms2 = subprocess.run(["nm", "-C", str(out2)], capture_output=True, text=True).stdout
     for name in ("less_than", "equal", "logical_and", "bitwise_xor", "silu", "leaky_relu", "max_grad",
-                 "maximum_grad"):
+                 "maximum_grad", "p_norm", "squared_l2_norm", "reduce_as", "logsumexp"):
         assert f"__reg_phi_kernel_{name}_GPU_ALL_LAYOUT" in syms2 or name in syms2, name
