@@ -266,8 +266,8 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
     if constexpr (Arity == 1) {  // a lone operand is always walked as a stream
       map_rows_kernel<TI, TO, F, 1, 1, 8><<<g, kBlock, 0, stream>>>(p, f);
     } else {
-      if (mask == kAll)
-        map_rows_kernel<TI, TO, F, Arity, kAll, 4><<<g, kBlock, 0, stream>>>(p, f);
+      if (mask == kAll)  // three streamed operands: 2 vectors each, or the buffers cost two CTAs per SM
+        map_rows_kernel<TI, TO, F, Arity, kAll, (Arity == 3 ? 2 : 4)><<<g, kBlock, 0, stream>>>(p, f);
       else if (mask == 1)
         map_rows_kernel<TI, TO, F, Arity, 1, 8><<<g, kBlock, 0, stream>>>(p, f);
       else

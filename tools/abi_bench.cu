@@ -20,7 +20,10 @@ __global__ void fill_random(unsigned* x, long long n, unsigned seed, unsigned ma
 }
 
 template <typename F> float time_it(F fn, int iters) {
-  for (int i = 0; i < 5; ++i) fn();
+  // ABI_BENCH_ONCE=1: one launch per kernel and no warm-up, for captures under ncu
+  static const bool once = getenv("ABI_BENCH_ONCE") != nullptr;
+  if (once) iters = 1;
+  for (int i = 0; i < (once ? 0 : 5); ++i) fn();
   CK(cudaDeviceSynchronize());
   cudaEvent_t a, b;
   cudaEventCreate(&a); cudaEventCreate(&b);
