@@ -345,6 +345,45 @@ def other_configs(torch, pb):
     assert torch.allclose(v.float(), x.float().var(1), rtol=2e-2)
     del x
     torch.cuda.empty_cache()
+
+    # SURVEY 8(f) rows 1-2 (context only): row logsumexp, max_grad, a compare
+    x = torch.randn(8192, 32000, device="cuda").bfloat16()
+    o = torch.empty(8192, device="cuda", dtype=torch.bfloat16)
+    ld = L.LogsumexpDesc()
+    ld.dtype, ld.rows, ld.cols, ld.x, ld.out = L.BFLOAT16, 8192, 32000, x.data_ptr(), o.data_ptr()
+    res["F_logsumexp_bf16_8192x32000"] = t(lambda: L.check(lib.b200phi_logsumexp(C.byref(ld), stream())), 524304384)
+    assert torch.allclose(o.float(), torch.logsumexp(x.float(), 1), rtol=1e-2)
+
+    def map_desc(op, ins, outt):
+        md = L.MapDesc()
+        md.op, md.in_dtype, md.out_dtype, md.arity, md.axis = L.MAP_OPS[op], pb.ops._phi_dtype(ins[0].dtype), 0, len(ins), -1
+        for i, tt in enumerate(ins):
+            md.in_[i].rank = tt.dim()
+            for j, sz in enumerate(tt.shape):
+                md.in_[i].dims[j] = sz
+            md.in_[i].data = tt.data_ptr()
+        md.out_rank = outt.dim()
+        for j, sz in enumerate(outt.shape):
+            md.out_dims[j] = sz
+        md.out = outt.data_ptr()
+        return md
+
+    mx = x.max(1, keepdim=True).values
+    g = torch.randn(8192, 1, device="cuda").bfloat16()
+    dx = torch.empty_like(x)
+    md = map_desc("equal_mul", [x, mx, g], dx)
+    res["F_max_grad_bf16_8192x32000"] = t(lambda: L.check(lib.b200phi_map(C.byref(md), stream())), 1048576000)
+    assert torch.equal(dx, (x == mx).to(x.dtype) * g)
+    del x, dx
+    torch.cuda.empty_cache()
+    x = torch.rand(256, 64, 112, 112, device="cuda")
+    y = torch.rand(64, 1, 1, device="cuda")
+    b = torch.empty(x.shape, device="cuda", dtype=torch.bool)
+    md2 = map_desc("less_than", [x, y], b)
+    res["F_less_than_fp32_256x64x112x112_vs_64x1x1"] = t(lambda: L.check(lib.b200phi_map(C.byref(md2), stream())), 1027604480)
+    assert torch.equal(b, x < y)
+    del x, y, b
+    torch.cuda.empty_cache()
     return res
 
 
