@@ -184,7 +184,31 @@ void ArgMinKernel(const Context& dev_ctx, const DenseTensor& x, const Scalar& ax
                     DenseTensor* out) {                                                       \
     b200::Elementwise(dev_ctx, BinaryId, B200PHI_ACT_NONE, 0, 0.f, x, y, -1, out, nullptr);   \
   }
-B200_DEFINE_ELEMENTWISE(Add, B200PHI_ADD)
+// AddKernel is not the macro form: a float32 x with a 16-bit y is the mixed-precision route
+// (kps/elementwise_kernel.cu:82-99)
+template <typename T, typename Context>
+void AddRawKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y, int axis,
+                  DenseTensor* out) {
+  b200::Elementwise(dev_ctx, B200PHI_ADD, B200PHI_ACT_NONE, 0, 0.f, x, y, axis, out, nullptr);
+}
+template <typename T, typename Context>
+void AddKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {
+  if (x.dtype() == DataType::FLOAT32 &&
+      (y.dtype() == DataType::BFLOAT16 || y.dtype() == DataType::FLOAT16)) {
+    dev_ctx.Alloc(out, DataType::FLOAT32);
+    b200phi_mixed_add_desc d = {};
+    d.y_dtype = static_cast<int>(y.dtype());
+    b200::FillDims(x, &d.x.rank, d.x.dims);
+    d.x.data = x.data();
+    b200::FillDims(y, &d.y.rank, d.y.dims);
+    d.y.data = y.data();
+    b200::FillDims(*out, &d.out_rank, d.out_dims);
+    d.out = out->data();
+    b200::Check(b200phi_mixed_add(&d, dev_ctx.stream()));
+    return;
+  }
+  b200::Elementwise(dev_ctx, B200PHI_ADD, B200PHI_ACT_NONE, 0, 0.f, x, y, -1, out, nullptr);
+}
 B200_DEFINE_ELEMENTWISE(Subtract, B200PHI_SUBTRACT)
 B200_DEFINE_ELEMENTWISE(Multiply, B200PHI_MULTIPLY)
 B200_DEFINE_ELEMENTWISE(Divide, B200PHI_DIVIDE)

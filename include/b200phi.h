@@ -353,6 +353,21 @@ typedef struct {
 
 B200PHI_API int b200phi_map(const b200phi_map_desc* d, void* stream);
 
+/* Mixed-precision add: out (FLOAT32) = x (FLOAT32) + widen(y), y BFLOAT16 or FLOAT16, numpy
+ * broadcasting.  The branch phi::AddKernel takes for a float32 x and a 16-bit y
+ * (MultiPrecisionAddKernelImpl, paddle/phi/kernels/kps/elementwise_kernel.cu:54-99): the
+ * master-gradient accumulation of mixed-precision training, without a cast pass over y. */
+typedef struct {
+  int32_t y_dtype;        /* BFLOAT16 or FLOAT16; x and out are FLOAT32 */
+  b200phi_tensor_view x;
+  b200phi_tensor_view y;
+  int32_t out_rank;
+  int64_t out_dims[B200PHI_MAX_RANK];
+  void* out;              /* may alias x.data when x is not broadcast (in-place accumulate) */
+} b200phi_mixed_add_desc;
+
+B200PHI_API int b200phi_mixed_add(const b200phi_mixed_add_desc* d, void* stream);
+
 /* ------------------------------------------------------------------------ */
 /* Sharded reduction: local reduce + allreduce of the partial               */
 /* ------------------------------------------------------------------------ */

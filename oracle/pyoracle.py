@@ -380,6 +380,23 @@ def logsumexp(x, axis=None, keepdim=False, impl="port"):
     return (map("log", [np.asarray(s)]) + np.asarray(m)).astype(x.dtype).reshape(out_shape)
 
 
+def mixed_add(x, y_bits, y_is_bf16=True, impl="port"):
+    """fp32 x + widen(16-bit y): MultiPrecisionAddFunctor (elementwise_functor.h:45-50).  y is
+    given as raw uint16 patterns (numpy has no bfloat16); same shape as x."""
+    x = _c(x, dtype=np.float32)
+    y_bits = _c(y_bits, dtype=np.uint16)
+    if impl == "ref":
+        out = np.empty_like(x)
+        rc = ref().phi_ref_mixed_add(int(y_is_bf16), x.ctypes.data_as(C.c_void_p),
+                                     y_bits.ctypes.data_as(C.c_void_p), C.c_int64(x.size),
+                                     out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise ValueError(f"oracle mixed_add status {rc}")
+        return out
+    yf = bf16_bits_to_f32(y_bits) if y_is_bf16 else y_bits.view(np.float16).astype(np.float32)
+    return (x + yf.reshape(y_bits.shape)).astype(np.float32)
+
+
 def rowstats_f32(x, unbiased=True):
     """(mean, var) over the last axis of a float32 array: paddle.var's composite in fp32."""
     x = _c(x, dtype=np.float32)

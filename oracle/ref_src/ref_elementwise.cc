@@ -99,3 +99,23 @@ REFPHI_EW(float, float)
 REFPHI_EW(double, double)
 REFPHI_EW(int32_t, int32)
 REFPHI_EW(int64_t, int64)
+
+// Mixed-precision add: funcs::MultiPrecisionAddFunctor<float, bfloat16 / float16>
+// (elementwise_functor.h:45-50), y given as raw 16-bit patterns, same shape.
+#include "paddle/phi/common/bfloat16.h"
+#include "paddle/phi/common/float16.h"
+REFPHI_EXPORT int phi_ref_mixed_add(int y_is_bf16, const float* x, const uint16_t* y_bits, int64_t n,
+                                    float* out) {
+  for (int64_t i = 0; i < n; ++i) {
+    if (y_is_bf16) {
+      phi::dtype::bfloat16 y;
+      y.x = y_bits[i];
+      out[i] = phi::funcs::MultiPrecisionAddFunctor<float, phi::dtype::bfloat16>()(x[i], y);
+    } else {
+      phi::dtype::float16 y;
+      y.x = y_bits[i];
+      out[i] = phi::funcs::MultiPrecisionAddFunctor<float, phi::dtype::float16>()(x[i], y);
+    }
+  }
+  return 0;
+}

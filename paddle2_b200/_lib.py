@@ -142,6 +142,17 @@ class LogsumexpDesc(C.Structure):
     ]
 
 
+class MixedAddDesc(C.Structure):
+    _fields_ = [
+        ("y_dtype", C.c_int32),
+        ("x", TensorView),
+        ("y", TensorView),
+        ("out_rank", C.c_int32),
+        ("out_dims", C.c_int64 * MAX_RANK),
+        ("out", C.c_void_p),
+    ]
+
+
 class MapDesc(C.Structure):
     _fields_ = [
         ("op", C.c_int32),
@@ -186,6 +197,7 @@ EXPORTS = [
     "b200phi_elementwise",
     "b200phi_map",
     "b200phi_logsumexp",
+    "b200phi_mixed_add",
     "b200phi_comm_unique_id",
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
@@ -228,6 +240,8 @@ def lib():
     L.b200phi_map.restype = C.c_int
     L.b200phi_logsumexp.argtypes = [C.POINTER(LogsumexpDesc), C.c_void_p]
     L.b200phi_logsumexp.restype = C.c_int
+    L.b200phi_mixed_add.argtypes = [C.POINTER(MixedAddDesc), C.c_void_p]
+    L.b200phi_mixed_add.restype = C.c_int
     L.b200phi_comm_unique_id.argtypes = [C.c_char_p]
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]

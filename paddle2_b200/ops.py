@@ -407,8 +407,45 @@ def _elementwise(binary, ins, act=L.ACT_NONE, compound=0, scale_v=0.0, axis=-1,
     return (out, inter) if want_intermediate else out
 
 
-def add(x, y, axis=-1):
+def add(x, y, axis=-1, out=None):
+    """paddle.add.  A float32 x with a bfloat16 / float16 y takes the mixed-precision route of
+    phi::AddKernel (kps/elementwise_kernel.cu:82-99): out = x + widen(y) in float32, one launch,
+    no cast pass; `out=x` accumulates in place (the master-gradient update)."""
+    if (isinstance(x, torch.Tensor) and isinstance(y, torch.Tensor) and x.dtype == torch.float32
+            and y.dtype in (torch.bfloat16, torch.float16)):
+        return _mixed_add(x, y, out)
+    if out is not None:
+        raise ValueError("out= is only supported on the mixed-precision route")
     return _elementwise(L.ADD, [x, y], axis=axis)
+
+
+def _mixed_add(x, y, out=None):
+    _require_cuda(x, y)
+    x, y = x.contiguous(), y.contiguous()
+    out_shape = broadcast_shape(x.shape, y.shape, -1)
+    if out is None:
+        out = torch.empty(out_shape, dtype=torch.float32, device=x.device)
+    else:
+        _require_cuda(out)
+        if list(out.shape) != out_shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous float32 tensor of shape {out_shape}")
+        if out.data_ptr() == x.data_ptr() and list(x.shape) != out_shape:
+            raise ValueError("in-place accumulation needs x to have the output shape")
+    d = L.MixedAddDesc()
+    d.y_dtype = _phi_dtype(y.dtype)
+    for view, t in ((d.x, x), (d.y, y)):
+        view.rank = t.dim()
+        for j, s_ in enumerate(t.shape):
+            view.dims[j] = s_
+        view.data = t.data_ptr()
+    d.out_rank = len(out_shape)
+    for j, s_ in enumerate(out_shape):
+        d.out_dims[j] = s_
+    d.out = out.data_ptr()
+    if out.numel() > 0:
+        with torch.cuda.device(out.device):
+            L.check(L.lib().b200phi_mixed_add(C.byref(d), _stream_ptr(out)))
+    return out
 
 
 def subtract(x, y, axis=-1):

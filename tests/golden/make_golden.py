@@ -112,6 +112,16 @@ def main():
         axes = [a % max(len(shape), 1) for a in axis]
         if sorted(axes) == list(range(min(axes), min(axes) + len(axes))) if axes else True:
             store[f"lse_{i}_y"] = O.logsumexp(x, axis if axis else None, keepdim, impl="ref")
+    # mixed-precision add (MultiPrecisionAddFunctor): fp32 + bf16 / fp16 bit patterns
+    rng = np.random.default_rng(9000)
+    x = cases.map_operand(rng, "float32", [33, 257])
+    bits = rng.integers(0, 1 << 16, size=[33, 257]).astype(np.uint16)
+    bits[(bits & 0x7F80) == 0x7F80] = 0x3F80  # keep bf16 finite
+    hbits = bits.copy()
+    hbits[(hbits & 0x7C00) == 0x7C00] = 0x3C00  # keep fp16 finite
+    store["mpadd_x"], store["mpadd_bf16_bits"], store["mpadd_fp16_bits"] = x, bits, hbits
+    store["mpadd_bf16_out"] = O.mixed_add(x, bits, True, impl="ref")
+    store["mpadd_fp16_out"] = O.mixed_add(x, hbits, False, impl="ref")
     np.savez_compressed(os.path.join(HERE, "phi_ref_golden.npz"), **store)
     print("wrote", len(store), "arrays")
 

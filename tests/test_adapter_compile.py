@@ -31,3 +31,6 @@ def test_adapter_compiles_against_reference_headers(tmp_path):
     for name in ("less_than", "equal", "logical_and", "bitwise_xor", "silu", "leaky_relu", "max_grad",
                  "maximum_grad", "p_norm", "squared_l2_norm", "reduce_as", "logsumexp"):
         assert f"__reg_phi_kernel_{name}_GPU_ALL_LAYOUT" in syms2 or name in syms2, name
+    # third TU: the auto-parallel hook type-checks against NCCLCommContext
+    out3 = tmp_path / "phi_b200_kernels_dist.o"
+    assert out3.exists() and out3.stat().st_size > 0

@@ -120,3 +120,52 @@ def test_errors(oracle):
         pb.add(torch.ones(2, 3, device="cuda"), torch.ones(2, 4, device="cuda"))
     with pytest.raises(TypeError):
         pb.add(torch.ones(2, device="cuda"), torch.ones(2, device="cuda", dtype=torch.float64))
+
+
+# ---- mixed-precision add (MultiPrecisionAddKernelImpl, kps/elementwise_kernel.cu:54-99) ---------
+def _bits_to_torch(bits, bf16):
+    t = torch.from_numpy(bits.view(np.int16).copy())
+    return t.view(torch.bfloat16 if bf16 else torch.float16)
+
+
+def test_mixed_add_golden():
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "phi_ref_golden.npz"))
+    x = G.to_dev(g["mpadd_x"])
+    for key, bf16 in (("bf16", True), ("fp16", False)):
+        y = _bits_to_torch(g[f"mpadd_{key}_bits"], bf16).cuda()
+        got = pb.add(x, y)
+        assert got.dtype == torch.float32
+        assert np.array_equal(G.to_np(got), g[f"mpadd_{key}_out"]), key   # one IEEE add: bit-exact
+
+
+@pytest.mark.parametrize("tdt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("xs,ys", [((4096, 4096), (4096, 4096)), ((257, 1031), (257, 1031)), ((64, 3, 500), (3, 1)),
+                                   ((500, 77), (77,)), ((9, 1000), (1,)), ((1, 4100), (33, 1)), ((7, 5, 3), (7, 1, 3))])
+def test_mixed_add_shapes(tdt, xs, ys):
+    gen = torch.Generator().manual_seed(4)
+    x = torch.randn(xs, generator=gen)
+    y = torch.randn(ys, generator=gen).to(tdt)
+    got = pb.add(x.cuda(), y.cuda())
+    want = x + y.float()          # exact: widening is exact, the add is one rounding
+    assert got.shape == want.shape
+    assert torch.equal(got.cpu(), want)
+
+
+def test_mixed_add_in_place_accumulate():
+    """master_grad += grad: out aliases x"""
+    gen = torch.Generator().manual_seed(5)
+    acc = torch.randn((1024, 2048), generator=gen).cuda()
+    want = acc.clone()
+    for _ in range(3):
+        gr = torch.randn((1024, 2048), generator=gen).bfloat16().cuda()
+        want = want + gr.float()
+        r = pb.add(acc, gr, out=acc)
+        assert r.data_ptr() == acc.data_ptr()
+    assert torch.equal(acc, want)
+    with pytest.raises(pb.B200PhiError):
+        from paddle2_b200 import _lib as L
+        import ctypes as C
+        d = L.MixedAddDesc()
+        d.y_dtype = L.FLOAT32
+        L.check(L.lib().b200phi_mixed_add(C.byref(d), None))

@@ -244,3 +244,9 @@ def test_norm_and_logsumexp_port_match_golden(oracle, golden):
         ax = tuple(axis) if axis else None
         np.testing.assert_allclose(got, np.log(np.exp(x.astype(np.float64)).sum(axis=ax, keepdims=keepdim)),
                                    rtol=1e-5, atol=1e-6, err_msg=src)
+
+
+def test_mixed_add_port_matches_golden(oracle, golden):
+    x = golden["mpadd_x"]
+    assert np.array_equal(oracle.mixed_add(x, golden["mpadd_bf16_bits"], True), golden["mpadd_bf16_out"])
+    assert np.array_equal(oracle.mixed_add(x, golden["mpadd_fp16_bits"], False), golden["mpadd_fp16_out"])

@@ -190,6 +190,19 @@ int main(int argc, char** argv) {
     }
     cudaFree(x); cudaFree(y); cudaFree(out);
   }
+  if (strstr(only, "A")) {  // mixed-precision add: fp32 accumulator += bf16 gradient, in place
+    const size_t n = (size_t)1 << 28;
+    float* acc = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
+    void* gr = dalloc(n * 2, 0xbf7fbf7f, 0x3c003c00);
+    b200phi_mixed_add_desc d = {};
+    d.y_dtype = B200PHI_BFLOAT16;
+    d.x.rank = d.y.rank = d.out_rank = 2;
+    d.x.dims[0] = d.y.dims[0] = d.out_dims[0] = 16384; d.x.dims[1] = d.y.dims[1] = d.out_dims[1] = 16384;
+    d.x.data = acc; d.y.data = gr; d.out = acc;
+    float ms = time_it([&] { OK(b200phi_mixed_add(&d, 0)); }, 20);
+    printf("A1 fp32 += bf16 [16384,16384] in place        %8.2f us  %7.1f GB/s\n", ms * 1e3, n * 10.0 / ms / 1e6);
+    cudaFree(acc); cudaFree(gr);
+  }
   if (strstr(only, "L")) {  // reduce-side plug-ins: logsumexp rows and norm reductions
     const size_t n = (size_t)8192 * 32000;
     void* x = dalloc(n * 4, 0x40ff40ff, 0x3c003c00);  // as bf16: pairs of moderate magnitude; as fp32: same range
