@@ -150,6 +150,20 @@ B200_DEFINE_COMPARE(BitwiseAnd, B200PHI_MAP_BITWISE_AND)
 B200_DEFINE_COMPARE(BitwiseOr, B200PHI_MAP_BITWISE_OR)
 B200_DEFINE_COMPARE(BitwiseXor, B200PHI_MAP_BITWISE_XOR)
 
+// bitwise_kernel.h:44-56
+template <typename T, typename Context>
+void BitwiseLeftShiftKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                            bool is_arithmetic, DenseTensor* out) {
+  b200::Map(dev_ctx, is_arithmetic ? B200PHI_MAP_LEFT_SHIFT_ARITHMETIC : B200PHI_MAP_LEFT_SHIFT_LOGIC,
+            {&x, &y}, -1, 0.f, 0.f, out);
+}
+template <typename T, typename Context>
+void BitwiseRightShiftKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                             bool is_arithmetic, DenseTensor* out) {
+  b200::Map(dev_ctx, is_arithmetic ? B200PHI_MAP_RIGHT_SHIFT_ARITHMETIC : B200PHI_MAP_RIGHT_SHIFT_LOGIC,
+            {&x, &y}, -1, 0.f, 0.f, out);
+}
+
 template <typename T, typename Context>
 void LogicalNotKernel(const Context& dev_ctx, const DenseTensor& x, DenseTensor* out) {
   b200::Map(dev_ctx, B200PHI_MAP_LOGICAL_NOT, {&x}, -1, 0.f, 0.f, out);
@@ -402,6 +416,10 @@ B200_REGISTER_BITWISE(bitwise_and, BitwiseAnd)
 B200_REGISTER_BITWISE(bitwise_or, BitwiseOr)
 B200_REGISTER_BITWISE(bitwise_xor, BitwiseXor)
 B200_REGISTER_BITWISE(bitwise_not, BitwiseNot)
+PD_REGISTER_KERNEL(bitwise_left_shift, GPU, ALL_LAYOUT, phi::BitwiseLeftShiftKernel, uint8_t, int8_t,
+                   int16_t, int, int64_t) {}
+PD_REGISTER_KERNEL(bitwise_right_shift, GPU, ALL_LAYOUT, phi::BitwiseRightShiftKernel, uint8_t, int8_t,
+                   int16_t, int, int64_t) {}
 
 #define B200_REGISTER_ACT(name, func) \
   PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, phi::func##Kernel, float, double, float16, bfloat16) {}

@@ -293,6 +293,13 @@ typedef enum {
   B200PHI_MAP_BITWISE_OR = 33,
   B200PHI_MAP_BITWISE_XOR = 34,
   B200PHI_MAP_BITWISE_NOT = 35, /* arity 1 */
+  /* integer dtypes except BOOL; funcs/bitwise_functors.h:49-206 (bitwise_left_shift /
+   * bitwise_right_shift with is_arithmetic).  A shift count that is negative or >= the bit width
+   * gives 0, except the arithmetic right shift of a signed type, which gives the sign fill. */
+  B200PHI_MAP_LEFT_SHIFT_ARITHMETIC = 36,
+  B200PHI_MAP_LEFT_SHIFT_LOGIC = 37,
+  B200PHI_MAP_RIGHT_SHIFT_ARITHMETIC = 38,
+  B200PHI_MAP_RIGHT_SHIFT_LOGIC = 39,
   /* three operands, out = in dtype: the functors the backward kernels feed to the
    * broadcast engine (funcs/elementwise_functor.h:173-179, 478-531; gpu/reduce_kernel.cu:74-119) */
   B200PHI_MAP_EQUAL_MUL = 48,  /* in2 * T(EQUAL(in0, in1))   max_grad / min_grad: (x, out, dout) */

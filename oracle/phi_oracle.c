@@ -624,7 +624,8 @@ EXPORT int phi_oracle_map(int op, int in_dtype, float p0, float p1, int arity, i
                           void* out) {
   if (arity != map_op_arity(op) || out_rank < 0 || out_rank > 9) return 1;
   const int flt = is_float_dt(in_dtype);
-  if (op >= 32 && op <= 35 && flt) return 2;
+  if (op >= 32 && op <= 39 && flt) return 2;
+  if (op >= 36 && op <= 39 && in_dtype == DT_BOOL) return 2;
   if ((op == 57 || (op >= 64 && op != 90 && op != 92)) && !flt) return 2;
   int64_t numel = 1;
   for (int i = 0; i < out_rank; ++i) numel *= out_dims[i];
@@ -700,6 +701,26 @@ EXPORT int phi_oracle_map(int op, int in_dtype, float p0, float p1, int arity, i
         case 33: r = a | b; break;
         case 34: r = a ^ b; break;
         case 35: r = in_dtype == DT_BOOL ? !a : ~a; break;
+        /* shifts, funcs/bitwise_functors.h:49-206: count outside [0, bits) gives 0, or the sign
+         * fill for the arithmetic right shift of a signed type; the logical right shift works on
+         * the unsigned image of the storage type; the store below truncates to the storage type */
+        case 36: case 37: {
+          const int bits = (int)dt_size(in_dtype) * 8;
+          r = (b < 0 || b >= bits) ? 0 : (int64_t)((uint64_t)a << b);
+          break;
+        }
+        case 38: {
+          const int bits = (int)dt_size(in_dtype) * 8;
+          if (b < 0 || b >= bits) r = (in_dtype != DT_UINT8 && a < 0) ? -1 : 0;
+          else r = a >> b;
+          break;
+        }
+        case 39: {
+          const int bits = (int)dt_size(in_dtype) * 8;
+          const uint64_t image = bits == 64 ? (uint64_t)a : ((uint64_t)a & ((1ull << bits) - 1));
+          r = (b < 0 || b >= bits) ? 0 : (int64_t)(image >> b);
+          break;
+        }
         case 48: r = c * (a == b); break;
         case 49: r = c * (a > b); break;
         case 50: r = c * (a <= b); break;

@@ -134,6 +134,10 @@ int map_impl(int op, int rank, const int64_t* out_dims, const int64_t* const* in
             case 33: ot[n] = BitwiseOrFunctor<T>()(a, b); break;
             case 34: ot[n] = BitwiseXorFunctor<T>()(a, b); break;
             case 35: ot[n] = BitwiseNotFunctor<T>()(a); break;
+            case 36: ot[n] = BitwiseLeftShiftArithmeticFunctor<T>()(a, b); break;
+            case 37: ot[n] = BitwiseLeftShiftLogicFunctor<T>()(a, b); break;
+            case 38: ot[n] = BitwiseRightShiftArithmeticFunctor<T>()(a, b); break;
+            case 39: ot[n] = BitwiseRightShiftLogicFunctor<T>()(a, b); break;
             default: return 2;
           }
         } else {

@@ -13,7 +13,7 @@ from .ops import (  # noqa: F401
     maximum, mean, min, minimum, multiply, prod, relu, row_mean_var, scale, subtract, sum, var,
 )
 from .ops import (  # noqa: F401  -- functor plug-ins on the broadcast engine (b200phi_map)
-    abs, bitwise_and, bitwise_not, bitwise_or, bitwise_xor, ceil, cos, elu, equal, exp, expm1, floor,
+    abs, bitwise_and, bitwise_left_shift, bitwise_not, bitwise_or, bitwise_right_shift, bitwise_xor, ceil, cos, elu, equal, exp, expm1, floor,
     greater_equal, greater_than, hardsigmoid, leaky_relu, less_equal, less_than, log, log10, log1p,
     log2, log_sigmoid, logical_and, logical_not, logical_or, logical_xor, mish, not_equal,
     reciprocal, relu6, rsqrt, sigmoid, silu, sin, softplus, softsign, sqrt, square, swish, tanh,

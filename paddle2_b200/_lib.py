@@ -32,6 +32,8 @@ MAP_OPS = {
     "greater_equal": 5,
     "logical_and": 16, "logical_or": 17, "logical_xor": 18, "logical_not": 19,
     "bitwise_and": 32, "bitwise_or": 33, "bitwise_xor": 34, "bitwise_not": 35,
+    "left_shift_arithmetic": 36, "left_shift_logic": 37, "right_shift_arithmetic": 38,
+    "right_shift_logic": 39,
     "equal_mul": 48, "max_grad_x": 49, "max_grad_y": 50, "min_grad_x": 51, "min_grad_y": 52,
     "div_grad_y": 53, "equal_t": 56, "sub_exp": 57,
     "exp": 64, "log": 65, "sqrt": 66, "rsqrt": 67, "square": 68, "reciprocal": 69, "sin": 70,

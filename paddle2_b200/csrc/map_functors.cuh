@@ -14,7 +14,7 @@
 
 namespace b200phi {
 
-constexpr bool map_out_is_bool(int op) { return op < B200PHI_MAP_BITWISE_AND; }
+constexpr bool map_out_is_bool(int op) { return op < B200PHI_MAP_BITWISE_AND; }  // compare, logical
 constexpr int map_arity(int op) {
   if (op == B200PHI_MAP_LOGICAL_NOT || op == B200PHI_MAP_BITWISE_NOT) return 1;
   if (op >= B200PHI_MAP_EQUAL_MUL && op <= B200PHI_MAP_DIV_GRAD_Y) return 3;
@@ -96,6 +96,26 @@ struct MapF {
       if constexpr (std::is_same<T, Bool8>::value) return static_cast<C>(a == 0);
       else if constexpr (kInt) return static_cast<C>(~a);
       else return a;
+    } else if constexpr (kOp >= B200PHI_MAP_LEFT_SHIFT_ARITHMETIC &&
+                         kOp <= B200PHI_MAP_RIGHT_SHIFT_LOGIC) {
+      if constexpr (kInt && !std::is_same<T, Bool8>::value) {
+        constexpr int kBits = static_cast<int>(sizeof(T)) * 8;
+        const bool in_range = b >= C(0) && b < C(kBits);
+        if constexpr (kOp == B200PHI_MAP_LEFT_SHIFT_ARITHMETIC || kOp == B200PHI_MAP_LEFT_SHIFT_LOGIC) {
+          // shifted in the unsigned image of C, truncated to T by the store
+          using UC = typename std::make_unsigned<C>::type;
+          return in_range ? static_cast<C>(static_cast<UC>(a) << static_cast<int>(b)) : C(0);
+        } else if constexpr (kOp == B200PHI_MAP_RIGHT_SHIFT_ARITHMETIC) {
+          if constexpr (std::is_unsigned<T>::value) return in_range ? static_cast<C>(a >> static_cast<int>(b)) : C(0);
+          else return in_range ? static_cast<C>(a >> static_cast<int>(b)) : static_cast<C>(a < C(0) ? -1 : 0);
+        } else {
+          // logical: shift the unsigned image of the STORAGE type (logic_shift_func, :137-146)
+          using UT = typename std::make_unsigned<T>::type;
+          return in_range ? static_cast<C>(static_cast<UT>(static_cast<UT>(a) >> static_cast<int>(b))) : C(0);
+        }
+      } else {
+        return a;
+      }
     } else if constexpr (kOp == B200PHI_MAP_EQUAL_MUL) {
       return static_cast<C>(c * static_cast<C>(phi_equal<T, C>(a, b)));
     } else if constexpr (kOp == B200PHI_MAP_MAX_GRAD_X) {

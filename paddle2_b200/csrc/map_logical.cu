@@ -66,8 +66,34 @@ static int bitwise_dtype(const b200phi_map_desc* d, const BcastPlan& bp, cudaStr
   }
 }
 
+template <int kOp>
+static int shift_dtype(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s) {
+  switch (d->in_dtype) {
+    case B200PHI_UINT8:
+      return launch_map_op<kOp, uint8_t>(d, bp, s);
+    case B200PHI_INT8:
+      return launch_map_op<kOp, int8_t>(d, bp, s);
+    case B200PHI_INT16:
+      return launch_map_op<kOp, int16_t>(d, bp, s);
+    case B200PHI_INT32:
+      return launch_map_op<kOp, int32_t>(d, bp, s);
+    case B200PHI_INT64:
+      return launch_map_op<kOp, long long>(d, bp, s);
+    default:
+      return set_error(B200PHI_UNSUPPORTED, "map: shifts take uint8 / int8 / int16 / int32 / int64");
+  }
+}
+
 int map_bitwise(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s) {
   switch (d->op) {
+    case B200PHI_MAP_LEFT_SHIFT_ARITHMETIC:
+      return shift_dtype<B200PHI_MAP_LEFT_SHIFT_ARITHMETIC>(d, bp, s);
+    case B200PHI_MAP_LEFT_SHIFT_LOGIC:
+      return shift_dtype<B200PHI_MAP_LEFT_SHIFT_LOGIC>(d, bp, s);
+    case B200PHI_MAP_RIGHT_SHIFT_ARITHMETIC:
+      return shift_dtype<B200PHI_MAP_RIGHT_SHIFT_ARITHMETIC>(d, bp, s);
+    case B200PHI_MAP_RIGHT_SHIFT_LOGIC:
+      return shift_dtype<B200PHI_MAP_RIGHT_SHIFT_LOGIC>(d, bp, s);
     case B200PHI_MAP_BITWISE_AND:
       return bitwise_dtype<B200PHI_MAP_BITWISE_AND>(d, bp, s);
     case B200PHI_MAP_BITWISE_OR:

@@ -594,6 +594,16 @@ bitwise_or = _binary_map("bitwise_or")
 bitwise_xor = _binary_map("bitwise_xor")
 bitwise_not = _unary_map("bitwise_not")
 
+
+def bitwise_left_shift(x, y, is_arithmetic=True):
+    """paddle.bitwise_left_shift (BitwiseLeftShiftKernel, kps/bitwise_kernel.cu)."""
+    return _map("left_shift_arithmetic" if is_arithmetic else "left_shift_logic", [x, y])
+
+
+def bitwise_right_shift(x, y, is_arithmetic=True):
+    """paddle.bitwise_right_shift: sign-filling when is_arithmetic, zero-filling otherwise."""
+    return _map("right_shift_arithmetic" if is_arithmetic else "right_shift_logic", [x, y])
+
 exp = _unary_map("exp")
 log = _unary_map("log")
 sqrt = _unary_map("sqrt")

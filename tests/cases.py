@@ -210,6 +210,8 @@ MAP_ERROR_SHAPES = [
 COMPARE_OPS = ["equal", "not_equal", "less_than", "less_equal", "greater_than", "greater_equal"]
 LOGICAL_OPS = ["logical_and", "logical_or", "logical_xor"]
 BITWISE_OPS = ["bitwise_and", "bitwise_or", "bitwise_xor"]
+SHIFT_OPS = ["left_shift_arithmetic", "left_shift_logic", "right_shift_arithmetic", "right_shift_logic"]
+SHIFT_DTYPES = ["uint8", "int8", "int16", "int32", "int64"]
 MAP_INT_DTYPES = ["bool", "uint8", "int8", "int16", "int32", "int64"]
 MAP_ALL_DTYPES = MAP_INT_DTYPES + ["float32", "float64"]
 

@@ -112,6 +112,16 @@ def main():
         axes = [a % max(len(shape), 1) for a in axis]
         if sorted(axes) == list(range(min(axes), min(axes) + len(axes))) if axes else True:
             store[f"lse_{i}_y"] = O.logsumexp(x, axis if axis else None, keepdim, impl="ref")
+    # shifts (funcs/bitwise_functors.h:49-206): counts below 0, inside and beyond the bit width
+    for dt in cases.SHIFT_DTYPES:
+        rng = np.random.default_rng(9100)
+        bits = np.dtype(dt).itemsize * 8
+        x = cases.map_operand(rng, dt, [7, 40])
+        lo = 0 if dt == "uint8" else -3
+        y = rng.integers(lo, bits + 4, size=[40]).astype(dt)
+        store[f"shift_{dt}_x"], store[f"shift_{dt}_y"] = x, y
+        for name in cases.SHIFT_OPS:
+            store[f"shift_{dt}_{name}"] = O.map(name, [x, y], impl="ref")
     # mixed-precision add (MultiPrecisionAddFunctor): fp32 + bf16 / fp16 bit patterns
     rng = np.random.default_rng(9000)
     x = cases.map_operand(rng, "float32", [33, 257])

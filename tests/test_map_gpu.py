@@ -170,3 +170,24 @@ def test_large_shape_properties():
     assert bool(torch.all(lt ^ ge))
     assert bool(torch.all(pb.logical_not(pb.logical_and(lt, ge)) == pb.logical_or(pb.logical_not(lt), pb.logical_not(ge))))
     assert int(lt.sum()) == int((x < y).sum())
+
+
+@pytest.mark.parametrize("dt", cases.SHIFT_DTYPES)
+def test_shifts_golden_and_shapes(oracle, golden, dt):
+    """bitwise_left_shift / bitwise_right_shift, arithmetic and logical: counts below zero, in range
+    and beyond the bit width (funcs/bitwise_functors.h:49-206); bit-exact."""
+    x, y = golden[f"shift_{dt}_x"], golden[f"shift_{dt}_y"]
+    for name in cases.SHIFT_OPS:
+        got = G.to_np(ops._map(name, [G.to_dev(x), G.to_dev(y)]))
+        assert np.array_equal(got, golden[f"shift_{dt}_{name}"]), (dt, name)
+    rng = np.random.default_rng(2)
+    bits = np.dtype(dt).itemsize * 8
+    info = np.iinfo(dt)
+    xx = rng.integers(info.min, info.max, size=(129, 1031), dtype=dt, endpoint=True)
+    yy = rng.integers(0 if dt == "uint8" else -2, bits + 2, size=(1031,)).astype(dt)
+    dx, dy = G.to_dev(xx), G.to_dev(yy)
+    for arith in (True, False):
+        assert np.array_equal(G.to_np(pb.bitwise_left_shift(dx, dy, arith)),
+                              oracle.map("left_shift_arithmetic" if arith else "left_shift_logic", [xx, yy]))
+        assert np.array_equal(G.to_np(pb.bitwise_right_shift(dx, dy, arith)),
+                              oracle.map("right_shift_arithmetic" if arith else "right_shift_logic", [xx, yy]))

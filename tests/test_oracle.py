@@ -250,3 +250,10 @@ def test_mixed_add_port_matches_golden(oracle, golden):
     x = golden["mpadd_x"]
     assert np.array_equal(oracle.mixed_add(x, golden["mpadd_bf16_bits"], True), golden["mpadd_bf16_out"])
     assert np.array_equal(oracle.mixed_add(x, golden["mpadd_fp16_bits"], False), golden["mpadd_fp16_out"])
+
+
+def test_shift_port_matches_golden(oracle, golden):
+    for dt in cases.SHIFT_DTYPES:
+        x, y = golden[f"shift_{dt}_x"], golden[f"shift_{dt}_y"]
+        for name in cases.SHIFT_OPS:
+            assert np.array_equal(oracle.map(name, [x, y]), golden[f"shift_{dt}_{name}"]), (dt, name)
