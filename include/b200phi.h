@@ -401,6 +401,17 @@ B200PHI_API int b200phi_comm_destroy(void* comm);
 B200PHI_API int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count,
                            void* comm, void* stream);
 
+/* argmax / argmin over the SHARDED leading axis.  d describes the local shard and must reduce
+ * axis 0; row_offset is the global index of the shard's first row.  Each rank reduces its rows to
+ * (value, global index) per column, the small pairs are all-gathered (NCCL has no arg-reduce)
+ * and every rank selects with the reference's tie rule: better value, else lowest index
+ * (cub::ArgMax as used by gpu/arg_min_max_kernel.cu:58-83).  d->out / d->max_out
+ * receive the replicated result.  nranks <= 1 or comm == NULL: plain b200phi_argreduce. */
+B200PHI_API size_t b200phi_sharded_argreduce_workspace(const b200phi_argreduce_desc* d, int nranks);
+B200PHI_API int b200phi_sharded_argreduce(const b200phi_argreduce_desc* d, int64_t row_offset,
+                                          int nranks, void* comm, void* workspace,
+                                          size_t workspace_bytes, void* stream);
+
 /* ---- fused variant: local reduce + exchange over NVLink peer memory in ONE kernel ---- */
 
 /* Replaces the same reference pair as b200phi_sharded_reduce

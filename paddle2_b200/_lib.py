@@ -204,6 +204,8 @@ EXPORTS = [
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
     "b200phi_sharded_reduce",
+    "b200phi_sharded_argreduce_workspace",
+    "b200phi_sharded_argreduce",
     "b200phi_p2p_buffer_bytes",
     "b200phi_p2p_alloc",
     "b200phi_p2p_open",
@@ -248,6 +250,11 @@ def lib():
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]
     L.b200phi_sharded_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_int64, C.c_void_p, C.c_void_p]
+    L.b200phi_sharded_argreduce_workspace.restype = C.c_size_t
+    L.b200phi_sharded_argreduce_workspace.argtypes = [C.POINTER(ArgReduceDesc), C.c_int]
+    L.b200phi_sharded_argreduce.restype = C.c_int
+    L.b200phi_sharded_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_int64, C.c_int, C.c_void_p,
+                                            C.c_void_p, C.c_size_t, C.c_void_p]
     L.b200phi_p2p_buffer_bytes.restype = C.c_size_t
     L.b200phi_p2p_buffer_bytes.argtypes = [C.c_int, C.c_int64, C.c_int64]
     L.b200phi_p2p_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]

@@ -31,6 +31,7 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t);
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                             cudaStream_t);
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
   const char* (*GetErrorString)(ncclResult_t);
   bool ok;
   std::string why;
@@ -62,6 +63,7 @@ static NcclApi* nccl_api() {
     B200PHI_SYM(CommInitRank, "ncclCommInitRank")
     B200PHI_SYM(CommDestroy, "ncclCommDestroy")
     B200PHI_SYM(AllReduce, "ncclAllReduce")
+    B200PHI_SYM(AllGather, "ncclAllGather")
     B200PHI_SYM(GetErrorString, "ncclGetErrorString")
 #undef B200PHI_SYM
     api.ok = true;
@@ -175,6 +177,16 @@ int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, voi
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_status(e);
   }
+  return B200PHI_OK;
+}
+
+// byte-wise all-gather on `stream` (used by the sharded arg-reduce)
+int comm_all_gather_bytes(const void* send, void* recv, size_t bytes_per_rank, void* comm,
+                          cudaStream_t stream) {
+  NcclApi* a = nccl_api();
+  if (!a->ok) return set_error(B200PHI_NCCL_ERROR, a->why);
+  ncclResult_t r = a->AllGather(send, recv, bytes_per_rank, ncclChar, static_cast<ncclComm_t>(comm), stream);
+  if (r != ncclSuccess) return nccl_status(a, r);
   return B200PHI_OK;
 }
 

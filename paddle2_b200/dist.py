@@ -52,6 +52,20 @@ def global_count(local_rows, group=None):
     return int(t.item())
 
 
+def row_offset_of(local_rows, group=None):
+    """Global index of this rank's first row: exclusive prefix sum of every rank's row count
+    (host-side, over the rendezvous group; works with gloo and nccl alike)."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 0
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    counts = [None] * world
+    dist.all_gather_object(counts, int(local_rows), group=group)
+    off = 0
+    for r in range(rank):
+        off += counts[r]
+    return off
+
+
 class ShardedReducer:
     """Owns one NCCL communicator created through the C ABI (b200phi_comm_*)."""
 
@@ -121,6 +135,47 @@ class ShardedReducer:
 
     def sum(self, x_local, **kw):  # noqa: A003
         return self.reduce(L.SUM, x_local, **kw)
+
+    def argreduce(self, op, x_local, row_offset=None, dtype="int64", want_value=False):
+        """argmax / argmin over axis 0 of the row-sharded tensor; every rank gets the global row
+        index per column (lowest index on ties) and, optionally, the extreme value.
+        `row_offset`: global index of this shard's first row; by default the exclusive prefix sum
+        of the shards' row counts, exchanged once over the rendezvous group."""
+        _ops._require_cuda(x_local)
+        x = x_local.contiguous()
+        if x.dim() < 1:
+            raise ValueError("sharded argreduce needs rank >= 1")
+        if row_offset is None:
+            row_offset = row_offset_of(x.shape[0], self.group)
+        idx_dtype = _ops._to_torch_dtype(dtype)
+        out = torch.empty(x.shape[1:], dtype=idx_dtype, device=x.device)
+        val = torch.empty(x.shape[1:], dtype=x.dtype, device=x.device) if want_value else None
+        d = L.ArgReduceDesc()
+        d.op = op
+        d.in_dtype = _ops._phi_dtype(x.dtype)
+        d.index_dtype = _ops._phi_dtype(idx_dtype)
+        d.rank = x.dim()
+        for i, s in enumerate(x.shape):
+            d.dims[i] = s
+        d.axis = 0
+        d.flatten = 0
+        d.x = x.data_ptr()
+        d.out = out.data_ptr()
+        d.max_out = val.data_ptr() if want_value else None
+        lib = L.lib()
+        with torch.cuda.device(x.device):
+            ws_bytes = lib.b200phi_sharded_argreduce_workspace(C.byref(d), self.world)
+            ws = torch.empty(max(ws_bytes, 256), dtype=torch.uint8, device=x.device)
+            stream = C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            L.check(lib.b200phi_sharded_argreduce(C.byref(d), int(row_offset), self.world, self.comm,
+                                                  ws.data_ptr(), ws.numel(), stream))
+        return (out, val) if want_value else out
+
+    def argmax(self, x_local, **kw):
+        return self.argreduce(L.ARGMAX, x_local, **kw)
+
+    def argmin(self, x_local, **kw):
+        return self.argreduce(L.ARGMIN, x_local, **kw)
 
 
 class P2PReducer:

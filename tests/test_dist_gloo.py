@@ -50,6 +50,19 @@ def _worker(rank, world, port, ret):
         # sharded mean = allreduced sum / GLOBAL count
         mean = partial.numpy() / np.float32(pdist.global_count(count))
         np.testing.assert_allclose(mean, O.reduce("mean", full, [0]), rtol=1e-5)
+        # sharded argmax: per-rank (value, global index) pairs, all-gathered, lowest index on ties
+        assert pdist.row_offset_of(count) == start
+        ti = np.random.default_rng(7).integers(0, 4, size=(total_rows, cols)).astype(np.int64)
+        lt = ti[start:start + count]
+        li = O.argreduce("argmax", lt, 0) + pdist.row_offset_of(count)   # stand-in for the GPU kernel
+        lv = O.reduce("max", lt, [0])
+        pairs = [None] * world
+        dist.all_gather_object(pairs, (lv, li))
+        bv, bi = pairs[0]
+        for v, i in pairs[1:]:
+            take = (v > bv) | ((v == bv) & (i < bi))
+            bv, bi = np.where(take, v, bv), np.where(take, i, bi)
+        assert np.array_equal(bi, O.argreduce("argmax", ti, 0))
         # single-rank ShardedReducer never creates a communicator
         ret[rank] = "ok"
     finally:

@@ -63,6 +63,18 @@ def _worker(rank, world, port, ret):
         dist.all_gather_object(gathered, fused.cpu().numpy().tobytes())
         assert all(b == gathered[0] for b in gathered)
         p2p.close()
+        # argmax / argmin across the shards: ties span ranks, the lowest GLOBAL row must win
+        ti = np.random.default_rng(7).integers(0, 5, size=(total_rows, cols)).astype(np.int64)
+        xs = torch.from_numpy(ti[start:start + count]).cuda()
+        gi, gv = red.argmax(xs, want_value=True)
+        assert np.array_equal(gi.cpu().numpy(), O.argreduce("argmax", ti, 0))
+        assert np.array_equal(gv.cpu().numpy(), ti.max(0))
+        gi = red.argmin(x, dtype="int32")
+        assert gi.dtype == torch.int32
+        assert np.array_equal(gi.cpu().numpy(), O.argreduce("argmin", full, 0, dtype=np.int32))
+        xb = torch.from_numpy(full[start:start + count]).cuda().bfloat16()     # bf16: natural ties
+        fb = torch.from_numpy(full).bfloat16().float().numpy()
+        assert np.array_equal(red.argmax(xb).cpu().numpy(), O.argreduce("argmax", fb, 0))
         red.close()
         ret[rank] = "ok"
     finally:
