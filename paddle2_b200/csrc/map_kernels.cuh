@@ -239,7 +239,10 @@ __global__ void __launch_bounds__(kBlock) map_generic_kernel(MapGenericParams<Ar
 template <typename TI, typename TO, typename F, int Arity>
 int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t stream) {
   constexpr int VE = VecOf<TI>::kElems;
-  if (bp.use_rows_kernel) {
+  // The row kernel walks a lone operand as a stream (no run-time mask is built for arity 1); a
+  // unary op whose operand is broadcast along the innermost dim goes through the generic walk.
+  const bool unary_splat = Arity == 1 && bp.stride[0][bp.ndim - 1] == 0 && bp.inner > 1;
+  if (bp.use_rows_kernel && !unary_splat) {
     MapRowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
     p.out = d->out;

@@ -191,3 +191,15 @@ def test_shifts_golden_and_shapes(oracle, golden, dt):
                               oracle.map("left_shift_arithmetic" if arith else "left_shift_logic", [xx, yy]))
         assert np.array_equal(G.to_np(pb.bitwise_right_shift(dx, dy, arith)),
                               oracle.map("right_shift_arithmetic" if arith else "right_shift_logic", [xx, yy]))
+
+
+def test_unary_into_a_larger_shape():
+    """a unary functor whose operand is broadcast (the expand form of reduce_grad.h:30-42): splat along
+    the row, splat across rows, and a single element"""
+    x = torch.linspace(-2, 2, 37)
+    for shape, src in (((5, 37), x), ((37, 40), x.reshape(37, 1)), ((3, 7, 9), x[:1].reshape(1, 1, 1)),
+                       ((6, 1, 37), x.reshape(1, 1, 37))):
+        got = ops._map("exp", [src.cuda()], out_shape=list(shape)).cpu()
+        assert torch.allclose(got, torch.exp(src).expand(shape), rtol=1e-6)
+        gotb = ops._map("logical_not", [src.cuda()], out_shape=list(shape)).cpu()
+        assert torch.equal(gotb, (src == 0).expand(shape))
