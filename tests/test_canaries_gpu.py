@@ -107,3 +107,77 @@ def test_arg_and_rowstats_outputs_stay_in_bounds():
     torch.cuda.synchronize()
     assert torch.equal(om, m) and torch.equal(ov, v)
     assert _intact(rawm, 999 * 2) and _intact(rawv, 999 * 2)
+
+
+def _fill_views(desc_views, tensors):
+    for view, t in zip(desc_views, tensors):
+        view.rank = t.dim()
+        for j, s in enumerate(t.shape):
+            view.dims[j] = s
+        view.data = t.data_ptr()
+
+
+@pytest.mark.parametrize("xs,ys", [((257, 1031), (1031,)), ((64, 3, 501), (3, 1)), ((1000, 7), (1000, 1)),
+                                   ((10, 3, 1, 4), (10, 1, 12, 1)), ((33, 4099), (33, 4099))])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.int64, torch.uint8])
+def test_map_outputs_stay_in_bounds(xs, ys, dtype):
+    """compare writes a packed group of bool bytes per input vector (2..16 bytes): odd widths and
+    unaligned rows must not spill; same for the ternary functor's same-dtype output"""
+    x = (torch.rand(xs, device="cuda") * 9).to(dtype)
+    y = (torch.rand(ys, device="cuda") * 9).to(dtype)
+    want = pb.less_equal(x, y)
+    raw, out = _guarded(tuple(want.shape), torch.bool)
+    d = L.MapDesc()
+    d.op, d.in_dtype, d.out_dtype, d.arity, d.axis = L.MAP_OPS["less_equal"], pb.ops._phi_dtype(dtype), 0, 2, -1
+    _fill_views(d.in_, (x, y))
+    d.out_rank = want.dim()
+    for j, s in enumerate(want.shape):
+        d.out_dims[j] = s
+    d.out = out.data_ptr()
+    L.check(L.lib().b200phi_map(C.byref(d), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    assert _intact(raw, want.numel())
+    if dtype in (torch.float32, torch.bfloat16, torch.int64):
+        g = (torch.rand(tuple(want.shape), device="cuda") * 3).to(dtype)
+        want3 = pb.ops._map("max_grad_x", [x.expand(want.shape).contiguous(), y.expand(want.shape).contiguous(), g])
+        raw3, out3 = _guarded(tuple(want.shape), dtype)
+        d3 = L.MapDesc()
+        d3.op, d3.in_dtype, d3.out_dtype, d3.arity, d3.axis = L.MAP_OPS["max_grad_x"], pb.ops._phi_dtype(dtype), 0, 3, -1
+        _fill_views(d3.in_, (x, y, g))
+        d3.out_rank = want.dim()
+        for j, s in enumerate(want.shape):
+            d3.out_dims[j] = s
+        d3.out = out3.data_ptr()
+        L.check(L.lib().b200phi_map(C.byref(d3), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        torch.cuda.synchronize()
+        assert torch.equal(out3, want3)
+        assert _intact(raw3, want3.numel() * want3.element_size())
+
+
+@pytest.mark.parametrize("rows,cols", [(1027, 513), (3, 99991), (100003, 3), (64, 32000), (5, 4099)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_logsumexp_and_mixed_add_stay_in_bounds(rows, cols, dtype):
+    x = torch.randn((rows, cols), device="cuda").to(dtype)
+    want = pb.ops.logsumexp(x, -1)
+    raw, out = _guarded((rows,), dtype)
+    d = L.LogsumexpDesc()
+    d.dtype, d.rows, d.cols, d.x, d.out = pb.ops._phi_dtype(dtype), rows, cols, x.data_ptr(), out.data_ptr()
+    L.check(L.lib().b200phi_logsumexp(C.byref(d), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    assert _intact(raw, rows * want.element_size())
+    if dtype == torch.bfloat16:
+        acc = torch.randn((rows, cols), device="cuda")
+        want2 = acc + x.float()
+        raw2, out2 = _guarded((rows, cols), torch.float32)
+        m = L.MixedAddDesc()
+        m.y_dtype = L.BFLOAT16
+        _fill_views((m.x, m.y), (acc, x))
+        m.out_rank = 2
+        m.out_dims[0], m.out_dims[1] = rows, cols
+        m.out = out2.data_ptr()
+        L.check(L.lib().b200phi_mixed_add(C.byref(m), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        torch.cuda.synchronize()
+        assert torch.equal(out2, want2)
+        assert _intact(raw2, rows * cols * 4)
