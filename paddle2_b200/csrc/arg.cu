@@ -197,7 +197,7 @@ __device__ __forceinline__ ArgPair<V> arg_span(const T* __restrict__ row, long l
 }
 
 // post == 1: [rows, n], G threads per row (as in row_reduce_kernel).
-template <typename T, typename V, bool kMax, int G, bool kAligned>
+template <typename T, typename V, bool kMax, int G, bool kAligned, int U = 8>
 __global__ void __launch_bounds__(kBlock)
     arg_row_kernel(const T* __restrict__ x, long long rows, long long n, void* out, int index_dtype,
                    void* val_out) {
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(kBlock)
   int parity = 0;
   for (long long row = static_cast<long long>(blockIdx.x) * kRowsPerCta + grp; row < rows;
        row += static_cast<long long>(gridDim.x) * kRowsPerCta) {
-    ArgPair<V> p = arg_span<T, V, kMax, G, 8, kAligned>(x + row * n, n, g);
+    ArgPair<V> p = arg_span<T, V, kMax, G, U, kAligned>(x + row * n, n, g);
     p = warp_arg<V, Op>(p);
     if constexpr (G > 32) {
       V* bv = s_v + parity * kWarps;
@@ -297,18 +297,29 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
                       cudaStream_t stream) {
   if (g.post == 1) {
     const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
-    // threads per row: about 32 vectors per thread (measured on C3b, 4000 vectors per row:
-    // G=128 reads 6.2 TB/s, G=256 6.0, G=64 and 32 5.7)
+    // threads per row: about 32 vectors per thread, 8 loads in flight each (measured on C3b,
+    // 4000 vectors per row: G=128 reads 6.22 TB/s, G=256 5.98, G=64 5.64).  Long rows of 16-bit
+    // elements do better with the whole CTA on one row and 4 loads in flight (40 registers, six
+    // CTAs per SM): 6.38 TB/s.
     int G = 32;
     while (G < 256 && static_cast<long long>(G) * 512 < row_bytes) G <<= 1;
     static const int force_g = getenv("B200PHI_ARG_G") ? atoi(getenv("B200PHI_ARG_G")) : 0;
+    static const int force_u = getenv("B200PHI_ARG_U") ? atoi(getenv("B200PHI_ARG_U")) : 0;
+    int arg_u = 8;
+    if (sizeof(T) == 2 && row_bytes > 32768 && !force_g) {
+      G = 256;
+      arg_u = 4;
+    }
     if (force_g == 32 || force_g == 64 || force_g == 128 || force_g == 256) G = force_g;
+    if (force_u == 4 || force_u == 8) arg_u = force_u;
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
     long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     const unsigned grid = static_cast<unsigned>(ctas);
 #define B200PHI_ARG_ROW(GG)                                                                          \
-  if (aligned)                                                                                       \
+  if (aligned && arg_u == 4)                                                                         \
+    arg_row_kernel<T, V, kMax, GG, true, 4><<<grid, kBlock, 0, stream>>>(x, g.pre, g.n, out, index_dtype, val_out); \
+  else if (aligned)                                                                                  \
     arg_row_kernel<T, V, kMax, GG, true><<<grid, kBlock, 0, stream>>>(x, g.pre, g.n, out, index_dtype, val_out); \
   else                                                                                               \
     arg_row_kernel<T, V, kMax, GG, false><<<grid, kBlock, 0, stream>>>(x, g.pre, g.n, out, index_dtype, val_out);
