@@ -108,6 +108,77 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Rows of up to ~16 KiB (hidden sizes, feature maps: the LayerNorm / softmax / per-channel
+// widths).  The cascade in reduce_span_aligned serves such a row in two or three dependent rounds
+// of one to four loads (a 1568-byte bf16 row: 3 vectors per lane, read at 3.4 TB/s; a 6 KiB row
+// 2.6 TB/s).  Here a group of G threads takes R rows at a time and issues ALL of their loads --
+// NV predicated 16-byte loads per row per thread, R * NV = 8 in flight -- in one round; the R
+// partial results then share one shuffle tree pass (interleaved chains) and one barrier.
+template <typename T, typename Acc, typename Op, int G, int NV, int R>
+__global__ void __launch_bounds__(kBlock)
+    row_batch_kernel(const T* __restrict__ x, long long rows, long long nvec, Epilogue ep) {
+  constexpr int VE = VecOf<T>::kElems;
+  constexpr int kGroups = kBlock / G;
+  constexpr int kW = G / 32;
+  __shared__ Acc smem[2][R][kWarps];
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long cols = nvec * VE;
+  int parity = 0;
+  for (long long r0 = (static_cast<long long>(blockIdx.x) * kGroups + grp) * R; r0 < rows;
+       r0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+    V16 buf[R][NV];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + (r0 + r) * cols);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = g + static_cast<long long>(k) * G;
+        if (r0 + r < rows && v < nvec) buf[r][k] = ldg_stream16(vp + v);
+      }
+    }
+    Acc a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      Acc acc[kFoldLanes];
+#pragma unroll
+      for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = g + static_cast<long long>(k) * G;
+        if (r0 + r < rows && v < nvec) fold_vec<Acc, Op, T, kFoldLanes>(buf[r][k], acc);
+      }
+      a[r] = fold_lanes<Acc, Op>(acc);
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) a[r] = Op::combine(a[r], shfl_xor(a[r], m));
+    }
+    if constexpr (G > 32) {
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) smem[parity][r][warp] = a[r];
+      }
+      group_barrier<G>();
+      if (g == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          a[r] = smem[parity][r][grp * kW];
+#pragma unroll
+          for (int w = 1; w < kW; ++w) a[r] = Op::combine(a[r], smem[parity][r][grp * kW + w]);
+        }
+      }
+      parity ^= 1;
+    }
+    if (g == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (r0 + r < rows) store_final<Op>(ep, r0 + r, a[r]);
+    }
+  }
+}
+
 // Short rows (softmax / classifier widths: a few to ~128 elements): G = 1, 2, 4, 8 or 16 lanes
 // per row, 32/G rows per warp, scalar loads (consecutive rows are contiguous, so a warp still
 // reads one contiguous span and L1 serves the strided revisits), xor-shuffle combine inside the

@@ -49,6 +49,23 @@ int launch_reduce_typed(const ReduceArgs& a) {
       }
 #undef B200PHI_ROW
       break;
+    case kRowBatch: {
+      const long long nvec = p.cols / VecOf<T>::kElems;
+#define B200PHI_ROWB(GG, NN, RR) \
+  row_batch_kernel<T, Acc, Op, GG, NN, RR><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, nvec, ep)
+      if (p.G == 32 && p.nv == 2)
+        B200PHI_ROWB(32, 2, 4);
+      else if (p.G == 32 && p.nv == 4)
+        B200PHI_ROWB(32, 4, 2);
+      else if (p.G == 32)
+        B200PHI_ROWB(32, 8, 1);
+      else if (p.G == 64)
+        B200PHI_ROWB(64, 8, 1);
+      else
+        B200PHI_ROWB(128, 8, 1);
+#undef B200PHI_ROWB
+      break;
+    }
     case kRowSmall: {
       const int c = static_cast<int>(p.cols);
       switch (p.G) {

@@ -48,6 +48,10 @@ Tunables default_tunables(int sm_count) {
   t.row_bytes_per_thread = env_ll("B200PHI_ROW_BYTES_PER_THREAD", 64);
   t.ctas_per_sm = static_cast<int>(env_ll("B200PHI_CTAS_PER_SM", 4));  // measured: profiles/r01_microbench.md
   t.force_kind = static_cast<int>(env_ll("B200PHI_FORCE_KIND", -1));
+  t.allow_narrow_out = 0;
+  t.no_two_stage = static_cast<int>(env_ll("B200PHI_NO_TWO_STAGE", 0));
+  t.no_row_batch = static_cast<int>(env_ll("B200PHI_NO_ROW_BATCH", 0));
+  t.row_batch_waves = static_cast<int>(env_ll("B200PHI_ROW_BATCH_WAVES", 8));
   return t;
 }
 
@@ -62,6 +66,32 @@ static int pow2_ceil(long long v) {
 static int fail(std::string* err, int code, const std::string& msg) {
   if (err) *err = msg;
   return code;
+}
+
+void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tmp,
+                     b200phi_reduce_desc* d1, b200phi_reduce_desc* d2) {
+  *d1 = b200phi_reduce_desc();
+  d1->op = p.ts_op1;
+  d1->in_dtype = d->in_dtype;
+  d1->out_dtype = p.ts_tmp_dtype;
+  d1->rank = 2;
+  d1->dims[0] = p.tsA * p.tsK;
+  d1->dims[1] = p.tsB;
+  d1->naxes = 1;
+  d1->axes[0] = 1;
+  d1->x = d->x;
+  d1->out = tmp;
+  *d2 = b200phi_reduce_desc();
+  d2->op = p.ts_op2;
+  d2->in_dtype = p.ts_tmp_dtype;
+  d2->out_dtype = p.out_dtype;
+  d2->rank = 2;
+  d2->dims[0] = p.tsA;
+  d2->dims[1] = p.tsK;
+  d2->naxes = 1;
+  d2->axes[0] = 0;
+  d2->x = tmp;
+  d2->out = d->out;
 }
 
 int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, std::string* err) {
@@ -84,11 +114,14 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     return fail(err, B200PHI_INVALID_ARGUMENT, "any/all write BOOL");
   if (!logical && out_dtype == B200PHI_BOOL && d->in_dtype != B200PHI_BOOL)
     return fail(err, B200PHI_UNSUPPORTED, "BOOL output needs any/all or a BOOL input");
-  if ((out_dtype == B200PHI_FLOAT16 || out_dtype == B200PHI_BFLOAT16) && out_dtype != d->in_dtype)
+  if ((out_dtype == B200PHI_FLOAT16 || out_dtype == B200PHI_BFLOAT16) && out_dtype != d->in_dtype &&
+      !t.allow_narrow_out)
     return fail(err, B200PHI_UNSUPPORTED,
                 "16-bit float output from a different input dtype is not built");
 
-  const bool sum_like = d->op == B200PHI_SUM || d->op == B200PHI_MEAN;
+  const bool sum_like = d->op == B200PHI_SUM || d->op == B200PHI_MEAN || d->op == B200PHI_SUM_ABS ||
+                        d->op == B200PHI_SUM_SQUARE || d->op == B200PHI_L2_NORM ||
+                        d->op == B200PHI_COUNT_NONZERO;
   if (!sum_like && !logical && out_dtype != d->in_dtype)
     return fail(err, B200PHI_UNSUPPORTED, "max/min/prod keep the input dtype");
   if (d->op >= B200PHI_SUM_ABS && !dtype_is_float(d->in_dtype))
@@ -202,6 +235,73 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   }
   if (kind == kCol && p->R < 16) kind = kGeneric;
 
+  // ---- [A, K, B] with A and B reduced: row kernel into scratch, then column kernel -------
+  if (kind == kGeneric && red_numel > 1 && m == 3 && isred[0] && !isred[1] && isred[2] &&
+      ext[2] >= 16 && !t.no_two_stage && t.force_kind < 0) {
+    int op1 = -1, op2 = -1, tmp_dtype = B200PHI_UNDEFINED;
+    const int acc_dtype = p->acc == 0 ? B200PHI_FLOAT32 : (p->acc == 1 ? B200PHI_FLOAT64 : B200PHI_INT64);
+    const bool wide_in = esize >= 4;
+    switch (d->op) {
+      case B200PHI_SUM:
+      case B200PHI_SUM_ABS:
+      case B200PHI_SUM_SQUARE:
+      case B200PHI_COUNT_NONZERO:
+        op1 = d->op, op2 = B200PHI_SUM, tmp_dtype = acc_dtype;
+        break;
+      case B200PHI_MEAN:  // equal-sized groups: the mean of the row means is the mean
+        if (p->acc <= 1) op1 = op2 = B200PHI_MEAN, tmp_dtype = acc_dtype;
+        break;
+      case B200PHI_MAX:
+      case B200PHI_AMAX:
+      case B200PHI_MIN:
+      case B200PHI_AMIN:
+        op1 = op2 = d->op, tmp_dtype = d->in_dtype;
+        break;
+      case B200PHI_MAX_ABS:
+        op1 = d->op, op2 = B200PHI_MAX, tmp_dtype = d->in_dtype;
+        break;
+      case B200PHI_MIN_ABS:
+        op1 = d->op, op2 = B200PHI_MIN, tmp_dtype = d->in_dtype;
+        break;
+      case B200PHI_PROD:  // a 16-bit intermediate would round the partial products
+        if (wide_in) op1 = op2 = d->op, tmp_dtype = d->in_dtype;
+        break;
+      case B200PHI_ANY:
+      case B200PHI_ALL:
+        op1 = op2 = d->op, tmp_dtype = B200PHI_BOOL;
+        break;
+      default:  // L2_NORM: the sqrt belongs after the second stage only
+        break;
+    }
+    if (op1 >= 0) {
+      p->kind = kTwoStage;
+      p->tsA = ext[0];
+      p->tsK = ext[1];
+      p->tsB = ext[2];
+      p->ts_op1 = op1;
+      p->ts_op2 = op2;
+      p->ts_tmp_dtype = tmp_dtype;
+      p->ts_tmp_bytes = static_cast<size_t>(round_up(ext[0] * ext[1] * static_cast<long long>(dtype_size(tmp_dtype)), 256));
+      b200phi_reduce_desc d1, d2;
+      two_stage_descs(*p, d, reinterpret_cast<void*>(static_cast<uintptr_t>(256)), &d1, &d2);
+      Tunables t2 = t;
+      t2.allow_narrow_out = 1;
+      ReducePlan p1, p2;
+      int rc = plan_reduce(&d1, t, &p1, err);
+      if (rc != B200PHI_OK) return rc;
+      rc = plan_reduce(&d2, t2, &p2, err);
+      if (rc != B200PHI_OK) return rc;
+      p->ts_ws1_bytes = static_cast<size_t>(round_up(static_cast<long long>(p1.ws_total_bytes), 256));
+      p->ts_ws2_bytes = static_cast<size_t>(round_up(static_cast<long long>(p2.ws_total_bytes), 256));
+      p->ws_partial_bytes = p->ts_tmp_bytes;
+      p->ws_ticket_bytes = 0;
+      p->ws_total_bytes = p->ts_tmp_bytes + p->ts_ws1_bytes + p->ts_ws2_bytes;
+      p->grid_x = p1.grid_x;
+      p->grid_y = p1.grid_y;
+      return B200PHI_OK;
+    }
+  }
+
   if (kind == kRowBlock) {
     const long long row_bytes = p->cols * static_cast<long long>(esize);
     // threads per row: each thread should own about 4 16-byte vectors of the row
@@ -225,6 +325,23 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       }
     }
     if (kind != kRowSplit) kind = (G == 256) ? kRowBlock : kRowWarp;
+    // rows under 16 KiB: every load of R rows in one round (row_batch_kernel)
+    const long long nvec_row = row_bytes / 16;
+    if (kind != kRowSplit && p->aligned && nvec_row < 1024 && p->cols > 128 && !t.no_row_batch &&
+        t.force_kind < 0) {
+      kind = kRowBatch;
+      if (nvec_row <= 64) {
+        p->G = 32, p->nv = 2, p->rpg = 4;
+      } else if (nvec_row <= 128) {
+        p->G = 32, p->nv = 4, p->rpg = 2;
+      } else if (nvec_row <= 256) {
+        p->G = 32, p->nv = 8, p->rpg = 1;
+      } else if (nvec_row <= 512) {
+        p->G = 64, p->nv = 8, p->rpg = 1;
+      } else {
+        p->G = 128, p->nv = 8, p->rpg = 1;
+      }
+    }
     // short rows: fewer than 32 lanes per row (about 8 elements per lane)
     if (kind == kRowWarp && p->cols <= 128 && p->rows >= 64 && t.force_kind < 0) {
       int g = pow2_ceil(ceil_div(p->cols, 8));
@@ -242,6 +359,15 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     case kRowSmall: {
       const long long ctas = ceil_div(p->rows, 256 / p->G);
       p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, 0x7fffffffLL));
+      p->grid_y = 1;
+      break;
+    }
+    case kRowBatch: {
+      const long long per_cta = static_cast<long long>(256 / p->G) * p->rpg;
+      long long ctas = ceil_div(p->rows, per_cta);
+      const long long cap = static_cast<long long>(t.sm_count) * 8 * std::max(1, t.row_batch_waves);
+      if (ctas > cap) ctas = cap;  // grid-stride beyond that
+      p->grid_x = static_cast<unsigned>(ctas);
       p->grid_y = 1;
       break;
     }

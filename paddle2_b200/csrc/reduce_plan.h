@@ -26,7 +26,10 @@ enum ReduceKind {
   kRowSplit = 2,  // [rows, cols], several CTAs per row + last-block finalise
   kCol = 3,       // [outer, R, inner]
   kGeneric = 4,   // anything else (also the reduce_num == 1 cast/copy)
-  kRowSmall = 5   // [rows, cols] with short rows: G < 32 lanes per row
+  kRowSmall = 5,  // [rows, cols] with short rows: G < 32 lanes per row
+  kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
+  kTwoStage = 6   // [A, K, B] with A and B reduced (per-channel statistics of [N,C,H,W]): the
+                  // row kernel over [A*K, B] into scratch, then the column kernel over [A, K]
 };
 
 struct ReducePlan {
@@ -40,6 +43,7 @@ struct ReducePlan {
   long long rows, cols, seg;
   int G;  // threads per row: 32, 64, 128 or 256
   int aligned;  // every row starts 16-byte aligned and is a whole number of 16-byte vectors
+  int nv, rpg;  // kRowBatch: 16-byte loads per row per thread, rows per group per round
   // col kind
   long long outer, R, inner, tiles, rows_per_split;
   int vec;  // elements per 16-byte vector on the col vector path, else 1
@@ -54,7 +58,15 @@ struct ReducePlan {
   size_t ws_partial_bytes;  // first region of the workspace
   size_t ws_ticket_bytes;   // second region (256-byte aligned start)
   size_t ws_total_bytes;
+  // two-stage kind: extents, the op / dtype of each stage, and how the workspace is cut
+  long long tsA, tsK, tsB;
+  int ts_op1, ts_op2, ts_tmp_dtype;
+  size_t ts_tmp_bytes, ts_ws1_bytes, ts_ws2_bytes;
 };
+
+// The two reductions a kTwoStage plan stands for; `tmp` is the [A*K] intermediate.
+void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tmp,
+                     b200phi_reduce_desc* d1, b200phi_reduce_desc* d2);
 
 size_t dtype_size(int dtype);
 bool dtype_known(int dtype);
@@ -66,6 +78,10 @@ struct Tunables {
   long long row_bytes_per_thread;  // a row gets ~row_bytes / this many threads (pow2, 32..256)
   int ctas_per_sm;          // resident CTAs per SM the split heuristics aim for
   int force_kind;           // -1, or a ReduceKind to force where legal (testing)
+  int allow_narrow_out;     // internal: a 16-bit float result from a wider intermediate (stage 2)
+  int no_two_stage;         // env B200PHI_NO_TWO_STAGE: keep [A,K,B] patterns on the generic kernel
+  int no_row_batch;         // env B200PHI_NO_ROW_BATCH: keep medium rows on row_reduce_kernel
+  int row_batch_waves;      // env B200PHI_ROW_BATCH_WAVES: grid cap = SMs * 8 * this
 };
 Tunables default_tunables(int sm_count);
 

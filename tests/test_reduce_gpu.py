@@ -159,3 +159,60 @@ def test_cast_shortcut(oracle):
     x = np.random.default_rng(2).random((1000, 37)).astype(np.float32) * 100
     assert np.array_equal(G.to_np(pb.cast(G.to_dev(x), "int64")), x.astype(np.int64))
     assert np.array_equal(G.to_np(pb.cast(G.to_dev(x), "float64")), x.astype(np.float64))
+
+
+# ---- per-channel pattern [A, K, B] with A and B reduced (two-stage plan) -------------------------
+@pytest.mark.parametrize("shape,axis", [((16, 8, 14, 14), [0, 2, 3]), ((33, 5, 1000), [0, 2]), ((2, 64, 4099), (0, 2)),
+                                        ((300, 3, 17), [0, 2]), ((4, 6, 1, 32), [0, 3])])
+@pytest.mark.parametrize("dt", ["float32", "float64", "int32", "int64", "bool"])
+def test_per_channel_reductions(oracle, shape, axis, dt):
+    """sum / mean / max / min / prod / any / all over (0, 2, ...) keeping the channel axis: the row
+    kernel into scratch, then the column kernel.  Integer and bool results are bit-exact."""
+    rng = np.random.default_rng(11)
+    axis = list(axis)
+    ops_for = {"float32": ["sum", "mean", "max", "min", "prod", "any", "all"],
+               "float64": ["sum", "mean", "max", "prod"], "int32": ["sum", "max", "min", "any"],
+               "int64": ["sum", "min", "prod", "all"], "bool": ["sum", "any", "all"]}[dt]
+    for op in ops_for:
+        kind = "logical" if op in ("any", "all") else ("prod" if op == "prod" else "uniform")
+        x = cases.make_input(rng, dt, shape, kind)
+        if op == "prod" and dt.startswith("float"):
+            x = (0.9 + 0.2 * rng.random(shape)).astype(dt)
+        for keepdim in (False, True):
+            odt = oracle.sum_out_dtype(x.dtype) if op == "sum" else None   # int32 / bool sum into int64
+            want = oracle.reduce(op, x, axis, keepdim, out_dtype=odt)
+            got = G.to_np(getattr(pb, op)(G.to_dev(x), axis=axis, keepdim=keepdim))
+            assert got.shape == want.shape and got.dtype == want.dtype, (op, dt)
+            if dt.startswith("float") and op == "prod":
+                # n factors = n roundings in either order: the two products drift apart like sqrt(n) ulp
+                n = x.size // max(want.size, 1)
+                eps = 6e-8 if dt == "float32" else 1.2e-16
+                np.testing.assert_allclose(got, want, rtol=max(G.FP32_RTOL if dt == "float32" else 1e-12,
+                                                               4 * eps * np.sqrt(n)))
+            elif dt.startswith("float") and op in ("sum", "mean"):
+                G.assert_reduce_close(got, want, x, axis, op, G.FP32_RTOL if dt == "float32" else 1e-12)
+            else:
+                assert np.array_equal(got, want), (op, dt, shape)
+
+
+@pytest.mark.parametrize("tdt", [torch.bfloat16, torch.float16])
+def test_per_channel_16bit(tdt):
+    x = torch.randn((64, 48, 28, 28), generator=torch.Generator().manual_seed(3)).to(tdt)
+    x64 = x.double()
+    got = pb.mean(x.cuda(), axis=[0, 2, 3])
+    assert got.dtype == tdt and tuple(got.shape) == (48,)
+    np.testing.assert_allclose(got.double().cpu().numpy(), x64.mean(dim=(0, 2, 3)).numpy(), rtol=1e-2, atol=1e-3)
+    got = pb.sum(x.cuda(), axis=[0, 2, 3], dtype="float32")      # bf16 in, fp32 out: the tighter check
+    np.testing.assert_allclose(got.cpu().numpy(), x64.sum(dim=(0, 2, 3)).numpy(), rtol=1e-4, atol=1e-2)
+    assert torch.equal(pb.max(x.cuda(), axis=[0, 2, 3]).cpu(), x.amax(dim=(0, 2, 3)))
+    assert torch.equal(pb.min(x.cuda(), axis=[0, 2, 3]).cpu(), x.amin(dim=(0, 2, 3)))
+
+
+def test_per_channel_full_size_properties():
+    """[256,64,112,112] fp32 over (0,2,3): equals the two one-axis reductions it stands for."""
+    x = torch.rand((256, 64, 112, 112), device="cuda")
+    got = pb.sum(x, axis=[0, 2, 3])
+    ref = pb.sum(pb.sum(x.reshape(256 * 64, 112 * 112), axis=-1).reshape(256, 64), axis=0)
+    assert torch.allclose(got, ref, rtol=1e-6)
+    assert torch.allclose(got.double(), x.double().sum(dim=(0, 2, 3)), rtol=1e-5)
+    assert torch.equal(pb.max(x, axis=[0, 2, 3]), x.amax(dim=(0, 2, 3)))

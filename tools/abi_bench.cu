@@ -190,6 +190,27 @@ int main(int argc, char** argv) {
     }
     cudaFree(x); cudaFree(y); cudaFree(out);
   }
+  if (strstr(only, "G")) {  // per-channel reductions: [N,C,H,W] over (0,2,3) -- batch-norm statistics, bias gradients
+    const size_t n = (size_t)256 * 64 * 112 * 112;
+    float* x = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
+    float* out; CK(cudaMalloc(&out, 4096 * 4));
+    b200phi_reduce_desc d = {};
+    d.op = B200PHI_SUM; d.in_dtype = d.out_dtype = B200PHI_FLOAT32; d.rank = 4;
+    d.dims[0] = 256; d.dims[1] = 64; d.dims[2] = 112; d.dims[3] = 112;
+    d.naxes = 3; d.axes[0] = 0; d.axes[1] = 2; d.axes[2] = 3; d.x = x; d.out = out;
+    size_t ws = b200phi_reduce_workspace(&d);
+    void* w; CK(cudaMalloc(&w, ws ? ws : 256)); d.workspace = w; d.workspace_bytes = ws;
+    float ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 10);
+    printf("G1 sum fp32 [256,64,112,112] over (0,2,3) (ws %zu) %8.2f us  %7.1f GB/s\n", ws, ms * 1e3, n * 4.0 / ms / 1e6);
+    cudaFree(w);
+    d.in_dtype = d.out_dtype = B200PHI_BFLOAT16; d.op = B200PHI_MEAN; d.rank = 3;
+    d.dims[0] = 512; d.dims[1] = 1024; d.dims[2] = 784; d.naxes = 2; d.axes[0] = 0; d.axes[1] = 2;
+    ws = b200phi_reduce_workspace(&d);
+    CK(cudaMalloc(&w, ws ? ws : 256)); d.workspace = w; d.workspace_bytes = ws;
+    ms = time_it([&] { OK(b200phi_reduce(&d, 0)); }, 10);
+    printf("G2 mean bf16 [512,1024,784] over (0,2) (ws %zu)   %8.2f us  %7.1f GB/s\n", ws, ms * 1e3, 512.0 * 1024 * 784 * 2 / ms / 1e6);
+    cudaFree(x); cudaFree(out); cudaFree(w);
+  }
   if (strstr(only, "A")) {  // mixed-precision add: fp32 accumulator += bf16 gradient, in place
     const size_t n = (size_t)1 << 28;
     float* acc = (float*)dalloc(n * 4, 0x807fffff, 0x3f000000);
