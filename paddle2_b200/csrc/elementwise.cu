@@ -9,8 +9,9 @@
 // offset of the row is unravelled once per CTA (not per element), then the inner
 // loop is pure 16-byte loads -> functor -> 16-byte streaming stores.  An input
 // that is broadcast along `inner` is read once per row and splatted.
-// bcast_generic_kernel: per-element unravel, for outputs whose innermost merged
-// dim is tiny (e.g. [10,3,1,4] + [10,1,12,1]).
+// bcast_flat_kernel: the output as one flat array of 16-byte vectors (or elements), for
+// outputs whose rows are short or ragged (feature maps, hidden sizes, [10,3,1,4] + [10,1,12,1]).
+#include <algorithm>
 #include <string>
 
 #include "../../include/b200phi.h"
@@ -289,58 +290,200 @@ __global__ void __launch_bounds__(kBlock) bcast_rows_kernel(RowsParams<Arity> p,
   }
 }
 
+// Flat walk for outputs whose rows are short (feature maps, hidden sizes, per-channel operands
+// against [N,C,H*W]): the row kernel above spends a whole CTA on one row -- relu(x+y) on
+// [42799,64,49]+[64,1] ran at 0.16 TB/s.  Here the output is one flat array of units (a 16-byte
+// vector when every row is a whole number of aligned vectors, else one element; the element
+// form is also the general fallback) and thread t of the grid takes units t, t+256, ... U at a
+// time.  Per unit: one multiply-shift divide for (row, position in row); an operand with the
+// output's own shape needs nothing more, an operand that is one shared row needs the position,
+// any other operand unravels the row over the outer dims.  32-bit indices: the host slices
+// outputs of 2^31 elements or more along the outermost dim.
 template <int Arity>
-struct GenericParams {
+struct FlatParams {
   const void* in[Arity];
   void* out;
   void* inter;
-  int ndim;
-  long long extent[B200PHI_MAX_RANK];
-  long long stride[Arity][B200PHI_MAX_RANK];
-  long long numel;
+  int nouter;
+  FastDiv oext[B200PHI_MAX_RANK];
+  unsigned ostride[Arity][B200PHI_MAX_RANK];
+  FastDiv upr;     // units per row
+  unsigned total;  // units in this slice of the output
+  int istride[Arity];
+  int kind[Arity];  // 0: same shape as the output, 1: one row shared by all rows, 2: general
 };
 
-template <typename T, typename F, int Arity>
-__global__ void __launch_bounds__(kBlock) bcast_generic_kernel(GenericParams<Arity> p, F f) {
+template <typename T, typename F, int Arity, bool kVec, int U>
+__global__ void __launch_bounds__(kBlock) bcast_flat_kernel(FlatParams<Arity> p, F f) {
   using C = typename ComputeT<T>::type;
-  for (long long o = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; o < p.numel;
-       o += static_cast<long long>(gridDim.x) * kBlock) {
-    long long off[Arity];
+  constexpr int VE = kVec ? VecOf<T>::kElems : 1;
+  bool need_row = false;
 #pragma unroll
-    for (int i = 0; i < Arity; ++i) off[i] = 0;
-    long long idx = o;
-    for (int k = p.ndim - 1; k >= 0; --k) {
-      const long long e = p.extent[k];
-      long long q, rem;
-      if ((static_cast<unsigned long long>(idx) | static_cast<unsigned long long>(e)) >> 32) {
-        q = idx / e;
-        rem = idx - q * e;
-      } else {
-        const unsigned qi = static_cast<unsigned>(idx) / static_cast<unsigned>(e);
-        q = qi;
-        rem = static_cast<unsigned>(idx) - qi * static_cast<unsigned>(e);
+  for (int i = 0; i < Arity; ++i) need_row = need_row || p.kind[i] == 2;
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < p.total;
+       base += gridDim.x * (kBlock * U)) {
+    unsigned off[U][Arity];
+    bool live[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      live[u] = id < p.total;
+      if (!live[u]) continue;
+      const unsigned row = fast_div(id, p.upr);
+      const unsigned col = id - row * p.upr.d;
+      unsigned gen[Arity];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) gen[i] = 0;
+      if (need_row) {
+        unsigned idx = row;
+        for (int k = p.nouter - 1; k >= 0; --k) {
+          const unsigned q = fast_div(idx, p.oext[k]);
+          const unsigned rem = idx - q * p.oext[k].d;
+#pragma unroll
+          for (int i = 0; i < Arity; ++i) gen[i] += rem * p.ostride[i][k];
+          idx = q;
+        }
       }
 #pragma unroll
-      for (int i = 0; i < Arity; ++i) off[i] += rem * p.stride[i][k];
-      idx = q;
+      for (int i = 0; i < Arity; ++i) {
+        if (p.kind[i] == 0)
+          off[u][i] = id * VE;
+        else if (p.kind[i] == 1)
+          off[u][i] = col * VE;
+        else
+          off[u][i] = gen[i] + (p.istride[i] ? col * VE : 0);
+      }
     }
-    C a[3] = {C(0), C(0), C(0)};
+    if constexpr (kVec) {
+      V16 raw[U][Arity];
+      C splat[U][Arity];
 #pragma unroll
-    for (int i = 0; i < Arity; ++i)
-      a[i] = Cvt<C, T>::to(ldg_scalar(static_cast<const T*>(p.in[i]) + off[i]));
-    const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
-    static_cast<T*>(p.out)[o] = from_compute<T, C>(f.template post<C>(t));
-    if (p.inter) static_cast<T*>(p.inter)[o] = from_compute<T, C>(t);
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+#pragma unroll
+        for (int i = 0; i < Arity; ++i) {
+          const T* src = static_cast<const T*>(p.in[i]) + off[u][i];
+          if (p.istride[i])  // only a full-shape operand is read once; the others repeat across rows
+            raw[u][i] = p.kind[i] == 0 ? ldg_stream16(src) : ldg_cached16(src);
+          else
+            splat[u][i] = Cvt<C, T>::to(ldg_scalar(src));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        typename VecOf<T>::U w[Arity], o, o2;
+#pragma unroll
+        for (int i = 0; i < Arity; ++i) w[i].raw = raw[u][i];
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+          for (int i = 0; i < Arity; ++i) a[i] = p.istride[i] ? Cvt<C, T>::to(w[i].e[e]) : splat[u][i];
+          const C t = f.template pre<C>(a[0], a[1], a[2], Arity);
+          o.e[e] = from_compute<T, C>(f.template post<C>(t));
+          if constexpr (F::kInter) o2.e[e] = from_compute<T, C>(t);
+        }
+        const unsigned id = base + u * kBlock;
+        stg_stream16(reinterpret_cast<V16*>(p.out) + id, o.raw);
+        if constexpr (F::kInter) {
+          if (p.inter) stg_stream16(reinterpret_cast<V16*>(p.inter) + id, o2.raw);
+        }
+      }
+    } else {
+      C a[U][3];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        a[u][0] = a[u][1] = a[u][2] = C(0);
+        if (!live[u]) continue;
+#pragma unroll
+        for (int i = 0; i < Arity; ++i)
+          a[u][i] = Cvt<C, T>::to(ldg_scalar(static_cast<const T*>(p.in[i]) + off[u][i]));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        const unsigned id = base + u * kBlock;
+        const C t = f.template pre<C>(a[u][0], a[u][1], a[u][2], Arity);
+        static_cast<T*>(p.out)[id] = from_compute<T, C>(f.template post<C>(t));
+        if constexpr (F::kInter) {
+          if (p.inter) static_cast<T*>(p.inter)[id] = from_compute<T, C>(t);
+        }
+      }
+    }
   }
 }
 
 // ---- launch -----------------------------------------------------------------------------
 template <typename T, typename F, int Arity>
+static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F f, void* inter,
+                       bool vec, cudaStream_t stream) {
+  constexpr int VE = VecOf<T>::kElems;
+  constexpr int U = 4;
+  constexpr long long kLimit = 1LL << 31;  // the kernel indexes with 32 bits
+  const int no = bp.ndim - 1;
+  long long full[B200PHI_MAX_RANK];  // the output's own strides over the outer dims
+  long long run = bp.inner;
+  for (int k = no - 1; k >= 0; --k) {
+    full[k] = run;
+    run *= bp.extent[k];
+  }
+  const long long slab = no > 0 ? full[0] : bp.inner;  // elements per index of the outermost dim
+  if (slab >= kLimit)
+    return set_error(B200PHI_UNSUPPORTED, "elementwise: a short-row output this large is not built");
+  const long long outer0 = no > 0 ? bp.extent[0] : 1;
+  const long long per_slice = std::max<long long>(1, (kLimit - 1) / slab);
+  for (long long a = 0; a < outer0; a += per_slice) {
+    const long long cnt = std::min(per_slice, outer0 - a);
+    FlatParams<Arity> p;
+    p.nouter = no;
+    for (int k = 0; k < no; ++k) {
+      p.oext[k] = make_fast_div(static_cast<unsigned>(k == 0 ? cnt : bp.extent[k]));
+      for (int i = 0; i < Arity; ++i) p.ostride[i][k] = static_cast<unsigned>(bp.stride[i][k]);
+    }
+    const long long upr = vec ? bp.inner / VE : bp.inner;
+    p.upr = make_fast_div(static_cast<unsigned>(upr));
+    const long long rows = no > 0 ? cnt * (bp.rows / outer0) : 1;
+    p.total = static_cast<unsigned>(rows * upr);
+    for (int i = 0; i < Arity; ++i) {
+      p.in[i] = static_cast<const T*>(d->in[i].data) + (no > 0 ? a * bp.stride[i][0] : 0);
+      p.istride[i] = bp.stride[i][bp.ndim - 1] ? 1 : 0;
+      bool same = p.istride[i] == 1, shared = p.istride[i] == 1;
+      for (int k = 0; k < no; ++k) {
+        same = same && bp.stride[i][k] == full[k];
+        shared = shared && bp.stride[i][k] == 0;
+      }
+      p.kind[i] = same ? 0 : (shared ? 1 : 2);
+    }
+    p.out = static_cast<T*>(d->out) + a * slab;
+    p.inter = inter ? static_cast<T*>(inter) + a * slab : nullptr;
+    long long blocks = (static_cast<long long>(p.total) + kBlock * U - 1) / (kBlock * U);
+    const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
+    if (blocks > cap) blocks = cap;
+    const unsigned g = static_cast<unsigned>(blocks);
+    if (vec)
+      bcast_flat_kernel<T, F, Arity, true, U><<<g, kBlock, 0, stream>>>(p, f);
+    else
+      bcast_flat_kernel<T, F, Arity, false, U><<<g, kBlock, 0, stream>>>(p, f);
+  }
+  return B200PHI_OK;
+}
+
+template <typename T, typename F, int Arity>
 static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, F f, void* inter,
                         cudaStream_t stream) {
   constexpr int VE = VecOf<T>::kElems;
   constexpr bool kStaticMask = !F::kInter && Arity == 2;
-  if (bp.use_rows_kernel) {
+  // Short rows go to the flat walk: as 16-byte vectors when every row is a whole number of
+  // aligned vectors (at most 256 of them), as single elements when rows are ragged and short.
+  bool whole_vectors = bp.inner % VE == 0 && reinterpret_cast<uintptr_t>(d->out) % 16 == 0 &&
+                       (!inter || reinterpret_cast<uintptr_t>(inter) % 16 == 0);
+  for (int i = 0; i < Arity; ++i)
+    if (bp.stride[i][bp.ndim - 1] != 0)
+      whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
+  const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 256;
+  const bool flat_scalar = !flat_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
+  if (bp.use_rows_kernel && !flat_vec && !flat_scalar) {
     RowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
     p.out = d->out;
@@ -376,19 +519,8 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
       bcast_rows_kernel<T, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
     }
   } else {
-    GenericParams<Arity> p;
-    for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
-    p.out = d->out;
-    p.inter = inter;
-    p.ndim = bp.ndim;
-    for (int k = 0; k < bp.ndim; ++k) {
-      p.extent[k] = bp.extent[k];
-      for (int i = 0; i < Arity; ++i) p.stride[i][k] = bp.stride[i][k];
-    }
-    p.numel = bp.out_numel;
-    long long blocks = (bp.out_numel + kBlock - 1) / kBlock;
-    if (blocks > 148LL * 8 * 64) blocks = 148LL * 8 * 64;
-    bcast_generic_kernel<T, F, Arity><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(p, f);
+    const int rc = launch_flat<T, F, Arity>(d, bp, f, inter, flat_vec, stream);
+    if (rc != B200PHI_OK) return rc;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);

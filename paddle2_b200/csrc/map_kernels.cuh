@@ -4,6 +4,7 @@
 // VE outputs, stored as one VE*sizeof(TO)-byte word (16 B when TO == TI, 4 B for fp32->bool).
 #pragma once
 
+#include <algorithm>
 #include <string>
 
 #include "bcast_plan.h"
@@ -201,48 +202,197 @@ __global__ void __launch_bounds__(kBlock) map_rows_kernel(MapRowsParams<Arity> p
   }
 }
 
+// Flat walk for outputs whose rows are short (an innermost merged dim of a few to ~1000
+// elements: feature maps, hidden sizes, per-channel operands).  The row kernel above spends a
+// whole CTA on one row; here the output is one flat array of units -- a unit is a 16-byte
+// vector (kVec: rows are whole, 16-byte aligned vectors) or one element (any shape at all: this
+// variant is also the fallback a per-element unravel kernel used to be) -- and thread t of the
+// grid takes units t, t + 256, ... U at a time, all loads issued before the first use.  Per
+// unit: one divide for (row, position in row); an operand that has the output's own shape
+// needs nothing more (its offset is the unit index), an operand that is one row for every
+// output row needs only the position, any other operand unravels the row over the outer dims.
 template <int Arity>
-struct MapGenericParams {
+struct MapFlatParams {
   const void* in[Arity];
   void* out;
-  int ndim;
-  long long extent[B200PHI_MAX_RANK];
-  long long stride[Arity][B200PHI_MAX_RANK];
-  long long numel;
+  int nouter;
+  FastDiv oext[B200PHI_MAX_RANK];
+  unsigned ostride[Arity][B200PHI_MAX_RANK];
+  FastDiv upr;     // units per row
+  unsigned total;  // units in the output (< 2^31, as is every element offset)
+  int istride[Arity];  // 0 or 1 along the row
+  int kind[Arity];     // 0: same shape as the output, 1: one row shared by all rows, 2: general
 };
 
-template <typename TI, typename TO, typename F, int Arity>
-__global__ void __launch_bounds__(kBlock) map_generic_kernel(MapGenericParams<Arity> p, F f) {
+template <typename TI, typename TO, typename F, int Arity, bool kVec, int U>
+__global__ void __launch_bounds__(kBlock) map_flat_kernel(MapFlatParams<Arity> p, F f) {
   using C = typename MapCompute<TI>::type;
-  for (long long o = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; o < p.numel;
-       o += static_cast<long long>(gridDim.x) * kBlock) {
-    long long off[Arity];
+  constexpr int VE = kVec ? VecOf<TI>::kElems : 1;
+  constexpr int kOutBytes = VE * static_cast<int>(sizeof(TO));
+  bool need_row = false;
 #pragma unroll
-    for (int i = 0; i < Arity; ++i) off[i] = 0;
-    long long idx = o;
-    for (int k = p.ndim - 1; k >= 0; --k) {
-      long long q, rem;
-      divmod_ll(idx, p.extent[k], &q, &rem);
+  for (int i = 0; i < Arity; ++i) need_row = need_row || p.kind[i] == 2;
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < p.total;
+       base += gridDim.x * (kBlock * U)) {
+    unsigned off[U][Arity];  // in elements
+    bool live[U];
 #pragma unroll
-      for (int i = 0; i < Arity; ++i) off[i] += rem * p.stride[i][k];
-      idx = q;
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      live[u] = id < p.total;
+      if (!live[u]) continue;
+      const unsigned row = fast_div(id, p.upr);
+      const unsigned col = id - row * p.upr.d;
+      unsigned gen[Arity];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) gen[i] = 0;
+      if (need_row) {
+        unsigned idx = row;
+        for (int k = p.nouter - 1; k >= 0; --k) {
+          const unsigned q = fast_div(idx, p.oext[k]);
+          const unsigned rem = idx - q * p.oext[k].d;
+#pragma unroll
+          for (int i = 0; i < Arity; ++i) gen[i] += rem * p.ostride[i][k];
+          idx = q;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) {
+        if (p.kind[i] == 0)
+          off[u][i] = id * VE;
+        else if (p.kind[i] == 1)
+          off[u][i] = col * VE;
+        else
+          off[u][i] = gen[i] + (p.istride[i] ? col * VE : 0);
+      }
     }
-    C a[3] = {C(0), C(0), C(0)};
+    if constexpr (kVec) {
+      V16 raw[U][Arity];
+      C splat[U][Arity];
 #pragma unroll
-    for (int i = 0; i < Arity; ++i)
-      a[i] = Cvt<C, TI>::to(ldg_scalar(static_cast<const TI*>(p.in[i]) + off[i]));
-    static_cast<TO*>(p.out)[o] = map_store_cast<TO>(f(a[0], a[1], a[2]));
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+#pragma unroll
+        for (int i = 0; i < Arity; ++i) {
+          const TI* src = static_cast<const TI*>(p.in[i]) + off[u][i];
+          if (p.istride[i])  // only a full-shape operand is read once; the others repeat across rows
+            raw[u][i] = p.kind[i] == 0 ? ldg_stream16(src) : ldg_cached16(src);
+          else
+            splat[u][i] = Cvt<C, TI>::to(ldg_scalar(src));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        struct alignas(kOutBytes) {
+          TO e[VE];
+        } o;
+        typename VecOf<TI>::U w[Arity];
+#pragma unroll
+        for (int i = 0; i < Arity; ++i) w[i].raw = raw[u][i];
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          C a[3] = {C(0), C(0), C(0)};
+#pragma unroll
+          for (int i = 0; i < Arity; ++i) a[i] = p.istride[i] ? Cvt<C, TI>::to(w[i].e[e]) : splat[u][i];
+          o.e[e] = map_store_cast<TO>(f(a[0], a[1], a[2]));
+        }
+        const unsigned id = base + u * kBlock;
+        store_packed<kOutBytes>(reinterpret_cast<unsigned char*>(p.out) +
+                                    static_cast<size_t>(id) * kOutBytes, &o);
+      }
+    } else {
+      C a[U][3];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        a[u][0] = a[u][1] = a[u][2] = C(0);
+        if (!live[u]) continue;
+#pragma unroll
+        for (int i = 0; i < Arity; ++i)
+          a[u][i] = Cvt<C, TI>::to(ldg_scalar(static_cast<const TI*>(p.in[i]) + off[u][i]));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        const unsigned id = base + u * kBlock;
+        static_cast<TO*>(p.out)[id] = map_store_cast<TO>(f(a[u][0], a[u][1], a[u][2]));
+      }
+    }
   }
 }
 
 // ---- launch ---------------------------------------------------------------------------------
+template <typename TI, typename TO, typename F, int Arity>
+int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, bool vec, cudaStream_t stream) {
+  constexpr int VE = VecOf<TI>::kElems;
+  constexpr int U = 4;
+  constexpr long long kLimit = 1LL << 31;  // the kernel indexes with 32 bits
+  const int no = bp.ndim - 1;              // outer dims
+  // the output's own (contiguous) strides over the outer dims, to recognise full-shape operands
+  long long full[B200PHI_MAX_RANK];
+  long long run = bp.inner;
+  for (int k = no - 1; k >= 0; --k) {
+    full[k] = run;
+    run *= bp.extent[k];
+  }
+  // slices of the outermost dim, each under 2^31 elements (one slice for all but huge outputs)
+  const long long slab = no > 0 ? full[0] : bp.inner;  // elements per index of the outermost dim
+  if (slab >= kLimit)
+    return set_error(B200PHI_UNSUPPORTED, "map: a short-row output this large is not built");
+  const long long outer0 = no > 0 ? bp.extent[0] : 1;
+  const long long per_slice = std::max<long long>(1, (kLimit - 1) / slab);
+  for (long long a = 0; a < outer0; a += per_slice) {
+    const long long cnt = std::min(per_slice, outer0 - a);
+    MapFlatParams<Arity> p;
+    p.nouter = no;
+    for (int k = 0; k < no; ++k) {
+      p.oext[k] = make_fast_div(static_cast<unsigned>(k == 0 ? cnt : bp.extent[k]));
+      for (int i = 0; i < Arity; ++i) p.ostride[i][k] = static_cast<unsigned>(bp.stride[i][k]);
+    }
+    const long long upr = vec ? bp.inner / VE : bp.inner;
+    p.upr = make_fast_div(static_cast<unsigned>(upr));
+    const long long rows = (no > 0 ? cnt * (bp.rows / outer0) : 1);
+    p.total = static_cast<unsigned>(rows * upr);
+    for (int i = 0; i < Arity; ++i) {
+      const long long shift = no > 0 ? a * bp.stride[i][0] : 0;
+      p.in[i] = static_cast<const TI*>(d->in[i].data) + shift;
+      p.istride[i] = bp.stride[i][bp.ndim - 1] ? 1 : 0;
+      bool same = p.istride[i] == 1, shared = p.istride[i] == 1;
+      for (int k = 0; k < no; ++k) {
+        same = same && bp.stride[i][k] == full[k];
+        shared = shared && bp.stride[i][k] == 0;
+      }
+      p.kind[i] = same ? 0 : (shared ? 1 : 2);
+    }
+    p.out = static_cast<TO*>(d->out) + a * slab;
+    long long blocks = (static_cast<long long>(p.total) + kBlock * U - 1) / (kBlock * U);
+    const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
+    if (blocks > cap) blocks = cap;
+    const unsigned g = static_cast<unsigned>(blocks);
+    if (vec)
+      map_flat_kernel<TI, TO, F, Arity, true, U><<<g, kBlock, 0, stream>>>(p, f);
+    else
+      map_flat_kernel<TI, TO, F, Arity, false, U><<<g, kBlock, 0, stream>>>(p, f);
+  }
+  return B200PHI_OK;
+}
+
 template <typename TI, typename TO, typename F, int Arity>
 int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t stream) {
   constexpr int VE = VecOf<TI>::kElems;
   // The row kernel walks a lone operand as a stream (no run-time mask is built for arity 1); a
   // unary op whose operand is broadcast along the innermost dim goes through the generic walk.
   const bool unary_splat = Arity == 1 && bp.stride[0][bp.ndim - 1] == 0 && bp.inner > 1;
-  if (bp.use_rows_kernel && !unary_splat) {
+  // Short rows go to the tiled walk: as 16-byte vectors when every row is a whole number of
+  // aligned vectors (at most 256 of them), as single elements when rows are ragged and short.
+  bool whole_vectors = bp.inner % VE == 0 &&
+                       reinterpret_cast<uintptr_t>(d->out) % (VE * sizeof(TO)) == 0;
+  for (int i = 0; i < Arity; ++i)
+    if (bp.stride[i][bp.ndim - 1] != 0)
+      whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
+  const bool tile_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 256;
+  const bool tile_scalar = !tile_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
+  if (bp.use_rows_kernel && !unary_splat && !tile_vec && !tile_scalar) {
     MapRowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
     p.out = d->out;
@@ -277,18 +427,8 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
         map_rows_kernel<TI, TO, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
     }
   } else {
-    MapGenericParams<Arity> p;
-    for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
-    p.out = d->out;
-    p.ndim = bp.ndim;
-    for (int k = 0; k < bp.ndim; ++k) {
-      p.extent[k] = bp.extent[k];
-      for (int i = 0; i < Arity; ++i) p.stride[i][k] = bp.stride[i][k];
-    }
-    p.numel = bp.out_numel;
-    long long blocks = (bp.out_numel + kBlock - 1) / kBlock;
-    if (blocks > 148LL * 8 * 64) blocks = 148LL * 8 * 64;
-    map_generic_kernel<TI, TO, F, Arity><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(p, f);
+    const int rc = launch_map_tile<TI, TO, F, Arity>(d, bp, f, tile_vec, stream);
+    if (rc != B200PHI_OK) return rc;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);

@@ -36,6 +36,16 @@ __device__ __forceinline__ V16 ldg_stream16(const void* p) {
   return r;
 }
 
+// Cached 16-byte load: for an operand that many threads re-read (a broadcast row): L1 serves the
+// repeats instead of one L2 slice taking every request.
+__device__ __forceinline__ V16 ldg_cached16(const void* p) {
+  V16 r;
+  asm("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
+      : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3])
+      : "l"(p));
+  return r;
+}
+
 __device__ __forceinline__ void stg_stream16(void* p, const V16& v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.w[0]),
                "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3])
@@ -457,6 +467,24 @@ template <typename Op, typename Acc>
 __device__ __forceinline__ void store_final(const Epilogue& ep, long long idx, Acc v) {
   if constexpr (OpPost<Op>::kSqrt) v = sqrt(v);
   store_result(ep, idx, v);
+}
+
+// Division by a run-time constant for 31-bit numerators (Granlund-Montgomery): with
+// l = ceil(log2 d) and m = floor(2^32 (2^l - d) / d) + 1,  n / d = (umulhi(m, n) + n) >> l.
+struct FastDiv {
+  unsigned d, m, l;
+};
+inline FastDiv make_fast_div(unsigned d) {
+  FastDiv f;
+  f.d = d;
+  unsigned l = 0;
+  while ((1ull << l) < d) ++l;
+  f.l = l;
+  f.m = static_cast<unsigned>(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+  return f;
+}
+__device__ __forceinline__ unsigned fast_div(unsigned n, const FastDiv& f) {
+  return (__umulhi(f.m, n) + n) >> f.l;
 }
 
 }  // namespace b200phi
