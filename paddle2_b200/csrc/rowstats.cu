@@ -122,6 +122,122 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// The same two sweeps for R rows at a time: rows shorter than G*8 vectors would leave most of the
+// eight load slots of rowstats_reg_kernel empty (a 256-column bf16 row is one vector per lane:
+// 1.2 TB/s; 4096 columns on G = 128 half fill it: 4.0 TB/s), so a group takes R rows with NV
+// vectors per thread each, R * NV = 8 loads in flight, and the R sums share each shuffle step
+// and each barrier.
+template <typename T, typename Acc, int G, int NV, int R>
+__global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
+    rowstats_multi_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+                          Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
+  constexpr int VE = VecOf<T>::kElems;
+  constexpr int kW = G / 32;
+  constexpr int kGroups = kBlock / G;
+  __shared__ Acc smem[2][2][R][kWarps];
+  const int g = threadIdx.x % G, grp = threadIdx.x / G;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long nvec = cols / VE;
+  int parity = 0;
+  for (long long r0 = (static_cast<long long>(blockIdx.x) * kGroups + grp) * R; r0 < rows;
+       r0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+    V16 buf[R][NV];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + (r0 + r) * cols);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = g + static_cast<long long>(k) * G;
+        if (r0 + r < rows && v < nvec) buf[r][k] = ldg_stream16(vp + v);
+      }
+    }
+    Acc sum[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      Acc s[2] = {Acc(0), Acc(0)};
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = g + static_cast<long long>(k) * G;
+        if (r0 + r < rows && v < nvec) {
+          Acc val[VE];
+          unpack_vec<T, Acc>(buf[r][k], val);
+#pragma unroll
+          for (int e = 0; e < VE; ++e) s[e & 1] += val[e];
+        }
+      }
+      sum[r] = s[0] + s[1];
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) sum[r] += shfl_xor(sum[r], m);
+    }
+    if constexpr (G > 32) {
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) smem[0][parity][r][warp] = sum[r];
+      }
+      group_barrier<G>();
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        sum[r] = smem[0][parity][r][grp * kW];
+#pragma unroll
+        for (int w = 1; w < kW; ++w) sum[r] += smem[0][parity][r][grp * kW + w];
+      }
+    }
+    Acc ss[R], mean[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      mean[r] = sum[r] / cols_acc;
+      Acc q[2] = {Acc(0), Acc(0)};
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = g + static_cast<long long>(k) * G;
+        if (r0 + r < rows && v < nvec) {
+          Acc val[VE];
+          unpack_vec<T, Acc>(buf[r][k], val);
+#pragma unroll
+          for (int e = 0; e < VE; ++e) {
+            const Acc dlt = val[e] - mean[r];
+            q[e & 1] += dlt * dlt;
+          }
+        }
+      }
+      ss[r] = q[0] + q[1];
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) ss[r] += shfl_xor(ss[r], m);
+    }
+    if constexpr (G > 32) {
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) smem[1][parity][r][warp] = ss[r];
+      }
+      group_barrier<G>();
+      if (g == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          ss[r] = smem[1][parity][r][grp * kW];
+#pragma unroll
+          for (int w = 1; w < kW; ++w) ss[r] += smem[1][parity][r][grp * kW + w];
+        }
+      }
+    }
+    parity ^= 1;
+    if (g == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        if (r0 + r < rows) {
+          if (mean_out) put_stat(mean_out, out_dtype, r0 + r, static_cast<double>(mean[r]));
+          if (var_out) put_stat(var_out, out_dtype, r0 + r, static_cast<double>(ss[r] / denom));
+        }
+      }
+    }
+  }
+}
+
 // Asynchronous-copy staging (LDGSTS): a persistent CTA owns rows blockIdx.x, +gridDim.x, ...;
 // every thread copies ITS OWN NV vectors of the rows ahead into a private slot of a shared-memory
 // ring with cp.async and later reads back only what it copied itself, so no barrier or mbarrier
@@ -461,7 +577,28 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   // kernel: opt-in for study only
   static const bool no_async = getenv("B200PHI_ROWSTATS_ASYNC") == nullptr;
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
-  if (aligned && nvec <= 32 * 8 && d->rows >= static_cast<long long>(sms) * 16) {
+  static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
+  if (aligned && !no_multi && force_g == 0 && (nvec <= 128 || (nvec > 256 && nvec <= 512)) && d->rows >= 64) {
+    // R rows per group so that all eight load slots are used (see rowstats_multi_kernel)
+    const Acc na = static_cast<Acc>(n);
+#define B200PHI_RS_MULTI(GG, NN, RR)                                                          \
+  {                                                                                           \
+    long long ctas = (d->rows + (kBlock / GG) * RR - 1) / ((kBlock / GG) * RR);                \
+    const long long cap = static_cast<long long>(sms) * 8 * 8;                                 \
+    if (ctas > cap) ctas = cap;                                                                \
+    rowstats_multi_kernel<T, Acc, GG, NN, RR><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>( \
+        x, d->rows, n, denom, na, d->mean, d->var, out_dtype);                                 \
+  }
+    if (nvec <= 32)
+      B200PHI_RS_MULTI(32, 1, 8)
+    else if (nvec <= 64)
+      B200PHI_RS_MULTI(32, 2, 4)
+    else if (nvec <= 128)
+      B200PHI_RS_MULTI(32, 4, 2)
+    else
+      B200PHI_RS_MULTI(64, 8, 1)
+#undef B200PHI_RS_MULTI
+  } else if (aligned && nvec <= 32 * 8 && d->rows >= static_cast<long long>(sms) * 16) {
     long long ctas = (d->rows + kWarps - 1) / kWarps;
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 32, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
