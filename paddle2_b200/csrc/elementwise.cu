@@ -415,9 +415,119 @@ __global__ void __launch_bounds__(kBlock) bcast_flat_kernel(FlatParams<Arity> p,
 }
 
 // ---- launch -----------------------------------------------------------------------------
+// Ragged rows (49- or 196-element feature maps, odd hidden sizes): a row is not a whole number
+// of 16-byte vectors, but the output -- and every operand that has the output's shape -- is
+// still one contiguous, aligned array.  Units are 16-byte vectors of that flat array; only the
+// broadcast operands are gathered element by element (cached loads), each element's
+// (row, position) stepped from the unit's first one.  Needs inner >= VE so that a unit touches
+// at most two rows.  FlatParams::upr holds the ELEMENTS per row here, total the element count.
+template <typename T, typename F, int Arity, int U>
+__global__ void __launch_bounds__(kBlock) bcast_ragged_kernel(FlatParams<Arity> p, F f) {
+  using C = typename ComputeT<T>::type;
+  constexpr int VE = VecOf<T>::kElems;
+  const unsigned inner = p.upr.d;
+  const unsigned units = (p.total + VE - 1) / VE;
+  bool need_row = false;
+#pragma unroll
+  for (int i = 0; i < Arity; ++i) need_row = need_row || p.kind[i] == 2;
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < units;
+       base += gridDim.x * (kBlock * U)) {
+    V16 raw[U][Arity];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id < units && (id + 1) * VE <= p.total) {
+#pragma unroll
+        for (int i = 0; i < Arity; ++i)
+          if (p.kind[i] == 0) raw[u][i] = ldg_stream16(reinterpret_cast<const V16*>(p.in[i]) + id);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id >= units) continue;
+      const bool whole = (id + 1) * VE <= p.total;
+      const unsigned e0 = id * VE;
+      const unsigned row0 = fast_div(e0, p.upr);
+      const unsigned col0 = e0 - row0 * inner;
+      unsigned gen[2][Arity];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) gen[0][i] = gen[1][i] = 0;
+      if (need_row) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          unsigned idx = row0 + h;
+          for (int k = p.nouter - 1; k >= 0; --k) {
+            const unsigned q = fast_div(idx, p.oext[k]);
+            const unsigned rem = idx - q * p.oext[k].d;
+#pragma unroll
+            for (int i = 0; i < Arity; ++i) gen[h][i] += rem * p.ostride[i][k];
+            idx = q;
+          }
+        }
+      }
+      typename VecOf<T>::U w[Arity], o, o2;
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) w[i].raw = raw[u][i];
+      // operand values for the unit's VE elements; the operand's kind is tested once per unit,
+      // not per element (with the test inside the element loop the kernel was instruction-bound)
+      C vals[Arity][VE];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) {
+        const T* src = static_cast<const T*>(p.in[i]);
+        if (p.kind[i] == 0) {
+#pragma unroll
+          for (int e = 0; e < VE; ++e)
+            vals[i][e] = whole ? Cvt<C, T>::to(w[i].e[e])
+                               : (e0 + e < p.total ? Cvt<C, T>::to(ldg_scalar(src + e0 + e)) : C(0));
+        } else if (p.kind[i] == 2 && !p.istride[i]) {
+          // one value per row (a per-channel bias): at most two values per unit
+          const C v0 = Cvt<C, T>::to(ldg_scalar(src + gen[0][i]));
+          const C v1 = (col0 + VE > inner && (row0 + 1) * inner < p.total)
+                           ? Cvt<C, T>::to(ldg_scalar(src + gen[1][i]))
+                           : v0;
+#pragma unroll
+          for (int e = 0; e < VE; ++e) vals[i][e] = (col0 + e >= inner) ? v1 : v0;
+        } else {
+#pragma unroll
+          for (int e = 0; e < VE; ++e) {
+            unsigned col = col0 + e;
+            const int h = col >= inner ? 1 : 0;
+            col -= h ? inner : 0;
+            const unsigned o_ = (p.kind[i] == 1 ? 0u : gen[h][i]) + (p.istride[i] ? col : 0u);
+            vals[i][e] = (whole || e0 + e < p.total) ? Cvt<C, T>::to(ldg_scalar(src + o_)) : C(0);
+          }
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < VE; ++e) {
+        const C a0 = vals[0][e];
+        const C a1 = Arity > 1 ? vals[Arity > 1 ? 1 : 0][e] : C(0);
+        const C a2 = Arity > 2 ? vals[Arity > 2 ? 2 : 0][e] : C(0);
+        const C t = f.template pre<C>(a0, a1, a2, Arity);
+        o.e[e] = from_compute<T, C>(f.template post<C>(t));
+        if constexpr (F::kInter) o2.e[e] = from_compute<T, C>(t);
+        if (!whole && e0 + e < p.total) {
+          static_cast<T*>(p.out)[e0 + e] = o.e[e];
+          if constexpr (F::kInter) {
+            if (p.inter) static_cast<T*>(p.inter)[e0 + e] = o2.e[e];
+          }
+        }
+      }
+      if (whole) {
+        stg_stream16(reinterpret_cast<V16*>(p.out) + id, o.raw);
+        if constexpr (F::kInter) {
+          if (p.inter) stg_stream16(reinterpret_cast<V16*>(p.inter) + id, o2.raw);
+        }
+      }
+    }
+  }
+}
+
 template <typename T, typename F, int Arity>
 static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F f, void* inter,
-                       bool vec, cudaStream_t stream) {
+                       int mode, cudaStream_t stream) {  // mode 0: elements, 1: whole vectors, 2: ragged
+  const bool vec = mode == 1;
   constexpr int VE = VecOf<T>::kElems;
   constexpr int U = 4;
   constexpr long long kLimit = 1LL << 31;  // the kernel indexes with 32 bits
@@ -433,6 +543,7 @@ static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F
     return set_error(B200PHI_UNSUPPORTED, "elementwise: a short-row output this large is not built");
   const long long outer0 = no > 0 ? bp.extent[0] : 1;
   const long long per_slice = std::max<long long>(1, (kLimit - 1) / slab);
+  if (mode == 2 && outer0 > per_slice) mode = 0;  // slices would lose the 16-byte alignment
   for (long long a = 0; a < outer0; a += per_slice) {
     const long long cnt = std::min(per_slice, outer0 - a);
     FlatParams<Arity> p;
@@ -461,10 +572,15 @@ static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F
     const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
     if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
-    if (vec)
+    if (mode == 2) {
+      long long rb = ((static_cast<long long>(p.total) + VE - 1) / VE + kBlock * 2 - 1) / (kBlock * 2);
+      if (rb > cap) rb = cap;
+      bcast_ragged_kernel<T, F, Arity, 2><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(p, f);
+    } else if (vec) {
       bcast_flat_kernel<T, F, Arity, true, U><<<g, kBlock, 0, stream>>>(p, f);
-    else
+    } else {
       bcast_flat_kernel<T, F, Arity, false, U><<<g, kBlock, 0, stream>>>(p, f);
+    }
   }
   return B200PHI_OK;
 }
@@ -483,6 +599,27 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
       whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
   const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 256;
   const bool flat_scalar = !flat_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
+  // ragged rows: the output and the full-shape operands as aligned vectors, the rest gathered
+  bool flat_ragged = flat_scalar && bp.inner >= VE && reinterpret_cast<uintptr_t>(d->out) % 16 == 0 &&
+                     (!inter || reinterpret_cast<uintptr_t>(inter) % 16 == 0);
+  if (flat_ragged) {
+    long long run = bp.inner;
+    bool any_full = false;
+    for (int i = 0; i < Arity; ++i) {
+      bool same = bp.stride[i][bp.ndim - 1] == 1;
+      long long r = bp.inner;
+      for (int k = bp.ndim - 2; k >= 0; --k) {
+        same = same && bp.stride[i][k] == r;
+        r *= bp.extent[k];
+      }
+      if (same) {
+        any_full = true;
+        flat_ragged = flat_ragged && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
+      }
+    }
+    (void)run;
+    flat_ragged = flat_ragged && any_full;
+  }
   if (bp.use_rows_kernel && !flat_vec && !flat_scalar) {
     RowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
@@ -519,7 +656,7 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
       bcast_rows_kernel<T, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
     }
   } else {
-    const int rc = launch_flat<T, F, Arity>(d, bp, f, inter, flat_vec, stream);
+    const int rc = launch_flat<T, F, Arity>(d, bp, f, inter, flat_vec ? 1 : (flat_ragged ? 2 : 0), stream);
     if (rc != B200PHI_OK) return rc;
   }
   cudaError_t e = cudaGetLastError();
