@@ -238,6 +238,53 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Rows of at most 128 vectors: one warp takes R rows at a time, NV vectors per lane each
+// (R * NV = 8 loads in flight), visits each row's vectors in index order and merges the R pairs
+// with shared shuffle steps.  One row per warp left a 256-column bf16 row at one load per lane
+// (1.7 TB/s).
+template <typename T, typename V, bool kMax, int NV, int R>
+__global__ void __launch_bounds__(kBlock, 4)
+    arg_multi_kernel(const T* __restrict__ x, long long rows, long long nvec, void* out, int index_dtype,
+                     void* val_out) {
+  using Op = ArgOp<V, kMax>;
+  constexpr int VE = VecOf<T>::kElems;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long n = nvec * VE;
+  for (long long r0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * R; r0 < rows;
+       r0 += static_cast<long long>(gridDim.x) * kWarps * R) {
+    V16 buf[R][NV];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + (r0 + r) * n);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = lane + 32LL * k;
+        if (r0 + r < rows && v < nvec) buf[r][k] = ldg_stream16(vp + v);
+      }
+    }
+    ArgPair<V> best[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      best[r] = Op::identity();
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long v = lane + 32LL * k;
+        if (r0 + r < rows && v < nvec) visit_vec<T, V, kMax>(best[r], buf[r][k], v * VE);
+      }
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) best[r] = Op::combine(best[r], shfl_pair(best[r], m));
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (r0 + r < rows) store_arg<T, V>(out, index_dtype, val_out, r0 + r, best[r]);
+    }
+  }
+}
+
 // post > 1: [pre, n, post].  Block = TX x TY: tx walks post (contiguous), ty walks n.
 template <typename T, typename V, bool kMax>
 __global__ void __launch_bounds__(kBlock)
@@ -313,6 +360,24 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     if (force_g == 32 || force_g == 64 || force_g == 128 || force_g == 256) G = force_g;
     if (force_u == 4 || force_u == 8) arg_u = force_u;
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
+    static const bool no_multi = getenv("B200PHI_ARG_NO_MULTI") != nullptr;
+    const long long nvec_row = row_bytes / 16;
+    if (aligned && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
+      const int R = nvec_row <= 32 ? 8 : (nvec_row <= 64 ? 4 : 2);
+      long long mc = (g.pre + kWarps * R - 1) / (kWarps * R);
+      const long long cap = 148LL * 8 * 8;
+      if (mc > cap) mc = cap;
+      const unsigned gm = static_cast<unsigned>(mc);
+      if (R == 8)
+        arg_multi_kernel<T, V, kMax, 1, 8><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+      else if (R == 4)
+        arg_multi_kernel<T, V, kMax, 2, 4><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+      else
+        arg_multi_kernel<T, V, kMax, 4, 2><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+      cudaError_t e0 = cudaGetLastError();
+      if (e0 != cudaSuccess) return cuda_status(e0);
+      return B200PHI_OK;
+    }
     long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     const unsigned grid = static_cast<unsigned>(ctas);

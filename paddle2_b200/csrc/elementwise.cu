@@ -591,13 +591,13 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
   constexpr int VE = VecOf<T>::kElems;
   constexpr bool kStaticMask = !F::kInter && Arity == 2;
   // Short rows go to the flat walk: as 16-byte vectors when every row is a whole number of
-  // aligned vectors (at most 256 of them), as single elements when rows are ragged and short.
+  // aligned vectors (at most 512 of them: 8 KiB; measured: 1024-vector rows with shared-row operands are faster on the row kernel), as single elements when rows are ragged and short.
   bool whole_vectors = bp.inner % VE == 0 && reinterpret_cast<uintptr_t>(d->out) % 16 == 0 &&
                        (!inter || reinterpret_cast<uintptr_t>(inter) % 16 == 0);
   for (int i = 0; i < Arity; ++i)
     if (bp.stride[i][bp.ndim - 1] != 0)
       whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
-  const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 256;
+  const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 512;
   const bool flat_scalar = !flat_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
   // ragged rows: the output and the full-shape operands as aligned vectors, the rest gathered
   bool flat_ragged = flat_scalar && bp.inner >= VE && reinterpret_cast<uintptr_t>(d->out) % 16 == 0 &&
