@@ -119,14 +119,19 @@ __global__ void __launch_bounds__(kBlock)
     row_batch_kernel(const T* __restrict__ x, long long rows, long long nvec, Epilogue ep) {
   constexpr int VE = VecOf<T>::kElems;
   constexpr int kGroups = kBlock / G;
-  constexpr int kW = G / 32;
+  constexpr int kW = G >= 32 ? G / 32 : 1;
   __shared__ Acc smem[2][R][kWarps];
   const int g = threadIdx.x % G, grp = threadIdx.x / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long cols = nvec * VE;
   int parity = 0;
-  for (long long r0 = (static_cast<long long>(blockIdx.x) * kGroups + grp) * R; r0 < rows;
-       r0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+  // the loop bound is the warp's FIRST group's row, so that lanes of one warp (which may hold
+  // several groups) leave the loop together: the shuffles below use the full mask
+  const int first_grp = G < 32 ? (threadIdx.x >> 5) * (32 / (G < 32 ? G : 32)) : grp;
+  const long long lag = static_cast<long long>(grp - first_grp) * R;
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kGroups + first_grp) * R; w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+    const long long r0 = w0 + lag;
     V16 buf[R][NV];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -150,8 +155,9 @@ __global__ void __launch_bounds__(kBlock)
       }
       a[r] = fold_lanes<Acc, Op>(acc);
     }
+    // G < 32: several rows share a warp, the tree stays inside the row's G lanes
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
+    for (int m = (G < 32 ? G / 2 : 16); m > 0; m >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) a[r] = Op::combine(a[r], shfl_xor(a[r], m));
     }

@@ -53,10 +53,12 @@ int launch_reduce_typed(const ReduceArgs& a) {
       const long long nvec = p.cols / VecOf<T>::kElems;
 #define B200PHI_ROWB(GG, NN, RR) \
   row_batch_kernel<T, Acc, Op, GG, NN, RR><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, nvec, ep)
-      if (p.G == 32 && p.nv == 2)
-        B200PHI_ROWB(32, 2, 4);
-      else if (p.G == 32 && p.nv == 4)
-        B200PHI_ROWB(32, 4, 2);
+      if (p.G == 8)
+        B200PHI_ROWB(8, 4, 2);
+      else if (p.G == 16 && p.nv == 4)
+        B200PHI_ROWB(16, 4, 2);
+      else if (p.G == 16)
+        B200PHI_ROWB(16, 8, 1);
       else if (p.G == 32)
         B200PHI_ROWB(32, 8, 1);
       else if (p.G == 64)

@@ -330,10 +330,12 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     if (kind != kRowSplit && p->aligned && nvec_row < 1024 && p->cols > 128 && !t.no_row_batch &&
         t.force_kind < 0) {
       kind = kRowBatch;
-      if (nvec_row <= 64) {
-        p->G = 32, p->nv = 2, p->rpg = 4;
+      if (nvec_row <= 32) {  // sub-warp groups: a 3- or 4-step shuffle tree instead of 5 per row
+        p->G = 8, p->nv = 4, p->rpg = 2;
+      } else if (nvec_row <= 64) {
+        p->G = 16, p->nv = 4, p->rpg = 2;
       } else if (nvec_row <= 128) {
-        p->G = 32, p->nv = 4, p->rpg = 2;
+        p->G = 16, p->nv = 8, p->rpg = 1;
       } else if (nvec_row <= 256) {
         p->G = 32, p->nv = 8, p->rpg = 1;
       } else if (nvec_row <= 512) {

@@ -132,15 +132,20 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
     rowstats_multi_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
                           Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
-  constexpr int kW = G / 32;
+  constexpr int kW = G >= 32 ? G / 32 : 1;
+  constexpr int kTree = G < 32 ? G / 2 : 16;  // shuffle tree inside the row's lanes
   constexpr int kGroups = kBlock / G;
   __shared__ Acc smem[2][2][R][kWarps];
   const int g = threadIdx.x % G, grp = threadIdx.x / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long nvec = cols / VE;
   int parity = 0;
-  for (long long r0 = (static_cast<long long>(blockIdx.x) * kGroups + grp) * R; r0 < rows;
-       r0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+  // warp-uniform loop bound (a warp may hold several groups when G < 32; full-mask shuffles)
+  const int first_grp = G < 32 ? (threadIdx.x >> 5) * (32 / (G < 32 ? G : 32)) : grp;
+  const long long lag = static_cast<long long>(grp - first_grp) * R;
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kGroups + first_grp) * R; w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kGroups * R) {
+    const long long r0 = w0 + lag;
     V16 buf[R][NV];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -168,7 +173,7 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
       sum[r] = s[0] + s[1];
     }
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
+    for (int m = kTree; m > 0; m >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) sum[r] += shfl_xor(sum[r], m);
     }
@@ -206,7 +211,7 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
       ss[r] = q[0] + q[1];
     }
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
+    for (int m = kTree; m > 0; m >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) ss[r] += shfl_xor(ss[r], m);
     }
@@ -589,12 +594,12 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     rowstats_multi_kernel<T, Acc, GG, NN, RR><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>( \
         x, d->rows, n, denom, na, d->mean, d->var, out_dtype);                                 \
   }
-    if (nvec <= 32)
-      B200PHI_RS_MULTI(32, 1, 8)
+    if (nvec <= 32)  // sub-warp groups: the shuffle tree spans 8 or 16 lanes, not 32
+      B200PHI_RS_MULTI(8, 4, 2)
     else if (nvec <= 64)
-      B200PHI_RS_MULTI(32, 2, 4)
+      B200PHI_RS_MULTI(16, 4, 2)
     else if (nvec <= 128)
-      B200PHI_RS_MULTI(32, 4, 2)
+      B200PHI_RS_MULTI(16, 8, 1)
     else
       B200PHI_RS_MULTI(64, 8, 1)
 #undef B200PHI_RS_MULTI
