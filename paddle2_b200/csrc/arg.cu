@@ -242,23 +242,27 @@ __global__ void __launch_bounds__(kBlock)
 // (R * NV = 8 loads in flight), visits each row's vectors in index order and merges the R pairs
 // with shared shuffle steps.  One row per warp left a 256-column bf16 row at one load per lane
 // (1.7 TB/s).
-template <typename T, typename V, bool kMax, int NV, int R>
+template <typename T, typename V, bool kMax, int G, int NV, int R>
 __global__ void __launch_bounds__(kBlock, 4)
     arg_multi_kernel(const T* __restrict__ x, long long rows, long long nvec, void* out, int index_dtype,
                      void* val_out) {
+  // G = 8, 16 or 32 lanes per row: 32 / G rows side by side in a warp, R rounds of them
   using Op = ArgOp<V, kMax>;
   constexpr int VE = VecOf<T>::kElems;
+  constexpr int kPerWarp = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
   const long long n = nvec * VE;
-  for (long long r0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * R; r0 < rows;
-       r0 += static_cast<long long>(gridDim.x) * kWarps * R) {
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * (kPerWarp * R); w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kWarps * (kPerWarp * R)) {
+    const long long r0 = w0 + static_cast<long long>(sub) * R;
     V16 buf[R][NV];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + (r0 + r) * n);
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
-        const long long v = lane + 32LL * k;
+        const long long v = g + static_cast<long long>(G) * k;
         if (r0 + r < rows && v < nvec) buf[r][k] = ldg_stream16(vp + v);
       }
     }
@@ -268,16 +272,16 @@ __global__ void __launch_bounds__(kBlock, 4)
       best[r] = Op::identity();
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
-        const long long v = lane + 32LL * k;
+        const long long v = g + static_cast<long long>(G) * k;
         if (r0 + r < rows && v < nvec) visit_vec<T, V, kMax>(best[r], buf[r][k], v * VE);
       }
     }
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
+    for (int m = G / 2; m > 0; m >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) best[r] = Op::combine(best[r], shfl_pair(best[r], m));
     }
-    if (lane == 0) {
+    if (g == 0) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
         if (r0 + r < rows) store_arg<T, V>(out, index_dtype, val_out, r0 + r, best[r]);
@@ -363,17 +367,18 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     static const bool no_multi = getenv("B200PHI_ARG_NO_MULTI") != nullptr;
     const long long nvec_row = row_bytes / 16;
     if (aligned && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
-      const int R = nvec_row <= 32 ? 8 : (nvec_row <= 64 ? 4 : 2);
-      long long mc = (g.pre + kWarps * R - 1) / (kWarps * R);
+      const int LG = nvec_row <= 32 ? 8 : 16;
+      const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
+      long long mc = (g.pre + kWarps * rows_per_warp - 1) / (kWarps * rows_per_warp);
       const long long cap = 148LL * 8 * 8;
       if (mc > cap) mc = cap;
       const unsigned gm = static_cast<unsigned>(mc);
-      if (R == 8)
-        arg_multi_kernel<T, V, kMax, 1, 8><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
-      else if (R == 4)
-        arg_multi_kernel<T, V, kMax, 2, 4><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+      if (nvec_row <= 32)
+        arg_multi_kernel<T, V, kMax, 8, 4, 2><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+      else if (nvec_row <= 64)
+        arg_multi_kernel<T, V, kMax, 16, 4, 2><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
       else
-        arg_multi_kernel<T, V, kMax, 4, 2><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
+        arg_multi_kernel<T, V, kMax, 16, 8, 1><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
       cudaError_t e0 = cudaGetLastError();
       if (e0 != cudaSuccess) return cuda_status(e0);
       return B200PHI_OK;

@@ -179,21 +179,26 @@ __global__ void __launch_bounds__(kBlock)
 // a time with NV vectors per lane each, R * NV = 8 loads in flight, and the R (max, sum) pairs
 // share every shuffle step.  One row per warp left a 256-column bf16 row at one load per lane
 // (1.7 TB/s; 1024 columns 4.3 TB/s).
-template <typename T, typename A, int NV, int R>
+template <typename T, typename A, int G, int NV, int R>
 __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
     lse_multi_kernel(const T* __restrict__ x, long long rows, long long nvec, void* out, int out_dtype) {
+  // G = 8, 16 or 32 lanes per row: 32 / G rows side by side in a warp, R rounds of them
   constexpr int VE = VecOf<T>::kElems;
+  constexpr int kPerWarp = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
   const long long cols = nvec * VE;
-  for (long long r0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * R; r0 < rows;
-       r0 += static_cast<long long>(gridDim.x) * kWarps * R) {
+  // the loop bound is per warp, so all 32 lanes stay together for the full-mask shuffles
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * (kPerWarp * R); w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kWarps * (kPerWarp * R)) {
+    const long long r0 = w0 + static_cast<long long>(sub) * R;
     V16 buf[R][NV];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + (r0 + r) * cols);
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
-        const long long v = lane + 32LL * k;
+        const long long v = g + static_cast<long long>(G) * k;
         if (r0 + r < rows && v < nvec) buf[r][k] = ldg_stream16(vp + v);
       }
     }
@@ -204,7 +209,7 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
       s[r] = A(0);
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
-        const long long v = lane + 32LL * k;
+        const long long v = g + static_cast<long long>(G) * k;
         if (r0 + r < rows && v < nvec) lse_fold_vec<T, A>(buf[r][k], m[r], s[r]);
       }
     }
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
 #pragma unroll
     for (int r = 0; r < R; ++r) M[r] = m[r];
 #pragma unroll
-    for (int k = 16; k > 0; k >>= 1) {
+    for (int k = G / 2; k > 0; k >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         const A o = shfl_xor(M[r], k);
@@ -223,11 +228,11 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
     for (int r = 0; r < R; ++r)
       s[r] = (m[r] > LseMath<A>::neg_inf()) ? s[r] * LseMath<A>::exp_diff(m[r], M[r]) : A(0);
 #pragma unroll
-    for (int k = 16; k > 0; k >>= 1) {
+    for (int k = G / 2; k > 0; k >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) s[r] += shfl_xor(s[r], k);
     }
-    if (lane == 0) {
+    if (g == 0) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
         if (r0 + r < rows) lse_put(out, out_dtype, r0 + r, static_cast<double>(M[r] + LseMath<A>::log_(s[r])));
@@ -259,17 +264,19 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   static const bool no_multi = getenv("B200PHI_LSE_NO_MULTI") != nullptr;
   if (aligned && !no_multi && !env_u && nvec_row <= 128 && rows >= 64) {
     // several rows per warp (lse_multi_kernel)
-    const int R = nvec_row <= 32 ? 8 : (nvec_row <= 64 ? 4 : 2);
-    long long ctas = (rows + kWarps * R - 1) / (kWarps * R);
+    // lanes per row G, vectors per lane NV, rounds R (R * NV = 8 loads in flight)
+    const int LG = nvec_row <= 32 ? 8 : 16;
+    const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
+    long long ctas = (rows + kWarps * rows_per_warp - 1) / (kWarps * rows_per_warp);
     const long long cap = 148LL * 8 * 8;
     if (ctas > cap) ctas = cap;
     const unsigned gm = static_cast<unsigned>(ctas);
-    if (R == 8)
-      lse_multi_kernel<T, A, 1, 8><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
-    else if (R == 4)
-      lse_multi_kernel<T, A, 2, 4><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
+    if (nvec_row <= 32)
+      lse_multi_kernel<T, A, 8, 4, 2><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
+    else if (nvec_row <= 64)
+      lse_multi_kernel<T, A, 16, 4, 2><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
     else
-      lse_multi_kernel<T, A, 4, 2><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
+      lse_multi_kernel<T, A, 16, 8, 1><<<gm, kBlock, 0, stream>>>(x, rows, nvec_row, d->out, d->dtype);
     cudaError_t e0 = cudaGetLastError();
     if (e0 != cudaSuccess) return cuda_status(e0);
     return B200PHI_OK;
