@@ -390,7 +390,17 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       const long long bxy = p->outer * p->tiles;
       if (bxy > 0x7fffffffLL) return fail(err, B200PHI_UNSUPPORTED, "output too large for col plan");
       long long max_splits = std::max<long long>(1, p->R / (static_cast<long long>(TY) * 8));
-      long long splits = std::min(std::max<long long>(1, ceil_div(want_ctas, bxy)), max_splits);
+      // fill the resident CTA slots; of the two neighbouring split counts take the one whose
+      // last wave wastes less (time ~ waves / splits): 128 tiles on 592 slots run as 4 splits in
+      // one wave, not 5 splits in two ([8192,131072] axis 0: 5.71 TB/s with 5)
+      long long splits = std::max<long long>(1, ceil_div(want_ctas, bxy));
+      if (splits > 1) {
+        const long long lo = splits - 1;
+        const double t_hi = static_cast<double>(ceil_div(bxy * splits, want_ctas)) / splits;
+        const double t_lo = static_cast<double>(ceil_div(bxy * lo, want_ctas)) / lo;
+        if (t_lo < t_hi) splits = lo;
+      }
+      splits = std::min(splits, max_splits);
       splits = std::min<long long>(splits, 65535);
       p->rows_per_split = round_up(ceil_div(p->R, splits), TY);
       splits = ceil_div(p->R, p->rows_per_split);
