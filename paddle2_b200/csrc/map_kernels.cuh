@@ -321,9 +321,108 @@ __global__ void __launch_bounds__(kBlock) map_flat_kernel(MapFlatParams<Arity> p
   }
 }
 
+// Ragged rows (a row is not a whole number of 16-byte vectors): the output and every operand
+// with the output's shape are still contiguous aligned arrays and move as 16-byte units; only
+// the broadcast operands are gathered per element (cached loads), the operand kind tested once
+// per unit.  Needs inner >= VE (a unit touches at most two rows).  MapFlatParams::upr holds the
+// ELEMENTS per row here, total the element count.
+template <typename TI, typename TO, typename F, int Arity, int U>
+__global__ void __launch_bounds__(kBlock) map_ragged_kernel(MapFlatParams<Arity> p, F f) {
+  using C = typename MapCompute<TI>::type;
+  constexpr int VE = VecOf<TI>::kElems;
+  constexpr int kOutBytes = VE * static_cast<int>(sizeof(TO));
+  const unsigned inner = p.upr.d;
+  const unsigned units = (p.total + VE - 1) / VE;
+  bool need_row = false;
+#pragma unroll
+  for (int i = 0; i < Arity; ++i) need_row = need_row || p.kind[i] == 2;
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < units;
+       base += gridDim.x * (kBlock * U)) {
+    V16 raw[U][Arity];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id < units && (id + 1) * VE <= p.total) {
+#pragma unroll
+        for (int i = 0; i < Arity; ++i)
+          if (p.kind[i] == 0) raw[u][i] = ldg_stream16(reinterpret_cast<const V16*>(p.in[i]) + id);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id >= units) continue;
+      const bool whole = (id + 1) * VE <= p.total;
+      const unsigned e0 = id * VE;
+      const unsigned row0 = fast_div(e0, p.upr);
+      const unsigned col0 = e0 - row0 * inner;
+      unsigned gen[2][Arity];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) gen[0][i] = gen[1][i] = 0;
+      if (need_row) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          unsigned idx = row0 + h;
+          for (int k = p.nouter - 1; k >= 0; --k) {
+            const unsigned q = fast_div(idx, p.oext[k]);
+            const unsigned rem = idx - q * p.oext[k].d;
+#pragma unroll
+            for (int i = 0; i < Arity; ++i) gen[h][i] += rem * p.ostride[i][k];
+            idx = q;
+          }
+        }
+      }
+      typename VecOf<TI>::U w[Arity];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) w[i].raw = raw[u][i];
+      C vals[Arity][VE];
+#pragma unroll
+      for (int i = 0; i < Arity; ++i) {
+        const TI* src = static_cast<const TI*>(p.in[i]);
+        if (p.kind[i] == 0) {
+#pragma unroll
+          for (int e = 0; e < VE; ++e)
+            vals[i][e] = whole ? Cvt<C, TI>::to(w[i].e[e])
+                               : (e0 + e < p.total ? Cvt<C, TI>::to(ldg_scalar(src + e0 + e)) : C(0));
+        } else if (p.kind[i] == 2 && !p.istride[i]) {
+          const C v0 = Cvt<C, TI>::to(ldg_scalar(src + gen[0][i]));
+          const C v1 = (col0 + VE > inner && (row0 + 1) * inner < p.total)
+                           ? Cvt<C, TI>::to(ldg_scalar(src + gen[1][i]))
+                           : v0;
+#pragma unroll
+          for (int e = 0; e < VE; ++e) vals[i][e] = (col0 + e >= inner) ? v1 : v0;
+        } else {
+#pragma unroll
+          for (int e = 0; e < VE; ++e) {
+            unsigned col = col0 + e;
+            const int h = col >= inner ? 1 : 0;
+            col -= h ? inner : 0;
+            const unsigned o_ = (p.kind[i] == 1 ? 0u : gen[h][i]) + (p.istride[i] ? col : 0u);
+            vals[i][e] = (whole || e0 + e < p.total) ? Cvt<C, TI>::to(ldg_scalar(src + o_)) : C(0);
+          }
+        }
+      }
+      struct alignas(kOutBytes) {
+        TO e[VE];
+      } o;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) {
+        const C a0 = vals[0][e];
+        const C a1 = Arity > 1 ? vals[Arity > 1 ? 1 : 0][e] : C(0);
+        const C a2 = Arity > 2 ? vals[Arity > 2 ? 2 : 0][e] : C(0);
+        o.e[e] = map_store_cast<TO>(f(a0, a1, a2));
+        if (!whole && e0 + e < p.total) static_cast<TO*>(p.out)[e0 + e] = o.e[e];
+      }
+      if (whole)
+        store_packed<kOutBytes>(reinterpret_cast<unsigned char*>(p.out) + static_cast<size_t>(id) * kOutBytes, &o);
+    }
+  }
+}
+
 // ---- launch ---------------------------------------------------------------------------------
 template <typename TI, typename TO, typename F, int Arity>
-int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, bool vec, cudaStream_t stream) {
+int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mode, cudaStream_t stream) {
+  const bool vec = mode == 1;  // mode 0: elements, 1: whole vectors per row, 2: ragged rows
   constexpr int VE = VecOf<TI>::kElems;
   constexpr int U = 4;
   constexpr long long kLimit = 1LL << 31;  // the kernel indexes with 32 bits
@@ -341,6 +440,7 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, bool ve
     return set_error(B200PHI_UNSUPPORTED, "map: a short-row output this large is not built");
   const long long outer0 = no > 0 ? bp.extent[0] : 1;
   const long long per_slice = std::max<long long>(1, (kLimit - 1) / slab);
+  if (mode == 2 && outer0 > per_slice) mode = 0;  // slices would lose the 16-byte alignment
   for (long long a = 0; a < outer0; a += per_slice) {
     const long long cnt = std::min(per_slice, outer0 - a);
     MapFlatParams<Arity> p;
@@ -369,10 +469,15 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, bool ve
     const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
     if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
-    if (vec)
+    if (mode == 2) {
+      long long rb = ((static_cast<long long>(p.total) + VE - 1) / VE + kBlock * 2 - 1) / (kBlock * 2);
+      if (rb > cap) rb = cap;
+      map_ragged_kernel<TI, TO, F, Arity, 2><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(p, f);
+    } else if (vec) {
       map_flat_kernel<TI, TO, F, Arity, true, U><<<g, kBlock, 0, stream>>>(p, f);
-    else
+    } else {
       map_flat_kernel<TI, TO, F, Arity, false, U><<<g, kBlock, 0, stream>>>(p, f);
+    }
   }
   return B200PHI_OK;
 }
@@ -392,6 +497,25 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
       whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
   const bool tile_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 512;
   const bool tile_scalar = !tile_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
+  // ragged rows: the output and the full-shape operands as aligned units, the rest gathered
+  bool tile_ragged = tile_scalar && Arity > 1 && bp.inner >= VE &&
+                     reinterpret_cast<uintptr_t>(d->out) % (VE * sizeof(TO)) == 0;
+  if (tile_ragged) {
+    bool any_full = false;
+    for (int i = 0; i < Arity; ++i) {
+      bool same = bp.stride[i][bp.ndim - 1] == 1;
+      long long r = bp.inner;
+      for (int k = bp.ndim - 2; k >= 0; --k) {
+        same = same && bp.stride[i][k] == r;
+        r *= bp.extent[k];
+      }
+      if (same) {
+        any_full = true;
+        tile_ragged = tile_ragged && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
+      }
+    }
+    tile_ragged = tile_ragged && any_full;
+  }
   if (bp.use_rows_kernel && !unary_splat && !tile_vec && !tile_scalar) {
     MapRowsParams<Arity> p;
     for (int i = 0; i < Arity; ++i) p.in[i] = d->in[i].data;
@@ -427,7 +551,7 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
         map_rows_kernel<TI, TO, F, Arity, -1, 4><<<g, kBlock, 0, stream>>>(p, f);
     }
   } else {
-    const int rc = launch_map_tile<TI, TO, F, Arity>(d, bp, f, tile_vec, stream);
+    const int rc = launch_map_tile<TI, TO, F, Arity>(d, bp, f, tile_vec ? 1 : (tile_ragged ? 2 : 0), stream);
     if (rc != B200PHI_OK) return rc;
   }
   cudaError_t e = cudaGetLastError();
