@@ -1,0 +1,73 @@
+"""Every launch class of the short-row kernels (sub-warp groups of 8 / 16 lanes, multi-row warps,
+row batches, flat and ragged broadcast walks) on row counts that do not fill the last CTA.
+Integer results bit-exact; floating point against float64 numpy."""
+import numpy as np
+import pytest
+import torch
+
+import gpu_util as G
+import paddle2_b200 as pb
+from paddle2_b200 import ops
+
+pytestmark = pytest.mark.gpu
+
+# columns chosen so that the row is 17, 33, 65, 129, 257, 513 16-byte vectors: one per class
+FP32_COLS = [132, 260, 516, 1028, 2052]       # 33, 65, 129, 257, 513 vectors
+BF16_COLS = [136, 264, 520, 1032, 2056, 4104]  # 17, 33, 65, 129, 257, 513 vectors
+
+
+@pytest.mark.parametrize("rows", [1, 63, 64, 777])
+@pytest.mark.parametrize("cols", FP32_COLS)
+def test_row_reduce_classes_fp32_and_int(oracle, rows, cols):
+    rng = np.random.default_rng(rows * 7 + cols)
+    x = rng.standard_normal((rows, cols)).astype(np.float32)
+    dx = G.to_dev(x)
+    np.testing.assert_allclose(G.to_np(pb.sum(dx, axis=-1)), x.astype(np.float64).sum(-1), rtol=1e-5, atol=1e-4)
+    assert np.array_equal(G.to_np(pb.max(dx, axis=-1)), x.max(-1))
+    assert np.array_equal(G.to_np(pb.min(dx, axis=-1)), x.min(-1))
+    xi = rng.integers(-1000, 1000, size=(rows, cols)).astype(np.int32)
+    assert np.array_equal(G.to_np(pb.sum(G.to_dev(xi), axis=-1)), xi.sum(-1, dtype=np.int64))
+    assert np.array_equal(G.to_np(pb.argmax(G.to_dev(xi), axis=-1)), oracle.argreduce("argmax", xi, -1))
+
+
+@pytest.mark.parametrize("rows", [1, 65, 1000])
+@pytest.mark.parametrize("cols", BF16_COLS)
+def test_row_ops_classes_bf16(rows, cols):
+    gen = torch.Generator().manual_seed(rows + cols)
+    x = (torch.randn((rows, cols), generator=gen) * 2 + 0.5).bfloat16()
+    x64 = x.double()
+    xd = x.cuda()
+    assert torch.equal(pb.max(xd, axis=-1).cpu(), x.amax(-1))
+    np.testing.assert_allclose(pb.sum(xd, axis=-1, dtype="float32").cpu().numpy(), x64.sum(-1).numpy(), rtol=1e-5, atol=1e-3)
+    m, v = pb.row_mean_var(xd, out_dtype="float32")
+    np.testing.assert_allclose(m.cpu().numpy(), x64.mean(-1).numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(v.cpu().numpy(), x64.var(-1, unbiased=True).numpy() if cols > 1 else 0, rtol=1e-4)
+    lse = ops.logsumexp(xd, -1)
+    np.testing.assert_allclose(lse.double().cpu().numpy(), torch.logsumexp(x64, -1).numpy(), rtol=1e-2)
+    # argmax: lowest index among the ties bf16 rounding creates
+    want = np.argmax(x.float().numpy(), axis=-1)
+    assert np.array_equal(pb.argmax(xd, axis=-1).cpu().numpy(), want)
+    assert np.array_equal(pb.argmin(xd, axis=-1).cpu().numpy(), np.argmin(x.float().numpy(), axis=-1))
+
+
+@pytest.mark.parametrize("xs,ys", [((7, 5, 49), (5, 1)), ((3, 64, 196), (64, 1)), ((33, 7, 50), (7, 50)),
+                                   ((129, 196), (196,)), ((65, 64), (64,)), ((300, 3, 1028), (3, 1)),
+                                   ((17, 2052), (17, 1)), ((5, 3, 7, 9), (3, 1, 9)), ((1000, 6), (6,))])
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.int64])
+def test_broadcast_walk_classes(xs, ys, dt):
+    """whole-vector rows, ragged rows with a per-row scalar / a shared row / a general operand,
+    tiny rows: add, fused relu, a compare and a ternary backward functor; all exact"""
+    gen = torch.Generator().manual_seed(len(xs) * 100 + xs[-1])
+    x = (torch.randn(xs, generator=gen) * 4).to(dt)
+    y = (torch.randn(ys, generator=gen) * 4).to(dt)
+    xd, yd = x.cuda(), y.cuda()
+    assert torch.equal(pb.add(xd, yd).cpu(), x + y)
+    assert torch.equal(pb.add(yd, xd).cpu(), y + x)
+    assert torch.equal(pb.less_than(xd, yd).cpu(), x < y)
+    assert torch.equal(pb.maximum(xd, yd).cpu(), torch.maximum(x, y))
+    if dt != torch.int64:
+        got = pb.fused_elemwise_add_activation(xd, yd, ["relu", "elementwise_add"]).cpu()
+        assert torch.equal(got, torch.relu(x + y))
+    g = (torch.randn(xs, generator=gen) * 2).to(dt)
+    got = ops._map("max_grad_x", [xd, yd, g.cuda()]).cpu()
+    assert torch.equal(got, g * (x > y).to(dt))
