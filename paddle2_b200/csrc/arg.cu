@@ -289,6 +289,39 @@ __global__ void __launch_bounds__(kBlock, 4)
   }
 }
 
+// Short rows of any alignment: G = 8, 16 or 32 lanes per row, NE scalar loads per lane visited in
+// index order (strict compare keeps the first occurrence), pairs merged inside the G lanes.
+template <typename T, typename V, bool kMax, int G, int NE>
+__global__ void __launch_bounds__(kBlock)
+    arg_scalar_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
+                      void* val_out) {
+  using Op = ArgOp<V, kMax>;
+  constexpr int kPerWarp = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
+    const long long row = w0 + sub;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + row * n;
+    T raw[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = g + k * G;
+      if (live && i < n) raw[k] = ldg_scalar(r + i);
+    }
+    ArgPair<V> best = Op::identity();
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = g + k * G;
+      if (live && i < n) Op::visit(best, Cvt<V, T>::to(raw[k]), i);
+    }
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) best = Op::combine(best, shfl_pair(best, m));
+    if (live && g == 0) store_arg<T, V>(out, index_dtype, val_out, row, best);
+  }
+}
+
 // post > 1: [pre, n, post].  Block = TX x TY: tx walks post (contiguous), ty walks n.
 template <typename T, typename V, bool kMax>
 __global__ void __launch_bounds__(kBlock)
@@ -381,6 +414,30 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
         arg_multi_kernel<T, V, kMax, 16, 8, 1><<<gm, kBlock, 0, stream>>>(x, g.pre, nvec_row, out, index_dtype, val_out);
       cudaError_t e0 = cudaGetLastError();
       if (e0 != cudaSuccess) return cuda_status(e0);
+      return B200PHI_OK;
+    }
+    // (measured at 1001 columns: fp32 6.5 TB/s against 4.3 for the peeled kernel, bf16 1.5 against
+    // 2.7 -- 2-byte scalar loads -- so 16-bit rows stop at 256 columns)
+    if (!aligned && g.n <= (sizeof(T) == 2 ? 256 : 1024) && g.pre >= 64 && !force_g && !force_u) {
+      const int c = static_cast<int>(g.n);
+#define B200PHI_ARG_SCALAR(GG, NN)                                                              \
+  {                                                                                             \
+    long long sc = (g.pre + kWarps * (32 / GG) - 1) / (kWarps * (32 / GG));                     \
+    if (sc > 148LL * 8 * 8) sc = 148LL * 8 * 8;                                                 \
+    arg_scalar_kernel<T, V, kMax, GG, NN><<<static_cast<unsigned>(sc), kBlock, 0, stream>>>(    \
+        x, g.pre, c, out, index_dtype, val_out);                                                \
+  }
+      if (g.n <= 128)
+        B200PHI_ARG_SCALAR(8, 16)
+      else if (g.n <= 256)
+        B200PHI_ARG_SCALAR(16, 16)
+      else if (g.n <= 512)
+        B200PHI_ARG_SCALAR(32, 16)
+      else
+        B200PHI_ARG_SCALAR(32, 32)
+#undef B200PHI_ARG_SCALAR
+      cudaError_t e1 = cudaGetLastError();
+      if (e1 != cudaSuccess) return cuda_status(e1);
       return B200PHI_OK;
     }
     long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);

@@ -360,6 +360,60 @@ static int launch_rowstats_async(const T* x, const b200phi_rowstats_desc* d, int
   return B200PHI_OK;
 }
 
+// Short rows of any alignment (101, 1001 columns): the sweep kernel below spends a CTA per row
+// (a 101-column row: 0.07-0.18 TB/s).  Here G = 8, 16 or 32 lanes take one row with NE scalar
+// loads per lane (consecutive lanes read consecutive elements, consecutive groups consecutive
+// rows: a warp still reads one contiguous span), keep the row in registers as Acc, and do both
+// sweeps from there; the shuffle tree stays inside the G lanes.  cols <= G * NE.
+template <typename T, typename Acc, int G, int NE>
+__global__ void __launch_bounds__(kBlock)
+    rowstats_scalar_kernel(const T* __restrict__ x, long long rows, int cols, Acc denom, Acc cols_acc,
+                           void* mean_out, void* var_out, int out_dtype) {
+  constexpr int kPerWarp = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  // warp-uniform loop bound: the shuffles use the full mask
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
+    const long long row = w0 + sub;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + row * cols;
+    Acc val[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = g + k * G;
+      val[k] = (live && i < cols) ? Cvt<Acc, T>::to(ldg_scalar(r + i)) : Acc(0);
+    }
+    Acc s0 = Acc(0), s1 = Acc(0);
+#pragma unroll
+    for (int k = 0; k < NE; k += 2) {
+      s0 += val[k];
+      if (k + 1 < NE) s1 += val[k + 1];
+    }
+    Acc sum = s0 + s1;
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) sum += shfl_xor(sum, m);
+    const Acc mean = sum / cols_acc;
+    Acc q0 = Acc(0), q1 = Acc(0);
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = g + k * G;
+      const Acc dlt = (i < cols) ? val[k] - mean : Acc(0);
+      if (k & 1)
+        q1 += dlt * dlt;
+      else
+        q0 += dlt * dlt;
+    }
+    Acc ss = q0 + q1;
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) ss += shfl_xor(ss, m);
+    if (live && g == 0) {
+      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
+      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+    }
+  }
+}
+
 // Any cols / alignment: one CTA per row, two sweeps (the second is an L2 hit for
 // rows up to tens of MB).
 template <typename T, typename Acc>
@@ -644,6 +698,27 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+  } else if (n <= 1024 && d->rows >= 64) {
+    // short rows that are ragged or unaligned: sub-warp groups, scalar loads, row in registers
+    const int c = static_cast<int>(n);
+    const Acc na = static_cast<Acc>(n);
+#define B200PHI_RS_SCALAR(GG, NN)                                                              \
+  {                                                                                            \
+    long long ctas = (d->rows + kWarps * (32 / GG) - 1) / (kWarps * (32 / GG));                \
+    const long long cap = static_cast<long long>(sms) * 8 * 8;                                 \
+    if (ctas > cap) ctas = cap;                                                                \
+    rowstats_scalar_kernel<T, Acc, GG, NN><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>( \
+        x, d->rows, c, denom, na, d->mean, d->var, out_dtype);                                 \
+  }
+    if (n <= 128)
+      B200PHI_RS_SCALAR(8, 16)
+    else if (n <= 256)
+      B200PHI_RS_SCALAR(16, 16)
+    else if (n <= 512)
+      B200PHI_RS_SCALAR(32, 16)
+    else
+      B200PHI_RS_SCALAR(32, 32)
+#undef B200PHI_RS_SCALAR
   } else {
     long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
     rowstats_sweep_kernel<T, Acc><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(

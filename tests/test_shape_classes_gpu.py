@@ -71,3 +71,25 @@ def test_broadcast_walk_classes(xs, ys, dt):
     g = (torch.randn(xs, generator=gen) * 2).to(dt)
     got = ops._map("max_grad_x", [xd, yd, g.cuda()]).cpu()
     assert torch.equal(got, g * (x > y).to(dt))
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(64, 101), (1000, 7), (777, 129), (200, 257), (129, 513), (65, 1001), (70, 1023),
+                                       (67, 4097), (3, 50257)])
+def test_unaligned_rows(rows, cols, dt):
+    """rows that are not whole 16-byte vectors: the scalar sub-warp kernels (<= 1024 columns), the
+    head / vectors / tail peel above that"""
+    gen = torch.Generator().manual_seed(rows * 3 + cols)
+    x = (torch.randn((rows, cols), generator=gen) * 3).to(dt)
+    x64, xd = x.double(), x.cuda()
+    m, v = pb.row_mean_var(xd, out_dtype="float32")
+    np.testing.assert_allclose(m.cpu().numpy(), x64.mean(-1).numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(v.cpu().numpy(), x64.var(-1, unbiased=True).numpy(), rtol=1e-4)
+    lse = ops.logsumexp(xd, -1)
+    np.testing.assert_allclose(lse.double().cpu().numpy(), torch.logsumexp(x64, -1).numpy(),
+                               rtol=1e-5 if dt == torch.float32 else 1e-2)
+    assert np.array_equal(pb.argmax(xd, axis=-1).cpu().numpy(), np.argmax(x.float().numpy(), axis=-1))
+    assert np.array_equal(pb.argmin(xd, axis=-1).cpu().numpy(), np.argmin(x.float().numpy(), axis=-1))
+    idx, val = pb.argmax_with_value(xd, axis=-1)
+    assert torch.equal(val.cpu(), x.amax(-1))
+    assert torch.equal(pb.max(xd, axis=-1).cpu(), x.amax(-1))
