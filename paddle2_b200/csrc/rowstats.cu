@@ -453,12 +453,29 @@ __global__ void __launch_bounds__(kBlock)
       const Acc dlt = Cvt<Acc, T>::to(ldg_scalar(r + threadIdx.x)) - mean;
       q[0] += dlt * dlt;
     }
-    for (v = threadIdx.x; v < nvec; v += kBlock) {
-      typename VecOf<T>::U w;
-      w.raw = *reinterpret_cast<const V16*>(vp + v);  // plain load: served by L2
+    // second sweep: served by L2; four loads in flight like the first
+    v = threadIdx.x;
+    for (; v + 3LL * kBlock < nvec; v += 4LL * kBlock) {
+      V16 b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) b[u] = ldg_cached16(vp + v + static_cast<long long>(u) * kBlock);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        Acc val[VE];
+        unpack_vec<T, Acc>(b[u], val);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          const Acc dlt = val[e] - mean;
+          q[e % 4] += dlt * dlt;
+        }
+      }
+    }
+    for (; v < nvec; v += kBlock) {
+      Acc val[VE];
+      unpack_vec<T, Acc>(ldg_cached16(vp + v), val);
 #pragma unroll
       for (int e = 0; e < VE; ++e) {
-        const Acc dlt = Cvt<Acc, T>::to(w.e[e]) - mean;
+        const Acc dlt = val[e] - mean;
         q[e % 4] += dlt * dlt;
       }
     }
