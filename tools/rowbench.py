@@ -13,4 +13,4 @@ for dt, rows, cols in [(torch.bfloat16, 524288, 784), (torch.float32, 262144, 78
     x = torch.randn(rows, cols, device='cuda').to(dt)
     out = torch.empty(rows, device='cuda', dtype=torch.float32 if dt != torch.float32 else dt)
     us = t(lambda: pb.sum(x, axis=-1, dtype='float32', out=out))
-    print(f"{dt} [{rows},{cols}] row sum: {us:8.1f} us  {x.numel()*x.element_size()/us/1e6:8.1f} GB/s")
+    print(f"{dt} [{rows},{cols}] row sum: {us:8.1f} us  {x.numel()*x.element_size()/us/1e6:8.1f} TB/s")
