@@ -414,6 +414,127 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Long rows in ONE sweep of global memory, any alignment.  Every thread keeps (n, mean, M2) and
+// merges one 16-byte vector at a time with the pairwise update of Chan, Golub & LeVeque: the
+// vector's own mean and sum of squared deviations are exact two-step quantities over its VE
+// registers, and the merge only ever subtracts two means, so nothing cancels catastrophically
+// (the accuracy is that of the two-sweep form, not of sum / sum-of-squares).  Threads and warps
+// merge their triples the same way.  Replaces the two-sweep kernel below wherever a row does not
+// fit the register kernels: its second sweep came from HBM again once the resident CTAs' rows
+// outgrew L2 (fp32 [21365,50257]: 3.6 TB/s).
+template <typename Acc>
+struct Moments {
+  Acc n, mean, m2;
+};
+template <typename Acc>
+__device__ __forceinline__ void moments_merge(Moments<Acc>& a, const Moments<Acc>& b) {
+  const Acc n = a.n + b.n;
+  if (n > Acc(0)) {
+    const Acc delta = b.mean - a.mean;
+    const Acc fb = b.n / n;
+    a.mean += delta * fb;
+    a.m2 += b.m2 + delta * delta * a.n * fb;
+    a.n = n;
+  }
+}
+template <typename T, typename Acc>
+__device__ __forceinline__ void moments_add_vec(Moments<Acc>& a, const V16& raw) {
+  constexpr int VE = VecOf<T>::kElems;
+  Acc val[VE];
+  unpack_vec<T, Acc>(raw, val);
+  Acc s0 = Acc(0), s1 = Acc(0);
+#pragma unroll
+  for (int e = 0; e < VE; e += 2) {
+    s0 += val[e];
+    s1 += val[e + 1];
+  }
+  const Acc vmean = (s0 + s1) * (Acc(1) / VE);
+  Acc q0 = Acc(0), q1 = Acc(0);
+#pragma unroll
+  for (int e = 0; e < VE; e += 2) {
+    const Acc d0 = val[e] - vmean, d1 = val[e + 1] - vmean;
+    q0 += d0 * d0;
+    q1 += d1 * d1;
+  }
+  const Acc n = a.n + Acc(VE);
+  const Acc delta = vmean - a.mean;
+  const Acc fb = Acc(VE) / n;
+  a.mean += delta * fb;
+  a.m2 += (q0 + q1) + delta * delta * a.n * fb;
+  a.n = n;
+}
+template <typename Acc>
+__device__ __forceinline__ void moments_add_one(Moments<Acc>& a, Acc v) {
+  const Acc n = a.n + Acc(1);
+  const Acc delta = v - a.mean;
+  a.mean += delta / n;
+  a.m2 += delta * (v - a.mean);
+  a.n = n;
+}
+
+template <typename T, typename Acc, int U>
+__global__ void __launch_bounds__(kBlock)
+    rowstats_stream_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+                           void* mean_out, void* var_out, int out_dtype) {
+  constexpr int VE = VecOf<T>::kElems;
+  __shared__ Acc sm[3][kWarps];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* __restrict__ r = x + row * cols;
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
+    long long head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
+    if (head > cols) head = cols;
+    const long long nvec = (cols - head) / VE;
+    const long long tail0 = head + nvec * VE;
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    Moments<Acc> a;
+    a.n = a.mean = a.m2 = Acc(0);
+    if (threadIdx.x < head) moments_add_one<Acc>(a, Cvt<Acc, T>::to(ldg_scalar(r + threadIdx.x)));
+    for (long long vb = threadIdx.x; vb < nvec; vb += static_cast<long long>(U) * kBlock) {
+      V16 buf[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long v = vb + static_cast<long long>(u) * kBlock;
+        if (v < nvec) buf[u] = ldg_stream16(vp + v);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long v = vb + static_cast<long long>(u) * kBlock;
+        if (v < nvec) moments_add_vec<T, Acc>(a, buf[u]);
+      }
+    }
+    for (long long i = tail0 + threadIdx.x; i < cols; i += kBlock)
+      moments_add_one<Acc>(a, Cvt<Acc, T>::to(ldg_scalar(r + i)));
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+      Moments<Acc> b;
+      b.n = shfl_xor(a.n, m);
+      b.mean = shfl_xor(a.mean, m);
+      b.m2 = shfl_xor(a.m2, m);
+      moments_merge<Acc>(a, b);
+    }
+    if (lane == 0) {
+      sm[0][warp] = a.n;
+      sm[1][warp] = a.mean;
+      sm[2][warp] = a.m2;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int w = 1; w < kWarps; ++w) {
+        Moments<Acc> b;
+        b.n = sm[0][w];
+        b.mean = sm[1][w];
+        b.m2 = sm[2][w];
+        moments_merge<Acc>(a, b);
+      }
+      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(a.mean));
+      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(a.m2 / denom));
+    }
+    __syncthreads();
+  }
+}
+
 // Any cols / alignment: one CTA per row, two sweeps (the second is an L2 hit for
 // rows up to tens of MB).
 template <typename T, typename Acc>
@@ -736,6 +857,15 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       B200PHI_RS_SCALAR(32, 32)
 #undef B200PHI_RS_SCALAR
+  } else if (getenv("B200PHI_ROWSTATS_SWEEP") == nullptr && row_bytes >= 24 * 1024) {
+    // (measured: 16 KiB rows are faster on the two-sweep kernel, 4.2 vs 3.5 TB/s -- the triple
+    // merges and two barriers per row weigh more on short rows; 32 KiB rows 5.2 vs 3.7)
+    // long rows (and medium rows of any alignment): one sweep, pairwise moment merges
+    long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
+    const long long cap = static_cast<long long>(sms) * 8 * 4;
+    if (ctas > cap) ctas = cap;
+    rowstats_stream_kernel<T, Acc, 4><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+        x, d->rows, n, denom, d->mean, d->var, out_dtype);
   } else {
     long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
     rowstats_sweep_kernel<T, Acc><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(

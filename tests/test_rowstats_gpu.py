@@ -71,3 +71,20 @@ def test_16bit_rows_poorly_conditioned(tdt, cols):
     c = torch.full((64, cols), 3.5, dtype=tdt)
     m, v = pb.row_mean_var(c.cuda(), out_dtype="float32")
     assert torch.all(v == 0) and torch.all(m == 3.5)
+
+
+@pytest.mark.parametrize("tdt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(33, 32000), (7, 50257), (5, 100003), (64, 16384)])
+def test_long_rows_one_sweep(tdt, rows, cols):
+    """rows that fit no register kernel go through the one-sweep pairwise-moments kernel (any
+    alignment); it must be as accurate as the two-sweep form, including on rows with a large
+    mean and a small spread, where a sum / sum-of-squares formulation would cancel"""
+    gen = torch.Generator().manual_seed(cols)
+    x = torch.randn((rows, cols), generator=gen)
+    x[1] = x[1] * 0.01 + 300.0
+    x[2, :16] = 5000.0
+    xt = x.to(tdt)
+    x64 = xt.double()
+    m, v = pb.row_mean_var(xt.cuda(), out_dtype="float32") if tdt != torch.float32 else pb.row_mean_var(xt.cuda())
+    np.testing.assert_allclose(m.cpu().numpy(), x64.mean(-1).numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(v.cpu().numpy(), x64.var(-1, unbiased=True).numpy(), rtol=1e-4)
