@@ -305,16 +305,13 @@ __global__ void __launch_bounds__(kBlock)
     const bool live = row < rows;
     const T* __restrict__ r = x + row * n;
     T raw[NE];
-#pragma unroll
-    for (int k = 0; k < NE; ++k) {
-      const int i = g + k * G;
-      if (live && i < n) raw[k] = ldg_scalar(r + i);
-    }
+    int odd;
+    short_row_load<T, G, NE>(r, n, g, live, raw, &odd);
     ArgPair<V> best = Op::identity();
 #pragma unroll
-    for (int k = 0; k < NE; ++k) {
-      const int i = g + k * G;
-      if (live && i < n) Op::visit(best, Cvt<V, T>::to(raw[k]), i);
+    for (int k = 0; k < NE; ++k) {  // ascending element index per lane: strict compare keeps the first
+      const int i = short_row_index<T, G, NE>(k, g, odd);
+      if (live && i >= 0 && i < n) Op::visit(best, Cvt<V, T>::to(raw[k]), i);
     }
 #pragma unroll
     for (int m = G / 2; m > 0; m >>= 1) best = Op::combine(best, shfl_pair(best, m));
@@ -418,7 +415,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     }
     // (measured at 1001 columns: fp32 6.5 TB/s against 4.3 for the peeled kernel, bf16 1.5 against
     // 2.7 -- 2-byte scalar loads -- so 16-bit rows stop at 256 columns)
-    if (!aligned && g.n <= (sizeof(T) == 2 ? 256 : 1024) && g.pre >= 64 && !force_g && !force_u) {
+    if (!aligned && g.n < (sizeof(T) == 2 ? 256 : 1024) && g.pre >= 64 && !force_g && !force_u) {
       const int c = static_cast<int>(g.n);
 #define B200PHI_ARG_SCALAR(GG, NN)                                                              \
   {                                                                                             \
@@ -427,11 +424,11 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     arg_scalar_kernel<T, V, kMax, GG, NN><<<static_cast<unsigned>(sc), kBlock, 0, stream>>>(    \
         x, g.pre, c, out, index_dtype, val_out);                                                \
   }
-      if (g.n <= 128)
+      if (g.n < 128)
         B200PHI_ARG_SCALAR(8, 16)
-      else if (g.n <= 256)
+      else if (g.n < 256)
         B200PHI_ARG_SCALAR(16, 16)
-      else if (g.n <= 512)
+      else if (g.n < 512)
         B200PHI_ARG_SCALAR(32, 16)
       else
         B200PHI_ARG_SCALAR(32, 32)

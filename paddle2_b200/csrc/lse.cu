@@ -276,12 +276,15 @@ __global__ void __launch_bounds__(kBlock)
     const long long row = w0 + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + row * cols;
+    T raw[NE];
+    int odd;
+    short_row_load<T, G, NE>(r, cols, g, live, raw, &odd);
     A val[NE];
     A m = LseMath<A>::neg_inf();
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-      const int i = g + k * G;
-      val[k] = (live && i < cols) ? Cvt<A, T>::to(ldg_scalar(r + i)) : LseMath<A>::neg_inf();
+      const int i = short_row_index<T, G, NE>(k, g, odd);
+      val[k] = (live && i >= 0 && i < cols) ? Cvt<A, T>::to(raw[k]) : LseMath<A>::neg_inf();
     }
 #pragma unroll
     for (int k = 0; k < NE; ++k) m = val[k] > m ? val[k] : m;
@@ -350,7 +353,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   }
   // (measured: at 1001 columns the peeled vector kernel is faster -- 6.6 vs 2.4 TB/s fp32 -- so the
   // scalar form stops at 256 columns)
-  if (!aligned && cols <= 256 && rows >= 64 && !env_u) {
+  if (!aligned && cols < 256 && rows >= 64 && !env_u) {
     const int c = static_cast<int>(cols);
 #define B200PHI_LSE_SCALAR(GG, NN)                                                              \
   {                                                                                             \
@@ -358,9 +361,9 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
     if (sc > 148LL * 8 * 8) sc = 148LL * 8 * 8;                                                 \
     lse_scalar_kernel<T, A, GG, NN><<<static_cast<unsigned>(sc), kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype); \
   }
-    if (cols <= 128)
+    if (cols < 128)
       B200PHI_LSE_SCALAR(8, 16)
-    else if (cols <= 256)
+    else if (cols < 256)
       B200PHI_LSE_SCALAR(16, 16)
     else if (cols <= 512)
       B200PHI_LSE_SCALAR(32, 16)

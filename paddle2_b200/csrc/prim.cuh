@@ -469,6 +469,53 @@ __device__ __forceinline__ void store_final(const Epilogue& ep, long long idx, A
   store_result(ep, idx, v);
 }
 
+// Element k of the NE a lane holds of a short row of any alignment (scalar sub-warp kernels):
+// which element index it is, and the loads.  4- and 8-byte types: lane g holds elements
+// g + k*G.  2-byte types: 4-byte words from the row's aligned-down base instead of 2-byte loads
+// (half the load instructions, 128 bytes per warp instruction): word j = g + (k/2)*G holds
+// elements 2j - o and 2j + 1 - o, o = 1 when the row starts on an odd element.
+// (pairs only for the 32-element-per-lane form: on 101-column rows the extra index arithmetic cost
+// more than the halved loads saved, 1.97 vs 2.36 TB/s; on 1001 columns pairs give 1.89 vs 0.99)
+template <typename T, int NE>
+constexpr bool short_row_pairs() {
+  return sizeof(T) == 2 && NE >= 32;
+}
+template <typename T, int G, int NE>
+__device__ __forceinline__ int short_row_index(int k, int g, int odd) {
+  if constexpr (short_row_pairs<T, NE>()) {
+    return 2 * (g + (k >> 1) * G) - odd + (k & 1);
+  } else {
+    return g + k * G;
+  }
+}
+template <typename T, int G, int NE>
+__device__ __forceinline__ void short_row_load(const T* __restrict__ r, int cols, int g, bool live,
+                                               T (&raw)[NE], int* odd_out) {
+  if constexpr (short_row_pairs<T, NE>()) {
+    static_assert(NE % 2 == 0, "pairs");
+    const int odd = static_cast<int>((reinterpret_cast<uintptr_t>(r) >> 1) & 1);
+    *odd_out = odd;
+    const uint32_t* __restrict__ wbase = reinterpret_cast<const uint32_t*>(r - odd);
+#pragma unroll
+    for (int j = 0; j < NE / 2; ++j) {
+      const int w = g + j * G;
+      const int i0 = 2 * w - odd;
+      uint32_t bits = 0;
+      if (live && i0 + 1 >= 0 && i0 < cols) bits = __ldg(wbase + w);
+      const T* pe = reinterpret_cast<const T*>(&bits);
+      raw[2 * j] = pe[0];
+      raw[2 * j + 1] = pe[1];
+    }
+  } else {
+    *odd_out = 0;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = g + k * G;
+      if (live && i < cols) raw[k] = ldg_scalar(r + i);
+    }
+  }
+}
+
 // Division by a run-time constant for 31-bit numerators (Granlund-Montgomery): with
 // l = ceil(log2 d) and m = floor(2^32 (2^l - d) / d) + 1,  n / d = (umulhi(m, n) + n) >> l.
 struct FastDiv {

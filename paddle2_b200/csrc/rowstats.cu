@@ -378,11 +378,14 @@ __global__ void __launch_bounds__(kBlock)
     const long long row = w0 + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + row * cols;
+    T raw[NE];
+    int odd;
+    short_row_load<T, G, NE>(r, cols, g, live, raw, &odd);
     Acc val[NE];
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-      const int i = g + k * G;
-      val[k] = (live && i < cols) ? Cvt<Acc, T>::to(ldg_scalar(r + i)) : Acc(0);
+      const int i = short_row_index<T, G, NE>(k, g, odd);
+      val[k] = (live && i >= 0 && i < cols) ? Cvt<Acc, T>::to(raw[k]) : Acc(0);
     }
     Acc s0 = Acc(0), s1 = Acc(0);
 #pragma unroll
@@ -397,8 +400,8 @@ __global__ void __launch_bounds__(kBlock)
     Acc q0 = Acc(0), q1 = Acc(0);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-      const int i = g + k * G;
-      const Acc dlt = (i < cols) ? val[k] - mean : Acc(0);
+      const int i = short_row_index<T, G, NE>(k, g, odd);
+      const Acc dlt = (i >= 0 && i < cols) ? val[k] - mean : Acc(0);
       if (k & 1)
         q1 += dlt * dlt;
       else
@@ -928,7 +931,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-  } else if (n <= 1024 && d->rows >= 64) {
+  } else if (n <= 1023 && d->rows >= 64) {  // (one slot spare: a 16-bit row may start mid-word)
     // short rows that are ragged or unaligned: sub-warp groups, scalar loads, row in registers
     const int c = static_cast<int>(n);
     const Acc na = static_cast<Acc>(n);
@@ -940,11 +943,11 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     rowstats_scalar_kernel<T, Acc, GG, NN><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>( \
         x, d->rows, c, denom, na, d->mean, d->var, out_dtype);                                 \
   }
-    if (n <= 128)
+    if (n < 128)
       B200PHI_RS_SCALAR(8, 16)
-    else if (n <= 256)
+    else if (n < 256)
       B200PHI_RS_SCALAR(16, 16)
-    else if (n <= 512)
+    else if (n < 512)
       B200PHI_RS_SCALAR(32, 16)
     else
       B200PHI_RS_SCALAR(32, 32)
