@@ -185,6 +185,36 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Short rows of any alignment, 129..1023 elements (odd hidden sizes): G = 16 or 32 lanes per row,
+// NE scalar loads per lane issued together (4-byte pair loads for 16-bit types in the 32-per-lane
+// form), shuffle tree inside the G lanes.  The peel in reduce_span costs such a row a scalar
+// head, a few vectors and a scalar tail in sequence (fp32 1001 columns: 4.5 TB/s).
+template <typename T, typename Acc, typename Op, int G, int NE>
+__global__ void __launch_bounds__(kBlock)
+    row_scalar_kernel(const T* __restrict__ x, long long rows, int cols, Epilogue ep) {
+  constexpr int kPerWarp = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
+       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
+    const long long row = w0 + sub;
+    const bool live = row < rows;
+    T raw[NE];
+    int odd;
+    short_row_load<T, G, NE>(x + row * cols, cols, g, live, raw, &odd);
+    Acc acc[2] = {Op::identity(), Op::identity()};
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int i = short_row_index<T, G, NE>(k, g, odd);
+      if (live && i >= 0 && i < cols) acc[k & 1] = Op::combine(acc[k & 1], load_as<Acc, Op>(raw[k]));
+    }
+    Acc v = Op::combine(acc[0], acc[1]);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) v = Op::combine(v, shfl_xor(v, m));
+    if (live && g == 0) store_final<Op>(ep, row, v);
+  }
+}
+
 // Short rows (softmax / classifier widths: a few to ~128 elements): G = 1, 2, 4, 8 or 16 lanes
 // per row, 32/G rows per warp, scalar loads (consecutive rows are contiguous, so a warp still
 // reads one contiguous span and L1 serves the strided revisits), xor-shuffle combine inside the

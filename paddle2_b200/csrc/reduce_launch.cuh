@@ -68,6 +68,16 @@ int launch_reduce_typed(const ReduceArgs& a) {
 #undef B200PHI_ROWB
       break;
     }
+    case kRowScalar: {
+      const int c = static_cast<int>(p.cols);
+      if (p.G == 16)
+        row_scalar_kernel<T, Acc, Op, 16, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      else if (p.nv == 16)
+        row_scalar_kernel<T, Acc, Op, 32, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      else
+        row_scalar_kernel<T, Acc, Op, 32, 32><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      break;
+    }
     case kRowSmall: {
       const int c = static_cast<int>(p.cols);
       switch (p.G) {

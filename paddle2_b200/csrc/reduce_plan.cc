@@ -344,6 +344,18 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         p->G = 128, p->nv = 8, p->rpg = 1;
       }
     }
+    // short rows that are not whole aligned vectors
+    if ((kind == kRowWarp || kind == kRowBlock) && !p->aligned && p->cols > 128 && p->cols < 1024 &&
+        p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch) {
+      kind = kRowScalar;
+      if (p->cols < 256) {
+        p->G = 16, p->nv = 16;
+      } else if (p->cols < 512) {
+        p->G = 32, p->nv = 16;
+      } else {
+        p->G = 32, p->nv = 32;
+      }
+    }
     // short rows: fewer than 32 lanes per row (about 8 elements per lane)
     if (kind == kRowWarp && p->cols <= 128 && p->rows >= 64 && t.force_kind < 0) {
       int g = pow2_ceil(ceil_div(p->cols, 8));
@@ -361,6 +373,15 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     case kRowSmall: {
       const long long ctas = ceil_div(p->rows, 256 / p->G);
       p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, 0x7fffffffLL));
+      p->grid_y = 1;
+      break;
+    }
+    case kRowScalar: {
+      const long long per_cta = 8LL * (32 / p->G);
+      long long ctas = ceil_div(p->rows, per_cta);
+      const long long cap = static_cast<long long>(t.sm_count) * 8 * std::max(1, t.row_batch_waves);
+      if (ctas > cap) ctas = cap;
+      p->grid_x = static_cast<unsigned>(ctas);
       p->grid_y = 1;
       break;
     }

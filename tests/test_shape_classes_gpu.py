@@ -93,3 +93,34 @@ def test_unaligned_rows(rows, cols, dt):
     idx, val = pb.argmax_with_value(xd, axis=-1)
     assert torch.equal(val.cpu(), x.amax(-1))
     assert torch.equal(pb.max(xd, axis=-1).cpu(), x.amax(-1))
+    assert torch.equal(pb.min(xd, axis=-1).cpu(), x.amin(-1))
+    s = pb.sum(xd, axis=-1).double().cpu().numpy()
+    tol = 1e-5 if dt == torch.float32 else 1e-2
+    np.testing.assert_allclose(s, x64.sum(-1).numpy(), rtol=tol, atol=tol * float(x64.abs().sum(-1).max()))
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.int32, torch.uint8, torch.float64])
+@pytest.mark.parametrize("rows,cols", [(64, 129), (333, 255), (200, 257), (129, 511), (65, 513), (4099, 1001), (70, 1023)])
+def test_unaligned_short_row_reduce(rows, cols, dt):
+    """the scalar row kernel of the reduce family (129..1023 columns, not whole vectors), also from a
+    base address that is one element past a 16-byte boundary"""
+    gen = torch.Generator().manual_seed(rows + cols)
+    if dt.is_floating_point:
+        flat = (torch.randn(rows * cols + 1, generator=gen) * 3).to(dt)
+    else:
+        flat = torch.randint(0, 100, (rows * cols + 1,), generator=gen).to(dt)
+    fd = flat.cuda()
+    for off in (0, 1):
+        x = flat[off:off + rows * cols].view(rows, cols)
+        xd = fd[off:off + rows * cols].view(rows, cols)
+        assert torch.equal(pb.max(xd, axis=-1).cpu(), x.amax(-1))
+        assert torch.equal(pb.min(xd, axis=-1).cpu(), x.amin(-1))
+        got = pb.sum(xd, axis=-1).cpu()
+        if dt.is_floating_point:
+            tol = {torch.float32: 1e-5, torch.bfloat16: 1e-2, torch.float64: 1e-12}[dt]
+            ref = x.double().sum(-1)
+            np.testing.assert_allclose(got.double().numpy(), ref.numpy(), rtol=tol,
+                                       atol=tol * float(x.double().abs().sum(-1).max()))
+        else:
+            # SumRawInferMeta: uint8 sums stay uint8 (wrap), int32 sums widen to int64
+            assert torch.equal(got.long(), x.long().sum(-1) % 256 if dt == torch.uint8 else x.long().sum(-1))
