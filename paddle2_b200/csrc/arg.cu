@@ -253,8 +253,9 @@ __global__ void __launch_bounds__(kBlock, 4)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
   const long long n = nvec * VE;
-  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * (kPerWarp * R); w0 < rows;
-       w0 += static_cast<long long>(gridDim.x) * kWarps * (kPerWarp * R)) {
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp * R); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp * R)) {
+    const long long w0 = c0 + warp * (kPerWarp * R);
     const long long r0 = w0 + static_cast<long long>(sub) * R;
     V16 buf[R][NV];
 #pragma unroll
@@ -299,8 +300,10 @@ __global__ void __launch_bounds__(kBlock)
   constexpr int kPerWarp = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
-  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
-       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
+  // (loop bound on blockIdx alone: the compiler then emits bare shuffles, not checked collectives)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long w0 = c0 + warp * kPerWarp;
     const long long row = w0 + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + row * n;

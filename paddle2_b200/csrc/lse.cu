@@ -210,9 +210,11 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
   const long long cols = nvec * VE;
-  // the loop bound is per warp, so all 32 lanes stay together for the full-mask shuffles
-  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * (kPerWarp * R); w0 < rows;
-       w0 += static_cast<long long>(gridDim.x) * kWarps * (kPerWarp * R)) {
+  // the loop bound depends on blockIdx alone: the body is provably convergent and the shuffles
+  // compile to bare SHFL (a per-warp bound gave each one a convergence check + collective path)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp * R); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp * R)) {
+    const long long w0 = c0 + warp * (kPerWarp * R);
     const long long r0 = w0 + static_cast<long long>(sub) * R;
     V16 buf[R][NV];
 #pragma unroll
@@ -271,8 +273,10 @@ __global__ void __launch_bounds__(kBlock)
   constexpr int kPerWarp = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
-  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
-       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
+  // (loop bound on blockIdx alone: the compiler then emits bare shuffles, not checked collectives)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long w0 = c0 + warp * kPerWarp;
     const long long row = w0 + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + row * cols;

@@ -125,9 +125,14 @@ __global__ void __launch_bounds__(kBlock)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long cols = nvec * VE;
   int parity = 0;
-  // the loop bound is the warp's FIRST group's row, so that lanes of one warp (which may hold
-  // several groups) leave the loop together: the shuffles below use the full mask
-  const int first_grp = G < 32 ? (threadIdx.x >> 5) * (32 / (G < 32 ? G : 32)) : grp;
+  // Loop bound.  R == 1 forms: it depends on blockIdx alone (every group of the CTA runs the same
+  // passes, dead rows predicated off), so the body is provably convergent and the shuffles compile
+  // to bare SHFL; with a per-warp bound each one carried a convergence check and a collective
+  // slow path (bf16 768 columns mean+var 5.47 -> 6.11 TB/s, 1024 columns 6.40 -> 6.95).
+  // R == 2 forms keep the per-warp bound (the warp's FIRST group's row, so its lanes leave
+  // together): measured faster there (bf16 256 columns: max 7.05 vs 6.66, mean+var 5.87 vs 5.10).
+  constexpr bool kWarpLoop = (R == 2);
+  const int first_grp = kWarpLoop ? (G < 32 ? (threadIdx.x >> 5) * (32 / (G < 32 ? G : 32)) : grp) : 0;
   const long long lag = static_cast<long long>(grp - first_grp) * R;
   for (long long w0 = (static_cast<long long>(blockIdx.x) * kGroups + first_grp) * R; w0 < rows;
        w0 += static_cast<long long>(gridDim.x) * kGroups * R) {
@@ -185,6 +190,59 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Aligned rows of 1..16 vectors (8..64 fp32, 8..128 bf16 elements: class counts, heads, small
+// feature maps).  G = 1, 2, 4, 8 or 16 lanes per row, one 16-byte load per lane per row, R rows
+// per group with all R loads issued together.  Rows are dealt round-robin over the warp's groups,
+// so one warp instruction reads 32/G consecutive rows: a contiguous 512 bytes when the row is
+// exactly G vectors.  row_small_kernel reads such a row element by element in a loop with one
+// load in flight (fp32 [., 32]: 4.1 TB/s).
+template <typename T, typename Acc, typename Op, int G, int R>
+__global__ void __launch_bounds__(kBlock)
+    row_tiny_kernel(const T* __restrict__ x, long long rows, int nvec, Epilogue ep) {
+  constexpr int kPerWarp = 32 / G;
+  constexpr int kPerCta = kWarps * kPerWarp * R;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  // The loop bound depends on blockIdx alone: the compiler then knows the body is not divergent
+  // and emits bare shuffles.  With a per-warp bound every shuffle carried a convergence check
+  // and a collective slow path (24 of them per pass at G = 8), and the kernel was issue-bound.
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kPerCta; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kPerCta) {
+    const long long left = rows - c0;
+    const int live = left > kPerCta ? kPerCta : static_cast<int>(left);  // rows of this pass
+    const int first = warp * (kPerWarp * R) + sub;                       // this lane's first row
+    const V16* __restrict__ xv = reinterpret_cast<const V16*>(x) + c0 * nvec;
+    V16 buf[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = first + r * kPerWarp;
+      if (row < live && g < nvec) buf[r] = ldg_stream16(xv + (row * nvec + g));
+    }
+    Acc a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = first + r * kPerWarp;
+      Acc acc[kFoldLanes];
+#pragma unroll
+      for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+      if (row < live && g < nvec) fold_vec<Acc, Op, T, kFoldLanes>(buf[r], acc);
+      a[r] = fold_lanes<Acc, Op>(acc);
+    }
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) a[r] = Op::combine(a[r], shfl_xor(a[r], m));
+    }
+    if (g == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int row = first + r * kPerWarp;
+        if (row < live) store_final<Op>(ep, c0 + row, a[r]);
+      }
+    }
+  }
+}
+
 // Short rows of any alignment, 129..1023 elements (odd hidden sizes): G = 16 or 32 lanes per row,
 // NE scalar loads per lane issued together (4-byte pair loads for 16-bit types in the 32-per-lane
 // form), shuffle tree inside the G lanes.  The peel in reduce_span costs such a row a scalar
@@ -195,9 +253,10 @@ __global__ void __launch_bounds__(kBlock)
   constexpr int kPerWarp = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
-  for (long long w0 = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kPerWarp; w0 < rows;
-       w0 += static_cast<long long>(gridDim.x) * kWarps * kPerWarp) {
-    const long long row = w0 + sub;
+  // (loop bound on blockIdx alone: bare shuffles, see row_tiny_kernel)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long row = c0 + warp * kPerWarp + sub;
     const bool live = row < rows;
     T raw[NE];
     int odd;
@@ -225,10 +284,10 @@ __global__ void __launch_bounds__(kBlock)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G;
   constexpr int kRowsPerWarp = 32 / G;
-  // the loop condition is warp-uniform: every lane takes part in the shuffles
-  for (long long wbase = (static_cast<long long>(blockIdx.x) * kWarps + warp) * kRowsPerWarp; wbase < rows;
-       wbase += static_cast<long long>(gridDim.x) * kWarps * kRowsPerWarp) {
-    const long long row = wbase + lane / G;
+  // the loop condition is CTA-uniform: every lane takes part in the shuffles
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kRowsPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kRowsPerWarp)) {
+    const long long row = c0 + warp * kRowsPerWarp + lane / G;
     const bool valid = row < rows;
     Acc acc = Op::identity();
     if (valid) {

@@ -68,9 +68,30 @@ int launch_reduce_typed(const ReduceArgs& a) {
 #undef B200PHI_ROWB
       break;
     }
+    case kRowTiny: {
+      const int nvec = static_cast<int>(p.cols / VecOf<T>::kElems);
+#define B200PHI_ROWT(GG) \
+  row_tiny_kernel<T, Acc, Op, GG, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, nvec, ep)
+      if (p.G == 1)
+        B200PHI_ROWT(1);
+      else if (p.G == 2)
+        B200PHI_ROWT(2);
+      else if (p.G == 4)
+        B200PHI_ROWT(4);
+      else if (p.G == 8)
+        B200PHI_ROWT(8);
+      else
+        B200PHI_ROWT(16);
+#undef B200PHI_ROWT
+      break;
+    }
     case kRowScalar: {
       const int c = static_cast<int>(p.cols);
-      if (p.G == 16)
+      if (p.G == 8 && p.nv == 8)
+        row_scalar_kernel<T, Acc, Op, 8, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      else if (p.G == 8)
+        row_scalar_kernel<T, Acc, Op, 8, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      else if (p.G == 16)
         row_scalar_kernel<T, Acc, Op, 16, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
       else if (p.nv == 16)
         row_scalar_kernel<T, Acc, Op, 32, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);

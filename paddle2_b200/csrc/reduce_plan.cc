@@ -327,7 +327,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     if (kind != kRowSplit) kind = (G == 256) ? kRowBlock : kRowWarp;
     // rows under 16 KiB: every load of R rows in one round (row_batch_kernel)
     const long long nvec_row = row_bytes / 16;
-    if (kind != kRowSplit && p->aligned && nvec_row < 1024 && p->cols > 128 && !t.no_row_batch &&
+    if (kind != kRowSplit && p->aligned && nvec_row < 1024 && (p->cols > 128 || nvec_row > 16) && !t.no_row_batch &&
         t.force_kind < 0) {
       kind = kRowBatch;
       if (nvec_row <= 32) {  // sub-warp groups: a 3- or 4-step shuffle tree instead of 5 per row
@@ -344,11 +344,23 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         p->G = 128, p->nv = 8, p->rpg = 1;
       }
     }
+    // aligned rows of at most 16 vectors
+    if ((kind == kRowWarp || kind == kRowBlock) && p->aligned && nvec_row >= 1 && nvec_row <= 16 &&
+        p->cols <= 128 && p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch) {
+      kind = kRowTiny;
+      p->G = pow2_ceil(nvec_row);
+      p->rpg = 8;
+    }
     // short rows that are not whole aligned vectors
-    if ((kind == kRowWarp || kind == kRowBlock) && !p->aligned && p->cols > 128 && p->cols < 1024 &&
-        p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch) {
+    // (rows of 33..128 elements take it whether aligned or not: the vector kernels start above that)
+    if ((kind == kRowWarp || kind == kRowBlock) && p->cols > 32 && p->cols < 1024 &&
+        (p->cols <= 128 || !p->aligned) && p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch) {
       kind = kRowScalar;
-      if (p->cols < 256) {
+      if (p->cols <= 64) {
+        p->G = 8, p->nv = 8;
+      } else if (p->cols <= 128) {
+        p->G = 8, p->nv = 16;
+      } else if (p->cols < 256) {
         p->G = 16, p->nv = 16;
       } else if (p->cols < 512) {
         p->G = 32, p->nv = 16;
@@ -373,6 +385,15 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     case kRowSmall: {
       const long long ctas = ceil_div(p->rows, 256 / p->G);
       p->grid_x = static_cast<unsigned>(std::min<long long>(ctas, 0x7fffffffLL));
+      p->grid_y = 1;
+      break;
+    }
+    case kRowTiny: {
+      const long long per_cta = 8LL * (32 / p->G) * p->rpg;
+      long long ctas = ceil_div(p->rows, per_cta);
+      const long long cap = static_cast<long long>(t.sm_count) * 8 * std::max(1, t.row_batch_waves);
+      if (ctas > cap) ctas = cap;
+      p->grid_x = static_cast<unsigned>(ctas);
       p->grid_y = 1;
       break;
     }

@@ -27,6 +27,7 @@ enum ReduceKind {
   kCol = 3,       // [outer, R, inner]
   kGeneric = 4,   // anything else (also the reduce_num == 1 cast/copy)
   kRowSmall = 5,  // [rows, cols] with short rows: G < 32 lanes per row
+  kRowTiny = 9,   // [rows, cols], aligned rows of 1..16 vectors: G <= 16 lanes per row, 8 rows per group
   kRowScalar = 8, // [rows, cols], 129..1023 columns of any alignment: G lanes per row, scalar loads
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
   kTwoStage = 6   // [A, K, B] with A and B reduced (per-channel statistics of [N,C,H,W]): the

@@ -124,3 +124,30 @@ def test_unaligned_short_row_reduce(rows, cols, dt):
         else:
             # SumRawInferMeta: uint8 sums stay uint8 (wrap), int32 sums widen to int64
             assert torch.equal(got.long(), x.long().sum(-1) % 256 if dt == torch.uint8 else x.long().sum(-1))
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.int32, torch.uint8, torch.float64, torch.int64])
+@pytest.mark.parametrize("rows,cols", [(64, 16), (1000, 32), (4099, 48), (777, 64), (513, 80), (300, 96), (65, 128),
+                                       (100000, 16), (33333, 112)])
+def test_tiny_aligned_row_reduce(rows, cols, dt):
+    """aligned rows of 1..16 vectors (row_tiny_kernel, G = 1..16 lanes per row, 8 rows per group) and
+    the 17..32-vector rows that now take the batch kernel; row counts that end inside a group"""
+    gen = torch.Generator().manual_seed(rows * 7 + cols)
+    if dt.is_floating_point:
+        x = (torch.randn(rows, cols, generator=gen) * 3).to(dt)
+    else:
+        x = torch.randint(0, 100, (rows, cols), generator=gen).to(dt)
+    xd = x.cuda()
+    assert torch.equal(pb.max(xd, axis=-1).cpu(), x.amax(-1))
+    assert torch.equal(pb.min(xd, axis=-1).cpu(), x.amin(-1))
+    got = pb.sum(xd, axis=-1).cpu()
+    if dt.is_floating_point:
+        tol = {torch.float32: 1e-5, torch.bfloat16: 1e-2, torch.float64: 1e-12}[dt]
+        np.testing.assert_allclose(got.double().numpy(), x.double().sum(-1).numpy(), rtol=tol,
+                                   atol=tol * float(x.double().abs().sum(-1).max()))
+    else:
+        assert torch.equal(got.long(), x.long().sum(-1) % 256 if dt == torch.uint8 else x.long().sum(-1))
+    if dt.is_floating_point:
+        m = pb.mean(xd, axis=-1).double().cpu().numpy()
+        np.testing.assert_allclose(m, x.double().mean(-1).numpy(), rtol=1e-2 if dt == torch.bfloat16 else 1e-5,
+                                   atol=1e-2 if dt == torch.bfloat16 else 1e-5)

@@ -1,0 +1,21 @@
+"""sum / max over rows of 8..128 elements, 4 GiB (fp32) tensors."""
+import sys, torch
+sys.path.insert(0, '.')
+import paddle2_b200 as pb
+def t(fn, n=5):
+    for _ in range(2): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n): fn()
+    b.record(); torch.cuda.synchronize()
+    return a.elapsed_time(b) / n * 1e3
+N = 1 << 30
+for dt in (torch.float32, torch.bfloat16):
+    for cols in (8, 16, 32, 40, 49, 64, 96, 101, 128):
+        rows = N // cols
+        x = torch.randn(rows, cols, device="cuda").to(dt)
+        for name, fn in (("sum", lambda: pb.sum(x, axis=-1)), ("max", lambda: pb.max(x, axis=-1))):
+            us = t(fn, 3)
+            print(f"{name:10s} {str(dt)[6:]:9s} [{rows},{cols}] {us:9.1f} us {x.numel()*x.element_size()/us/1e6:6.2f} TB/s", flush=True)
+        del x
