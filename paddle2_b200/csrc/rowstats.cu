@@ -845,6 +845,84 @@ static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int o
   return B200PHI_OK;
 }
 
+
+// Rows of 1 .. 16 KiB that are not whole aligned vectors (1025-, 2049-, 4097-column rows): one WARP
+// per row, the row kept in registers -- up to VE-1 head elements (one per lane), NV 16-byte
+// vectors per lane from the first aligned address, up to VE-1 tail elements -- so both passes of
+// the two-pass variance read registers, no barrier, no second sweep of L2.  The CTA-per-row
+// sweep kernel above spends two block reductions per 4 KiB row (fp32 1025 columns: 1.6 TB/s).
+template <typename T, typename Acc, int NV>
+__global__ void __launch_bounds__(kBlock)
+    rowstats_warp_peel_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+                              Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
+  constexpr int VE = VecOf<T>::kElems;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // (loop bound on blockIdx alone: the shuffles compile to bare SHFL)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kWarps; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kWarps) {
+    const long long row = c0 + warp;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + (live ? row : 0) * cols;
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
+    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
+    if (head > cols) head = static_cast<int>(cols);
+    const int nvec = static_cast<int>((cols - head) / VE);
+    const int tail0 = head + nvec * VE;
+    const int ntail = static_cast<int>(cols) - tail0;
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    const bool has_h = live && lane < head, has_t = live && lane < ntail;
+    Acc hv = Acc(0), tv = Acc(0);
+    if (has_h) hv = Cvt<Acc, T>::to(ldg_scalar(r + lane));
+    if (has_t) tv = Cvt<Acc, T>::to(ldg_scalar(r + tail0 + lane));
+    V16 buf[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
+    }
+    Acc s[4] = {hv, tv, Acc(0), Acc(0)};
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (live && v < nvec) fold_vec<Acc, SumOp<Acc>, T, 4>(buf[k], s);
+    }
+    const Acc sum = warp_combine<Acc, SumOp<Acc>>((s[0] + s[1]) + (s[2] + s[3]));
+    const Acc mean = sum / cols_acc;
+    Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    if (has_h) q[0] = (hv - mean) * (hv - mean);
+    if (has_t) q[1] = (tv - mean) * (tv - mean);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (live && v < nvec) {
+        Acc val[VE];
+        unpack_vec<T, Acc>(buf[k], val);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          const Acc dlt = val[e] - mean;
+          q[e % 4] += dlt * dlt;
+        }
+      }
+    }
+    const Acc ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    if (live && lane == 0) {
+      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
+      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+    }
+  }
+}
+
+// Smallest row, in bytes, that takes the one-sweep moments kernel instead of the two-sweep one
+// (B200PHI_ROWSTATS_STREAM_MIN overrides, for measurement).
+static long long stream_min_bytes(bool aligned) {
+  static const long long env = [] {
+    const char* e = getenv("B200PHI_ROWSTATS_STREAM_MIN");
+    return e ? atoll(e) : -1LL;
+  }();
+  if (env >= 0) return env;
+  (void)aligned;
+  return 24 * 1024;
+}
 template <typename T, typename Acc>
 static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaStream_t stream) {
   constexpr int VE = VecOf<T>::kElems;
@@ -960,7 +1038,24 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       B200PHI_RS_SCALAR(32, 32)
 #undef B200PHI_RS_SCALAR
-  } else if (getenv("B200PHI_ROWSTATS_SWEEP") == nullptr && row_bytes >= 24 * 1024) {
+  } else if (!aligned && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
+    // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
+    long long ctas = (d->rows + kWarps - 1) / kWarps;
+    const long long cap = static_cast<long long>(sms) * 8 * 8;
+    if (ctas > cap) ctas = cap;
+    if (row_bytes < 4112)
+      rowstats_warp_peel_kernel<T, Acc, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (row_bytes < 8208)
+      rowstats_warp_peel_kernel<T, Acc, 16><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (row_bytes < 12304)
+      rowstats_warp_peel_kernel<T, Acc, 24><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else
+      rowstats_warp_peel_kernel<T, Acc, 32><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+  } else if (getenv("B200PHI_ROWSTATS_SWEEP") == nullptr && row_bytes >= stream_min_bytes(aligned)) {
     // (measured: 16 KiB rows are faster on the two-sweep kernel, 4.2 vs 3.5 TB/s -- the triple
     // merges and two barriers per row weigh more on short rows; 32 KiB rows 5.2 vs 3.7)
     // long rows (and medium rows of any alignment): one sweep, pairwise moment merges

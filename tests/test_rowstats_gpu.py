@@ -88,3 +88,24 @@ def test_long_rows_one_sweep(tdt, rows, cols):
     m, v = pb.row_mean_var(xt.cuda(), out_dtype="float32") if tdt != torch.float32 else pb.row_mean_var(xt.cuda())
     np.testing.assert_allclose(m.cpu().numpy(), x64.mean(-1).numpy(), rtol=1e-5, atol=1e-5)
     np.testing.assert_allclose(v.cpu().numpy(), x64.var(-1, unbiased=True).numpy(), rtol=1e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("rows,cols", [(64, 1025), (777, 1027), (130, 2049), (65, 2051), (100, 3001), (67, 4097), (3, 1025),
+                                       (70, 6001), (66, 8191), (64, 8193)])
+def test_unaligned_medium_rows_warp_peel(rows, cols, dt):
+    """1..16 KiB rows that are not whole aligned vectors: a warp per row with the row in registers
+    (head / vectors / tail); also from a base one element past a 16-byte boundary"""
+    import numpy as np
+    import paddle2_b200 as pb
+    gen = torch.Generator().manual_seed(rows + 31 * cols)
+    flat = (torch.randn(rows * cols + 1, generator=gen) * 2 + 0.5).to(dt)
+    fd = flat.cuda()
+    for off in (0, 1):
+        x = flat[off:off + rows * cols].view(rows, cols)
+        xd = fd[off:off + rows * cols].view(rows, cols)
+        m, v = pb.row_mean_var(xd, out_dtype="float32")
+        x64 = x.double()
+        np.testing.assert_allclose(m.cpu().numpy(), x64.mean(-1).numpy(), rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(v.cpu().numpy(), x64.var(-1, unbiased=True).numpy(), rtol=1e-4)
