@@ -846,7 +846,7 @@ static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int o
 }
 
 
-// Rows of 1 .. 16 KiB that are not whole aligned vectors (1025-, 2049-, 4097-column rows): one WARP
+// Rows of 0.6 .. 16 KiB that are not whole aligned vectors (301- .. 4097-column rows): one WARP
 // per row, the row kept in registers -- up to VE-1 head elements (one per lane), NV 16-byte
 // vectors per lane from the first aligned address, up to VE-1 tail elements -- so both passes of
 // the two-pass variance read registers, no barrier, no second sweep of L2.  The CTA-per-row
@@ -910,6 +910,18 @@ __global__ void __launch_bounds__(kBlock)
       if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
     }
   }
+}
+
+// Smallest row, in bytes, that takes the warp-per-row peel kernel rather than the sub-warp scalar
+// one (B200PHI_ROWSTATS_PEEL_MIN overrides, for measurement).
+// Measured (4 GiB tensors): fp32 301 columns (1204 B) 4.64 vs 3.79 TB/s for the scalar kernel,
+// 201 columns (804 B) 3.22 vs 4.91; bf16 301 columns (602 B) 1.97 vs 1.59, 201 columns 1.48 vs 2.11.
+static long long peel_min_bytes(size_t esize) {
+  static const long long env = [] {
+    const char* e = getenv("B200PHI_ROWSTATS_PEEL_MIN");
+    return e ? atoll(e) : -1LL;
+  }();
+  return env >= 0 ? env : (esize == 2 ? 600 : 1024);
 }
 
 // Smallest row, in bytes, that takes the one-sweep moments kernel instead of the two-sweep one
@@ -1017,6 +1029,26 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+  } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
+    // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
+    long long ctas = (d->rows + kWarps - 1) / kWarps;
+    const long long cap = static_cast<long long>(sms) * 8 * 8;
+    if (ctas > cap) ctas = cap;
+    if (row_bytes < 2064)
+      rowstats_warp_peel_kernel<T, Acc, 4><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (row_bytes < 4112)
+      rowstats_warp_peel_kernel<T, Acc, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (row_bytes < 8208)
+      rowstats_warp_peel_kernel<T, Acc, 16><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (row_bytes < 12304)
+      rowstats_warp_peel_kernel<T, Acc, 24><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else
+      rowstats_warp_peel_kernel<T, Acc, 32><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (n <= 1023 && d->rows >= 64) {  // (one slot spare: a 16-bit row may start mid-word)
     // short rows that are ragged or unaligned: sub-warp groups, scalar loads, row in registers
     const int c = static_cast<int>(n);
@@ -1038,23 +1070,6 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       B200PHI_RS_SCALAR(32, 32)
 #undef B200PHI_RS_SCALAR
-  } else if (!aligned && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
-    // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
-    long long ctas = (d->rows + kWarps - 1) / kWarps;
-    const long long cap = static_cast<long long>(sms) * 8 * 8;
-    if (ctas > cap) ctas = cap;
-    if (row_bytes < 4112)
-      rowstats_warp_peel_kernel<T, Acc, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-    else if (row_bytes < 8208)
-      rowstats_warp_peel_kernel<T, Acc, 16><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-    else if (row_bytes < 12304)
-      rowstats_warp_peel_kernel<T, Acc, 24><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-    else
-      rowstats_warp_peel_kernel<T, Acc, 32><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (getenv("B200PHI_ROWSTATS_SWEEP") == nullptr && row_bytes >= stream_min_bytes(aligned)) {
     // (measured: 16 KiB rows are faster on the two-sweep kernel, 4.2 vs 3.5 TB/s -- the triple
     // merges and two barriers per row weigh more on short rows; 32 KiB rows 5.2 vs 3.7)

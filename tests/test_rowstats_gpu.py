@@ -92,7 +92,7 @@ def test_long_rows_one_sweep(tdt, rows, cols):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("rows,cols", [(64, 1025), (777, 1027), (130, 2049), (65, 2051), (100, 3001), (67, 4097), (3, 1025),
+@pytest.mark.parametrize("rows,cols", [(64, 301), (333, 501), (129, 701), (65, 1001), (64, 1025), (777, 1027), (130, 2049), (65, 2051), (100, 3001), (67, 4097), (3, 1025),
                                        (70, 6001), (66, 8191), (64, 8193)])
 def test_unaligned_medium_rows_warp_peel(rows, cols, dt):
     """1..16 KiB rows that are not whole aligned vectors: a warp per row with the row in registers
