@@ -322,6 +322,54 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// 16-bit rows of 0.5 .. 4 KiB that are not whole aligned vectors (1001-, 2049-column rows): one
+// WARP per row, all loads issued together -- up to 7 head elements (one per lane), NV 16-byte
+// vectors per lane from the first aligned address, up to 7 tail elements -- and visited in
+// ascending index order per lane, so the strict compare keeps the first occurrence.  The scalar
+// kernel above reads such a row with 2-byte loads (bf16 1001 columns: 1.5 TB/s), the peeled
+// arg_row_kernel in three dependent phases (2.7 TB/s).
+template <typename T, typename V, bool kMax, int NV>
+__global__ void __launch_bounds__(kBlock)
+    arg_warp_peel_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
+                         void* val_out) {
+  using Op = ArgOp<V, kMax>;
+  constexpr int VE = VecOf<T>::kElems;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // (loop bound on blockIdx alone: bare shuffles)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kWarps; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kWarps) {
+    const long long row = c0 + warp;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + (live ? row : 0) * n;
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
+    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
+    if (head > n) head = n;
+    const int nvec = (n - head) / VE;
+    const int tail0 = head + nvec * VE;
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    const bool has_h = live && lane < head, has_t = live && tail0 + lane < n;
+    T hv, tv;
+    if (has_h) hv = ldg_scalar(r + lane);
+    if (has_t) tv = ldg_scalar(r + tail0 + lane);
+    V16 buf[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
+    }
+    ArgPair<V> best = Op::identity();
+    if (has_h) Op::visit(best, Cvt<V, T>::to(hv), lane);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (live && v < nvec) visit_vec<T, V, kMax>(best, buf[k], head + static_cast<long long>(v) * VE);
+    }
+    if (has_t) Op::visit(best, Cvt<V, T>::to(tv), tail0 + lane);
+    best = warp_arg<V, Op>(best);
+    if (live && lane == 0) store_arg<T, V>(out, index_dtype, val_out, row, best);
+  }
+}
+
 // post > 1: [pre, n, post].  Block = TX x TY: tx walks post (contiguous), ty walks n.
 template <typename T, typename V, bool kMax>
 __global__ void __launch_bounds__(kBlock)
@@ -439,6 +487,24 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       cudaError_t e1 = cudaGetLastError();
       if (e1 != cudaSuccess) return cuda_status(e1);
       return B200PHI_OK;
+    }
+    if constexpr (sizeof(T) == 2) {
+      static const bool no_peel = getenv("B200PHI_ARG_NO_PEEL") != nullptr;
+      // (measured, bf16: 1001 columns 4.89 TB/s against 2.65 for the peeled row kernel; at 4097
+      // columns a 16-vector form was slower, 4.78 against 5.39, so rows stop at 4 KiB here)
+      if (!aligned && !no_peel && g.n >= 256 && row_bytes < 4112 && g.pre >= 64 && !force_g && !force_u) {
+        long long pc = (g.pre + kWarps - 1) / kWarps;
+        if (pc > 148LL * 8 * 8) pc = 148LL * 8 * 8;
+        const unsigned gp = static_cast<unsigned>(pc);
+        const int c = static_cast<int>(g.n);
+        if (row_bytes < 2064)
+          arg_warp_peel_kernel<T, V, kMax, 4><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        else
+          arg_warp_peel_kernel<T, V, kMax, 8><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        cudaError_t e2 = cudaGetLastError();
+        if (e2 != cudaSuccess) return cuda_status(e2);
+        return B200PHI_OK;
+      }
     }
     long long ctas = (g.pre + (kBlock / G) - 1) / (kBlock / G);
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;

@@ -66,3 +66,33 @@ def test_int32_indices_keepdim_flatten(oracle):
     assert tuple(got.shape) == (1, 1, 1) and int(got) == int(np.argmin(x))
     with pytest.raises(ValueError):
         pb.argmax(torch.empty(0, device="cuda"))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16, torch.int16])
+@pytest.mark.parametrize("rows,cols", [(64, 257), (333, 1001), (129, 1031), (65, 2049), (70, 3001), (67, 4097), (66, 4103)])
+def test_16bit_unaligned_rows_warp_peel(rows, cols, dt):
+    """16-bit rows that are not whole aligned vectors (arg_warp_peel_kernel): many ties (small value
+    range) so the first occurrence matters, head and tail elements included; also from a base one
+    element past a 16-byte boundary"""
+    import numpy as np
+    import paddle2_b200 as pb
+    gen = torch.Generator().manual_seed(rows * 5 + cols)
+    flat = torch.randint(-6, 7, (rows * cols + 1,), generator=gen).to(dt)
+    fd = flat.cuda()
+    for off in (0, 1):
+        x = flat[off:off + rows * cols].view(rows, cols)
+        xd = fd[off:off + rows * cols].view(rows, cols)
+        ref = x.float().numpy()
+        assert np.array_equal(pb.argmax(xd, axis=-1).cpu().numpy(), np.argmax(ref, axis=-1))
+        assert np.array_equal(pb.argmin(xd, axis=-1).cpu().numpy(), np.argmin(ref, axis=-1))
+        idx, val = pb.argmax_with_value(xd, axis=-1)
+        assert np.array_equal(idx.cpu().numpy(), np.argmax(ref, axis=-1))
+        assert torch.equal(val.cpu(), x.amax(-1))
+    # the extreme sits in the head / in the tail of the row
+    x = torch.zeros(rows, cols, dtype=dt)
+    x[:, 0] = 3
+    x[1::2, 0] = 0
+    x[1::2, cols - 1] = 5
+    xd = x.cuda()
+    assert np.array_equal(pb.argmax(xd, axis=-1).cpu().numpy(), np.argmax(x.float().numpy(), axis=-1))
