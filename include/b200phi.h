@@ -60,7 +60,8 @@ typedef enum {
   B200PHI_UNSUPPORTED = 2,      /* dtype / op combination not built */
   B200PHI_CUDA_ERROR = 3,
   B200PHI_WORKSPACE_TOO_SMALL = 4,
-  B200PHI_NCCL_ERROR = 5
+  B200PHI_NCCL_ERROR = 5,
+  B200PHI_PEER_TIMEOUT = 6 /* b200phi_sharded_reduce_p2p: a peer never published its partial */
 } b200phi_status;
 
 /* ------------------------------------------------------------------------ */
@@ -126,8 +127,9 @@ B200PHI_API size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d);
  * is fused into the load. */
 B200PHI_API int b200phi_reduce(const b200phi_reduce_desc* d, void* stream);
 
-/* No counterpart in the reference.  The same column (leading-axis) reduce as
- * b200phi_reduce, for hosts that cannot hand over a workspace because they may not, or
+/* No counterpart in the reference.  The same reductions as b200phi_reduce (any shape: column
+ * reduces, few very long rows, two-stage [A,K,B] patterns -- the ones that need scratch -- and
+ * all the others), for hosts that cannot hand over a workspace because they may not, or
  * cannot, allocate device memory where the call is made: a C/Go service linking this
  * library with no device allocator of its own, a server whose memory plan is frozen before
  * the first request, a callback that must not take the allocator lock.  The scratch is a
@@ -162,7 +164,18 @@ typedef struct {
   const void* x;
   void* out;
   void* max_out;       /* optional: also write the extreme value (in_dtype); NULL to skip */
+  void* workspace;     /* device scratch, >= b200phi_argreduce_workspace() bytes, 256-B aligned; may be NULL if 0 */
+  size_t workspace_bytes;
 } b200phi_argreduce_desc;
+
+/* Bytes of device scratch b200phi_argreduce needs for this descriptor on the current device: 0
+ * when there is a thread-block group per slice (many rows reduced over the last axis); non-zero
+ * when the reduced extent is cut across thread blocks -- `flatten` (paddle.argmax's default
+ * axis=None: the whole tensor is ONE slice), few long rows, or a non-last axis -- and the block
+ * that finishes last combines the (value, index) partials.  ComputeFullArg
+ * (gpu/arg_min_max_kernel.cu:85-145) has no counterpart: it gives every slice one block.  The
+ * answer does not depend on d->x.  Returns 0 on a bad descriptor; b200phi_argreduce reports it. */
+B200PHI_API size_t b200phi_argreduce_workspace(const b200phi_argreduce_desc* d);
 
 B200PHI_API int b200phi_argreduce(const b200phi_argreduce_desc* d, void* stream);
 
@@ -401,6 +414,14 @@ B200PHI_API int b200phi_comm_destroy(void* comm);
 B200PHI_API int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count,
                            void* comm, void* stream);
 
+/* Scratch b200phi_sharded_reduce needs in d->workspace: b200phi_reduce_workspace(d), plus --
+ * when the result is a SUM / MEAN into FLOAT16 / BFLOAT16 -- room for the rank's partial in
+ * FLOAT32.  Such a partial is the reference's MPType (amp_type_traits.h:25-53): it is all-reduced
+ * in fp32 and rounded to the 16-bit type once, after the ranks are combined, where an allreduce
+ * in the output dtype would round once per rank and once per NCCL step.  Every argument is
+ * checked before anything is enqueued, so a rank that gets an error has launched nothing. */
+B200PHI_API size_t b200phi_sharded_reduce_workspace(const b200phi_reduce_desc* d);
+
 /* argmax / argmin over the SHARDED leading axis.  d describes the local shard and must reduce
  * axis 0; row_offset is the global index of the shard's first row.  Each rank reduces its rows to
  * (value, global index) per column, the small pairs are all-gathered (NCCL has no arg-reduce)
@@ -412,27 +433,34 @@ B200PHI_API int b200phi_sharded_argreduce(const b200phi_argreduce_desc* d, int64
                                           int nranks, void* comm, void* workspace,
                                           size_t workspace_bytes, void* stream);
 
-/* ---- fused variant: local reduce + exchange over NVLink peer memory in ONE kernel ---- */
+/* ---- without a collective library: local reduce + exchange over NVLink peer memory ---- */
 
 /* Replaces the same reference pair as b200phi_sharded_reduce
- * (SumKernel + ProcessGroupNCCL::AllReduce, process_group_nccl.cc:267-298), without a
- * collective library on the path: the thread block that finishes an output tile writes it
- * into every peer's buffer (CUDA IPC mapping), publishes an epoch flag and combines the
- * ranks' slots in rank order, so every rank ends with identical bits.
+ * (SumKernel + ProcessGroupNCCL::AllReduce, process_group_nccl.cc:267-298).  The local reduce
+ * (the unchanged kernels of b200phi_reduce) writes the rank's partial -- in the accumulation
+ * type, so 16-bit float sums are rounded once -- into the rank's own exchange buffer; a small
+ * second kernel, launched with programmatic dependent launch so that its launch latency hides
+ * under the reduce, pushes the partial into every peer's buffer (CUDA IPC mapping), publishes an
+ * epoch flag, waits for the peers' flags and combines the ranks' slots in rank order, so every
+ * rank ends with identical bits.  Any shape / dtype / op b200phi_sharded_reduce takes.
  * Set-up (once): every rank allocates b200phi_p2p_buffer_bytes(...) with b200phi_p2p_alloc,
  * exchanges the 64-byte handles with its rendezvous, maps the peers' buffers with
- * b200phi_p2p_open and fills base[r] (base[rank] = its own pointer).
+ * b200phi_p2p_open and fills base[r] (base[rank] = its own pointer, which must come from
+ * b200phi_p2p_alloc).
  * Per call: the same epoch on every rank, starting at 1 and growing by 1; calls of one
- * group must be issued in the same order on every rank; the kernels of all ranks must be
- * able to run at the same time (one GPU per rank).  Covers the vectorised column reduce
- * (leading axis sharded) for fp32 sum/mean/max/min, bf16/fp64/int64 sum; anything else
- * returns B200PHI_UNSUPPORTED and b200phi_sharded_reduce is the route. */
+ * group must be issued in the same order, with the same output shape, on every rank and on one
+ * stream per rank; the kernels of all ranks must be able to run at the same time (one GPU per rank).
+ * Failure mode: a peer that does not publish within B200PHI_P2P_TIMEOUT_MS (environment, read
+ * once; default 4000) makes the waiting rank write NOTHING to d->out for that call and record
+ * the epoch in a host-visible status word; the next b200phi_sharded_reduce_p2p on the group, or
+ * b200phi_p2p_status(base[rank]) after a stream synchronise, returns B200PHI_PEER_TIMEOUT.  A
+ * group that timed out is out of step and must be torn down. */
 typedef struct {
   int32_t nranks;        /* 1..8 */
   int32_t rank;
   void* base[8];         /* base[r]: rank r's buffer as mapped into this process */
   int64_t max_out_numel; /* output elements the buffers were sized for */
-  int64_t max_tiles;     /* output tiles (thread blocks along the kept axis) they were sized for */
+  int64_t max_tiles;     /* flags per rank: the exchange runs on min(64, max_tiles, what the size needs) CTAs */
 } b200phi_p2p_group;
 
 B200PHI_API size_t b200phi_p2p_buffer_bytes(int nranks, int64_t max_out_numel, int64_t max_tiles);
@@ -440,6 +468,10 @@ B200PHI_API int b200phi_p2p_alloc(size_t bytes, void** ptr, unsigned char handle
 B200PHI_API int b200phi_p2p_open(const unsigned char handle[64], void** ptr);
 B200PHI_API int b200phi_p2p_close(void* ptr);
 B200PHI_API int b200phi_p2p_free(void* ptr);
+/* B200PHI_OK, or B200PHI_PEER_TIMEOUT if an exchange on this buffer (own_ptr from
+ * b200phi_p2p_alloc) gave up waiting for a peer.  Host-side read of a mapped word: no stream
+ * synchronisation, so call it after synchronising the stream of the call it should cover. */
+B200PHI_API int b200phi_p2p_status(void* own_ptr);
 B200PHI_API int b200phi_sharded_reduce_p2p(const b200phi_reduce_desc* d, int64_t global_reduce_count,
                                            const b200phi_p2p_group* g, uint32_t epoch, void* stream);
 

@@ -61,6 +61,7 @@ STATUS_NAMES = {
     3: "CUDA_ERROR",
     4: "WORKSPACE_TOO_SMALL",
     5: "NCCL_ERROR",
+    6: "PEER_TIMEOUT",
 }
 
 
@@ -93,6 +94,8 @@ class ArgReduceDesc(C.Structure):
         ("x", C.c_void_p),
         ("out", C.c_void_p),
         ("max_out", C.c_void_p),
+        ("workspace", C.c_void_p),
+        ("workspace_bytes", C.c_size_t),
     ]
 
 
@@ -194,6 +197,7 @@ EXPORTS = [
     "b200phi_reduce_workspace",
     "b200phi_reduce",
     "b200phi_reduce_noalloc",
+    "b200phi_argreduce_workspace",
     "b200phi_argreduce",
     "b200phi_rowstats",
     "b200phi_elementwise",
@@ -204,6 +208,7 @@ EXPORTS = [
     "b200phi_comm_init_rank",
     "b200phi_comm_destroy",
     "b200phi_sharded_reduce",
+    "b200phi_sharded_reduce_workspace",
     "b200phi_sharded_argreduce_workspace",
     "b200phi_sharded_argreduce",
     "b200phi_p2p_buffer_bytes",
@@ -211,6 +216,7 @@ EXPORTS = [
     "b200phi_p2p_open",
     "b200phi_p2p_close",
     "b200phi_p2p_free",
+    "b200phi_p2p_status",
     "b200phi_sharded_reduce_p2p",
     "b200phi_last_error",
     "b200phi_version",
@@ -238,6 +244,8 @@ def lib():
     L.b200phi_reduce_noalloc.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
     L.b200phi_reduce_noalloc.restype = C.c_int
     L.b200phi_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_void_p]
+    L.b200phi_argreduce_workspace.restype = C.c_size_t
+    L.b200phi_argreduce_workspace.argtypes = [C.POINTER(ArgReduceDesc)]
     L.b200phi_rowstats.argtypes = [C.POINTER(RowStatsDesc), C.c_void_p]
     L.b200phi_elementwise.argtypes = [C.POINTER(ElementwiseDesc), C.c_void_p]
     L.b200phi_map.argtypes = [C.POINTER(MapDesc), C.c_void_p]
@@ -250,6 +258,10 @@ def lib():
     L.b200phi_comm_init_rank.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.b200phi_comm_destroy.argtypes = [C.c_void_p]
     L.b200phi_sharded_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_int64, C.c_void_p, C.c_void_p]
+    L.b200phi_sharded_reduce_workspace.restype = C.c_size_t
+    L.b200phi_sharded_reduce_workspace.argtypes = [C.POINTER(ReduceDesc)]
+    L.b200phi_p2p_status.argtypes = [C.c_void_p]
+    L.b200phi_p2p_status.restype = C.c_int
     L.b200phi_sharded_argreduce_workspace.restype = C.c_size_t
     L.b200phi_sharded_argreduce_workspace.argtypes = [C.POINTER(ArgReduceDesc), C.c_int]
     L.b200phi_sharded_argreduce.restype = C.c_int

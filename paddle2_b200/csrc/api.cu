@@ -44,6 +44,9 @@ int current_sm_count() {
   return cache[dev];
 }
 
+// Tunables of the current device (environment part cached, see reduce_plan.cc).
+Tunables tunables() { return default_tunables(current_sm_count()); }
+
 static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, cudaStream_t stream);
 static int run_reduce_stage(const b200phi_reduce_desc* d, int second, cudaStream_t stream) {
   return run_reduce_impl(d, second, stream);
@@ -53,7 +56,7 @@ int run_reduce(const b200phi_reduce_desc* d, cudaStream_t stream) { return run_r
 static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, cudaStream_t stream) {
   ReducePlan plan;
   std::string err;
-  Tunables tun = default_tunables(current_sm_count());
+  Tunables tun = tunables();
   tun.allow_narrow_out = allow_narrow_out;
   int rc = plan_reduce(d, tun, &plan, &err);
   if (rc != B200PHI_OK) return set_error(rc, err);
@@ -110,11 +113,32 @@ static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, c
   return rc;
 }
 
+// The plan may depend on whether x is 16-byte aligned (vector or scalar column walk); the query
+// must not: it answers for the worse of the two, whatever d->x holds (NULL included).
+size_t reduce_workspace_bytes(const b200phi_reduce_desc* d) {
+  if (!d) return 0;
+  const Tunables t = tunables();
+  size_t need = 0;
+  const size_t es = dtype_size(d->in_dtype) ? dtype_size(d->in_dtype) : 1;
+  for (int k = 0; k < 2; ++k) {
+    b200phi_reduce_desc probe = *d;
+    probe.x = reinterpret_cast<const void*>(static_cast<uintptr_t>(k == 0 ? 256 : 256 + es));
+    ReducePlan plan;
+    std::string err;
+    if (plan_reduce(&probe, t, &plan, &err) != B200PHI_OK) return 0;
+    if (plan.ws_total_bytes > need) need = plan.ws_total_bytes;
+    if (es >= 16) break;
+  }
+  return need;
+}
+
 int run_argreduce(const b200phi_argreduce_desc* d, cudaStream_t stream);
+size_t argreduce_workspace_bytes(const b200phi_argreduce_desc* d);
 int run_rowstats(const b200phi_rowstats_desc* d, cudaStream_t stream);
 int run_elementwise(const b200phi_elementwise_desc* d, cudaStream_t stream);
 int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, void* comm,
                        cudaStream_t stream);
+size_t sharded_reduce_workspace_bytes(const b200phi_reduce_desc* d);
 int comm_unique_id(unsigned char id[128]);
 int comm_init_rank(const unsigned char id[128], int nranks, int rank, void** comm);
 int comm_destroy(void* comm);
@@ -130,15 +154,14 @@ const char* b200phi_last_error(void) { return g_last_error.c_str(); }
 const char* b200phi_version(void) { return "b200phi 0.1 sm_100a"; }
 
 size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d) {
-  ReducePlan plan;
-  std::string err;
-  if (plan_reduce(d, default_tunables(current_sm_count()), &plan, &err) != B200PHI_OK) return 0;
-  return plan.ws_total_bytes;
+  return reduce_workspace_bytes(d);
 }
 
 int b200phi_reduce(const b200phi_reduce_desc* d, void* stream) {
   return run_reduce(d, static_cast<cudaStream_t>(stream));
 }
+
+size_t b200phi_argreduce_workspace(const b200phi_argreduce_desc* d) { return argreduce_workspace_bytes(d); }
 
 int b200phi_argreduce(const b200phi_argreduce_desc* d, void* stream) {
   return run_argreduce(d, static_cast<cudaStream_t>(stream));
@@ -159,6 +182,10 @@ int b200phi_comm_init_rank(const unsigned char id[128], int nranks, int rank, vo
 }
 
 int b200phi_comm_destroy(void* comm) { return comm_destroy(comm); }
+
+size_t b200phi_sharded_reduce_workspace(const b200phi_reduce_desc* d) {
+  return sharded_reduce_workspace_bytes(d);
+}
 
 int b200phi_sharded_reduce(const b200phi_reduce_desc* d, int64_t global_reduce_count, void* comm,
                            void* stream) {

@@ -4,12 +4,14 @@
 // streamed with 16-byte loads, indices are 64-bit, and the combine rule
 // "better value, else lower index" is applied at every level so ties are
 // bit-exact with the CPU kernel (Eigen argmax, cpu/arg_min_max_kernel.cc:46-59).
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <string>
 
 #include "../../include/b200phi.h"
-#include "prim.cuh"
+#include "arg_common.cuh"
+#include "arg_plan.h"
 #include "reduce_plan.h"
 
 namespace b200phi {
@@ -17,183 +19,20 @@ namespace b200phi {
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
 int current_sm_count();
+Tunables tunables();
+int launch_arg_split(int op, const ArgPlan& p, const void* x, void* out, void* val_out, void* ws,
+                     cudaStream_t s);
 
-template <typename V>
-struct ArgPair {
-  V v;
-  long long i;
+// probe knobs (environment, read once per process)
+struct ArgKnobs {
+  int force_g, force_u;
+  bool no_multi, no_peel;
 };
-
-// kMax: b replaces a when b.v > a.v, or equal and b.i < a.i.
-template <typename V, bool kMax>
-struct ArgOp {
-  static __device__ __forceinline__ ArgPair<V> identity() {
-    ArgPair<V> p;
-    p.v = kMax ? Limits<V>::lowest() : Limits<V>::highest();
-    p.i = 0;  // an all-identity slice answers 0, like the CPU kernel
-    return p;
-  }
-  static __device__ __forceinline__ bool better(V b, V a) { return kMax ? (b > a) : (b < a); }
-  static __device__ __forceinline__ ArgPair<V> combine(ArgPair<V> a, ArgPair<V> b) {
-    const bool take = better(b.v, a.v) || (b.v == a.v && b.i < a.i);
-    return take ? b : a;
-  }
-  // in-order visit by one thread: strict comparison keeps the first occurrence
-  static __device__ __forceinline__ void visit(ArgPair<V>& a, V v, long long i) {
-    if (better(v, a.v)) {
-      a.v = v;
-      a.i = i;
-    }
-  }
-};
-
-template <typename V>
-__device__ __forceinline__ ArgPair<V> shfl_pair(ArgPair<V> p, int m) {
-  ArgPair<V> r;
-  r.v = __shfl_xor_sync(0xffffffffu, p.v, m);
-  r.i = __shfl_xor_sync(0xffffffffu, p.i, m);
-  return r;
-}
-
-template <typename V, typename Op>
-__device__ __forceinline__ ArgPair<V> warp_arg(ArgPair<V> p) {
-#pragma unroll
-  for (int m = 16; m > 0; m >>= 1) p = Op::combine(p, shfl_pair(p, m));
-  return p;
-}
-
-template <typename T>
-struct StoreVal {
-  template <typename V>
-  static __device__ __forceinline__ void put(void* p, long long slot, V v) {
-    reinterpret_cast<T*>(p)[slot] = static_cast<T>(v);
-  }
-};
-template <>
-struct StoreVal<__nv_bfloat16> {
-  static __device__ __forceinline__ void put(void* p, long long slot, float v) {
-    reinterpret_cast<__nv_bfloat16*>(p)[slot] = __float2bfloat16_rn(v);  // exact: v came from bf16
-  }
-};
-template <>
-struct StoreVal<__half> {
-  static __device__ __forceinline__ void put(void* p, long long slot, float v) {
-    reinterpret_cast<__half*>(p)[slot] = __float2half_rn(v);
-  }
-};
-
-template <typename T, typename V>
-__device__ __forceinline__ void store_arg(void* out, int index_dtype, void* val_out, long long slot,
-                                          const ArgPair<V>& p) {
-  if (index_dtype == B200PHI_INT32)
-    reinterpret_cast<int*>(out)[slot] = static_cast<int>(p.i);
-  else
-    reinterpret_cast<long long*>(out)[slot] = p.i;
-  if (val_out) StoreVal<T>::put(val_out, slot, p.v);
-}
-
-// Extreme value of one 16-byte vector: a short tree instead of VE dependent compare/select
-// steps (the per-element chain made config C3b latency-bound at 5.1 TB/s).  16-bit floats use
-// the packed min/max instructions on the raw pairs.
-template <typename T, typename V, bool kMax>
-struct VecExtreme {
-  static __device__ __forceinline__ V of(const V16& raw) {
-    typename VecOf<T>::U w;
-    w.raw = raw;
-    V m[VecOf<T>::kElems];
-#pragma unroll
-    for (int e = 0; e < VecOf<T>::kElems; ++e) m[e] = Cvt<V, T>::to(w.e[e]);
-#pragma unroll
-    for (int half = VecOf<T>::kElems / 2; half > 0; half >>= 1)
-#pragma unroll
-      for (int e = 0; e < half; ++e) m[e] = ArgOp<V, kMax>::better(m[e + half], m[e]) ? m[e + half] : m[e];
-    return m[0];
-  }
-};
-template <bool kMax>
-struct VecExtreme<__nv_bfloat16, float, kMax> {
-  static __device__ __forceinline__ float of(const V16& raw) {
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
-    __nv_bfloat162 a = kMax ? __hmax2(h[0], h[1]) : __hmin2(h[0], h[1]);
-    __nv_bfloat162 b = kMax ? __hmax2(h[2], h[3]) : __hmin2(h[2], h[3]);
-    a = kMax ? __hmax2(a, b) : __hmin2(a, b);
-    const float lo = __low2float(a), hi = __high2float(a);
-    return kMax ? fmaxf(lo, hi) : fminf(lo, hi);
-  }
-};
-template <bool kMax>
-struct VecExtreme<__half, float, kMax> {
-  static __device__ __forceinline__ float of(const V16& raw) {
-    const __half2* h = reinterpret_cast<const __half2*>(&raw);
-    __half2 a = kMax ? __hmax2(h[0], h[1]) : __hmin2(h[0], h[1]);
-    __half2 b = kMax ? __hmax2(h[2], h[3]) : __hmin2(h[2], h[3]);
-    a = kMax ? __hmax2(a, b) : __hmin2(a, b);
-    const float lo = __low2float(a), hi = __high2float(a);
-    return kMax ? fmaxf(lo, hi) : fminf(lo, hi);
-  }
-};
-
-// Visit one vector whose first element has index i0.  Only when the vector's extreme beats
-// the thread's best (rare after the first few vectors) is the position inside it looked up;
-// scanning downwards leaves the LOWEST matching position.
-template <typename T, typename V, bool kMax>
-__device__ __forceinline__ void visit_vec(ArgPair<V>& best, const V16& raw, long long i0) {
-  const V vm = VecExtreme<T, V, kMax>::of(raw);
-  if (ArgOp<V, kMax>::better(vm, best.v)) {
-    typename VecOf<T>::U w;
-    w.raw = raw;
-    int first = 0;
-#pragma unroll
-    for (int e = VecOf<T>::kElems - 1; e >= 0; --e)
-      if (Cvt<V, T>::to(w.e[e]) == vm) first = e;
-    best.v = vm;
-    best.i = i0 + first;
-  }
-}
-
-// Batches of UU strided vectors, all loads issued before the first visit.  The caller
-// cascades UU = 8, 4, 2, 1 so the remainder of a row never degenerates into one load at a time
-// (a 62.5 KiB bf16 row left up to 7 serial loads per thread: 5.8 TB/s on C3b).
-template <typename T, typename V, bool kMax, int G, int UU>
-__device__ __forceinline__ void arg_step(ArgPair<V>& best, const V16* __restrict__ vp, long long& v,
-                                         long long nvec, long long head) {
-  constexpr int VE = VecOf<T>::kElems;
-  for (; v + static_cast<long long>(UU - 1) * G < nvec; v += static_cast<long long>(UU) * G) {
-    V16 buf[UU];
-#pragma unroll
-    for (int u = 0; u < UU; ++u) buf[u] = ldg_stream16(vp + v + static_cast<long long>(u) * G);
-#pragma unroll
-    for (int u = 0; u < UU; ++u)
-      visit_vec<T, V, kMax>(best, buf[u], head + (v + static_cast<long long>(u) * G) * VE);
-  }
-}
-
-// Scan `n` contiguous elements with a group of G threads.  kAligned: the row starts on a
-// 16-byte boundary and is a whole number of vectors (no head / tail).
-template <typename T, typename V, bool kMax, int G, int U, bool kAligned>
-__device__ __forceinline__ ArgPair<V> arg_span(const T* __restrict__ row, long long n, int g) {
-  using Op = ArgOp<V, kMax>;
-  constexpr int VE = VecOf<T>::kElems;
-  ArgPair<V> best = Op::identity();
-  long long head = 0;
-  if constexpr (!kAligned) {
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(row);
-    head = static_cast<long long>(((16 - (addr & 15)) & 15) / sizeof(T));
-    if (head > n) head = n;
-    if (g < head) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + g)), g);
-  }
-  const long long nvec = (n - head) / VE;
-  const long long tail0 = head + nvec * VE;
-  const V16* __restrict__ vp = reinterpret_cast<const V16*>(row + head);
-  long long v = g;
-  arg_step<T, V, kMax, G, U>(best, vp, v, nvec, head);
-  if constexpr (U > 4) arg_step<T, V, kMax, G, 4>(best, vp, v, nvec, head);
-  if constexpr (U > 2) arg_step<T, V, kMax, G, 2>(best, vp, v, nvec, head);
-  if constexpr (U > 1) arg_step<T, V, kMax, G, 1>(best, vp, v, nvec, head);
-  if constexpr (!kAligned) {
-    for (long long i = tail0 + g; i < n; i += G) Op::visit(best, Cvt<V, T>::to(ldg_scalar(row + i)), i);
-  }
-  return best;
+static const ArgKnobs& arg_knobs() {
+  static const ArgKnobs k = {getenv("B200PHI_ARG_G") ? atoi(getenv("B200PHI_ARG_G")) : 0,
+                             getenv("B200PHI_ARG_U") ? atoi(getenv("B200PHI_ARG_U")) : 0,
+                             getenv("B200PHI_ARG_NO_MULTI") != nullptr, getenv("B200PHI_ARG_NO_PEEL") != nullptr};
+  return k;
 }
 
 // post == 1: [rows, n], G threads per row (as in row_reduce_kernel).
@@ -370,56 +209,6 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
-// post > 1: [pre, n, post].  Block = TX x TY: tx walks post (contiguous), ty walks n.
-template <typename T, typename V, bool kMax>
-__global__ void __launch_bounds__(kBlock)
-    arg_col_kernel(const T* __restrict__ x, long long n, long long post, int TX, long long tiles,
-                   void* out, int index_dtype, void* val_out) {
-  using Op = ArgOp<V, kMax>;
-  __shared__ V s_v[kBlock];
-  __shared__ long long s_i[kBlock];
-  const int TY = kBlock / TX;
-  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
-  const long long o = blockIdx.x / tiles, tile = blockIdx.x % tiles;
-  const long long c = tile * TX + tx;
-  const bool live = c < post;
-  ArgPair<V> best = Op::identity();
-  if (live) {
-    const T* __restrict__ base = x + o * n * post + c;
-    long long r = ty;
-    for (; r + 3LL * TY < n; r += 4LL * TY) {
-      T b[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) b[u] = ldg_scalar(base + (r + static_cast<long long>(u) * TY) * post);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) Op::visit(best, Cvt<V, T>::to(b[u]), r + static_cast<long long>(u) * TY);
-    }
-    for (; r < n; r += TY) Op::visit(best, Cvt<V, T>::to(ldg_scalar(base + r * post)), r);
-  }
-  s_v[ty * TX + tx] = best.v;
-  s_i[ty * TX + tx] = best.i;
-  __syncthreads();
-  for (int half = TY >> 1; half > 0; half >>= 1) {
-    if (ty < half) {
-      ArgPair<V> a, b;
-      a.v = s_v[ty * TX + tx];
-      a.i = s_i[ty * TX + tx];
-      b.v = s_v[(ty + half) * TX + tx];
-      b.i = s_i[(ty + half) * TX + tx];
-      a = Op::combine(a, b);
-      s_v[ty * TX + tx] = a.v;
-      s_i[ty * TX + tx] = a.i;
-    }
-    __syncthreads();
-  }
-  if (ty == 0 && live) {
-    ArgPair<V> r;
-    r.v = s_v[tx];
-    r.i = s_i[tx];
-    store_arg<T, V>(out, index_dtype, val_out, o * post + c, r);
-  }
-}
-
 struct ArgGeom {
   long long pre, n, post;
 };
@@ -427,7 +216,8 @@ struct ArgGeom {
 template <typename T, typename V, bool kMax>
 static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, void* val_out,
                       cudaStream_t stream) {
-  if (g.post == 1) {
+  const long long sm_cap = static_cast<long long>(current_sm_count()) * 8 * 8;  // grid-stride beyond that
+  {  // post == 1 (the column and split plans are arg_split.cu's)
     const long long row_bytes = g.n * static_cast<long long>(sizeof(T));
     // threads per row: about 32 vectors per thread, 8 loads in flight each (measured on C3b,
     // 4000 vectors per row: G=128 reads 6.22 TB/s, G=256 5.98, G=64 5.64).  Long rows of 16-bit
@@ -435,8 +225,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     // CTAs per SM): 6.38 TB/s.
     int G = 32;
     while (G < 256 && static_cast<long long>(G) * 512 < row_bytes) G <<= 1;
-    static const int force_g = getenv("B200PHI_ARG_G") ? atoi(getenv("B200PHI_ARG_G")) : 0;
-    static const int force_u = getenv("B200PHI_ARG_U") ? atoi(getenv("B200PHI_ARG_U")) : 0;
+    const int force_g = arg_knobs().force_g, force_u = arg_knobs().force_u;
     int arg_u = 8;
     if (sizeof(T) == 2 && row_bytes > 32768 && !force_g) {
       G = 256;
@@ -445,13 +234,13 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     if (force_g == 32 || force_g == 64 || force_g == 128 || force_g == 256) G = force_g;
     if (force_u == 4 || force_u == 8) arg_u = force_u;
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
-    static const bool no_multi = getenv("B200PHI_ARG_NO_MULTI") != nullptr;
+    const bool no_multi = arg_knobs().no_multi;
     const long long nvec_row = row_bytes / 16;
     if (aligned && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
       const int LG = nvec_row <= 32 ? 8 : 16;
       const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
       long long mc = (g.pre + kWarps * rows_per_warp - 1) / (kWarps * rows_per_warp);
-      const long long cap = 148LL * 8 * 8;
+      const long long cap = sm_cap;
       if (mc > cap) mc = cap;
       const unsigned gm = static_cast<unsigned>(mc);
       if (nvec_row <= 32)
@@ -471,7 +260,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
 #define B200PHI_ARG_SCALAR(GG, NN)                                                              \
   {                                                                                             \
     long long sc = (g.pre + kWarps * (32 / GG) - 1) / (kWarps * (32 / GG));                     \
-    if (sc > 148LL * 8 * 8) sc = 148LL * 8 * 8;                                                 \
+    if (sc > sm_cap) sc = sm_cap;                                                 \
     arg_scalar_kernel<T, V, kMax, GG, NN><<<static_cast<unsigned>(sc), kBlock, 0, stream>>>(    \
         x, g.pre, c, out, index_dtype, val_out);                                                \
   }
@@ -489,12 +278,12 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       return B200PHI_OK;
     }
     if constexpr (sizeof(T) == 2) {
-      static const bool no_peel = getenv("B200PHI_ARG_NO_PEEL") != nullptr;
+      const bool no_peel = arg_knobs().no_peel;
       // (measured, bf16: 1001 columns 4.89 TB/s against 2.65 for the peeled row kernel; at 4097
       // columns a 16-vector form was slower, 4.78 against 5.39, so rows stop at 4 KiB here)
       if (!aligned && !no_peel && g.n >= 256 && row_bytes < 4112 && g.pre >= 64 && !force_g && !force_u) {
         long long pc = (g.pre + kWarps - 1) / kWarps;
-        if (pc > 148LL * 8 * 8) pc = 148LL * 8 * 8;
+        if (pc > sm_cap) pc = sm_cap;
         const unsigned gp = static_cast<unsigned>(pc);
         const int c = static_cast<int>(g.n);
         if (row_bytes < 2064)
@@ -527,14 +316,6 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
         B200PHI_ARG_ROW(256) break;
     }
 #undef B200PHI_ARG_ROW
-  } else {
-    int TX = 1;
-    while (TX < g.post && TX < kBlock) TX <<= 1;
-    const long long tiles = (g.post + TX - 1) / TX;
-    const long long blocks = g.pre * tiles;
-    if (blocks > 0x7fffffffLL) return set_error(B200PHI_UNSUPPORTED, "argreduce: output too large");
-    arg_col_kernel<T, V, kMax><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(
-        x, g.n, g.post, TX, tiles, out, index_dtype, val_out);
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);
@@ -549,40 +330,45 @@ static int launch_arg_op(int op, const void* x, const ArgGeom& g, void* out, int
   return launch_arg<T, V, false>(static_cast<const T*>(x), g, out, index_dtype, val_out, s);
 }
 
+// Scratch for this descriptor: the worse of the aligned / unaligned plans, whatever d->x holds.
+size_t argreduce_workspace_bytes(const b200phi_argreduce_desc* d) {
+  size_t need = 0;
+  const Tunables t = tunables();
+  for (int k = 0; k < 2; ++k) {
+    ArgPlan p;
+    std::string err;
+    if (plan_arg(d, t, k == 0, &p, &err) != B200PHI_OK) return 0;
+    if (p.ws_total_bytes > need) need = p.ws_total_bytes;
+  }
+  return need;
+}
+
 int run_argreduce(const b200phi_argreduce_desc* d, cudaStream_t stream) {
-  if (!d) return set_error(B200PHI_INVALID_ARGUMENT, "null descriptor");
-  if (d->op != B200PHI_ARGMAX && d->op != B200PHI_ARGMIN)
-    return set_error(B200PHI_INVALID_ARGUMENT, "unknown arg op");
-  if (d->rank < 0 || d->rank > B200PHI_MAX_RANK)
-    return set_error(B200PHI_INVALID_ARGUMENT, "rank must be in [0, 9]");
-  int index_dtype = d->index_dtype == B200PHI_UNDEFINED ? B200PHI_INT64 : d->index_dtype;
-  if (index_dtype != B200PHI_INT32 && index_dtype != B200PHI_INT64)
-    return set_error(B200PHI_INVALID_ARGUMENT, "argmax/argmin index dtype must be int32 or int64");
-  long long numel = 1;
-  for (int i = 0; i < d->rank; ++i) {
-    if (d->dims[i] < 0) return set_error(B200PHI_INVALID_ARGUMENT, "negative extent");
-    numel *= d->dims[i];
-  }
-  if (numel <= 0)
-    return set_error(B200PHI_INVALID_ARGUMENT, "argmin/argmax input numel must > 0, bug got 0");
+  ArgPlan plan;
+  std::string err;
+  const bool x_aligned = d && reinterpret_cast<uintptr_t>(d->x) % 16 == 0;
+  int rc = plan_arg(d, tunables(), x_aligned, &plan, &err);
+  if (rc != B200PHI_OK) return set_error(rc, err);
   if (!d->x || !d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null tensor pointer");
-  ArgGeom g;
-  if (d->flatten || d->rank == 0) {
-    g.pre = 1;
-    g.n = numel;
-    g.post = 1;
-  } else {
-    long long axis = d->axis;
-    if (axis < -d->rank || axis >= d->rank)
-      return set_error(B200PHI_INVALID_ARGUMENT, "argmax/argmin axis out of range");
-    if (axis < 0) axis += d->rank;
-    g.pre = g.post = 1;
-    for (int i = 0; i < axis; ++i) g.pre *= d->dims[i];
-    g.n = d->dims[axis];
-    for (int i = static_cast<int>(axis) + 1; i < d->rank; ++i) g.post *= d->dims[i];
+  const int index_dtype = plan.index_dtype;
+  if (plan.kind != kArgRows) {
+    if (plan.ws_total_bytes > 0) {
+      if (!d->workspace || d->workspace_bytes < plan.ws_total_bytes) {
+        char buf[200];
+        snprintf(buf, sizeof(buf),
+                 "argmax/argmin: workspace too small: need %zu bytes (b200phi_argreduce_workspace), got %zu",
+                 plan.ws_total_bytes, d->workspace ? d->workspace_bytes : (size_t)0);
+        return set_error(B200PHI_WORKSPACE_TOO_SMALL, buf);
+      }
+      if (reinterpret_cast<uintptr_t>(d->workspace) % 256 != 0)
+        return set_error(B200PHI_INVALID_ARGUMENT, "workspace must be 256-byte aligned");
+    }
+    return launch_arg_split(d->op, plan, d->x, d->out, d->max_out, d->workspace, stream);
   }
-  if (index_dtype == B200PHI_INT32 && g.n > 0x7fffffffLL)
-    return set_error(B200PHI_INVALID_ARGUMENT, "int32 indices need the reduced extent <= INT_MAX");
+  ArgGeom g;
+  g.pre = plan.pre;
+  g.n = plan.n;
+  g.post = plan.post;
   switch (d->in_dtype) {
     case B200PHI_FLOAT32:
       return launch_arg_op<float, float>(d->op, d->x, g, d->out, index_dtype, d->max_out, stream);

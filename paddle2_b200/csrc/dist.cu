@@ -8,6 +8,7 @@
 // has no link-time NCCL dependency.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -24,6 +25,9 @@ int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
 int current_sm_count();
 int run_reduce(const b200phi_reduce_desc* d, cudaStream_t stream);
+Tunables tunables();
+size_t reduce_workspace_bytes(const b200phi_reduce_desc* d);
+int sharded_partial_dtype(int op, int out_dtype);
 
 struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId*);
@@ -75,27 +79,42 @@ static int nccl_status(NcclApi* a, ncclResult_t r) {
   return set_error(B200PHI_NCCL_ERROR, std::string("NCCL: ") + a->GetErrorString(r));
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kBlock) divide_inplace_kernel(T* p, long long n, double count) {
+// After the allreduce: out[i] = convert(partial[i] / count) (count == 1 unless MEAN).  `partial`
+// may alias `out` when the two dtypes are the same.
+template <typename P>
+__global__ void __launch_bounds__(kBlock)
+    finish_partial_kernel(const P* partial, long long n, Epilogue ep) {
   for (long long i = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * kBlock) {
-    if constexpr (std::numeric_limits<T>::is_integer) {
-      p[i] = static_cast<T>(p[i] / static_cast<long long>(count));
-    } else {
-      p[i] = p[i] / static_cast<T>(count);
-    }
+       i += static_cast<long long>(gridDim.x) * kBlock)
+    store_result<P>(ep, i, partial[i]);
+}
+
+static bool nccl_dtype(int dtype, ncclDataType_t* ty) {
+  switch (dtype) {
+    case B200PHI_FLOAT32: *ty = ncclFloat32; return true;
+    case B200PHI_FLOAT64: *ty = ncclFloat64; return true;
+    case B200PHI_FLOAT16: *ty = ncclFloat16; return true;
+    case B200PHI_BFLOAT16: *ty = ncclBfloat16; return true;
+    case B200PHI_INT32: *ty = ncclInt32; return true;
+    case B200PHI_INT64: *ty = ncclInt64; return true;
+    case B200PHI_INT8: *ty = ncclInt8; return true;
+    case B200PHI_UINT8:
+    case B200PHI_BOOL: *ty = ncclUint8; return true;
+    default: return false;
   }
 }
-__global__ void __launch_bounds__(kBlock)
-    divide_inplace_bf16(__nv_bfloat16* p, long long n, float count) {
-  for (long long i = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * kBlock)
-    p[i] = __float2bfloat16_rn(__bfloat162float(p[i]) / count);
-}
-__global__ void __launch_bounds__(kBlock) divide_inplace_f16(__half* p, long long n, float count) {
-  for (long long i = static_cast<long long>(blockIdx.x) * kBlock + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * kBlock)
-    p[i] = __float2half_rn(__half2float(p[i]) / count);
+
+static size_t round256(size_t v) { return (v + 255) / 256 * 256; }
+
+// Scratch of the sharded reduce: [wide partial, if the result is a 16-bit float sum][local reduce's own]
+size_t sharded_reduce_workspace_bytes(const b200phi_reduce_desc* d) {
+  ReducePlan plan;
+  std::string err;
+  if (plan_reduce(d, tunables(), &plan, &err) != B200PHI_OK) return 0;
+  size_t need = reduce_workspace_bytes(d);
+  if (sharded_partial_dtype(d->op, plan.out_dtype) != plan.out_dtype)
+    need = round256(need) + round256(static_cast<size_t>(plan.out_numel) * 4);
+  return need;
 }
 
 int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, void* comm,
@@ -108,30 +127,26 @@ int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, voi
   NcclApi* a = nccl_api();
   if (!a->ok) return set_error(B200PHI_NCCL_ERROR, a->why);
 
+  // ---- every argument is checked before anything is enqueued: a rank that returned an error
+  //      has launched nothing, so it cannot leave a half-done result or a one-sided collective
   ReducePlan plan;
   std::string err;
-  int rc = plan_reduce(d, default_tunables(current_sm_count()), &plan, &err);
+  int rc = plan_reduce(d, tunables(), &plan, &err);
   if (rc != B200PHI_OK) return set_error(rc, err);
-
-  b200phi_reduce_desc local = *d;
-  if (d->op == B200PHI_MEAN) local.op = B200PHI_SUM;  // divide by the GLOBAL count after the exchange
-  rc = run_reduce(&local, stream);
-  if (rc != B200PHI_OK) return rc;
-
+  if (!d->x || !d->out) return set_error(B200PHI_INVALID_ARGUMENT, "null tensor pointer");
+  const bool mean = d->op == B200PHI_MEAN;
+  if (mean && global_count <= 0)
+    return set_error(B200PHI_INVALID_ARGUMENT, "global_reduce_count must be > 0");
+  // Sums into bf16 / fp16 travel as fp32 partials (MPType) and are rounded ONCE, after the ranks
+  // are combined; an allreduce in the 16-bit type would round per rank and per NCCL step.
+  const int partial_dtype = sharded_partial_dtype(d->op, plan.out_dtype);
+  const bool wide = partial_dtype != plan.out_dtype;
   ncclDataType_t ty;
-  switch (plan.out_dtype) {
-    case B200PHI_FLOAT32: ty = ncclFloat32; break;
-    case B200PHI_FLOAT64: ty = ncclFloat64; break;
-    case B200PHI_FLOAT16: ty = ncclFloat16; break;
-    case B200PHI_BFLOAT16: ty = ncclBfloat16; break;
-    case B200PHI_INT32: ty = ncclInt32; break;
-    case B200PHI_INT64: ty = ncclInt64; break;
-    case B200PHI_INT8: ty = ncclInt8; break;
-    case B200PHI_UINT8:
-    case B200PHI_BOOL: ty = ncclUint8; break;
-    default:
-      return set_error(B200PHI_UNSUPPORTED, "sharded reduce: output dtype has no NCCL type");
-  }
+  if (!nccl_dtype(partial_dtype, &ty))
+    return set_error(B200PHI_UNSUPPORTED, "sharded reduce: output dtype has no NCCL type");
+  if (mean && partial_dtype != B200PHI_FLOAT32 && partial_dtype != B200PHI_FLOAT64 &&
+      partial_dtype != B200PHI_INT64 && partial_dtype != B200PHI_INT32)
+    return set_error(B200PHI_UNSUPPORTED, "sharded mean: dtype not built");
   ncclRedOp_t op;
   switch (d->op) {  // red-op mapping of gpu/all_reduce_kernel.cu:46-65
     case B200PHI_SUM:
@@ -142,37 +157,56 @@ int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, voi
     case B200PHI_ANY: op = ncclMax; break;
     default: op = ncclMin; break;  // MIN, AMIN, ALL
   }
-  ncclResult_t r = a->AllReduce(d->out, d->out, static_cast<size_t>(plan.out_numel), ty, op,
+  b200phi_reduce_desc local = *d;
+  if (mean) local.op = B200PHI_SUM;  // divide by the GLOBAL count after the exchange
+  void* partial = d->out;
+  if (wide) {
+    const size_t wide_bytes = round256(static_cast<size_t>(plan.out_numel) * 4);
+    const size_t inner = reduce_workspace_bytes(d);
+    if (!d->workspace || d->workspace_bytes < wide_bytes + inner ||
+        reinterpret_cast<uintptr_t>(d->workspace) % 256 != 0) {
+      char buf[200];
+      snprintf(buf, sizeof(buf),
+               "sharded reduce into a 16-bit float needs %zu bytes of 256-byte aligned workspace for "
+               "the fp32 partial (b200phi_sharded_reduce_workspace), got %zu",
+               wide_bytes + inner, d->workspace ? d->workspace_bytes : (size_t)0);
+      return set_error(B200PHI_WORKSPACE_TOO_SMALL, buf);
+    }
+    partial = d->workspace;
+    local.out = partial;
+    local.out_dtype = partial_dtype;
+    local.workspace = static_cast<unsigned char*>(d->workspace) + wide_bytes;
+    local.workspace_bytes = d->workspace_bytes - wide_bytes;
+  }
+
+  rc = run_reduce(&local, stream);
+  if (rc != B200PHI_OK) return rc;
+  ncclResult_t r = a->AllReduce(partial, partial, static_cast<size_t>(plan.out_numel), ty, op,
                                 static_cast<ncclComm_t>(comm), stream);
   if (r != ncclSuccess) return nccl_status(a, r);
 
-  if (d->op == B200PHI_MEAN) {
-    if (global_count <= 0) return set_error(B200PHI_INVALID_ARGUMENT, "global_reduce_count must be > 0");
+  if (mean || wide) {
     const long long n = plan.out_numel;
     long long blocks = (n + kBlock - 1) / kBlock;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    const long long cap = static_cast<long long>(current_sm_count()) * 8;
+    if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
-    switch (plan.out_dtype) {
+    const Epilogue ep = make_epilogue(d->out, plan.out_dtype, mean, mean ? global_count : 1);
+    switch (partial_dtype) {
       case B200PHI_FLOAT32:
-        divide_inplace_kernel<float><<<g, kBlock, 0, stream>>>(static_cast<float*>(d->out), n, (double)global_count);
+        finish_partial_kernel<float><<<g, kBlock, 0, stream>>>(static_cast<const float*>(partial), n, ep);
         break;
       case B200PHI_FLOAT64:
-        divide_inplace_kernel<double><<<g, kBlock, 0, stream>>>(static_cast<double*>(d->out), n, (double)global_count);
-        break;
-      case B200PHI_INT32:
-        divide_inplace_kernel<int><<<g, kBlock, 0, stream>>>(static_cast<int*>(d->out), n, (double)global_count);
+        finish_partial_kernel<double><<<g, kBlock, 0, stream>>>(static_cast<const double*>(partial), n, ep);
         break;
       case B200PHI_INT64:
-        divide_inplace_kernel<long long><<<g, kBlock, 0, stream>>>(static_cast<long long*>(d->out), n, (double)global_count);
+        finish_partial_kernel<long long><<<g, kBlock, 0, stream>>>(static_cast<const long long*>(partial), n, ep);
         break;
-      case B200PHI_BFLOAT16:
-        divide_inplace_bf16<<<g, kBlock, 0, stream>>>(static_cast<__nv_bfloat16*>(d->out), n, (float)global_count);
-        break;
-      case B200PHI_FLOAT16:
-        divide_inplace_f16<<<g, kBlock, 0, stream>>>(static_cast<__half*>(d->out), n, (float)global_count);
+      case B200PHI_INT32:
+        finish_partial_kernel<int><<<g, kBlock, 0, stream>>>(static_cast<const int*>(partial), n, ep);
         break;
       default:
-        return set_error(B200PHI_UNSUPPORTED, "sharded mean: dtype not built");
+        break;  // unreachable: rejected before the first launch
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_status(e);

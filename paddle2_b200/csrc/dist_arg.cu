@@ -13,6 +13,8 @@ namespace b200phi {
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
 int run_argreduce(const b200phi_argreduce_desc* d, cudaStream_t stream);
+size_t argreduce_workspace_bytes(const b200phi_argreduce_desc* d);
+int current_sm_count();
 int comm_all_gather_bytes(const void* send, void* recv, size_t bytes_per_rank, void* comm,
                           cudaStream_t stream);
 
@@ -37,7 +39,7 @@ static size_t elem_size(int dt) {
 
 struct ShardArgLayout {
   long long cols;
-  size_t off_idx_local, off_val_local, off_idx_all, off_val_all, total;
+  size_t off_idx_local, off_val_local, off_idx_all, off_val_all, off_local_ws, local_ws_bytes, total;
 };
 
 static bool shard_arg_layout(const b200phi_argreduce_desc* d, int nranks, ShardArgLayout* L) {
@@ -56,6 +58,12 @@ static bool shard_arg_layout(const b200phi_argreduce_desc* d, int nranks, ShardA
   off = align256(off + static_cast<size_t>(cols) * 8 * nranks);
   L->off_val_all = off;
   off = align256(off + static_cast<size_t>(cols) * es * nranks);
+  // the local step's own scratch: the shard's rows are split across thread blocks
+  b200phi_argreduce_desc local = *d;
+  local.index_dtype = B200PHI_INT64;
+  L->off_local_ws = off;
+  L->local_ws_bytes = argreduce_workspace_bytes(&local);
+  off = align256(off + L->local_ws_bytes);
   L->total = off;
   return true;
 }
@@ -99,7 +107,7 @@ template <typename T, typename V>
 static void launch_combine(bool is_max, const void* vals, const long long* idx, int nranks, long long cols,
                            void* out, int index_dtype, void* val_out, cudaStream_t s) {
   long long blocks = (cols + kBlock - 1) / kBlock;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > current_sm_count() * 8LL) blocks = current_sm_count() * 8LL;
   const unsigned g = static_cast<unsigned>(blocks);
   if (is_max)
     arg_combine_kernel<T, V, true><<<g, kBlock, 0, s>>>(static_cast<const T*>(vals), idx, nranks, cols, out,
@@ -126,7 +134,12 @@ extern "C" int b200phi_sharded_argreduce(const b200phi_argreduce_desc* d, int64_
   if (!d) return set_error(B200PHI_INVALID_ARGUMENT, "null descriptor");
   if (nranks <= 1 || !comm) {  // single GPU: no exchange (north star)
     if (row_offset != 0) return set_error(B200PHI_INVALID_ARGUMENT, "row_offset without a communicator");
-    return run_argreduce(d, stream);
+    b200phi_argreduce_desc one = *d;
+    if (!one.workspace) {  // the scratch handed to this entry point serves the local reduce
+      one.workspace = workspace;
+      one.workspace_bytes = workspace_bytes;
+    }
+    return run_argreduce(&one, stream);
   }
   if (d->flatten || d->rank < 1 || (d->axis != 0 && d->axis != -d->rank))
     return set_error(B200PHI_INVALID_ARGUMENT, "sharded argreduce reduces the sharded leading axis (axis 0)");
@@ -149,11 +162,13 @@ extern "C" int b200phi_sharded_argreduce(const b200phi_argreduce_desc* d, int64_
   local.index_dtype = B200PHI_INT64;
   local.out = idx_local;
   local.max_out = val_local;
+  local.workspace = L.local_ws_bytes ? ws + L.off_local_ws : nullptr;
+  local.workspace_bytes = L.local_ws_bytes;
   int rc = run_argreduce(&local, stream);
   if (rc != B200PHI_OK) return rc;
   if (row_offset != 0) {
     long long blocks = (L.cols + kBlock - 1) / kBlock;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > current_sm_count() * 8LL) blocks = current_sm_count() * 8LL;
     add_offset_kernel<<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(idx_local, L.cols, row_offset);
   }
   const size_t es = elem_size(d->in_dtype);

@@ -22,6 +22,7 @@ namespace b200phi {
 
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
+int current_sm_count();
 
 // ---- compute type ------------------------------------------------------------------
 template <typename T>
@@ -569,7 +570,7 @@ static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F
     p.out = static_cast<T*>(d->out) + a * slab;
     p.inter = inter ? static_cast<T*>(inter) + a * slab : nullptr;
     long long blocks = (static_cast<long long>(p.total) + kBlock * U - 1) / (kBlock * U);
-    const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
+    const long long cap = static_cast<long long>(current_sm_count()) * 8 * 32;  // grid-stride beyond that
     if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
     if (mode == 2) {

@@ -18,6 +18,7 @@ namespace b200phi {
 
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
+int current_sm_count();
 
 template <typename A>
 struct LseMath;
@@ -342,7 +343,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
     const int LG = nvec_row <= 32 ? 8 : 16;
     const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
     long long ctas = (rows + kWarps * rows_per_warp - 1) / (kWarps * rows_per_warp);
-    const long long cap = 148LL * 8 * 8;
+    const long long cap = static_cast<long long>(current_sm_count()) * 8 * 8;
     if (ctas > cap) ctas = cap;
     const unsigned gm = static_cast<unsigned>(ctas);
     if (nvec_row <= 32)
@@ -362,7 +363,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
 #define B200PHI_LSE_SCALAR(GG, NN)                                                              \
   {                                                                                             \
     long long sc = (rows + kWarps * (32 / GG) - 1) / (kWarps * (32 / GG));                      \
-    if (sc > 148LL * 8 * 8) sc = 148LL * 8 * 8;                                                 \
+    if (sc > static_cast<long long>(current_sm_count()) * 8 * 8) sc = static_cast<long long>(current_sm_count()) * 8 * 8;                                                 \
     lse_scalar_kernel<T, A, GG, NN><<<static_cast<unsigned>(sc), kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype); \
   }
     if (cols < 128)
@@ -380,7 +381,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   }
   const long long rows_per_cta = kBlock / G;
   long long ctas = (rows + rows_per_cta - 1) / rows_per_cta;
-  const long long cap = 148LL * 8 * 16;  // grid-stride beyond that
+  const long long cap = static_cast<long long>(current_sm_count()) * 8 * 16;  // grid-stride beyond that
   if (ctas > cap) ctas = cap;
   const unsigned gr = static_cast<unsigned>(ctas);
 #define B200PHI_LSE(GG)                                                                              \

@@ -14,6 +14,7 @@ namespace b200phi {
 
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
+int current_sm_count();
 
 template <typename T>
 struct MapCompute {
@@ -466,7 +467,7 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mod
     }
     p.out = static_cast<TO*>(d->out) + a * slab;
     long long blocks = (static_cast<long long>(p.total) + kBlock * U - 1) / (kBlock * U);
-    const long long cap = 148LL * 8 * 32;  // grid-stride beyond that
+    const long long cap = static_cast<long long>(current_sm_count()) * 8 * 32;  // grid-stride beyond that
     if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
     if (mode == 2) {

@@ -16,6 +16,7 @@ namespace b200phi {
 
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
+int current_sm_count();
 
 struct MpAddParams {
   const float* x;
@@ -162,7 +163,7 @@ static int launch_mpadd(const b200phi_mixed_add_desc* d, const BcastPlan& bp, cu
       p.ostride[1][k] = bp.stride[1][k];
     }
     long long blocks = (bp.out_numel + kBlock - 1) / kBlock;
-    if (blocks > 148LL * 8 * 64) blocks = 148LL * 8 * 64;
+    if (blocks > static_cast<long long>(current_sm_count()) * 8 * 64) blocks = static_cast<long long>(current_sm_count()) * 8 * 64;
     mpadd_generic_kernel<TY><<<static_cast<unsigned>(blocks), kBlock, 0, stream>>>(
         p.x, static_cast<const TY*>(p.y), p.out, bp.ndim, p, bp.out_numel);
   }

@@ -1,9 +1,10 @@
-// b200phi_reduce_noalloc: the column (leading-axis) reduce for callers that have no way to
-// give it scratch memory.
+// b200phi_reduce_noalloc: b200phi_reduce for callers that have no way to give it scratch
+// memory.
 //
 // The ordinary entry point, b200phi_reduce, asks its caller for a workspace whenever the
-// reduced extent is cut across thread blocks (partials + tickets for the last-block
-// finalise).  Some hosts cannot provide one: a C or Go service that links this library
+// reduced extent is cut across thread blocks (partials + tickets for the last-block finalise
+// of a column reduce or of a few very long rows) or the reduce runs as two stages through an
+// intermediate ([A, K, B] with A and B reduced).  Some hosts cannot provide one: a C or Go service that links this library
 // without any device allocator of its own, an inference server whose memory plan is frozen
 // before the first request so that nothing on the request path may call cudaMalloc, a
 // callback that runs where taking the allocator's lock is forbidden.  For them the scratch
@@ -37,6 +38,7 @@ namespace b200phi {
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
 int current_sm_count();
+Tunables tunables();
 int run_reduce(const b200phi_reduce_desc* d, cudaStream_t stream);
 
 namespace {
@@ -77,12 +79,9 @@ using namespace b200phi;
 extern "C" int b200phi_reduce_noalloc(const b200phi_reduce_desc* d, void* stream) {
   ReducePlan plan;
   std::string err;
-  int rc = plan_reduce(d, default_tunables(current_sm_count()), &plan, &err);
+  int rc = plan_reduce(d, tunables(), &plan, &err);
   if (rc != B200PHI_OK) return set_error(rc, err);
-  if (plan.kind != kCol)
-    return set_error(B200PHI_UNSUPPORTED,
-                     "b200phi_reduce_noalloc covers the column reduce (leading axes reduced, "
-                     "innermost kept); other shapes need no scratch: call b200phi_reduce");
+  // every shape is served: the ones that need no scratch simply do not touch the array
   if (plan.ws_total_bytes > static_cast<size_t>(B200PHI_NOALLOC_SCRATCH_BYTES)) {
     char buf[200];
     snprintf(buf, sizeof(buf),
@@ -98,6 +97,6 @@ extern "C" int b200phi_reduce_noalloc(const b200phi_reduce_desc* d, void* stream
   local.workspace = scratch;
   local.workspace_bytes = static_cast<size_t>(B200PHI_NOALLOC_SCRATCH_BYTES);
   // run_reduce clears the tickets (cudaMemsetAsync on `stream`) and launches the same
-  // col_reduce_kernel that b200phi_reduce launches; it allocates nothing
+  // kernels that b200phi_reduce launches; it allocates nothing
   return run_reduce(&local, static_cast<cudaStream_t>(stream));
 }

@@ -368,108 +368,22 @@ __device__ __forceinline__ void col_step(const unsigned char* __restrict__& p, s
   }
 }
 
-// ---- finishing a column reduce across GPUs over NVLink peer memory ---------------------------
-// Every rank owns one buffer that all ranks can address (CUDA IPC mapping):
-//   slots [2 parities][nranks][max_out] of 8-byte cells   rank r's result, written BY rank r
-//   flags [nranks][max_tiles] uint32                      epoch of the last publication
-// The CTA that holds a finished output tile stores it into every rank's slot (its own too),
-// publishes the epoch with a system-scope release store, waits until every rank's flag for
-// that tile has reached the epoch, and combines the nranks slots in rank order -- the same
-// order on every rank, so all ranks end with identical bits.  Slots alternate by epoch parity:
-// a rank can only get two epochs ahead of a peer after that peer has left the older kernel.
-struct P2PArgs {
-  int nranks, rank, parity;
-  unsigned epoch;
-  long long max_out;   // cells per (parity, rank) slot
-  long long max_tiles;
-  unsigned char* base[8];  // base[r] = rank r's buffer as mapped into this process
-  unsigned long long flags_offset;  // bytes from base to the flags
-};
-struct NoP2P {};
-
-__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-
-// Out of line: inlined, its registers changed the allocation of the streaming loop in front of
-// it (46 vs 54 registers, +35 us on config C5 with a one-rank group).
-// Called by the whole CTA; `vals` valid where owner is true.  All indexing of g.base[] is by
-// unrolled constant index: a run-time index would force the whole argument struct into local
-// memory and change the register allocation of the streaming loop in front of it.
-template <typename Acc, typename Op, int VE>
-__device__ __noinline__ void p2p_finish(const P2PArgs g, bool owner, long long out_base,
-                                           const Acc* vals, const Epilogue& ep) {
-  const long long my_cell = (static_cast<long long>(g.parity) * g.nranks + g.rank) * g.max_out + out_base;
-  if (owner) {
-#pragma unroll
-    for (int p = 0; p < 8; ++p) {
-      if (p < g.nranks) {
-        volatile Acc* dst = reinterpret_cast<volatile Acc*>(g.base[p] + my_cell * 8);
-#pragma unroll
-        for (int e = 0; e < VE; ++e) dst[e] = vals[e];
-      }
-    }
-  }
-  __threadfence_system();
-  __syncthreads();
-  unsigned char* own = nullptr;
-#pragma unroll
-  for (int p = 0; p < 8; ++p)
-    if (p == g.rank) own = g.base[p];
-  if (threadIdx.x < g.nranks) {
-    unsigned char* peer = nullptr;
-#pragma unroll
-    for (int p = 0; p < 8; ++p)
-      if (p == static_cast<int>(threadIdx.x)) peer = g.base[p];
-    unsigned* f = reinterpret_cast<unsigned*>(peer + g.flags_offset) +
-                  static_cast<long long>(g.rank) * g.max_tiles + blockIdx.x;
-    st_release_sys(f, g.epoch);
-    const unsigned* mine = reinterpret_cast<const unsigned*>(own + g.flags_offset) +
-                           static_cast<long long>(threadIdx.x) * g.max_tiles + blockIdx.x;
-    const unsigned long long t0 = global_timer_ns();
-    while (static_cast<int>(ld_acquire_sys(mine) - g.epoch) < 0) {
-      if (global_timer_ns() - t0 > 4000000000ull) break;  // 4 s: a peer never launched; do not hang the GPU
-    }
-  }
-  __syncthreads();
-  if (owner) {
-    Acc r[VE];
-#pragma unroll
-    for (int e = 0; e < VE; ++e) r[e] = Op::identity();
-    for (int k = 0; k < g.nranks; ++k) {
-      const volatile Acc* src = reinterpret_cast<const volatile Acc*>(
-          own + ((static_cast<long long>(g.parity) * g.nranks + k) * g.max_out + out_base) * 8);
-#pragma unroll
-      for (int e = 0; e < VE; ++e) r[e] = Op::combine(r[e], src[e]);
-    }
-#pragma unroll
-    for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, r[e]);
-  }
-}
-
 // [outer, R, inner] -> [outer, inner].  Block = TX x TY (TX*TY == kBlock): tx walks
 // the kept contiguous axis in units of VE elements (VE = 16/sizeof(T) when inner
 // allows 16-byte loads, else 1), ty walks the reduced axis.  grid.x = outer * tiles,
 // grid.y = splits of R.  U row-loads are in flight per thread.
-template <typename T, typename Acc, typename Op, int VE, int U, typename PX = NoP2P>
+template <typename T, typename Acc, typename Op, int VE, int U>
 __global__ void __launch_bounds__(kBlock)
     col_reduce_kernel(const T* __restrict__ x, long long R, long long inner, int TX,
                       long long tiles, long long rows_per_split, Acc* __restrict__ partial,
-                      unsigned* __restrict__ tickets, Epilogue ep, PX px = PX()) {
-  constexpr bool kP2P = !std::is_same<PX, NoP2P>::value;
+                      unsigned* __restrict__ tickets, Epilogue ep) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Acc* smem = reinterpret_cast<Acc*>(smem_raw);  // [TY][TX][VE]
   __shared__ unsigned s_ticket;
+  // A kernel queued behind this one with programmatic dependent launch (the peer exchange of
+  // b200phi_sharded_reduce_p2p) may be scheduled now; it waits for this grid to finish before
+  // it reads anything.  No effect on an ordinary launch.
+  asm volatile("griddepcontrol.launch_dependents;");
   const int TY = kBlock / TX;
   const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
   const long long o = blockIdx.x / tiles, tile = blockIdx.x % tiles;
@@ -512,13 +426,9 @@ __global__ void __launch_bounds__(kBlock)
 
   const long long out_base = o * inner + cv * VE;
   if (splits == 1) {
-    if constexpr (kP2P) {
-      p2p_finish<Acc, Op, VE>(px, ty == 0 && live, out_base, &smem[tx * VE], ep);
-    } else {
-      if (ty == 0 && live) {
+    if (ty == 0 && live) {
 #pragma unroll
-        for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
-      }
+      for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
     }
     return;
   }
@@ -573,13 +483,9 @@ __global__ void __launch_bounds__(kBlock)
     }
     __syncthreads();
   }
-  if constexpr (kP2P) {
-    p2p_finish<Acc, Op, VE>(px, ty == 0 && live, out_base, &smem[tx * VE], ep);
-  } else {
-    if (ty == 0 && live) {
+  if (ty == 0 && live) {
 #pragma unroll
-      for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
-    }
+    for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
   }
   if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
 }

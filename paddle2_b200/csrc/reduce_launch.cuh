@@ -129,10 +129,10 @@ int launch_reduce_typed(const ReduceArgs& a) {
       if (p.vec > 1) {
         col_reduce_kernel<T, Acc, Op, VecOf<T>::kElems, 8>
             <<<dim3(p.grid_x, p.grid_y), kBlock, smem, a.stream>>>(
-                x, p.R, p.inner, p.TX, p.tiles, p.rows_per_split, partial, tickets, ep, NoP2P());
+                x, p.R, p.inner, p.TX, p.tiles, p.rows_per_split, partial, tickets, ep);
       } else {
         col_reduce_kernel<T, Acc, Op, 1, 8><<<dim3(p.grid_x, p.grid_y), kBlock, smem, a.stream>>>(
-            x, p.R, p.inner, p.TX, p.tiles, p.rows_per_split, partial, tickets, ep, NoP2P());
+            x, p.R, p.inner, p.TX, p.tiles, p.rows_per_split, partial, tickets, ep);
       }
       break;
     }

@@ -42,9 +42,10 @@ static long long env_ll(const char* name, long long dflt) {
   return atoll(s);
 }
 
-Tunables default_tunables(int sm_count) {
+// The environment is read ONCE per process (first use); a knob changed later is not seen.
+static Tunables read_env_tunables() {
   Tunables t;
-  t.sm_count = sm_count > 0 ? sm_count : 148;
+  t.sm_count = 148;
   t.row_bytes_per_thread = env_ll("B200PHI_ROW_BYTES_PER_THREAD", 64);
   t.ctas_per_sm = static_cast<int>(env_ll("B200PHI_CTAS_PER_SM", 4));  // measured: profiles/r01_microbench.md
   t.force_kind = static_cast<int>(env_ll("B200PHI_FORCE_KIND", -1));
@@ -52,6 +53,15 @@ Tunables default_tunables(int sm_count) {
   t.no_two_stage = static_cast<int>(env_ll("B200PHI_NO_TWO_STAGE", 0));
   t.no_row_batch = static_cast<int>(env_ll("B200PHI_NO_ROW_BATCH", 0));
   t.row_batch_waves = static_cast<int>(env_ll("B200PHI_ROW_BATCH_WAVES", 8));
+  t.no_tiled = static_cast<int>(env_ll("B200PHI_NO_TILED", 0));
+  t.p2p_timeout_ms = env_ll("B200PHI_P2P_TIMEOUT_MS", 4000);
+  return t;
+}
+
+Tunables default_tunables(int sm_count) {
+  static const Tunables env = read_env_tunables();
+  Tunables t = env;
+  t.sm_count = sm_count > 0 ? sm_count : 148;
   return t;
 }
 

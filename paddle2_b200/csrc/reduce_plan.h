@@ -84,6 +84,8 @@ struct Tunables {
   int no_two_stage;         // env B200PHI_NO_TWO_STAGE: keep [A,K,B] patterns on the generic kernel
   int no_row_batch;         // env B200PHI_NO_ROW_BATCH: keep medium rows on row_reduce_kernel
   int row_batch_waves;      // env B200PHI_ROW_BATCH_WAVES: grid cap = SMs * 8 * this
+  int no_tiled;             // env B200PHI_NO_TILED: keep general keep/reduce patterns on the scalar walk
+  long long p2p_timeout_ms; // env B200PHI_P2P_TIMEOUT_MS: how long the peer exchange waits for a flag
 };
 Tunables default_tunables(int sm_count);
 

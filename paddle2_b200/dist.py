@@ -121,7 +121,7 @@ class ShardedReducer:
         d.out = out.data_ptr()
         lib = L.lib()
         with torch.cuda.device(x.device):
-            ws_bytes = lib.b200phi_reduce_workspace(C.byref(d))
+            ws_bytes = lib.b200phi_sharded_reduce_workspace(C.byref(d))
             if ws_bytes:
                 if workspace is None or workspace.numel() < ws_bytes:
                     workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
@@ -179,11 +179,11 @@ class ShardedReducer:
 
 
 class P2PReducer:
-    """Fused sharded reduce: local column reduce + exchange over NVLink peer memory in one
-    kernel per rank (b200phi_sharded_reduce_p2p).  torch.distributed only carries the 64-byte
-    CUDA IPC handles at set-up; the data path is the kernel's own peer loads/stores."""
+    """Sharded reduce without a collective library: local reduce + a small exchange kernel over
+    NVLink peer memory (b200phi_sharded_reduce_p2p).  torch.distributed only carries the 64-byte
+    CUDA IPC handles at set-up; the data path is the kernel's own peer stores and loads."""
 
-    def __init__(self, max_out_numel, max_tiles=4096, group=None):
+    def __init__(self, max_out_numel, max_tiles=64, group=None):
         if not dist.is_initialized():
             raise RuntimeError("torch.distributed must be initialised (it is the rendezvous)")
         self.group = group
@@ -227,10 +227,16 @@ class P2PReducer:
         self.lib.b200phi_p2p_free(self.own)
         self.own, self.peers = None, []
 
+    def status(self):
+        """Raises B200PhiError(PEER_TIMEOUT) if an exchange gave up waiting for a peer."""
+        L.check(self.lib.b200phi_p2p_status(self.own))
+
     def reduce(self, op, x_local, global_rows=0, out=None, workspace=None):
         _ops._require_cuda(x_local)
         x = x_local.contiguous()
         out_dtype = _ops._sum_out_dtype(x.dtype, None) if op == L.SUM else x.dtype
+        if op in (L.ANY, L.ALL):
+            out_dtype = torch.bool
         if out is None:
             out = torch.empty(x.shape[1:], dtype=out_dtype, device=x.device)
         d = L.ReduceDesc()

@@ -260,6 +260,10 @@ def _arg(op, x, axis, keepdim, dtype, want_value=False):
     d.out = out.data_ptr()
     d.max_out = val.data_ptr() if want_value else None
     with torch.cuda.device(x.device):
+        ws_bytes = L.lib().b200phi_argreduce_workspace(C.byref(d))
+        if ws_bytes:   # flatten, few long rows, a non-last axis: the reduced extent is split across CTAs
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+            d.workspace, d.workspace_bytes = ws.data_ptr(), ws_bytes
         L.check(L.lib().b200phi_argreduce(C.byref(d), _stream_ptr(x)))
     return (out, val) if want_value else out
 

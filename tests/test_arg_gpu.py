@@ -96,3 +96,111 @@ def test_16bit_unaligned_rows_warp_peel(rows, cols, dt):
     x[1::2, cols - 1] = 5
     xd = x.cuda()
     assert np.array_equal(pb.argmax(xd, axis=-1).cpu().numpy(), np.argmax(x.float().numpy(), axis=-1))
+
+
+# ---- split plans: flatten / few long rows (arg_row_split_kernel), non-last axis (arg_col_split_kernel)
+def _arg_plan(x, axis):
+    """(workspace bytes the C ABI asks for) -- non-zero means the reduced extent is split across CTAs."""
+    import ctypes as C
+    from paddle2_b200 import _lib as L
+    d = L.ArgReduceDesc()
+    d.op, d.in_dtype, d.index_dtype, d.rank = L.ARGMAX, pb.ops._phi_dtype(x.dtype), L.INT64, x.dim()
+    for i, s in enumerate(x.shape):
+        d.dims[i] = s
+    d.flatten = 1 if axis is None else 0
+    d.axis = 0 if axis is None else axis
+    return L.lib().b200phi_argreduce_workspace(C.byref(d)), d
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.int64, torch.uint8, torch.float64])
+@pytest.mark.parametrize("n,off", [(1 << 22, 0), ((1 << 22) + 12345, 0), ((1 << 21) + 3, 1)])
+def test_flatten_is_split_across_ctas_ties_at_every_boundary(dt, n, off):
+    """paddle.argmax's default axis=None: one long row.  Few distinct values, and the extreme planted on
+    BOTH sides of every split boundary (so equal maxima sit in different CTAs): the lowest index wins."""
+    gen = torch.Generator(device="cuda").manual_seed(n % 1000 + off)
+    flat = torch.randint(0, 4, (n + off,), device="cuda", generator=gen).to(dt)
+    x = flat[off:]
+    ws, _ = _arg_plan(x, None)
+    assert ws > 0, "this size must take the split plan"
+    ref = x.float().cpu().numpy() if dt != torch.int64 else x.cpu().numpy()
+    assert int(pb.argmax(x)) == int(np.argmax(ref)) and int(pb.argmin(x)) == int(np.argmin(ref))
+    # plant the maximum 9 at both sides of every possible segment boundary of a few split counts
+    y = x.clone()
+    first = None
+    for splits in (37, 148, 592):
+        seg = -(-n // splits)
+        for b in range(seg, n, seg):
+            for j in (b - 1, b):
+                y[j] = 9
+                first = j if first is None else min(first, j)
+    idx, val = pb.argmax_with_value(y)
+    assert int(idx) == first and float(val) == 9.0
+    y2 = x.clone()
+    y2[n - 1] = 9            # the very last element, alone
+    assert int(pb.argmax(y2)) == n - 1
+    y2[0] = 9
+    assert int(pb.argmax(y2)) == 0
+    got32 = pb.argmax(y, dtype="int32")
+    assert got32.dtype == torch.int32 and int(got32) == first
+
+
+def test_flatten_all_identity_answers_zero():
+    for dt, lo, hi in ((torch.float32, -3.4028234663852886e38, 3.4028234663852886e38),
+                       (torch.int64, -(2 ** 63), 2 ** 63 - 1)):
+        x = torch.full((1 << 22,), lo, device="cuda", dtype=dt)
+        assert _arg_plan(x, None)[0] > 0
+        assert int(pb.argmax(x)) == 0
+        x = torch.full((1 << 22,), hi, device="cuda", dtype=dt)
+        assert int(pb.argmin(x)) == 0
+    f = torch.full((3, 1 << 21), float("-inf"), device="cuda")
+    assert pb.argmax(f, axis=1).tolist() == [0, 0, 0]
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.float16, torch.int64, torch.int32,
+                                torch.int16, torch.uint8, torch.float64])
+@pytest.mark.parametrize("shape,axis", [((50000, 512), 0), ((30011, 257), 0), ((7, 9000, 96), 1),
+                                        ((3, 4001, 5), 1), ((2, 70000, 1, 2), 1), ((100003, 8), 0)])
+def test_non_last_axis_split_with_ties(oracle, dt, shape, axis):
+    """[pre, n, post] with n split over grid.y: vector path (post a whole number of 16-byte vectors),
+    scalar path (post 257, 5, 2), ties across split boundaries, optional value output."""
+    gen = torch.Generator(device="cuda").manual_seed(sum(shape) + axis)
+    x = torch.randint(0, 5, shape, device="cuda", generator=gen).to(dt)
+    ref = x.cpu().numpy() if dt in (torch.int64, torch.int32, torch.int16, torch.uint8, torch.float64) \
+        else x.float().cpu().numpy()
+    for op in ("argmax", "argmin"):
+        want = oracle.argreduce(op, ref, axis)
+        assert np.array_equal(G.to_np(getattr(pb, op)(x, axis=axis)), want), (op, shape, dt)
+    idx, val = pb.argmin_with_value(x, axis=axis, keepdim=True)
+    assert np.array_equal(G.to_np(idx), oracle.argreduce("argmin", ref, axis, True))
+    assert np.array_equal(G.to_np(val).astype(np.float64), ref.min(axis=axis, keepdims=True).astype(np.float64))
+    # one odd-offset base: the vector path must fall back cleanly
+    if x.dim() == 2 and dt == torch.float32:
+        flat = torch.cat([torch.zeros(1, device="cuda"), x.flatten()])
+        xo = flat[1:].view(shape)
+        assert np.array_equal(G.to_np(pb.argmax(xo, axis=axis)), oracle.argreduce("argmax", ref, axis))
+
+
+def test_axis0_of_a_large_shard_matches_torch():
+    """The local step of the sharded argmax: fp32 [65536*2, 4096] axis 0 (1 GiB)."""
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(131072, 4096, device="cuda", generator=gen)
+    idx, val = pb.argmax_with_value(x, axis=0)
+    tv, ti = torch.max(x, dim=0)
+    assert torch.equal(val, tv)
+    assert torch.equal(x.gather(0, idx[None, :])[0], tv)          # the index points at the maximum
+    xb = x.bfloat16()                                              # natural ties: first occurrence
+    idx = pb.argmax(xb, axis=0)
+    m = xb.max(dim=0).values
+    firsts = (xb == m[None, :]).to(torch.uint8).argmax(dim=0)
+    assert torch.equal(idx, firsts)
+
+
+def test_split_plans_refuse_a_missing_workspace():
+    import ctypes as C
+    from paddle2_b200 import _lib as L
+    x = torch.rand(1 << 22, device="cuda")
+    out = torch.empty((), device="cuda", dtype=torch.int64)
+    ws, d = _arg_plan(x, None)
+    d.x, d.out = x.data_ptr(), out.data_ptr()
+    rc = L.lib().b200phi_argreduce(C.byref(d), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 4 and str(ws).encode() in L.lib().b200phi_last_error()

@@ -96,6 +96,63 @@ def test_workspace_query_is_pure_host_logic():
     assert 0 < ws < (1 << 20)
 
 
+def test_arg_workspace_query_is_pure_host_logic():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+
+    def desc(dims, axis=None, dt=10):
+        d = _lib.ArgReduceDesc()
+        d.op, d.in_dtype, d.index_dtype, d.rank = 0, dt, 9, len(dims)
+        for i, s in enumerate(dims):
+            d.dims[i] = s
+        d.flatten = 1 if axis is None else 0
+        d.axis = 0 if axis is None else axis
+        return d
+
+    # C3: many rows over the last axis -> a group of threads per row, no scratch
+    assert lib.b200phi_argreduce_workspace(C.byref(desc([8192, 32000], 1))) == 0
+    # flatten (paddle.argmax's default axis=None) of 2^30 bf16: split across CTAs
+    ws = lib.b200phi_argreduce_workspace(C.byref(desc([1 << 30], None, 16)))
+    assert 0 < ws < (1 << 20)
+    # the sharded argmax's local step: axis 0 of [524288, 4096] fp32 -> (value, index) partials per split
+    ws = lib.b200phi_argreduce_workspace(C.byref(desc([524288, 4096], 0)))
+    assert ws >= 2 * 4096 * 12 and ws < (64 << 20)
+    # bad descriptors answer 0 and the call reports the reference's wording
+    d = desc([0, 4], 1)
+    assert lib.b200phi_argreduce_workspace(C.byref(d)) == 0
+    assert lib.b200phi_argreduce(C.byref(d), None) == 1
+    assert b"numel must > 0" in lib.b200phi_last_error()
+    d = desc([3, 4], 2)
+    assert lib.b200phi_argreduce(C.byref(d), None) == 1
+    assert b"axis out of range" in lib.b200phi_last_error()
+
+
+def test_sharded_workspace_adds_the_wide_partial_only_for_16bit_sums():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    base = lib.b200phi_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0])))
+    assert lib.b200phi_sharded_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0]))) == base
+    b16 = lib.b200phi_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0], in_dtype=16)))
+    w16 = lib.b200phi_sharded_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0], in_dtype=16)))
+    assert w16 >= b16 + 4096 * 4
+    # max keeps the dtype: no rounding, no wide partial
+    m16 = lib.b200phi_sharded_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0], op=2, in_dtype=16)))
+    assert m16 == lib.b200phi_reduce_workspace(C.byref(_reduce_desc([524288, 4096], [0], op=2, in_dtype=16)))
+
+
+def test_workspace_query_ignores_the_data_pointer():
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    for dims, axes, dt in (([40000, 1024], [0], 10), ([30011, 768], [0], 16), ([7, 3000, 512], [1], 10)):
+        d = _reduce_desc(dims, axes, in_dtype=dt)
+        a = lib.b200phi_reduce_workspace(C.byref(d))
+        d.x = 0x7f0000000010
+        b = lib.b200phi_reduce_workspace(C.byref(d))
+        d.x = 0x7f0000000012
+        c = lib.b200phi_reduce_workspace(C.byref(d))
+        assert a == b == c > 0
+
+
 def test_elementwise_plan_errors():
     from paddle2_b200 import _lib
     lib = _lib.lib()

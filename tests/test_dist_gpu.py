@@ -46,9 +46,20 @@ def _worker(rank, world, port, ret):
         got = red.reduce(L.MEAN, x).cpu().numpy()
         G.assert_reduce_close(got, O.reduce("mean", full, [0]), full, [0], "mean", G.FP32_RTOL)
         torch.cuda.synchronize()
-        # the fused variant: one kernel per rank, exchange over peer memory, no NCCL
+        # bf16 sum: the ranks' partials travel in fp32 and the result is rounded once
+        import paddle2_b200 as pb
+        xb16 = x.bfloat16()
+        part = pb.sum(xb16, axis=0, dtype="float32").cpu().numpy()
+        parts = [None] * world
+        dist.all_gather_object(parts, part)
+        want16 = torch.from_numpy(np.sum(np.stack(parts), axis=0, dtype=np.float32)).bfloat16()
+        assert torch.equal(red.sum(xb16).cpu(), want16)
+        got16 = red.reduce(L.MEAN, xb16).float().cpu().numpy()
+        np.testing.assert_allclose(got16, np.stack(parts).sum(0) / total_rows, rtol=G.BF16_RTOL)
+        # without a collective library: exchange kernel over peer memory behind the local reduce
         from paddle2_b200.dist import P2PReducer
         p2p = P2PReducer(max_out_numel=cols, max_tiles=64)
+        assert torch.equal(p2p.sum(xb16).cpu(), want16)
         nccl_sum = red.sum(x)
         for _ in range(3):                       # epochs 1..3: slots alternate by parity
             fused = p2p.sum(x)
@@ -62,6 +73,7 @@ def _worker(rank, world, port, ret):
         gathered = [None] * world
         dist.all_gather_object(gathered, fused.cpu().numpy().tobytes())
         assert all(b == gathered[0] for b in gathered)
+        p2p.status()
         p2p.close()
         # argmax / argmin across the shards: ties span ranks, the lowest GLOBAL row must win
         ti = np.random.default_rng(7).integers(0, 5, size=(total_rows, cols)).astype(np.int64)

@@ -97,7 +97,42 @@ def test_max_uses_the_same_path():
     assert torch.equal(got, want)
 
 
-def test_refuses_what_does_not_fit_and_what_it_does_not_cover():
+def test_long_rows_and_two_stage_shapes_use_the_built_in_scratch_too():
+    """A full reduce of a long 1-D tensor (row cut across CTAs) and the per-channel sum of
+    [N,C,HW] (row stage -> intermediate -> column stage) also need scratch; twice in a row each."""
+    lib = L.lib()
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.rand(1 << 26, device="cuda", generator=g)
+    want = torch.empty((), device="cuda")
+    assert _with_caller_workspace(x, want) <= L.NOALLOC_SCRATCH_BYTES
+    for call in range(2):
+        got = torch.full((), float("nan"), device="cuda")
+        L.check(lib.b200phi_reduce_noalloc(C.byref(_desc(x, got)), _stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(got, want), f"call {call}"
+    x = torch.rand(64, 96, 3136, device="cuda", generator=g)
+
+    def two_axes(out):
+        d = _desc(x, out)
+        d.naxes = 2
+        d.axes[0], d.axes[1] = 0, 2
+        return d
+
+    want = torch.empty(96, device="cuda")
+    d0 = two_axes(want)
+    ws_bytes = lib.b200phi_reduce_workspace(C.byref(d0))
+    assert 0 < ws_bytes <= L.NOALLOC_SCRATCH_BYTES
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    d0.workspace, d0.workspace_bytes = ws.data_ptr(), ws_bytes
+    L.check(lib.b200phi_reduce(C.byref(d0), _stream()))
+    for call in range(2):
+        got = torch.full((96,), float("nan"), device="cuda")
+        L.check(lib.b200phi_reduce_noalloc(C.byref(two_axes(got)), _stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(got, want), f"call {call}"
+
+
+def test_refuses_what_does_not_fit_and_serves_what_needs_no_scratch():
     lib = L.lib()
     # int8 -> int64 column sum: 16 int64 partials per 16-byte vector, far more than 4 MiB
     x = torch.zeros(4096, 65536, device="cuda", dtype=torch.int8)
@@ -109,10 +144,11 @@ def test_refuses_what_does_not_fit_and_what_it_does_not_cover():
     assert rc == 4                                           # B200PHI_WORKSPACE_TOO_SMALL
     msg = lib.b200phi_last_error().decode()
     assert str(need) in msg and str(L.NOALLOC_SCRATCH_BYTES) in msg
-    # a last-axis reduce needs no scratch: it is not this entry point's business
+    # a last-axis reduce needs no scratch: served all the same, the array stays untouched
     x = torch.rand(64, 4096, device="cuda")
     out = torch.empty(64, device="cuda")
     d = _desc(x, out)
     d.axes[0] = 1
-    assert lib.b200phi_reduce_noalloc(C.byref(d), _stream()) == 2   # B200PHI_UNSUPPORTED
-    assert "column reduce" in lib.b200phi_last_error().decode()
+    L.check(lib.b200phi_reduce_noalloc(C.byref(d), _stream()))
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(G.to_np(out), G.to_np(x.double().sum(1).float()), rtol=G.FP32_RTOL)
