@@ -127,6 +127,14 @@ B200PHI_API size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d);
  * is fused into the load. */
 B200PHI_API int b200phi_reduce(const b200phi_reduce_desc* d, void* stream);
 
+/* Diagnostic: which kernel family b200phi_reduce would launch for this descriptor on the current
+ * device (the ReduceKind of csrc/reduce_plan.h: 0/1 row, 2 split row, 3 column, 4 scalar index
+ * walk, 5/7/8/9 short-row forms, 6 two-stage, 10/11 tiled general patterns), or -1 for a bad
+ * descriptor.  Tests and benchmarks use it to assert that a shape runs on the path they mean to
+ * measure; the reference exposes the same decision as ReduceConfig::reduce_type
+ * (reduce_function.h:410-431).  Pure host logic. */
+B200PHI_API int b200phi_reduce_plan_kind(const b200phi_reduce_desc* d);
+
 /* No counterpart in the reference.  The same reductions as b200phi_reduce (any shape: column
  * reduces, few very long rows, two-stage [A,K,B] patterns -- the ones that need scratch -- and
  * all the others), for hosts that cannot hand over a workspace because they may not, or

@@ -196,6 +196,7 @@ class B200PhiError(RuntimeError):
 EXPORTS = [
     "b200phi_reduce_workspace",
     "b200phi_reduce",
+    "b200phi_reduce_plan_kind",
     "b200phi_reduce_noalloc",
     "b200phi_argreduce_workspace",
     "b200phi_argreduce",
@@ -241,6 +242,8 @@ def lib():
     L.b200phi_reduce_workspace.restype = C.c_size_t
     L.b200phi_reduce_workspace.argtypes = [C.POINTER(ReduceDesc)]
     L.b200phi_reduce.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
+    L.b200phi_reduce_plan_kind.argtypes = [C.POINTER(ReduceDesc)]
+    L.b200phi_reduce_plan_kind.restype = C.c_int
     L.b200phi_reduce_noalloc.argtypes = [C.POINTER(ReduceDesc), C.c_void_p]
     L.b200phi_reduce_noalloc.restype = C.c_int
     L.b200phi_argreduce.argtypes = [C.POINTER(ArgReduceDesc), C.c_void_p]

@@ -72,9 +72,8 @@ static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, c
       return set_error(B200PHI_INVALID_ARGUMENT, "workspace must be 256-byte aligned");
   }
   if (plan.kind == kTwoStage) {
-    // row sums of [A*K, B] into the scratch, then the column reduce of [A, K]: two launches of
-    // the streaming kernels instead of the generic walk (64 CTAs of scalar loads for the
-    // per-channel sum of [256,64,112,112]: 0.42 TB/s)
+    // one reduced dim peeled by a streaming row / column kernel into the scratch, then the rest
+    // (itself possibly two stages): [A,K,B] -> row sums of [A*K, B], then the column reduce of [A, K]
     unsigned char* ws = static_cast<unsigned char*>(d->workspace);
     b200phi_reduce_desc d1, d2;
     two_stage_descs(plan, d, ws, &d1, &d2);
@@ -87,26 +86,27 @@ static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, c
     return run_reduce_stage(&d2, 1, stream);
   }
   ReduceArgs a{&plan, d->x, d->out, d->workspace, stream};
+  const bool tiled = plan.kind == kTiledKeep || plan.kind == kTiledRed;
   switch (d->op) {
     case B200PHI_SUM:
     case B200PHI_MEAN:
-      rc = launch_sum(a);
+      rc = tiled ? launch_sum_tiled(a) : launch_sum(a);
       break;
     case B200PHI_PROD:
-      rc = launch_prod(a);
+      rc = tiled ? launch_prod_tiled(a) : launch_prod(a);
       break;
     case B200PHI_MAX:
     case B200PHI_MIN:
     case B200PHI_AMAX:
     case B200PHI_AMIN:
-      rc = launch_minmax(a);
+      rc = tiled ? launch_minmax_tiled(a) : launch_minmax(a);
       break;
     case B200PHI_ANY:
     case B200PHI_ALL:
-      rc = launch_logical(a);
+      rc = tiled ? launch_logical_tiled(a) : launch_logical(a);
       break;
     default:
-      rc = launch_norm(a);
+      rc = tiled ? launch_norm_tiled(a) : launch_norm(a);
       break;
   }
   if (rc == B200PHI_UNSUPPORTED) return set_error(rc, "dtype/op combination not built");
@@ -155,6 +155,13 @@ const char* b200phi_version(void) { return "b200phi 0.1 sm_100a"; }
 
 size_t b200phi_reduce_workspace(const b200phi_reduce_desc* d) {
   return reduce_workspace_bytes(d);
+}
+
+int b200phi_reduce_plan_kind(const b200phi_reduce_desc* d) {
+  ReducePlan plan;
+  std::string err;
+  if (plan_reduce(d, tunables(), &plan, &err) != B200PHI_OK) return -1;
+  return plan.kind;
 }
 
 int b200phi_reduce(const b200phi_reduce_desc* d, void* stream) {

@@ -3,6 +3,7 @@
 
 #include "reduce_kernels.cuh"
 #include "reduce_plan.h"
+#include "reduce_tiled.cuh"
 
 namespace b200phi {
 
@@ -16,8 +17,63 @@ struct ReduceArgs {
 
 int cuda_status(cudaError_t e);  // api.cu: records the message, returns B200PHI_CUDA_ERROR
 
+// The tiled kinds (general keep/reduce patterns).  Each op family instantiates them in a TU of its
+// own (reduce_*_tiled.cu defines B200PHI_TILED_TU) so the build stays parallel; the typed
+// launchers have internal linkage because the two TUs of a family give them different bodies.
 template <typename T, typename Acc, typename Op>
-int launch_reduce_typed(const ReduceArgs& a) {
+static int launch_reduce_tiled(const ReduceArgs& a) {
+  const ReducePlan& p = *a.plan;
+  const T* x = static_cast<const T*>(a.x);
+  const Epilogue ep = make_epilogue(a.out, p.out_dtype, p.op == B200PHI_MEAN, p.red_numel);
+  Acc* partial = static_cast<Acc*>(a.ws);
+  unsigned* tickets =
+      reinterpret_cast<unsigned*>(static_cast<unsigned char*>(a.ws) + p.ws_partial_bytes);
+  if (p.ws_ticket_bytes) {
+    cudaError_t e = cudaMemsetAsync(tickets, 0, p.ws_ticket_bytes, a.stream);
+    if (e != cudaSuccess) return cuda_status(e);
+  }
+  TiledDims td;
+  td.nkeep = p.td_nkeep;
+  td.nred = p.td_nred;
+  for (int k = 0; k < kTiledMaxDims; ++k) {  // right-aligned: the innermost dim sits at the last slot
+    const int ik = p.td_nkeep - kTiledMaxDims + k, ir = p.td_nred - kTiledMaxDims + k;
+    td.keep_div[k] = make_fast_div(ik >= 0 ? p.td_keep_extent[ik] : 1u);
+    td.keep_stride[k] = ik >= 0 ? p.td_keep_stride[ik] : 0;
+    td.red_div[k] = make_fast_div(ir >= 0 ? p.td_red_extent[ir] : 1u);
+    td.red_stride[k] = ir >= 0 ? p.td_red_stride[ir] : 0;
+  }
+  constexpr int VE = VecOf<T>::kElems;
+  const dim3 grid(p.grid_x, p.grid_y);
+  if (p.kind == kTiledKeep) {
+    const unsigned R = static_cast<unsigned>(p.red_numel);
+    const unsigned rps = static_cast<unsigned>(p.rows_per_split);
+    const size_t smem = static_cast<size_t>(kBlock) * p.vec * sizeof(Acc);
+    if (p.vec > 1)
+      tile_keep_kernel<T, Acc, Op, VE, 8><<<grid, kBlock, smem, a.stream>>>(x, td, p.nq, p.TX, R, rps, partial, tickets, ep);
+    else
+      tile_keep_kernel<T, Acc, Op, 1, 8><<<grid, kBlock, smem, a.stream>>>(x, td, p.nq, p.TX, R, rps, partial, tickets, ep);
+  } else {
+    const FastDiv lv = make_fast_div(p.Lv);
+    const unsigned on = static_cast<unsigned>(p.out_numel);
+    if (p.vec > 1 && p.G == 256)
+      tile_red_kernel<T, Acc, Op, VE, 256, 8><<<grid, kBlock, 0, a.stream>>>(x, td, lv, p.W, p.chunk, on, partial, tickets, ep);
+    else if (p.vec > 1)
+      tile_red_kernel<T, Acc, Op, VE, 32, 8><<<grid, kBlock, 0, a.stream>>>(x, td, lv, p.W, p.chunk, on, partial, tickets, ep);
+    else if (p.G == 256)
+      tile_red_kernel<T, Acc, Op, 1, 256, 8><<<grid, kBlock, 0, a.stream>>>(x, td, lv, p.W, p.chunk, on, partial, tickets, ep);
+    else
+      tile_red_kernel<T, Acc, Op, 1, 32, 8><<<grid, kBlock, 0, a.stream>>>(x, td, lv, p.W, p.chunk, on, partial, tickets, ep);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_status(e);
+  return B200PHI_OK;
+}
+
+template <typename T, typename Acc, typename Op>
+static int launch_reduce_typed(const ReduceArgs& a) {
+#ifdef B200PHI_TILED_TU
+  return launch_reduce_tiled<T, Acc, Op>(a);
+#else
   const ReducePlan& p = *a.plan;
   const T* x = static_cast<const T*>(a.x);
   const Epilogue ep = make_epilogue(a.out, p.out_dtype, p.op == B200PHI_MEAN, p.red_numel);
@@ -155,11 +211,12 @@ int launch_reduce_typed(const ReduceArgs& a) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);
   return B200PHI_OK;
+#endif
 }
 
 // in_dtype -> storage type
 template <typename Acc, template <typename> class OpT>
-int dispatch_reduce_in(const ReduceArgs& a) {
+static int dispatch_reduce_in(const ReduceArgs& a) {
   using Op = OpT<Acc>;
   switch (a.plan->in_dtype) {
     case B200PHI_BOOL:
@@ -189,7 +246,7 @@ int dispatch_reduce_in(const ReduceArgs& a) {
 
 // Natural accumulation type only (max/min/prod keep the input dtype).
 template <template <typename> class OpT>
-int dispatch_reduce_natural(const ReduceArgs& a) {
+static int dispatch_reduce_natural(const ReduceArgs& a) {
   switch (a.plan->in_dtype) {
     case B200PHI_BOOL:
       return launch_reduce_typed<Bool8, long long, OpT<long long>>(a);
@@ -216,11 +273,21 @@ int dispatch_reduce_natural(const ReduceArgs& a) {
   }
 }
 
-// one translation unit per op family keeps nvcc parallel
+// one translation unit per op family (two: classic kinds, tiled kinds) keeps nvcc parallel
+#ifdef B200PHI_TILED_TU
+#define B200PHI_LAUNCH_NAME(n) n##_tiled
+#else
+#define B200PHI_LAUNCH_NAME(n) n
+#endif
 int launch_sum(const ReduceArgs& a);      // SUM, MEAN
 int launch_prod(const ReduceArgs& a);     // PROD
 int launch_minmax(const ReduceArgs& a);   // MAX, MIN, AMAX, AMIN
 int launch_logical(const ReduceArgs& a);  // ANY, ALL
 int launch_norm(const ReduceArgs& a);     // SUM_ABS, SUM_SQUARE, L2_NORM, MAX_ABS, MIN_ABS, COUNT_NONZERO
+int launch_sum_tiled(const ReduceArgs& a);
+int launch_prod_tiled(const ReduceArgs& a);
+int launch_minmax_tiled(const ReduceArgs& a);
+int launch_logical_tiled(const ReduceArgs& a);
+int launch_norm_tiled(const ReduceArgs& a);
 
 }  // namespace b200phi

@@ -3,7 +3,7 @@
 #include "reduce_launch.cuh"
 
 namespace b200phi {
-int launch_logical(const ReduceArgs& a) {
+int B200PHI_LAUNCH_NAME(launch_logical)(const ReduceArgs& a) {
   if (a.plan->op == B200PHI_ANY) return dispatch_reduce_in<int, AnyOp>(a);
   return dispatch_reduce_in<int, AllOp>(a);
 }

@@ -3,7 +3,7 @@
 #include "reduce_launch.cuh"
 
 namespace b200phi {
-int launch_minmax(const ReduceArgs& a) {
+int B200PHI_LAUNCH_NAME(launch_minmax)(const ReduceArgs& a) {
   const int op = a.plan->op;
   if (op == B200PHI_MAX || op == B200PHI_AMAX) return dispatch_reduce_natural<MaxOp>(a);
   return dispatch_reduce_natural<MinOp>(a);

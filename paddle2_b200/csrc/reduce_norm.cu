@@ -21,7 +21,7 @@ static int dispatch_norm(const ReduceArgs& a) {
   }
 }
 
-int launch_norm(const ReduceArgs& a) {
+int B200PHI_LAUNCH_NAME(launch_norm)(const ReduceArgs& a) {
   switch (a.plan->op) {
     case B200PHI_SUM_ABS:
       return dispatch_norm<SumAbsOp>(a);

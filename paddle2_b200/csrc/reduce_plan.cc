@@ -80,26 +80,30 @@ static int fail(std::string* err, int code, const std::string& msg) {
 
 void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tmp,
                      b200phi_reduce_desc* d1, b200phi_reduce_desc* d2) {
+  // stage 1: the merged tensor, reduced over the peeled dim alone
   *d1 = b200phi_reduce_desc();
   d1->op = p.ts_op1;
   d1->in_dtype = d->in_dtype;
   d1->out_dtype = p.ts_tmp_dtype;
-  d1->rank = 2;
-  d1->dims[0] = p.tsA * p.tsK;
-  d1->dims[1] = p.tsB;
+  d1->rank = p.ts_rank;
+  for (int i = 0; i < p.ts_rank; ++i) d1->dims[i] = p.ts_dims[i];
   d1->naxes = 1;
-  d1->axes[0] = 1;
+  d1->axes[0] = p.ts_peel;
   d1->x = d->x;
   d1->out = tmp;
+  // stage 2: what is left of it, reduced over the remaining reduced dims
   *d2 = b200phi_reduce_desc();
   d2->op = p.ts_op2;
   d2->in_dtype = p.ts_tmp_dtype;
   d2->out_dtype = p.out_dtype;
-  d2->rank = 2;
-  d2->dims[0] = p.tsA;
-  d2->dims[1] = p.tsK;
-  d2->naxes = 1;
-  d2->axes[0] = 0;
+  d2->rank = p.ts_rank - 1;
+  d2->naxes = 0;
+  for (int i = 0, k = 0; i < p.ts_rank; ++i) {
+    if (i == p.ts_peel) continue;
+    d2->dims[k] = p.ts_dims[i];
+    if (p.ts_isred[i]) d2->axes[d2->naxes++] = k;
+    ++k;
+  }
   d2->x = tmp;
   d2->out = d->out;
 }
@@ -245,9 +249,29 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   }
   if (kind == kCol && p->R < 16) kind = kGeneric;
 
-  // ---- [A, K, B] with A and B reduced: row kernel into scratch, then column kernel -------
-  if (kind == kGeneric && red_numel > 1 && m == 3 && isred[0] && !isred[1] && isred[2] &&
-      ext[2] >= 16 && !t.no_two_stage && t.force_kind < 0) {
+  // ---- two stages: peel ONE reduced dim with a streaming kernel, then reduce what is left ------
+  // [A, K, B] with A and B reduced (per-channel statistics of [N,C,H,W]) peels B with the row
+  // kernel and finishes with the column kernel over [A, K].  Any other interleaving
+  // ([R,K,R,K], [K,R,K,R], ...) peels its longest reduced dim the same way: with everything
+  // inside that dim treated as kept, stage 1 is a plain column (or row) reduce at streaming speed
+  // over the whole input, and stage 2 sees a tensor smaller by that dim's extent.  The dim must be
+  // long enough (>= 64 bytes of elements) for the intermediate's write + read to stay a small
+  // fraction of the input; otherwise the single-pass tiled kernels below take the shape.
+  int peel = -1;
+  if (kind == kGeneric && red_numel > 1 && m >= 3 && !t.no_two_stage && t.force_kind < 0) {
+    if (m == 3 && isred[0] && !isred[1] && isred[2] && ext[2] >= 16) {
+      peel = 2;
+    } else {
+      for (int i = 0; i < m; ++i) {
+        if (!isred[i]) continue;
+        const bool innermost = i == m - 1;
+        const bool friendly = ext[i] * static_cast<long long>(esize) >= 64 &&
+                              (innermost || (ext[i] >= 16 && stride[i] * static_cast<long long>(esize) >= 64));
+        if (friendly && (peel < 0 || ext[i] > ext[peel])) peel = i;
+      }
+    }
+  }
+  if (peel >= 0) {
     int op1 = -1, op2 = -1, tmp_dtype = B200PHI_UNDEFINED;
     const int acc_dtype = p->acc == 0 ? B200PHI_FLOAT32 : (p->acc == 1 ? B200PHI_FLOAT64 : B200PHI_INT64);
     const bool wide_in = esize >= 4;
@@ -285,13 +309,17 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     }
     if (op1 >= 0) {
       p->kind = kTwoStage;
-      p->tsA = ext[0];
-      p->tsK = ext[1];
-      p->tsB = ext[2];
+      p->ts_rank = m;
+      p->ts_peel = peel;
+      for (int i = 0; i < m; ++i) {
+        p->ts_dims[i] = ext[i];
+        p->ts_isred[i] = isred[i] ? 1 : 0;
+      }
       p->ts_op1 = op1;
       p->ts_op2 = op2;
       p->ts_tmp_dtype = tmp_dtype;
-      p->ts_tmp_bytes = static_cast<size_t>(round_up(ext[0] * ext[1] * static_cast<long long>(dtype_size(tmp_dtype)), 256));
+      p->ts_tmp_bytes = static_cast<size_t>(
+          round_up((numel / ext[peel]) * static_cast<long long>(dtype_size(tmp_dtype)), 256));
       b200phi_reduce_desc d1, d2;
       two_stage_descs(*p, d, reinterpret_cast<void*>(static_cast<uintptr_t>(256)), &d1, &d2);
       Tunables t2 = t;
@@ -308,6 +336,81 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->ws_total_bytes = p->ts_tmp_bytes + p->ts_ws1_bytes + p->ts_ws2_bytes;
       p->grid_x = p1.grid_x;
       p->grid_y = p1.grid_y;
+      return B200PHI_OK;
+    }
+  }
+
+  // ---- every other keep/reduce interleaving: the tiled kernels (32-bit index spaces) ----------
+  if (kind == kGeneric && red_numel > 1 && m >= 2 && !t.no_tiled && t.force_kind < 0 &&
+      red_numel < 0x7fffffffLL && out_numel < 0x7fffffffLL) {
+    const bool inner_kept = !isred[m - 1];
+    const long long inner = ext[m - 1];
+    const bool vec_ok = VE > 1 && inner % VE == 0 && reinterpret_cast<uintptr_t>(d->x) % 16 == 0;
+    p->vec = vec_ok ? VE : 1;
+    p->td_nkeep = p->td_nred = 0;
+    for (int i = 0; i < m; ++i) {
+      long long e = ext[i], st = stride[i];
+      const bool last = i == m - 1;
+      if (!isred[i]) {
+        if (last) e /= p->vec, st = p->vec;  // the kept innermost dim is walked in vectors
+        p->td_keep_extent[p->td_nkeep] = static_cast<unsigned>(e);
+        p->td_keep_stride[p->td_nkeep++] = st;
+      } else if (!last) {  // the reduced innermost dim is the contiguous run, not a divided dim
+        p->td_red_extent[p->td_nred] = static_cast<unsigned>(e);
+        p->td_red_stride[p->td_nred++] = st;
+      }
+    }
+    if (inner_kept) {
+      kind = kTiledKeep;
+      p->nq = static_cast<unsigned>(out_numel / p->vec);
+      p->TX = std::min(256, pow2_ceil(p->nq));
+      const int TY = 256 / p->TX;
+      const long long gx = ceil_div(p->nq, p->TX);
+      long long max_splits = std::max<long long>(1, red_numel / (static_cast<long long>(TY) * 8));
+      long long splits = std::max<long long>(1, ceil_div(want_ctas, gx));
+      if (splits > 1) {
+        const long long lo = splits - 1;
+        const double t_hi = static_cast<double>(ceil_div(gx * splits, want_ctas)) / splits;
+        const double t_lo = static_cast<double>(ceil_div(gx * lo, want_ctas)) / lo;
+        if (t_lo < t_hi) splits = lo;
+      }
+      splits = std::min(splits, max_splits);
+      splits = std::min<long long>(splits, 65535);
+      p->rows_per_split = round_up(ceil_div(red_numel, splits), TY);
+      splits = ceil_div(red_numel, p->rows_per_split);
+      p->splits = static_cast<int>(splits);
+      p->grid_x = static_cast<unsigned>(gx);
+      p->grid_y = static_cast<unsigned>(splits);
+    } else {
+      const long long Lv = inner / p->vec;
+      const long long W = (red_numel / inner) * Lv;
+      if (W < 0x7fffffffLL) {
+        kind = kTiledRed;
+        p->Lv = static_cast<unsigned>(Lv);
+        p->W = static_cast<unsigned>(W);
+        p->G = W >= 1024 ? 256 : 32;
+        const long long gx = ceil_div(out_numel, 256 / p->G);
+        long long splits = 1;
+        if (p->G == 256) {
+          splits = std::max<long long>(1, ceil_div(want_ctas, gx));
+          splits = std::min(splits, std::max<long long>(1, W / (256 * 16)));
+          splits = std::min<long long>(splits, 65535);
+        }
+        p->chunk = static_cast<unsigned>(round_up(ceil_div(W, splits), 256));
+        splits = ceil_div(W, p->chunk);
+        p->splits = static_cast<int>(splits);
+        p->grid_x = static_cast<unsigned>(gx);
+        p->grid_y = static_cast<unsigned>(splits);
+      }
+    }
+    if (kind != kGeneric) {
+      p->kind = kind;
+      if (p->splits > 1) {
+        p->ws_partial_bytes = static_cast<size_t>(p->splits) * out_numel * acc_size;
+        p->ws_ticket_bytes = static_cast<size_t>(p->grid_x) * 4;
+      }
+      p->ws_partial_bytes = static_cast<size_t>(round_up(static_cast<long long>(p->ws_partial_bytes), 256));
+      p->ws_total_bytes = p->ws_partial_bytes + p->ws_ticket_bytes;
       return B200PHI_OK;
     }
   }

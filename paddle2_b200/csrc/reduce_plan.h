@@ -30,9 +30,13 @@ enum ReduceKind {
   kRowTiny = 9,   // [rows, cols], aligned rows of 1..16 vectors: G <= 16 lanes per row, 8 rows per group
   kRowScalar = 8, // [rows, cols], 129..1023 columns of any alignment: G lanes per row, scalar loads
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
-  kTwoStage = 6   // [A, K, B] with A and B reduced (per-channel statistics of [N,C,H,W]): the
-                  // row kernel over [A*K, B] into scratch, then the column kernel over [A, K]
+  kTwoStage = 6,  // two or more reduced dims: one of them peeled by a streaming row / column kernel
+                  // into scratch, then the (much smaller) rest reduced by whatever its plan says
+  kTiledKeep = 10,  // any other pattern whose innermost merged dim is kept (tile_keep_kernel)
+  kTiledRed = 11    // any other pattern whose innermost merged dim is reduced (tile_red_kernel)
 };
+
+constexpr int kPlanTiledMaxDims = 5;
 
 struct ReducePlan {
   int kind;
@@ -54,19 +58,28 @@ struct ReducePlan {
   int nkeep, nred;
   long long keep_extent[B200PHI_MAX_RANK], keep_stride[B200PHI_MAX_RANK];
   long long red_extent[B200PHI_MAX_RANK], red_stride[B200PHI_MAX_RANK];
+  // tiled kinds: dims walked with 32-bit divides, innermost last (extents < 2^31)
+  int td_nkeep, td_nred;
+  unsigned td_keep_extent[kPlanTiledMaxDims], td_red_extent[kPlanTiledMaxDims];
+  long long td_keep_stride[kPlanTiledMaxDims], td_red_stride[kPlanTiledMaxDims];
+  unsigned nq;        // kTiledKeep: output vectors; (TX, vec, rows_per_split as in the col kind)
+  unsigned Lv, W, chunk;  // kTiledRed: units per contiguous run, units per output, units per split; G = 32 or 256
   // launch
   unsigned grid_x, grid_y;
   int splits;
   size_t ws_partial_bytes;  // first region of the workspace
   size_t ws_ticket_bytes;   // second region (256-byte aligned start)
   size_t ws_total_bytes;
-  // two-stage kind: extents, the op / dtype of each stage, and how the workspace is cut
-  long long tsA, tsK, tsB;
+  // two-stage kind: the merged dims, which reduced dim stage 1 peels, the op / dtype of each
+  // stage, and how the workspace is cut
+  int ts_rank, ts_peel;
+  long long ts_dims[B200PHI_MAX_RANK];
+  int ts_isred[B200PHI_MAX_RANK];
   int ts_op1, ts_op2, ts_tmp_dtype;
   size_t ts_tmp_bytes, ts_ws1_bytes, ts_ws2_bytes;
 };
 
-// The two reductions a kTwoStage plan stands for; `tmp` is the [A*K] intermediate.
+// The two reductions a kTwoStage plan stands for; `tmp` is the intermediate (input without the peeled dim).
 void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tmp,
                      b200phi_reduce_desc* d1, b200phi_reduce_desc* d2);
 

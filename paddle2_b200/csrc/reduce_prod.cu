@@ -2,5 +2,5 @@
 #include "reduce_launch.cuh"
 
 namespace b200phi {
-int launch_prod(const ReduceArgs& a) { return dispatch_reduce_natural<ProdOp>(a); }
+int B200PHI_LAUNCH_NAME(launch_prod)(const ReduceArgs& a) { return dispatch_reduce_natural<ProdOp>(a); }
 }  // namespace b200phi

@@ -2,7 +2,7 @@
 #include "reduce_launch.cuh"
 
 namespace b200phi {
-int launch_sum(const ReduceArgs& a) {
+int B200PHI_LAUNCH_NAME(launch_sum)(const ReduceArgs& a) {
   switch (a.plan->acc) {
     case 0:
       return dispatch_reduce_in<float, SumOp>(a);
