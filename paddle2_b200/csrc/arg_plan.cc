@@ -110,16 +110,11 @@ int plan_arg(const b200phi_argreduce_desc* d, const Tunables& t, bool x_aligned1
     p->tiles = a_ceil_div(post_v, p->TX);
     const long long bxy = p->pre * p->tiles;
     if (bxy > 0x7fffffffLL) return a_fail(err, B200PHI_UNSUPPORTED, "argreduce: output too large");
-    const long long max_splits = std::max<long long>(1, p->n / (static_cast<long long>(TY) * 8));
-    long long splits = std::max<long long>(1, a_ceil_div(want_ctas, bxy));
-    if (splits > 1) {  // of two neighbouring counts, the one whose last wave wastes less
-      const long long lo = splits - 1;
-      const double t_hi = static_cast<double>(a_ceil_div(bxy * splits, want_ctas)) / splits;
-      const double t_lo = static_cast<double>(a_ceil_div(bxy * lo, want_ctas)) / lo;
-      if (t_lo < t_hi) splits = lo;
-    }
-    splits = std::min(splits, max_splits);
-    splits = std::min<long long>(splits, 65535);
+    const long long max_splits = std::max<long long>(
+        1, std::min(p->n / (static_cast<long long>(TY) * 8),
+                    p->n * p->TX * p->vec * static_cast<long long>(esize) / (256 << 10)));
+    long long splits = pick_splits(bxy, want_ctas, max_splits,  // whole waves (reduce_plan.cc)
+                                  static_cast<double>(p->n) * esize / (p->val_size + 8));
     p->rows_per_split = a_round_up(a_ceil_div(p->n, splits), TY);
     if (p->rows_per_split > 0x7fffffffLL)
       return a_fail(err, B200PHI_UNSUPPORTED, "argreduce: reduced extent too long for the column plan");

@@ -73,6 +73,31 @@ static int pow2_ceil(long long v) {
   return p;
 }
 
+// How many ways to cut the reduced extent when `bxy` thread blocks already come from the
+// outputs.  The blocks run in waves of `slots` and every block does 1/s of a column's work, so
+// compute time ~ ceil(bxy * s / slots) / s; a split also writes and re-reads one partial per
+// output per split, `ratio` = (input bytes per output) / (partial bytes per output) says how
+// much that weighs.  The smallest s within 0.5 % of the best cost: 392 tiles on 592 slots run as
+// 3 splits in two full waves (0.67), not as 1 or 2 (one and a third waves: 1.0); 16384 tiles of
+// a 64-row reduce are never split (28 waves either way, and the partials would be a quarter of
+// the input).
+long long pick_splits(long long bxy, long long slots, long long max_splits, double ratio) {
+  if (bxy < 1) bxy = 1;
+  if (ratio < 1.0) ratio = 1.0;
+  long long hi = std::min<long long>(max_splits, ceil_div(slots, bxy) * 4 + 4);
+  hi = std::max<long long>(1, std::min<long long>(hi, 65535));
+  auto cost = [&](long long s) {
+    const double waves = static_cast<double>(ceil_div(bxy * s, slots)) / static_cast<double>(s);
+    // (5 % flat: the ticket, the finalise and the memset are not free either)
+    return waves * (1.0 + (s > 1 ? 0.05 + 2.0 * static_cast<double>(s) / ratio : 0.0));
+  };
+  double best = 1e300;
+  for (long long s = 1; s <= hi; ++s) best = std::min(best, cost(s));
+  for (long long s = 1; s <= hi; ++s)
+    if (cost(s) <= best * 1.005) return s;
+  return 1;
+}
+
 static int fail(std::string* err, int code, const std::string& msg) {
   if (err) *err = msg;
   return code;
@@ -261,6 +286,11 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   if (kind == kGeneric && red_numel > 1 && m >= 3 && !t.no_two_stage && t.force_kind < 0) {
     if (m == 3 && isred[0] && !isred[1] && isred[2] && ext[2] >= 16) {
       peel = 2;
+    } else if (esize <= 2 && isred[m - 1] && ext[m - 1] * static_cast<long long>(esize) < 512 &&
+               !t.no_tiled && red_numel < 0x7fffffffLL && out_numel < 0x7fffffffLL) {
+      // 16-bit tensors whose contiguous run is short and reduced: the single-pass kernel reads
+      // them faster than two stages through an fp32 intermediate twice their element size
+      // (bf16 sum([256,64,112,112], (1,3)): 6.0 TB/s against 4.9)
     } else {
       for (int i = 0; i < m; ++i) {
         if (!isred[i]) continue;
@@ -366,16 +396,13 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->TX = std::min(256, pow2_ceil(p->nq));
       const int TY = 256 / p->TX;
       const long long gx = ceil_div(p->nq, p->TX);
-      long long max_splits = std::max<long long>(1, red_numel / (static_cast<long long>(TY) * 8));
-      long long splits = std::max<long long>(1, ceil_div(want_ctas, gx));
-      if (splits > 1) {
-        const long long lo = splits - 1;
-        const double t_hi = static_cast<double>(ceil_div(gx * splits, want_ctas)) / splits;
-        const double t_lo = static_cast<double>(ceil_div(gx * lo, want_ctas)) / lo;
-        if (t_lo < t_hi) splits = lo;
-      }
-      splits = std::min(splits, max_splits);
-      splits = std::min<long long>(splits, 65535);
+      // a split must keep at least 8 rows per thread and 256 KiB per block: below that the block's
+      // start-up and the finalise cost more than the better wave fit gives back
+      const long long max_splits = std::max<long long>(
+          1, std::min(red_numel / (static_cast<long long>(TY) * 8),
+                      red_numel * p->TX * p->vec * static_cast<long long>(esize) / (256 << 10)));
+      long long splits = pick_splits(gx, want_ctas, max_splits,
+                                      static_cast<double>(red_numel) * esize / acc_size);
       p->rows_per_split = round_up(ceil_div(red_numel, splits), TY);
       splits = ceil_div(red_numel, p->rows_per_split);
       p->splits = static_cast<int>(splits);
@@ -388,7 +415,9 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         kind = kTiledRed;
         p->Lv = static_cast<unsigned>(Lv);
         p->W = static_cast<unsigned>(W);
-        p->G = W >= 1024 ? 256 : 32;
+        // a warp per output unless an output is long (>= 128 KiB) or there are too few outputs to
+        // fill the machine with warps; a CTA per 28 KiB output spent its time in barriers
+        p->G = (W >= 8192 || out_numel < 8 * want_ctas) ? 256 : 32;
         const long long gx = ceil_div(out_numel, 256 / p->G);
         long long splits = 1;
         if (p->G == 256) {
@@ -544,19 +573,14 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->tiles = ceil_div(inner_v, p->TX);
       const long long bxy = p->outer * p->tiles;
       if (bxy > 0x7fffffffLL) return fail(err, B200PHI_UNSUPPORTED, "output too large for col plan");
-      long long max_splits = std::max<long long>(1, p->R / (static_cast<long long>(TY) * 8));
-      // fill the resident CTA slots; of the two neighbouring split counts take the one whose
-      // last wave wastes less (time ~ waves / splits): 128 tiles on 592 slots run as 4 splits in
-      // one wave, not 5 splits in two ([8192,131072] axis 0: 5.71 TB/s with 5)
-      long long splits = std::max<long long>(1, ceil_div(want_ctas, bxy));
-      if (splits > 1) {
-        const long long lo = splits - 1;
-        const double t_hi = static_cast<double>(ceil_div(bxy * splits, want_ctas)) / splits;
-        const double t_lo = static_cast<double>(ceil_div(bxy * lo, want_ctas)) / lo;
-        if (t_lo < t_hi) splits = lo;
-      }
-      splits = std::min(splits, max_splits);
-      splits = std::min<long long>(splits, 65535);
+      // (a split keeps at least 8 rows per thread and 256 KiB per block)
+      const long long max_splits = std::max<long long>(
+          1, std::min(p->R / (static_cast<long long>(TY) * 8),
+                      p->R * p->TX * p->vec * static_cast<long long>(esize) / (256 << 10)));
+      // fill the resident CTA slots in whole waves (pick_splits): 128 tiles on 592 slots run as 4
+      // splits in one wave, not 5 splits in two ([8192,131072] axis 0: 5.71 TB/s with 5)
+      long long splits = pick_splits(bxy, want_ctas, max_splits,
+                                      static_cast<double>(p->R) * esize / acc_size);
       p->rows_per_split = round_up(ceil_div(p->R, splits), TY);
       splits = ceil_div(p->R, p->rows_per_split);
       p->splits = static_cast<int>(splits);

@@ -83,6 +83,10 @@ struct ReducePlan {
 void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tmp,
                      b200phi_reduce_desc* d1, b200phi_reduce_desc* d2);
 
+// Split count of a reduced extent given `bxy` blocks from the outputs, `slots` resident blocks and
+// the input-to-partial byte ratio per output (reduce_plan.cc).
+long long pick_splits(long long bxy, long long slots, long long max_splits, double ratio);
+
 size_t dtype_size(int dtype);
 bool dtype_known(int dtype);
 bool dtype_is_float(int dtype);

@@ -49,7 +49,7 @@ def main():
         ("sum fp32 [256,64,112,112] axes (0,2)", (256, 64, 112, 112), [0, 2], torch.float32, L.SUM),
         ("sum fp32 [256,64,112,112] axes (1,3)", (256, 64, 112, 112), [1, 3], torch.float32, L.SUM),
         ("min fp32 [32,64,48,80,6,10] axes (2,4)", (32, 64, 48, 80, 6, 10), [2, 4], torch.float32, L.MIN),
-        ("prod fp32 [8,10,6,7,8,9,10,11] axes (2,3,4)", (8, 10, 6, 7, 8, 9, 10, 11), [2, 3, 4], torch.float32, L.PROD),
+        ("prod fp32 [40,10,6,7,8,9,10,22] axes (2,3,4)", (40, 10, 6, 7, 8, 9, 10, 22), [2, 3, 4], torch.float32, L.PROD),
         ("sum bf16 [256,64,112,112] axes (0,2)", (256, 64, 112, 112), [0, 2], torch.bfloat16, L.SUM),
         ("sum bf16 [256,64,112,112] axes (1,3)", (256, 64, 112, 112), [1, 3], torch.bfloat16, L.SUM),
         ("sum fp32 [8, 16M, 8] axis 0 (R<16 column)", (8, 1 << 24, 8), [0], torch.float32, L.SUM),
