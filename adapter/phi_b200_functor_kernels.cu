@@ -6,8 +6,10 @@
 //   paddle/phi/kernels/kps/logical_kernel.cu            (logical_and/or/xor/not)
 //   paddle/phi/kernels/kps/bitwise_kernel.cu            (bitwise_and/or/xor/not)
 //   paddle/phi/kernels/gpu/activation_kernel.cu         (the activations listed below)
-//   paddle/phi/kernels/gpu/reduce_kernel.cu:74-187      (ReduceMax/MinGradKernel)
-//   paddle/phi/kernels/gpu/elementwise_grad_kernel.cu   (Maximum/MinimumGradKernel)
+//   paddle/phi/kernels/gpu/reduce_kernel.cu:42-232      (ReduceSum/Mean/Max/Min/AMax/AMinGradKernel; its
+//                                                        `reduce` collective kernel stays where it is)
+//   paddle/phi/kernels/gpu/elementwise_grad_kernel.cu   (Add/Subtract/Multiply/Divide/Maximum/MinimumGradKernel:
+//                                                        those registrations only)
 //   paddle/phi/kernels/gpu/{p_norm,squared_l2_norm,mean_all,reduce_as,logsumexp}_kernel.cu
 // Compile-checked against the reference headers (adapter/check_compile.sh).
 #include <vector>
@@ -17,6 +19,7 @@
 #include "paddle/phi/common/int_array.h"
 #include "paddle/phi/core/dense_tensor.h"
 #include "paddle/phi/core/kernel_registry.h"
+#include "paddle/phi/core/tensor_utils.h"
 
 namespace phi {
 namespace b200 {
@@ -386,6 +389,255 @@ void LogsumexpKernel(const Context& dev_ctx, const DenseTensor& x, const std::ve
   out->Resize(out_dims);
 }
 
+// ---- backward of the reductions and of add .. divide ---------------------------
+namespace b200 {
+
+// One launch of the broadcast engine with a single operand: out = act(broadcast(in)), the unary
+// BroadcastKernel call of ReduceGrad (gpu/reduce_grad.h:30-85).
+template <typename Context>
+void BroadcastUnary(const Context& dev_ctx, const b200phi_tensor_view& in, DataType dtype, int act,
+                    float scale, DenseTensor* out) {
+  dev_ctx.Alloc(out, dtype);
+  b200phi_elementwise_desc e = {};
+  e.binary = B200PHI_ADD;
+  e.act = act;
+  e.scale = scale;
+  e.dtype = static_cast<int>(dtype);
+  e.arity = 1;
+  e.axis = -1;
+  e.in[0] = in;
+  e.out_rank = out->dims().size();
+  for (int i = 0; i < e.out_rank; ++i) e.out_dims[i] = out->dims()[i];
+  e.out = out->data();
+  CheckMap(b200phi_elementwise(&e, dev_ctx.stream()));
+}
+
+template <typename Context>
+void Binary(const Context& dev_ctx, int binary, const DenseTensor& x, const DenseTensor& y, int axis,
+            DenseTensor* out) {
+  dev_ctx.Alloc(out, x.dtype());
+  b200phi_elementwise_desc e = {};
+  e.binary = binary;
+  e.dtype = static_cast<int>(x.dtype());
+  e.arity = 2;
+  e.axis = axis;
+  View(x, &e.in[0]);
+  View(y, &e.in[1]);
+  e.out_rank = out->dims().size();
+  for (int i = 0; i < e.out_rank; ++i) e.out_dims[i] = out->dims()[i];
+  e.out = out->data();
+  CheckMap(b200phi_elementwise(&e, dev_ctx.stream()));
+}
+
+// grad of a (possibly broadcast) operand shaped like `like`: `src` itself when the shapes agree,
+// else its sum over the dims funcs::GetReduceDim(like.dims(), src.dims(), axis) names
+// (elementwise_base.h; gpu/elementwise_grad.h:29-105 reduces with phi::SumKernel the same way).
+template <typename Context>
+void SumTo(const Context& dev_ctx, const DenseTensor& src, const DenseTensor& like, int axis,
+           DenseTensor* dst) {
+  if (dst == nullptr) return;
+  if (like.dims() == src.dims()) {
+    phi::Copy(dev_ctx, src, dev_ctx.GetPlace(), false, dst);
+    return;
+  }
+  const int r = src.dims().size(), lr = like.dims().size();
+  const int off = axis < 0 ? r - lr : axis;
+  b200phi_reduce_desc d = {};
+  d.op = B200PHI_SUM;
+  d.in_dtype = d.out_dtype = static_cast<int>(src.dtype());
+  d.rank = r;
+  for (int i = 0; i < r; ++i) {
+    d.dims[i] = src.dims()[i];
+    const bool outside = i < off || i >= off + lr;
+    if (outside || (like.dims()[i - off] == 1 && src.dims()[i] != 1)) d.axes[d.naxes++] = i;
+  }
+  dst->Resize(like.dims());
+  dev_ctx.Alloc(dst, src.dtype());
+  d.x = src.data();
+  d.out = dst->data();
+  DenseTensor scratch;
+  const size_t ws = b200phi_reduce_workspace(&d);
+  if (ws > 0) {
+    scratch.Resize({static_cast<int64_t>(ws)});
+    d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+    d.workspace_bytes = ws;
+  }
+  CheckMap(b200phi_reduce(&d, dev_ctx.stream()));
+}
+
+inline int AxisFor(const DenseTensor& operand, const DenseTensor& other, int axis) {
+  return operand.dims().size() < other.dims().size() ? axis : -1;
+}
+
+}  // namespace b200
+
+// gpu/reduce_kernel.cu:42-75: out_grad viewed with the reduced dims as 1, broadcast to x's shape
+template <typename T, typename Context>
+void ReduceSumGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out_grad,
+                         const IntArray& dims, bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  PADDLE_ENFORCE_EQ(out_grad.dtype(), x.dtype(),
+                    common::errors::Unimplemented("sum_grad: out_grad and x must share a dtype here"));
+  b200phi_tensor_view g;
+  b200::KeepDimView(out_grad, x, dims.GetData(), reduce_all, &g);
+  x_grad->Resize(x.dims());
+  b200::BroadcastUnary(dev_ctx, g, x.dtype(), B200PHI_ACT_NONE, 0.f, x_grad);
+}
+
+// gpu/reduce_kernel.cu:124-158: the same broadcast with kps::DivideFunctor(reduce_num) fused in
+template <typename T, typename Context>
+void ReduceMeanGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out_grad,
+                          const IntArray& dims, bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  b200phi_tensor_view g;
+  b200::KeepDimView(out_grad, x, dims.GetData(), reduce_all, &g);
+  int64_t reduce_num = 1;
+  for (int i = 0; i < g.rank; ++i)
+    if (g.dims[i] == 1) reduce_num *= x.dims()[i];
+  x_grad->Resize(x.dims());
+  b200::BroadcastUnary(dev_ctx, g, x.dtype(), B200PHI_ACT_SCALE, 1.0f / static_cast<float>(reduce_num),
+                       x_grad);
+}
+
+// gpu/reduce_amin_amax_common.h:28-107: the gradient is shared evenly between the positions that
+// tie with the extreme: mask = T(x == out); x_grad = mask * (out_grad / sum(mask))
+template <typename Context>
+void AMaxAMinGrad(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                  const DenseTensor& out_grad, const std::vector<int64_t>& dims, bool reduce_all,
+                  DenseTensor* x_grad) {
+  b200phi_tensor_view o, g;
+  b200::KeepDimView(out, x, dims, reduce_all, &o);
+  b200::KeepDimView(out_grad, x, dims, reduce_all, &g);
+  // mask over x's shape
+  DenseTensor mask;
+  mask.Resize(x.dims());
+  dev_ctx.Alloc(&mask, x.dtype());
+  b200phi_map_desc m = {};
+  m.op = B200PHI_MAP_EQUAL_T;
+  m.in_dtype = static_cast<int>(x.dtype());
+  m.arity = 2;
+  m.axis = -1;
+  b200::View(x, &m.in[0]);
+  m.in[1] = o;
+  m.out_rank = x.dims().size();
+  for (int i = 0; i < m.out_rank; ++i) m.out_dims[i] = x.dims()[i];
+  m.out = mask.data();
+  b200::CheckMap(b200phi_map(&m, dev_ctx.stream()));
+  // count of ties per output, kept dims as 1
+  DenseTensor count;
+  std::vector<int64_t> kept(g.dims, g.dims + g.rank);
+  count.Resize(common::make_ddim(kept));
+  dev_ctx.Alloc(&count, x.dtype());
+  b200phi_reduce_desc r = {};
+  r.op = B200PHI_SUM;
+  r.in_dtype = r.out_dtype = static_cast<int>(x.dtype());
+  r.rank = x.dims().size();
+  for (int i = 0; i < r.rank; ++i) {
+    r.dims[i] = x.dims()[i];
+    if (g.dims[i] == 1 && x.dims()[i] != 1) r.axes[r.naxes++] = i;
+  }
+  r.reduce_all = 0;
+  r.x = mask.data();
+  r.out = count.data();
+  DenseTensor scratch;
+  if (r.naxes > 0) {
+    const size_t ws = b200phi_reduce_workspace(&r);
+    if (ws > 0) {
+      scratch.Resize({static_cast<int64_t>(ws)});
+      r.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+      r.workspace_bytes = ws;
+    }
+    b200::CheckMap(b200phi_reduce(&r, dev_ctx.stream()));
+  } else {
+    phi::Copy(dev_ctx, mask, dev_ctx.GetPlace(), false, &count);
+  }
+  // share = out_grad / count on the small tensor, then x_grad = share * T(x == out)
+  DenseTensor share, gview;
+  gview.ShareDataWith(out_grad);
+  gview.Resize(common::make_ddim(kept));
+  share.Resize(common::make_ddim(kept));
+  b200::Binary(dev_ctx, B200PHI_DIVIDE, gview, count, -1, &share);
+  x_grad->Resize(x.dims());
+  dev_ctx.Alloc(x_grad, x.dtype());
+  b200phi_map_desc e = {};
+  e.op = B200PHI_MAP_EQUAL_MUL;
+  e.in_dtype = static_cast<int>(x.dtype());
+  e.arity = 3;
+  e.axis = -1;
+  b200::View(x, &e.in[0]);
+  e.in[1] = o;
+  b200::View(share, &e.in[2]);
+  e.out_rank = x.dims().size();
+  for (int i = 0; i < e.out_rank; ++i) e.out_dims[i] = x.dims()[i];
+  e.out = x_grad->data();
+  b200::CheckMap(b200phi_map(&e, dev_ctx.stream()));
+}
+template <typename T, typename Context>
+void ReduceAMaxGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                          const DenseTensor& out_grad, const std::vector<int64_t>& dims, bool keep_dim,
+                          bool reduce_all, DenseTensor* x_grad) {
+  AMaxAMinGrad(dev_ctx, x, out, out_grad, dims, reduce_all, x_grad);
+}
+template <typename T, typename Context>
+void ReduceAMinGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& out,
+                          const DenseTensor& out_grad, const std::vector<int64_t>& dims, bool keep_dim,
+                          bool reduce_all, DenseTensor* x_grad) {
+  AMaxAMinGrad(dev_ctx, x, out, out_grad, dims, reduce_all, x_grad);
+}
+
+// gpu/elementwise_grad.h:29-105,173-304 and elementwise_{add,subtract,multiply,divide}_grad_kernel.h
+template <typename T, typename Context>
+void AddGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                   const DenseTensor& dout, int axis, DenseTensor* dx, DenseTensor* dy) {
+  b200::SumTo(dev_ctx, dout, x, b200::AxisFor(x, y, axis), dx);
+  b200::SumTo(dev_ctx, dout, y, b200::AxisFor(y, x, axis), dy);
+}
+template <typename T, typename Context>
+void SubtractGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                        const DenseTensor& dout, int axis, DenseTensor* dx, DenseTensor* dy) {
+  b200::SumTo(dev_ctx, dout, x, b200::AxisFor(x, y, axis), dx);
+  if (dy != nullptr) {  // dy = -sum(dout): negate on the small side
+    DenseTensor pos;
+    b200::SumTo(dev_ctx, dout, y, b200::AxisFor(y, x, axis), &pos);
+    b200phi_tensor_view v;
+    b200::View(pos, &v);
+    dy->Resize(y.dims());
+    b200::BroadcastUnary(dev_ctx, v, pos.dtype(), B200PHI_ACT_SCALE, -1.0f, dy);
+  }
+}
+template <typename T, typename Context>
+void MultiplyGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                        const DenseTensor& dout, int axis, DenseTensor* dx, DenseTensor* dy) {
+  if (dx != nullptr) {
+    DenseTensor full;
+    full.Resize(dout.dims());
+    b200::Binary(dev_ctx, B200PHI_MULTIPLY, dout, y, b200::AxisFor(y, dout, axis), &full);
+    b200::SumTo(dev_ctx, full, x, b200::AxisFor(x, y, axis), dx);
+  }
+  if (dy != nullptr) {
+    DenseTensor full;
+    full.Resize(dout.dims());
+    b200::Binary(dev_ctx, B200PHI_MULTIPLY, dout, x, b200::AxisFor(x, dout, axis), &full);
+    b200::SumTo(dev_ctx, full, y, b200::AxisFor(y, x, axis), dy);
+  }
+}
+template <typename T, typename Context>
+void DivideGradKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                      const DenseTensor& out, const DenseTensor& dout, int axis, DenseTensor* dx,
+                      DenseTensor* dy) {
+  if (dx != nullptr) {  // dout / y
+    DenseTensor full;
+    full.Resize(dout.dims());
+    b200::Binary(dev_ctx, B200PHI_DIVIDE, dout, y, b200::AxisFor(y, dout, axis), &full);
+    b200::SumTo(dev_ctx, full, x, b200::AxisFor(x, y, axis), dx);
+  }
+  if (dy != nullptr) {  // -dout * ((out / y) / y): DivGradYFunctor, one ternary launch
+    DenseTensor full;
+    full.Resize(dout.dims());
+    b200::Map(dev_ctx, B200PHI_MAP_DIV_GRAD_Y, {&dout, &out, &y}, b200::AxisFor(y, dout, axis), 0.f, 0.f,
+              &full);
+    b200::SumTo(dev_ctx, full, y, b200::AxisFor(y, x, axis), dy);
+  }
+}
+
 }  // namespace phi
 
 using float16 = phi::dtype::float16;
@@ -455,6 +707,24 @@ PD_REGISTER_KERNEL(max_grad, GPU, ALL_LAYOUT, phi::ReduceMaxGradKernel, float, d
                    float16, bfloat16) {}
 PD_REGISTER_KERNEL(min_grad, GPU, ALL_LAYOUT, phi::ReduceMinGradKernel, float, double, int, int64_t,
                    float16, bfloat16) {}
+// gpu/reduce_kernel.cu:317-388 and gpu/elementwise_grad_kernel.cu:320-445, minus complex
+// (and, for divide_grad, minus the 8/16-bit integer and bool instantiations)
+PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, phi::ReduceSumGradKernel, bool, float, double, float16,
+                   bfloat16, int8_t, uint8_t, int16_t, int, int64_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, phi::ReduceMeanGradKernel, bool, float, double, float16,
+                   bfloat16, int, int64_t) {}
+PD_REGISTER_KERNEL(amax_grad, GPU, ALL_LAYOUT, phi::ReduceAMaxGradKernel, float, double, int, int64_t) {}
+PD_REGISTER_KERNEL(amin_grad, GPU, ALL_LAYOUT, phi::ReduceAMinGradKernel, float, double, int, int64_t) {}
+PD_REGISTER_KERNEL(add_grad, GPU, ALL_LAYOUT, phi::AddGradKernel, float, double, int, int64_t, float16,
+                   bfloat16) {}
+PD_REGISTER_KERNEL(subtract_grad, GPU, ALL_LAYOUT, phi::SubtractGradKernel, float, double, int, int64_t,
+                   float16, bfloat16) {}
+PD_REGISTER_KERNEL(multiply_grad, GPU, ALL_LAYOUT, phi::MultiplyGradKernel, float, float16, double, int,
+                   int64_t, bool, bfloat16) {}
+PD_REGISTER_KERNEL(divide_grad, GPU, ALL_LAYOUT, phi::DivideGradKernel, float, float16, bfloat16, double,
+                   int, int64_t) {}
 PD_REGISTER_KERNEL(maximum_grad, GPU, ALL_LAYOUT, phi::MaximumGradKernel, float, double, int,
                    int64_t, float16, bfloat16) {}
 PD_REGISTER_KERNEL(minimum_grad, GPU, ALL_LAYOUT, phi::MinimumGradKernel, float, double, int,

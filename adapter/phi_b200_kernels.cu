@@ -5,8 +5,12 @@
 //   paddle/phi/kernels/kps/reduce_kernel.cu            (SumRaw/MeanRaw/Max/MinRaw/Prod/AnyRaw/AllRaw/AMaxRaw/AMinRaw)
 //   paddle/phi/kernels/legacy/kps/reduce_max_kernel.cu (MaxRaw)
 //   paddle/phi/kernels/gpu/arg_min_max_kernel.cu       (ArgMax/ArgMin)
-//   paddle/phi/kernels/kps/elementwise_kernel.cu + legacy/kps/elementwise_kernel.cu (Add..Minimum, *Raw)
-//   paddle/phi/kernels/fusion/gpu/fused_elemwise_activation_kernel.cu
+//   paddle/phi/kernels/kps/elementwise_kernel.cu        (add, grad_add, subtract, multiply, divide, maximum, minimum,
+//                                                        remainder, floor_divide, elementwise_pow, copysign, fmax, fmin, heaviside)
+//   paddle/phi/kernels/legacy/kps/elementwise_kernel.cu (add_raw ... elementwise_pow_raw)
+//   paddle/phi/kernels/fusion/gpu/fused_elemwise_activation_kernel.cu (fused_elemwise_activation, fused_elemwise_add_activation)
+// EVERY kernel name those files register is registered here (tests/test_adapter_compile.py checks the
+// registrar symbols one by one), minus the complex64/128 instantiations.
 // (those files are globbed by paddle/phi/kernels/CMakeLists.txt:33-34, so swapping the
 // file swaps the kernel).  Here it is compile-checked against the
 // reference headers (tests/test_adapter_compile.py); it cannot be linked without libphi.
@@ -77,7 +81,35 @@ void Arg(const Context& dev_ctx, int op, const DenseTensor& x, const Scalar& axi
   d.flatten = flatten ? 1 : 0;
   d.x = x.data();
   d.out = out->data();
+  DenseTensor scratch;  // flatten / few long rows / a non-last axis split the reduced extent across CTAs
+  const size_t ws = b200phi_argreduce_workspace(&d);
+  if (ws > 0) {
+    scratch.Resize({static_cast<int64_t>(ws)});
+    d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);
+    d.workspace_bytes = ws;
+  }
   Check(b200phi_argreduce(&d, dev_ctx.stream()));
+}
+
+// The arithmetic binaries that are functor plug-ins of the broadcast engine (b200phi_map):
+// out dtype = x dtype, the legacy `axis` placement as in AddRawKernel.
+template <typename Context>
+void MapBinary(const Context& dev_ctx, int op, const DenseTensor& x, const DenseTensor& y, int axis,
+               DenseTensor* out) {
+  dev_ctx.Alloc(out, x.dtype());
+  b200phi_map_desc d = {};
+  d.op = op;
+  d.in_dtype = static_cast<int>(x.dtype());
+  d.out_dtype = B200PHI_UNDEFINED;
+  d.arity = 2;
+  d.axis = axis;
+  FillDims(x, &d.in[0].rank, d.in[0].dims);
+  d.in[0].data = x.data();
+  FillDims(y, &d.in[1].rank, d.in[1].dims);
+  d.in[1].data = y.data();
+  FillDims(*out, &d.out_rank, d.out_dims);
+  d.out = out->data();
+  Check(b200phi_map(&d, dev_ctx.stream()));
 }
 
 template <typename Context>
@@ -215,13 +247,50 @@ B200_DEFINE_ELEMENTWISE(Divide, B200PHI_DIVIDE)
 B200_DEFINE_ELEMENTWISE(Maximum, B200PHI_MAXIMUM)
 B200_DEFINE_ELEMENTWISE(Minimum, B200PHI_MINIMUM)
 
-// ---- fused add + activation: impl/fused_elemwise_activation_kernel_impl.h:202-222 ----------------
+// grad_add: kps/elementwise_kernel.cu:100-106
 template <typename T, typename Context>
-void FusedElemwiseAddActivationKernel(const Context& dev_ctx, const DenseTensor& x,
-                                      const DenseTensor& y,
-                                      const std::vector<std::string>& functor_list, int axis,
-                                      float scale, bool save_intermediate_out, DenseTensor* out,
-                                      DenseTensor* intermediate_out) {
+void GradAddKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {
+  b200::Elementwise(dev_ctx, B200PHI_ADD, B200PHI_ACT_NONE, 0, 0.f, x, y, -1, out, nullptr);
+}
+
+// remainder / floor_divide / elementwise_pow: DEFINE_CUDA_ELEMENTWISE_OP in
+// legacy/kps/elementwise_kernel.cu:30-32 (raw, with axis) + kps/elementwise_kernel.cu:126-168
+#define B200_DEFINE_MAP_BINARY(Name, OpId)                                                       \
+  template <typename T, typename Context>                                                        \
+  void Name##RawKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,       \
+                       int axis, DenseTensor* out) {                                             \
+    b200::MapBinary(dev_ctx, OpId, x, y, axis, out);                                             \
+  }                                                                                              \
+  template <typename T, typename Context>                                                        \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,          \
+                    DenseTensor* out) {                                                          \
+    b200::MapBinary(dev_ctx, OpId, x, y, -1, out);                                               \
+  }
+B200_DEFINE_MAP_BINARY(Remainder, B200PHI_MAP_REMAINDER)
+B200_DEFINE_MAP_BINARY(FloorDivide, B200PHI_MAP_FLOOR_DIVIDE)
+B200_DEFINE_MAP_BINARY(ElementwisePow, B200PHI_MAP_POW)
+// copysign / fmax / fmin / heaviside have no raw form (kps/elementwise_kernel.cu:142-180,
+// impl/elementwise_kernel_impl.h FMax/FMinKernel)
+#define B200_DEFINE_MAP_BINARY_NOAXIS(Name, OpId)                                                \
+  template <typename T, typename Context>                                                        \
+  void Name##Kernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,          \
+                    DenseTensor* out) {                                                          \
+    b200::MapBinary(dev_ctx, OpId, x, y, -1, out);                                               \
+  }
+B200_DEFINE_MAP_BINARY_NOAXIS(CopySign, B200PHI_MAP_COPYSIGN)
+B200_DEFINE_MAP_BINARY_NOAXIS(FMax, B200PHI_MAP_FMAX)
+B200_DEFINE_MAP_BINARY_NOAXIS(FMin, B200PHI_MAP_FMIN)
+B200_DEFINE_MAP_BINARY_NOAXIS(Heaviside, B200PHI_MAP_HEAVISIDE)
+
+// ---- fused binary + activation: impl/fused_elemwise_activation_kernel_impl.h:30-222 ----------------
+// functor_list = [outer, inner]: Unary(Binary(x, y)) or Binary(x, Unary(y)) with Binary in
+// {elementwise_add, elementwise_sub, elementwise_mul} and Unary in {scale, relu, gelu, sigmoid, tanh}
+// (RunFunctors, funcs/fused_elemwise_activation_functor.h:388-458, covers a subset of these pairs).
+template <typename T, typename Context>
+void FusedElemwiseActivationKernel(const Context& dev_ctx, const DenseTensor& x, const DenseTensor& y,
+                                   const std::vector<std::string>& functor_list, int axis,
+                                   float scale, bool save_intermediate_out, DenseTensor* out,
+                                   DenseTensor* intermediate_out) {
   PADDLE_ENFORCE_EQ(functor_list.size(), 2UL,
                     common::errors::InvalidArgument("functor_list must hold two functors"));
   auto unary_id = [](const std::string& s) -> int {
@@ -232,17 +301,35 @@ void FusedElemwiseAddActivationKernel(const Context& dev_ctx, const DenseTensor&
     if (s == "tanh") return B200PHI_ACT_TANH;
     return -1;
   };
-  int compound = 0, act = -1;
-  if (functor_list[1] == "elementwise_add") {         // Unary(Binary(x, y))
+  auto binary_id = [](const std::string& s) -> int {
+    if (s == "elementwise_add") return B200PHI_ADD;
+    if (s == "elementwise_sub") return B200PHI_SUBTRACT;
+    if (s == "elementwise_mul") return B200PHI_MULTIPLY;
+    return -1;
+  };
+  int compound = 0, act = -1, binary = binary_id(functor_list[1]);
+  if (binary >= 0) {  // Unary(Binary(x, y))
     act = unary_id(functor_list[0]);
-  } else if (functor_list[0] == "elementwise_add") {  // Binary(x, Unary(y))
+  } else {            // Binary(x, Unary(y))
+    binary = binary_id(functor_list[0]);
     act = unary_id(functor_list[1]);
     compound = 1;
   }
-  PADDLE_ENFORCE_GE(act, 0, common::errors::InvalidArgument(
-                                "%s, %s is not a supported functor pair", functor_list[0], functor_list[1]));
-  b200::Elementwise(dev_ctx, B200PHI_ADD, act, compound, scale, x, y, axis, out,
+  PADDLE_ENFORCE_EQ(binary >= 0 && act >= 0, true,
+                    common::errors::InvalidArgument("%s, %s is not a supported functor pair",
+                                                    functor_list[0], functor_list[1]));
+  b200::Elementwise(dev_ctx, binary, act, compound, scale, x, y, axis, out,
                     save_intermediate_out ? intermediate_out : nullptr);
+}
+
+template <typename T, typename Context>
+void FusedElemwiseAddActivationKernel(const Context& dev_ctx, const DenseTensor& x,
+                                      const DenseTensor& y,
+                                      const std::vector<std::string>& functor_list, int axis,
+                                      float scale, bool save_intermediate_out, DenseTensor* out,
+                                      DenseTensor* intermediate_out) {
+  FusedElemwiseActivationKernel<T, Context>(dev_ctx, x, y, functor_list, axis, scale,
+                                            save_intermediate_out, out, intermediate_out);
 }
 
 }  // namespace phi
@@ -283,19 +370,40 @@ PD_REGISTER_KERNEL(argmin, GPU, ALL_LAYOUT, phi::ArgMinKernel, float16, bfloat16
                    int32_t, int64_t, int16_t, uint8_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
 }
-PD_REGISTER_KERNEL(add, GPU, ALL_LAYOUT, phi::AddKernel, float, double, int16_t, int, bool, uint8_t,
-                   int8_t, int64_t, float16, bfloat16) {}
-PD_REGISTER_KERNEL(add_raw, GPU, ALL_LAYOUT, phi::AddRawKernel, float, double, int16_t, int, bool,
-                   uint8_t, int8_t, int64_t, float16, bfloat16) {}
-PD_REGISTER_KERNEL(subtract, GPU, ALL_LAYOUT, phi::SubtractKernel, float, double, int16_t, int,
-                   int64_t, float16, bfloat16) {}
-PD_REGISTER_KERNEL(multiply, GPU, ALL_LAYOUT, phi::MultiplyKernel, float, double, int, int64_t, bool,
-                   float16, bfloat16) {}
-PD_REGISTER_KERNEL(divide, GPU, ALL_LAYOUT, phi::DivideKernel, float, double, int, int64_t, float16,
-                   bfloat16) {}
-PD_REGISTER_KERNEL(maximum, GPU, ALL_LAYOUT, phi::MaximumKernel, float, double, int, int64_t,
-                   float16, bfloat16) {}
-PD_REGISTER_KERNEL(minimum, GPU, ALL_LAYOUT, phi::MinimumKernel, float, double, int, int64_t,
-                   float16, bfloat16) {}
+// kps/elementwise_kernel.cu:183-381 and legacy/kps/elementwise_kernel.cu:60-165, dtype for dtype
+// (minus complex64/128)
+#define B200_ADD_TYPES float, double, int16_t, int, bool, uint8_t, int8_t, int64_t, float16, bfloat16
+#define B200_DIV_TYPES float, double, int8_t, uint8_t, int16_t, int, int64_t, bool, float16, bfloat16
+#define B200_MUL_TYPES float, double, int, int64_t, bool, float16, bfloat16
+#define B200_SUB_TYPES float, double, int16_t, int, int64_t, float16, bfloat16
+#define B200_NUM_TYPES float, double, int, int64_t, float16, bfloat16
+#define B200_FDIV_TYPES uint8_t, int8_t, int16_t, int, int64_t, float, double, float16, bfloat16
+PD_REGISTER_KERNEL(add, GPU, ALL_LAYOUT, phi::AddKernel, B200_ADD_TYPES) {}
+PD_REGISTER_KERNEL(add_raw, GPU, ALL_LAYOUT, phi::AddRawKernel, B200_ADD_TYPES) {}
+PD_REGISTER_KERNEL(grad_add, GPU, ALL_LAYOUT, phi::GradAddKernel, B200_ADD_TYPES) {}
+PD_REGISTER_KERNEL(subtract, GPU, ALL_LAYOUT, phi::SubtractKernel, B200_SUB_TYPES) {}
+PD_REGISTER_KERNEL(subtract_raw, GPU, ALL_LAYOUT, phi::SubtractRawKernel, B200_SUB_TYPES) {}
+PD_REGISTER_KERNEL(multiply, GPU, ALL_LAYOUT, phi::MultiplyKernel, B200_MUL_TYPES) {}
+PD_REGISTER_KERNEL(multiply_raw, GPU, ALL_LAYOUT, phi::MultiplyRawKernel, B200_MUL_TYPES) {}
+PD_REGISTER_KERNEL(divide, GPU, ALL_LAYOUT, phi::DivideKernel, B200_DIV_TYPES) {}
+PD_REGISTER_KERNEL(divide_raw, GPU, ALL_LAYOUT, phi::DivideRawKernel, B200_DIV_TYPES) {}
+PD_REGISTER_KERNEL(maximum, GPU, ALL_LAYOUT, phi::MaximumKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(maximum_raw, GPU, ALL_LAYOUT, phi::MaximumRawKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(minimum, GPU, ALL_LAYOUT, phi::MinimumKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(minimum_raw, GPU, ALL_LAYOUT, phi::MinimumRawKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(remainder, GPU, ALL_LAYOUT, phi::RemainderKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(remainder_raw, GPU, ALL_LAYOUT, phi::RemainderRawKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(floor_divide, GPU, ALL_LAYOUT, phi::FloorDivideKernel, B200_FDIV_TYPES) {}
+PD_REGISTER_KERNEL(floor_divide_raw, GPU, ALL_LAYOUT, phi::FloorDivideRawKernel, B200_FDIV_TYPES) {}
+PD_REGISTER_KERNEL(elementwise_pow, GPU, ALL_LAYOUT, phi::ElementwisePowKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(elementwise_pow_raw, GPU, ALL_LAYOUT, phi::ElementwisePowRawKernel, B200_NUM_TYPES) {}
+PD_REGISTER_KERNEL(copysign, GPU, ALL_LAYOUT, phi::CopySignKernel, bool, uint8_t, int8_t, int16_t, int,
+                   int64_t, float, double, float16, bfloat16) {}
+PD_REGISTER_KERNEL(fmax, GPU, ALL_LAYOUT, phi::FMaxKernel, float, double, int, float16, bfloat16, int64_t) {}
+PD_REGISTER_KERNEL(fmin, GPU, ALL_LAYOUT, phi::FMinKernel, float, double, int, float16, bfloat16, int64_t) {}
+PD_REGISTER_KERNEL(heaviside, GPU, ALL_LAYOUT, phi::HeavisideKernel, float, double, int, float16, bfloat16,
+                   int64_t) {}
+PD_REGISTER_KERNEL(fused_elemwise_activation, GPU, ALL_LAYOUT, phi::FusedElemwiseActivationKernel, float,
+                   double, float16) {}
 PD_REGISTER_KERNEL(fused_elemwise_add_activation, GPU, ALL_LAYOUT,
                    phi::FusedElemwiseAddActivationKernel, float, double, float16) {}

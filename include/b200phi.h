@@ -330,8 +330,21 @@ typedef enum {
   B200PHI_MAP_MIN_GRAD_Y = 52, /* in2 * T(in0 >= in1) */
   B200PHI_MAP_DIV_GRAD_Y = 53, /* -in0 * ((in1 / in2) / in2)  (dout, out, y) */
   /* two operands, out = in dtype */
+  B200PHI_MAP_HEAVISIDE = 54,  /* in0 == 0 ? in1 : T(in0 > 0)   ElementwiseHeavisideFunctor, elementwise_functor.h:614-619 */
   B200PHI_MAP_EQUAL_T = 56,    /* T(EQUAL(in0, in1)): the mask amax_grad / amin_grad count */
   B200PHI_MAP_SUB_EXP = 57,    /* exp(in0 - in1): logsumexp's second pass (gpu/logsumexp_kernel.cu:64-67) */
+  /* the other binary functors registered by kps/elementwise_kernel.cu:183-293 and
+   * legacy/kps/elementwise_kernel.cu:139-165 (funcs/elementwise_functor.h:190-290, 540-734, 844-963).
+   * 16-bit floats compute in fp32.  Integer REMAINDER / FLOOR_DIVIDE by zero give 0 (the
+   * reference asserts there).  FMAX / FMIN on INT32 go through fp32 and on INT64 through fp64, as
+   * the reference's specialisations do; integer POW is llrint(pow(double, double)); integer
+   * COPYSIGN goes through fp64. */
+  B200PHI_MAP_REMAINDER = 58,    /* result takes the divisor's sign */
+  B200PHI_MAP_FLOOR_DIVIDE = 59,
+  B200PHI_MAP_POW = 60,          /* elementwise_pow */
+  B200PHI_MAP_COPYSIGN = 61,
+  B200PHI_MAP_FMAX = 62,         /* NaN-ignoring maximum */
+  B200PHI_MAP_FMIN = 63,
   /* one operand, floating point, computed in fp32 for 16-bit dtypes (MPType); the Cuda*Functor
    * forms of funcs/activation_functor.h driven through ElementwiseKernel by
    * gpu/activation_kernel.cu.  p0 / p1 are the functor's attributes. */

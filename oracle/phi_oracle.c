@@ -673,6 +673,33 @@ EXPORT int phi_oracle_map(int op, int in_dtype, float p0, float p1, int arity, i
           break;
         case 56: r = eq; break;
         case 57: r = f32 ? (double)expf((float)a - (float)b) : exp(a - b); break;
+        /* the arithmetic binary functors of funcs/elementwise_functor.h:190-290,540-734,844-963,
+         * each in the operand's own precision */
+        case 54: r = (a == 0) ? b : (double)(a > 0); break;
+        case 58:
+          if (f32) { float fb = (float)b, res = fmodf((float)a, fb); if (res != 0 && ((res < 0) != (fb < 0))) res += fb; r = res; }
+          else { double res = fmod(a, b); if (res != 0 && ((res < 0) != (b < 0))) res += b; r = res; }
+          break;
+        case 59:
+          if (f32) {
+            float fa = (float)a, fb = (float)b;
+            if (fb == 0) { r = fa / fb; break; }
+            float mod = fmodf(fa, fb), dv = (fa - mod) / fb, fd;
+            if ((mod != 0) && ((fb < 0) != (mod < 0))) dv -= 1.0f;
+            if (dv != 0) { fd = floorf(dv); if (dv - fd > 0.5f) fd += 1.0f; } else fd = copysignf(0.0f, fa / fb);
+            r = fd;
+          } else {
+            if (b == 0) { r = a / b; break; }
+            double mod = fmod(a, b), dv = (a - mod) / b, fd;
+            if ((mod != 0) && ((b < 0) != (mod < 0))) dv -= 1.0;
+            if (dv != 0) { fd = floor(dv); if (dv - fd > 0.5) fd += 1.0; } else fd = copysign(0.0, a / b);
+            r = fd;
+          }
+          break;
+        case 60: r = f32 ? (double)powf((float)a, (float)b) : pow(a, b); break;
+        case 61: r = f32 ? (double)copysignf((float)a, (float)b) : copysign(a, b); break;
+        case 62: r = f32 ? (double)fmaxf((float)a, (float)b) : fmax(a, b); break;
+        case 63: r = f32 ? (double)fminf((float)a, (float)b) : fmin(a, b); break;
         default:
           r = f32 ? (double)map_act_f32(op, (float)a, p0, p1) : map_act_f64(op, a, p0, p1);
           break;
@@ -728,6 +755,24 @@ EXPORT int phi_oracle_map(int op, int in_dtype, float p0, float p1, int arity, i
         case 52: r = c * (a >= b); break;
         case 53: r = c == 0 ? 0 : -a * ((b / c) / c); break;
         case 56: r = a == b; break;
+        case 54: r = (a == 0) ? b : (a > 0); break;
+        case 58:  /* the remainder takes the divisor's sign; b == 0 is an assert in the reference */
+          if (b == 0) r = 0;
+          else { r = a % b; if (r != 0 && ((b ^ r) < 0)) r += b; }
+          break;
+        case 59:
+          if (b == 0) r = 0;
+          else if ((a < 0) != (b < 0)) { const int64_t q = a / b, rem = a % b; r = rem ? q - 1 : q; }
+          else r = a / b;
+          break;
+        case 60: r = (int64_t)pow((double)a, (double)b); break;       /* host branch of compute_pow */
+        case 61: r = (int64_t)copysign((double)a, (double)b); break;
+        case 62:  /* FMaxFunctor<int> goes through float, <int64_t> through double */
+          r = in_dtype == DT_INT32 ? (int64_t)lrintf(fmaxf((float)a, (float)b)) : (int64_t)llrint(fmax((double)a, (double)b));
+          break;
+        case 63:
+          r = in_dtype == DT_INT32 ? (int64_t)lrintf(fminf((float)a, (float)b)) : (int64_t)llrint(fmin((double)a, (double)b));
+          break;
         case 90: r = a < 0 ? -a : a; break;
         case 92: r = a > 0 ? a : 0; break;
         default: return 2;

@@ -123,11 +123,26 @@ int map_impl(int op, int rank, const int64_t* out_dims, const int64_t* const* in
       case 52: ot[n] = MinGradYFunctor<T>()(a, b, c); break;
       case 53: ot[n] = DivGradYFunctor<T>()(a, b, c); break;
       case 56: ot[n] = static_cast<T>(EqualFunctor<T>()(a, b)); break;
+      // the other binary functors of kps/elementwise_kernel.cu:183-293 (elementwise_functor.h)
+      case 54: ot[n] = ElementwiseHeavisideFunctor<T>()(a, b); break;
+      case 61: ot[n] = CopySignFunctor<T>()(a, b); break;
       case 57:
         if constexpr (std::is_floating_point<T>::value) ot[n] = std::exp(a - b);
         else return 2;
         break;
       default:
+        if constexpr (!std::is_same<T, bool>::value) {
+          bool done = true;
+          switch (op) {
+            case 58: ot[n] = RemainderFunctor<T>()(a, b); break;
+            case 59: ot[n] = FloorDivideFunctor<T>()(a, b); break;
+            case 60: ot[n] = ElementwisePowFunctor<T>()(a, b); break;
+            case 62: ot[n] = FMaxFunctor<T>()(a, b); break;
+            case 63: ot[n] = FMinFunctor<T>()(a, b); break;
+            default: done = false; break;
+          }
+          if (done) break;
+        }
         if constexpr (std::is_integral<T>::value) {
           switch (op) {
             case 32: ot[n] = BitwiseAndFunctor<T>()(a, b); break;

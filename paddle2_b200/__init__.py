@@ -17,5 +17,6 @@ from .ops import (  # noqa: F401  -- functor plug-ins on the broadcast engine (b
     greater_equal, greater_than, hardsigmoid, leaky_relu, less_equal, less_than, log, log10, log1p,
     log2, log_sigmoid, logical_and, logical_not, logical_or, logical_xor, mish, not_equal,
     reciprocal, relu6, rsqrt, sigmoid, silu, sin, softplus, softsign, sqrt, square, swish, tanh,
+    copysign, elementwise_pow, floor_divide, fmax, fmin, heaviside, remainder,
 )
 from ._lib import B200PhiError  # noqa: F401

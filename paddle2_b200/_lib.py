@@ -35,7 +35,8 @@ MAP_OPS = {
     "left_shift_arithmetic": 36, "left_shift_logic": 37, "right_shift_arithmetic": 38,
     "right_shift_logic": 39,
     "equal_mul": 48, "max_grad_x": 49, "max_grad_y": 50, "min_grad_x": 51, "min_grad_y": 52,
-    "div_grad_y": 53, "equal_t": 56, "sub_exp": 57,
+    "div_grad_y": 53, "heaviside": 54, "equal_t": 56, "sub_exp": 57,
+    "remainder": 58, "floor_divide": 59, "elementwise_pow": 60, "copysign": 61, "fmax": 62, "fmin": 63,
     "exp": 64, "log": 65, "sqrt": 66, "rsqrt": 67, "square": 68, "reciprocal": 69, "sin": 70,
     "cos": 71, "tanh": 72, "sigmoid": 73, "silu": 74, "leaky_relu": 75, "elu": 76,
     "softplus": 77, "floor": 78, "ceil": 79, "expm1": 80, "log1p": 81, "log2": 82, "log10": 83,

@@ -33,7 +33,8 @@ int run_map(const b200phi_map_desc* d, cudaStream_t stream) {
                      (op >= B200PHI_MAP_LOGICAL_AND && op <= B200PHI_MAP_LOGICAL_NOT) ||
                      (op >= B200PHI_MAP_BITWISE_AND && op <= B200PHI_MAP_RIGHT_SHIFT_LOGIC) ||
                      (op >= B200PHI_MAP_EQUAL_MUL && op <= B200PHI_MAP_DIV_GRAD_Y) ||
-                     op == B200PHI_MAP_EQUAL_T || op == B200PHI_MAP_SUB_EXP ||
+                     op == B200PHI_MAP_EQUAL_T || op == B200PHI_MAP_SUB_EXP || op == B200PHI_MAP_HEAVISIDE ||
+                     (op >= B200PHI_MAP_REMAINDER && op <= B200PHI_MAP_FMIN) ||
                      (op >= B200PHI_MAP_EXP && op <= B200PHI_MAP_RELU);
   if (!known) return set_error(B200PHI_INVALID_ARGUMENT, "map: unknown functor");
   if (d->arity != map_expected_arity(op))
@@ -64,6 +65,8 @@ int run_map(const b200phi_map_desc* d, cudaStream_t stream) {
   if (op <= B200PHI_MAP_GREATER_EQUAL) return map_compare(d, bp, stream);
   if (op <= B200PHI_MAP_LOGICAL_NOT) return map_logical(d, bp, stream);
   if (op <= B200PHI_MAP_RIGHT_SHIFT_LOGIC) return map_bitwise(d, bp, stream);
+  if (op == B200PHI_MAP_HEAVISIDE || (op >= B200PHI_MAP_REMAINDER && op <= B200PHI_MAP_FMIN))
+    return map_binary(d, bp, stream);
   if (op <= B200PHI_MAP_SUB_EXP) {
     if (op == B200PHI_MAP_SUB_EXP && !is_float_dtype(d->in_dtype))
       return set_error(B200PHI_UNSUPPORTED, "map: this functor needs a floating-point dtype");

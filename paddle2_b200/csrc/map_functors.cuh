@@ -131,6 +131,58 @@ struct MapF {
       else return static_cast<C>(-a * ((b / c) / c));
     } else if constexpr (kOp == B200PHI_MAP_EQUAL_T) {
       return static_cast<C>(phi_equal<T, C>(a, b));
+    } else if constexpr (kOp == B200PHI_MAP_HEAVISIDE) {
+      return a == C(0) ? b : static_cast<C>(a > C(0));
+    } else if constexpr (kOp == B200PHI_MAP_REMAINDER) {  // RemainderFunctor, :540-592
+      if constexpr (kInt) {
+        if (b == C(0)) return C(0);
+        C res = a % b;
+        if ((res != C(0)) && ((b ^ res) < C(0))) res += b;
+        return res;
+      } else {
+        C res = fmod(a, b);
+        if ((res != C(0)) && ((res < C(0)) != (b < C(0)))) res += b;
+        return res;
+      }
+    } else if constexpr (kOp == B200PHI_MAP_FLOOR_DIVIDE) {  // FloorDivideFunctor, :621-734
+      if constexpr (kInt) {
+        if (b == C(0)) return C(0);
+        if ((a < C(0)) != (b < C(0))) {
+          const C quot = a / b, rem = a % b;
+          return rem ? static_cast<C>(quot - 1) : quot;
+        }
+        return static_cast<C>(a / b);
+      } else {
+        if (b == C(0)) return static_cast<C>(a / b);  // the IEEE result
+        const C mod = fmod(a, b);
+        C div = (a - mod) / b;
+        if ((mod != C(0)) && ((b < C(0)) != (mod < C(0)))) div -= C(1);
+        C fd;
+        if (div != C(0)) {
+          fd = floor(div);
+          if (div - fd > C(0.5)) fd += C(1);
+        } else {
+          fd = copysign(C(0), a / b);
+        }
+        return fd;
+      }
+    } else if constexpr (kOp == B200PHI_MAP_POW) {  // ElementwisePowFunctor, :844-889 (device branch)
+      if constexpr (kInt) return static_cast<C>(llrint(pow(static_cast<double>(a), static_cast<double>(b))));
+      else return pow(a, b);
+    } else if constexpr (kOp == B200PHI_MAP_COPYSIGN) {  // copysign_func, :903-921
+      if constexpr (kInt) return static_cast<C>(copysign(static_cast<double>(a), static_cast<double>(b)));
+      else return copysign(a, b);
+    } else if constexpr (kOp == B200PHI_MAP_FMAX || kOp == B200PHI_MAP_FMIN) {  // :190-290
+      constexpr bool kMx = kOp == B200PHI_MAP_FMAX;
+      if constexpr (std::is_same<T, int32_t>::value) {
+        const float fa = static_cast<float>(a), fb = static_cast<float>(b);
+        return static_cast<C>(lrintf(kMx ? fmaxf(fa, fb) : fminf(fa, fb)));
+      } else if constexpr (kInt) {
+        const double fa = static_cast<double>(a), fb = static_cast<double>(b);
+        return static_cast<C>(llrint(kMx ? fmax(fa, fb) : fmin(fa, fb)));
+      } else {
+        return kMx ? fmax(a, b) : fmin(a, b);
+      }
     } else if constexpr (kOp == B200PHI_MAP_ABS) {
       return static_cast<C>(a < C(0) ? -a : a);
     } else if constexpr (kOp == B200PHI_MAP_RELU) {

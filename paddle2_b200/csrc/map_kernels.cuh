@@ -573,6 +573,7 @@ int map_compare(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
 int map_logical(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
 int map_bitwise(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
 int map_ternary(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
+int map_binary(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
 int map_unary(const b200phi_map_desc* d, const BcastPlan& bp, cudaStream_t s);
 
 }  // namespace b200phi

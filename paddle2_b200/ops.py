@@ -597,6 +597,15 @@ bitwise_and = _binary_map("bitwise_and")
 bitwise_or = _binary_map("bitwise_or")
 bitwise_xor = _binary_map("bitwise_xor")
 bitwise_not = _unary_map("bitwise_not")
+# the other arithmetic binaries of kps/elementwise_kernel.cu:183-293 (python/paddle/tensor/math.py:
+# remainder / mod, floor_divide, pow(x, Tensor), copysign, fmax, fmin, heaviside)
+remainder = _binary_map("remainder")
+floor_divide = _binary_map("floor_divide")
+elementwise_pow = _binary_map("elementwise_pow")
+copysign = _binary_map("copysign")
+fmax = _binary_map("fmax")
+fmin = _binary_map("fmin")
+heaviside = _binary_map("heaviside")
 
 
 def bitwise_left_shift(x, y, is_arithmetic=True):

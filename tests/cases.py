@@ -278,3 +278,43 @@ LOGSUMEXP_CASES = [
     ([37, 1000], [-1], False, "vocabulary-sized rows"),
     ([5, 4099], [-1], False, "ragged rows (scalar route)"),
 ]
+
+
+# ---- the arithmetic binary functors registered by kps/elementwise_kernel.cu:183-293 next to add ..
+# minimum: (name, dtypes as the reference registers them)
+ARITH_OPS = [
+    ("remainder", ["float32", "float64", "int32", "int64"]),
+    ("floor_divide", ["uint8", "int8", "int16", "int32", "int64", "float32", "float64"]),
+    ("elementwise_pow", ["float32", "float64", "int32", "int64"]),
+    ("copysign", ["bool", "uint8", "int8", "int16", "int32", "int64", "float32", "float64"]),
+    ("fmax", ["float32", "float64", "int32", "int64"]),
+    ("fmin", ["float32", "float64", "int32", "int64"]),
+    ("heaviside", ["float32", "float64", "int32", "int64"]),
+]
+ARITH_SHAPES = [([7, 33], [7, 33]), ([5, 1, 9], [4, 1]), ([3, 4], [1]), ([2, 3, 4, 5], [3, 1, 5]), ([40], [6, 40])]
+
+
+def arith_operands(rng, name, dtype, xs, ys):
+    """Operands inside each functor's domain: no integer division by zero (the reference asserts
+    there), small non-negative integer exponents, positive float bases for pow; zeros, sign
+    changes and exact ties elsewhere."""
+    dt = np.dtype(dtype)
+    if dt == np.bool_:
+        return rng.integers(0, 2, size=xs).astype(dt), rng.integers(0, 2, size=ys).astype(dt)
+    if np.issubdtype(dt, np.integer):
+        lo = 0 if dt == np.uint8 else -9
+        x = rng.integers(lo, 10, size=xs).astype(dt)
+        y = rng.integers(lo, 10, size=ys).astype(dt)
+        if name in ("remainder", "floor_divide"):
+            y[y == 0] = 3
+        if name == "elementwise_pow":
+            y = (np.abs(y) % 5).astype(dt)
+        return x, y
+    x = np.round(rng.standard_normal(xs) * 5, 1).astype(dt)
+    y = np.round(rng.standard_normal(ys) * 3, 1).astype(dt)
+    x.reshape(-1)[::7] = 0
+    if name == "elementwise_pow":
+        x = (np.abs(x) + 0.1).astype(dt)
+    if name in ("remainder", "floor_divide"):
+        y[y == 0] = dt.type(1.5)
+    return x, y

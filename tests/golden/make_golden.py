@@ -122,6 +122,15 @@ def main():
         store[f"shift_{dt}_x"], store[f"shift_{dt}_y"] = x, y
         for name in cases.SHIFT_OPS:
             store[f"shift_{dt}_{name}"] = O.map(name, [x, y], impl="ref")
+    # the arithmetic binary functors next to add .. minimum in kps/elementwise_kernel.cu:183-293:
+    # the reference's own Remainder / FloorDivide / ElementwisePow / CopySign / FMax / FMin /
+    # ElementwiseHeaviside functors over a small broadcast matrix
+    for name, dtypes in cases.ARITH_OPS:
+        for dt in dtypes:
+            for j, (xs, ys) in enumerate(cases.ARITH_SHAPES):
+                x, y = cases.arith_operands(np.random.default_rng(9500 + j), name, dt, xs, ys)
+                store[f"arith_{name}_{dt}_{j}_x"], store[f"arith_{name}_{dt}_{j}_y"] = x, y
+                store[f"arith_{name}_{dt}_{j}_out"] = O.map(name, [x, y], impl="ref")
     # mixed-precision add (MultiPrecisionAddFunctor): fp32 + bf16 / fp16 bit patterns
     rng = np.random.default_rng(9000)
     x = cases.map_operand(rng, "float32", [33, 257])

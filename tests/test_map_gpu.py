@@ -203,3 +203,44 @@ def test_unary_into_a_larger_shape():
         assert torch.allclose(got, torch.exp(src).expand(shape), rtol=1e-6)
         gotb = ops._map("logical_not", [src.cuda()], out_shape=list(shape)).cpu()
         assert torch.equal(gotb, (src == 0).expand(shape))
+
+
+@pytest.mark.parametrize("name,dtypes", cases.ARITH_OPS)
+def test_arith_binary_functors(oracle, golden, name, dtypes):
+    """The arithmetic binaries the reference registers next to add .. minimum
+    (kps/elementwise_kernel.cu:183-293): golden arrays from its own functors.  Integer results,
+    copysign / fmax / fmin / heaviside / remainder / floor_divide are bit-exact; pow within 2 ulp
+    (device pow vs libm)."""
+    for dt in dtypes:
+        for j in range(len(cases.ARITH_SHAPES)):
+            x, y = golden[f"arith_{name}_{dt}_{j}_x"], golden[f"arith_{name}_{dt}_{j}_y"]
+            want = golden[f"arith_{name}_{dt}_{j}_out"]
+            got = G.to_np(getattr(pb, name)(G.to_dev(x), G.to_dev(y)))
+            assert got.dtype == want.dtype and got.shape == want.shape, (name, dt, j)
+            if name == "elementwise_pow" and dt.startswith("float"):
+                np.testing.assert_allclose(got, want, rtol=4e-7 if dt == "float32" else 1e-15)
+            else:
+                assert np.array_equal(got, want, equal_nan=True), (name, dt, j)
+                if dt.startswith("float") and name not in ("fmax", "fmin"):   # signed zeros too (fmax(+0,-0) is open)
+                    assert np.array_equal(np.signbit(got), np.signbit(want)), (name, dt, j)
+
+
+@pytest.mark.parametrize("tdt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("name", ["remainder", "floor_divide", "elementwise_pow", "copysign", "fmax", "fmin", "heaviside"])
+def test_arith_binary_16bit_and_large(oracle, name, tdt):
+    """16-bit floats compute in fp32 and round once (the reference's float16 / bfloat16
+    specialisations); a large aligned shape and a channel broadcast exercise the vector paths."""
+    rng = np.random.default_rng(17)
+    for xs, ys in (((257, 1032), (257, 1032)), ((64, 8, 196), (8, 1))):
+        x32, y32 = cases.arith_operands(rng, name, "float32", xs, ys)
+        xt, yt = torch.from_numpy(x32).cuda().to(tdt), torch.from_numpy(y32).cuda().to(tdt)
+        xw, yw = xt.float().cpu().numpy(), yt.float().cpu().numpy()
+        if name in ("remainder", "floor_divide"):
+            yw[yw == 0] = 1.5
+            yt = torch.from_numpy(yw).cuda().to(tdt)
+        want = torch.from_numpy(oracle.map(name, [xw, yw])).to(tdt)
+        got = getattr(pb, name)(xt, yt).cpu()
+        if name == "elementwise_pow":
+            torch.testing.assert_close(got.float(), want.float(), rtol=1e-2, atol=0)
+        else:
+            assert torch.equal(got, want), (name, tdt, xs)

@@ -257,3 +257,21 @@ def test_shift_port_matches_golden(oracle, golden):
         x, y = golden[f"shift_{dt}_x"], golden[f"shift_{dt}_y"]
         for name in cases.SHIFT_OPS:
             assert np.array_equal(oracle.map(name, [x, y]), golden[f"shift_{dt}_{name}"]), (dt, name)
+
+
+@pytest.mark.parametrize("name,dtypes", cases.ARITH_OPS)
+def test_arith_binary_port_matches_golden(oracle, golden, name, dtypes):
+    """remainder / floor_divide / elementwise_pow / copysign / fmax / fmin / heaviside: the C port
+    against the arrays the reference's own functors produced, bit for bit."""
+    for dt in dtypes:
+        for j in range(len(cases.ARITH_SHAPES)):
+            x, y = golden[f"arith_{name}_{dt}_{j}_x"], golden[f"arith_{name}_{dt}_{j}_y"]
+            want = golden[f"arith_{name}_{dt}_{j}_out"]
+            got = oracle.map(name, [x, y])
+            assert got.dtype == want.dtype and got.shape == want.shape
+            if name in ("fmax", "fmin"):   # fmax(+0, -0) may be either zero (IEEE 754 leaves it open)
+                assert np.array_equal(got, want), (name, dt, j)
+            else:
+                assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, j)
+            if oracle.have_ref():
+                assert np.array_equal(oracle.map(name, [x, y], impl="ref").view(np.uint8), want.view(np.uint8))
