@@ -38,7 +38,7 @@ inline void ShardedReduce(const phi::GPUContext& dev_ctx, distributed::NCCLCommC
   d.x = x.data();
   d.out = out->data();
   DenseTensor scratch;
-  const size_t ws = b200phi_reduce_workspace(&d);
+  const size_t ws = b200phi_sharded_reduce_workspace(&d);  // + the fp32 partial for 16-bit sums
   if (ws > 0) {
     scratch.Resize({static_cast<int64_t>(ws)});
     d.workspace = dev_ctx.template Alloc<uint8_t>(&scratch);

@@ -85,6 +85,17 @@ static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, c
     if (rc != B200PHI_OK) return rc;
     return run_reduce_stage(&d2, 1, stream);
   }
+  if (plan.red_numel == 1 && plan.in_dtype == plan.out_dtype && d->op <= B200PHI_AMIN &&
+      d->op != B200PHI_ANY && d->op != B200PHI_ALL) {
+    // nothing to combine and nothing to convert (reduce_function.h:1087-1092 runs an identity
+    // transform kernel here): a device-to-device copy on the caller's stream
+    if (d->out != d->x) {
+      cudaError_t e = cudaMemcpyAsync(d->out, d->x, static_cast<size_t>(plan.in_numel) * dtype_size(plan.in_dtype),
+                                      cudaMemcpyDeviceToDevice, stream);
+      if (e != cudaSuccess) return cuda_status(e);
+    }
+    return B200PHI_OK;
+  }
   ReduceArgs a{&plan, d->x, d->out, d->workspace, stream};
   const bool tiled = plan.kind == kTiledKeep || plan.kind == kTiledRed;
   switch (d->op) {

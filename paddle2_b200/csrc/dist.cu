@@ -179,9 +179,19 @@ int run_sharded_reduce(const b200phi_reduce_desc* d, long long global_count, voi
     local.workspace_bytes = d->workspace_bytes - wide_bytes;
   }
 
-  rc = run_reduce(&local, stream);
-  if (rc != B200PHI_OK) return rc;
-  ncclResult_t r = a->AllReduce(partial, partial, static_cast<size_t>(plan.out_numel), ty, op,
+  // A shard with nothing to reduce locally (one row: the Partial -> Replicate reshard of an
+  // already-reduced tensor) is all-reduced straight out of x: no copy in front of the collective.
+  const bool plain_op = d->op == B200PHI_SUM || d->op == B200PHI_MEAN || d->op == B200PHI_MAX ||
+                        d->op == B200PHI_MIN || d->op == B200PHI_PROD || d->op == B200PHI_AMAX ||
+                        d->op == B200PHI_AMIN;
+  const void* send = partial;
+  if (plan.red_numel == 1 && plain_op && plan.in_dtype == partial_dtype) {
+    send = d->x;
+  } else {
+    rc = run_reduce(&local, stream);
+    if (rc != B200PHI_OK) return rc;
+  }
+  ncclResult_t r = a->AllReduce(send, partial, static_cast<size_t>(plan.out_numel), ty, op,
                                 static_cast<ncclComm_t>(comm), stream);
   if (r != ncclSuccess) return nccl_status(a, r);
 
