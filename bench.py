@@ -37,7 +37,7 @@ ROWS, COLS = 524288, 4096                      # 8 GiB of fp32 per GPU
 ALGO_BYTES = ROWS * COLS * 4 + COLS * 4        # 8,589,950,976 B per GPU per step
 METRIC = "phi_global_sum_fp32_axis0_hbm_gbs"
 UNIT = "GB/s"
-DEFAULT_COLLECTIVE = "nccl"
+DEFAULT_COLLECTIVE = "p2p"
 WORKLOAD = "C5 global paddle.sum fp32 axis=0, [524288,4096] per GPU (8 GiB)"   # both arms
 
 
