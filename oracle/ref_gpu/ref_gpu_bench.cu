@@ -3,6 +3,14 @@
 // /root/reference and compiled for sm_100a ("the kernel to beat"):
 //   ReduceAnyKernel        paddle/phi/kernels/funcs/reduce_function.h:573-699   (C1, last-dim reduce)
 //   ReduceHigherDimKernel  paddle/phi/kernels/funcs/reduce_function.h:706-788   (C5-like, two passes)
+//   ArgCUDAKernel          paddle/phi/kernels/gpu/arg_min_max_kernel.cu:58-83     (C3a / C3b; the .cu is
+//                          included whole with PD_REGISTER_KERNEL neutralised: no registry to link)
+//   FusedElemwiseAndActBroadcast2CUDAKernel  funcs/elementwise/elementwise_op_function.h:273-350  (C2, the
+//                          2018 fused kernel: grid = 64 CTAs; its header needs <cblas.h>, taken from
+//                          the vendored third_party/openblas)
+//   the paddle.var composite (python/paddle/tensor/stat.py:184-197) as its data launches: mean
+//                          (ReduceAnyKernel), subtract (VectorizedBroadcastKernel), pow 2
+//                          (VectorizedElementwiseKernel), sum (ReduceAnyKernel), divide            (C4)
 // launched with the geometry ReduceConfig would choose (SetBlockDimForReduceAny :434-498,
 // SetBlockDimForHigher :504-531), re-derived here by those formulas because ReduceConfig::Run
 // needs a live GPUContext (libphi) that cannot be linked in this image.
@@ -11,6 +19,15 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include "paddle/phi/core/kernel_registry.h"
+// no kernel registry to link against: the registration blocks of the reference .cu included below
+// become unused functions (their bodies only touch `kernel`)
+#undef PD_REGISTER_KERNEL
+#define PD_REGISTER_KERNEL(name, backend, layout, fn, ...) \
+  [[maybe_unused]] static void ref_gpu_bench_unused_reg_##name(phi::Kernel* kernel)
+#include "paddle/phi/kernels/gpu/arg_min_max_kernel.cu"
+#include "paddle/phi/kernels/funcs/elementwise/elementwise_op_function.h"
+#include "paddle/phi/kernels/funcs/compound_functors.h"
 #include "paddle/phi/kernels/funcs/reduce_function.h"
 #include "paddle/phi/kernels/funcs/broadcast_function.h"
 #include "paddle/phi/kernels/funcs/elementwise_functor.h"
@@ -164,6 +181,133 @@ int main() {
     printf("REF C2 add + relu, two launches as the reference runs them        %8.2f us  %7.1f GB/s (of the fused op's algorithmic bytes)\n",
            ms_both * 1e3, 1644167424.0 / ms_both / 1e6);
     cudaFree(x); cudaFree(y); cudaFree(t); cudaFree(out);
+  }
+  // ---------------- C2 again: the 2018 fused kernel, as FusedElemwiseAndActBroadcast2CUDA launches it --
+  {
+    using T = float;
+    const int pre = 256, n = 64, post = 112 * 112;
+    const int64_t numel = (int64_t)pre * n * post;
+    T *x, *y, *out;
+    CK(cudaMalloc(&x, numel * 4)); CK(cudaMalloc(&out, numel * 4)); CK(cudaMalloc(&y, n * 4));
+    fill<<<1184, 256>>>(x, numel);
+    fill<<<1, 64>>>(y, n);
+    using Compound = phi::funcs::UnaryCompoundFunctor<T, phi::funcs::ReluFunctor<T>, phi::funcs::AddFunctor<T>>;
+    const int block_size = std::min(ELEMWISE_MAX_BLOCK_DIM, pre * post), grid_size = n;
+    float ms = time_it([&] {
+      phi::funcs::FusedElemwiseAndActBroadcast2CUDAKernel<T, Compound, true, false, true>
+          <<<grid_size, block_size>>>(x, y, Compound(phi::funcs::ReluFunctor<T>(), phi::funcs::AddFunctor<T>()), pre, n, post, out, nullptr);
+    }, 5);
+    printf("REF C2 FusedElemwiseAndActBroadcast2CUDAKernel relu(x+y) (grid %d x %d)  %8.2f us  %7.1f GB/s\n", grid_size,
+           block_size, ms * 1e3, 1644167424.0 / ms / 1e6);
+    cudaFree(x); cudaFree(y); cudaFree(out);
+  }
+  // ---------------- C3: ArgCUDAKernel, argmax over the last axis of [8192, 32000] ------------------------
+  {
+    const int64_t height = 8192, width = 32000, post = 1;
+    {
+      using T = int64_t;
+      T* x; int64_t* idx;
+      CK(cudaMalloc(&x, height * width * 8)); CK(cudaMalloc(&idx, height * 8));
+      fill<<<1184, 256>>>(reinterpret_cast<float*>(x), height * width * 2);  // any bit pattern will do
+      float ms = time_it([&] {
+        phi::ArgCUDAKernel<T, int64_t, cub::ArgMax, 1024><<<(int)height, 1024>>>(
+            height, width, post, cub::ArgMax(), std::numeric_limits<T>::lowest(), x, idx);
+      }, 10);
+      printf("REF C3a ArgCUDAKernel argmax int64 [8192,32000] (grid 8192 x 1024)  %8.2f us  %7.1f GB/s  (max is a second pass of the same size)\n",
+             ms * 1e3, (double)(height * width * 8 + height * 8) / ms / 1e6);
+      cudaFree(x); cudaFree(idx);
+    }
+    {
+      using T = phi::dtype::bfloat16;
+      T* x; int64_t* idx;
+      CK(cudaMalloc(&x, height * width * 2)); CK(cudaMalloc(&idx, height * 8));
+      CK(cudaMemset(x, 0x3c, height * width * 2));
+      float ms = time_it([&] {
+        phi::ArgCUDAKernel<T, int64_t, cub::ArgMax, 1024><<<(int)height, 1024>>>(
+            height, width, post, cub::ArgMax(), std::numeric_limits<T>::lowest(), x, idx);
+      }, 10);
+      printf("REF C3b ArgCUDAKernel argmax bf16 [8192,32000] (grid 8192 x 1024)   %8.2f us  %7.1f GB/s\n", ms * 1e3,
+             (double)(height * width * 2 + height * 8) / ms / 1e6);
+      cudaFree(x); cudaFree(idx);
+    }
+  }
+  // ---------------- C4: paddle.var(x, axis=-1) of bf16 [16384, 8192] as the composite's data launches ----
+  {
+    using T = phi::dtype::bfloat16;
+    const int rows = 16384, cols = 8192;
+    const int64_t numel = (int64_t)rows * cols;
+    T *x, *u, *d, *sq, *s, *v;
+    CK(cudaMalloc(&x, numel * 2)); CK(cudaMalloc(&d, numel * 2)); CK(cudaMalloc(&sq, numel * 2));
+    CK(cudaMalloc(&u, rows * 2)); CK(cudaMalloc(&s, rows * 2)); CK(cudaMalloc(&v, rows * 2));
+    CK(cudaMemset(x, 0x3c, numel * 2));
+    // mean / sum: ReduceAnyKernel, last-dim mode, geometry of SetBlockDimForReduceAny (block 128, grid rows)
+    using RO = kps::AddFunctor<float>;
+    using TO = kps::IdentityFunctor<T, float>;
+    dim3 rblock(128, 1, 1), rgrid(rows, 1, 1);
+    kps::DimConfig rdim(rgrid.x, rgrid.y, rgrid.z, rblock.x, rblock.y, 0);
+    rdim.SetRem(cols % rblock.x, 0, 0);
+    OneDimIndexCal reduce_cal(1), left_cal(cols);
+    RO reducer;
+    auto mean = [&] {
+      phi::funcs::ReduceAnyKernel<T, T, float, RO, TO, OneDimIndexCal><<<rgrid, rblock>>>(
+          x, u, reducer, TO(), reducer.initial(), cols, rows, true, reduce_cal, left_cal, rdim, true, nullptr, false);
+    };
+    auto sum = [&] {
+      phi::funcs::ReduceAnyKernel<T, T, float, RO, TO, OneDimIndexCal><<<rgrid, rblock>>>(
+          sq, s, reducer, TO(), reducer.initial(), cols, rows, true, reduce_cal, left_cal, rdim, false, nullptr, false);
+    };
+    // subtract: x [rows, cols] - u [rows, 1] through the broadcast kernel (dims reversed, fastest first)
+    constexpr int VecSize = 4;
+    const int threads = 512;
+    const int blocks = (int)(((numel + VecSize - 1) / VecSize + threads - 1) / threads);
+    std::vector<int64_t> out_dims = {cols, rows}, x_dims = {cols, rows}, u_dims = {1, rows};
+    phi::Array<const char* __restrict__, 2> ins;
+    ins[0] = reinterpret_cast<const char*>(x);
+    ins[1] = reinterpret_cast<const char*>(u);
+    phi::Array<T*, 1> outs;
+    outs[0] = d;
+    phi::Array<bool, 2> use_bc;
+    use_bc[0] = false;
+    use_bc[1] = true;
+    phi::Array<kps::details::BroadcastConfig, 2> configs;
+    configs[0] = kps::details::BroadcastConfig(out_dims, x_dims, 2);
+    configs[1] = kps::details::BroadcastConfig(out_dims, u_dims, 2);
+    const int main_offset = (int)((numel / (VecSize * threads)) * VecSize * threads);
+    const int tail_tid = (int)(numel % (VecSize * threads));
+    auto sub = [&] {
+      phi::funcs::VectorizedBroadcastKernel<phi::funcs::SubtractFunctor<T>, T, 2, 1, VecSize, phi::funcs::kMixed>
+          <<<blocks, threads>>>(ins, outs, use_bc, (uint32_t)numel, configs, main_offset, tail_tid, VecSize,
+                                phi::funcs::SubtractFunctor<T>());
+    };
+    // pow(., 2): a unary elementwise kernel (MultiplyFunctor on (d, d) reads the tensor twice through
+    // L2; the reference's pow kernel is unary, so the unary square functor is the fair stand-in)
+    phi::Array<const char* __restrict__, 1> ins2;
+    ins2[0] = reinterpret_cast<const char*>(d);
+    phi::Array<T*, 1> outs2;
+    outs2[0] = sq;
+    auto pow2 = [&] {
+      phi::funcs::VectorizedElementwiseKernel<T, kps::SquareFunctor<T, T>, 1, 1, VecSize>
+          <<<blocks, threads>>>(ins2, outs2, numel, (int64_t)main_offset, VecSize, kps::SquareFunctor<T, T>());
+    };
+    // divide by (n - 1): [rows] elements, one small elementwise launch
+    phi::Array<const char* __restrict__, 1> ins3;
+    ins3[0] = reinterpret_cast<const char*>(s);
+    phi::Array<T*, 1> outs3;
+    outs3[0] = v;
+    const int blocks3 = (rows / VecSize + threads - 1) / threads;
+    auto div = [&] {
+      phi::funcs::VectorizedElementwiseKernel<T, kps::DivideFunctor<T, T>, 1, 1, VecSize>
+          <<<blocks3, threads>>>(ins3, outs3, rows, (int64_t)((rows / (VecSize * threads)) * VecSize * threads), VecSize,
+                                 kps::DivideFunctor<T, T>(cols - 1));
+    };
+    const float t_mean = time_it(mean, 10), t_sub = time_it(sub, 10), t_pow = time_it(pow2, 10),
+                t_sum = time_it(sum, 10), t_div = time_it(div, 10);
+    const float t_all = time_it([&] { mean(); sub(); pow2(); sum(); div(); }, 10);
+    printf("REF C4 var composite bf16 [16384,8192]: mean %.1f us, subtract %.1f us, pow2 %.1f us, sum %.1f us, divide %.1f us\n",
+           t_mean * 1e3, t_sub * 1e3, t_pow * 1e3, t_sum * 1e3, t_div * 1e3);
+    printf("REF C4 var composite, the five launches back to back   %8.2f us  %7.1f GB/s (of the one-read algorithmic bytes, 268,500,992)\n",
+           t_all * 1e3, 268500992.0 / t_all / 1e6);
+    cudaFree(x); cudaFree(d); cudaFree(sq); cudaFree(u); cudaFree(s); cudaFree(v);
   }
   printf("done\n");
   return 0;

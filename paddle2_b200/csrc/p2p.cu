@@ -88,7 +88,8 @@ __device__ __forceinline__ V16 ld_volatile16(const void* p) {
 // per round.  Indexing of a.base[] is by unrolled constant index only (a run-time index would
 // put the argument struct in local memory).
 template <typename P, typename Acc, typename Op>
-__global__ void __launch_bounds__(kBlock) p2p_exchange_kernel(const ExchangeArgs a, const Epilogue ep) {
+__global__ void __launch_bounds__(kBlock)
+    p2p_exchange_kernel(const __grid_constant__ ExchangeArgs a, const __grid_constant__ Epilogue ep) {
   constexpr int VE = 16 / sizeof(P);
   __shared__ int s_timeout;
   // the reduce in front of this kernel must have finished and its stores be visible
