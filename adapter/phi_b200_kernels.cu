@@ -10,7 +10,7 @@
 //   paddle/phi/kernels/legacy/kps/elementwise_kernel.cu (add_raw ... elementwise_pow_raw)
 //   paddle/phi/kernels/fusion/gpu/fused_elemwise_activation_kernel.cu (fused_elemwise_activation, fused_elemwise_add_activation)
 // EVERY kernel name those files register is registered here (tests/test_adapter_compile.py checks the
-// registrar symbols one by one), minus the complex64/128 instantiations.
+// registrar symbols one by one); of the dtype lists only complex multiply / divide are left out.
 // (those files are globbed by paddle/phi/kernels/CMakeLists.txt:33-34, so swapping the
 // file swaps the kernel).  Here it is compile-checked against the
 // reference headers (tests/test_adapter_compile.py); it cannot be linked without libphi.
@@ -335,21 +335,23 @@ void FusedElemwiseAddActivationKernel(const Context& dev_ctx, const DenseTensor&
 }  // namespace phi
 
 // ---- registrations: same names, backend GPU (KPS folds into GPU, backend.h:140-148) ------------
-// dtype lists follow kps/reduce_kernel.cu:302-410 and reduce_sum_kernel.cc:60-77 minus the
-// complex types, which this library does not implement ("what stays").
+// dtype lists follow kps/reduce_kernel.cu:302-410 and reduce_sum_kernel.cc:60-77, complex64/128
+// (sum, mean) and float8 (max) included.
 using float16 = phi::dtype::float16;
 using bfloat16 = phi::dtype::bfloat16;
+using complex64 = ::phi::dtype::complex<float>;
+using complex128 = ::phi::dtype::complex<double>;
 
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, phi::SumRawKernel, bool, float, double, float16,
-                   bfloat16, int16_t, int, int64_t, uint8_t, int8_t) {
+                   bfloat16, int16_t, int, int64_t, uint8_t, int8_t, complex64, complex128) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
 }
 PD_REGISTER_KERNEL(mean_raw, GPU, ALL_LAYOUT, phi::MeanRawKernel, float, double, bool, float16,
-                   bfloat16, int, int64_t) {}
+                   bfloat16, int, int64_t, complex64, complex128) {}
 PD_REGISTER_KERNEL(max_raw, GPU, ALL_LAYOUT, phi::MaxRawKernel, float, double, int, int64_t, float16,
                    bfloat16) {}
 PD_REGISTER_KERNEL(max, GPU, ALL_LAYOUT, phi::MaxKernel, float, double, int, int64_t, float16,
-                   bfloat16) {}
+                   bfloat16, phi::dtype::float8_e4m3fn, phi::dtype::float8_e5m2) {}
 PD_REGISTER_KERNEL(min_raw, GPU, ALL_LAYOUT, phi::MinRawKernel, float, double, int, int64_t, float16,
                    bfloat16) {}
 PD_REGISTER_KERNEL(amax_raw, GPU, ALL_LAYOUT, phi::AMaxRawKernel, float, double, int, int64_t) {}
@@ -371,11 +373,12 @@ PD_REGISTER_KERNEL(argmin, GPU, ALL_LAYOUT, phi::ArgMinKernel, float16, bfloat16
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
 }
 // kps/elementwise_kernel.cu:183-381 and legacy/kps/elementwise_kernel.cu:60-165, dtype for dtype
-// (minus complex64/128)
-#define B200_ADD_TYPES float, double, int16_t, int, bool, uint8_t, int8_t, int64_t, float16, bfloat16
+// (complex64/128 for add / subtract, which are component-wise; multiply and divide are not and stay
+// with the reference for those two dtypes)
+#define B200_ADD_TYPES float, double, int16_t, int, bool, uint8_t, int8_t, int64_t, float16, bfloat16, complex64, complex128
 #define B200_DIV_TYPES float, double, int8_t, uint8_t, int16_t, int, int64_t, bool, float16, bfloat16
 #define B200_MUL_TYPES float, double, int, int64_t, bool, float16, bfloat16
-#define B200_SUB_TYPES float, double, int16_t, int, int64_t, float16, bfloat16
+#define B200_SUB_TYPES float, double, int16_t, int, int64_t, float16, bfloat16, complex64, complex128
 #define B200_NUM_TYPES float, double, int, int64_t, float16, bfloat16
 #define B200_FDIV_TYPES uint8_t, int8_t, int16_t, int, int64_t, float, double, float16, bfloat16
 PD_REGISTER_KERNEL(add, GPU, ALL_LAYOUT, phi::AddKernel, B200_ADD_TYPES) {}

@@ -50,8 +50,15 @@ typedef enum {
   B200PHI_INT64 = 9,
   B200PHI_FLOAT32 = 10,
   B200PHI_FLOAT64 = 11,
+  /* SUM / MEAN reductions and ADD / SUBTRACT only (kps/reduce_kernel.cu:382-397,
+   * kps/elementwise_kernel.cu:304-381): component-wise on the (re, im) pairs */
+  B200PHI_COMPLEX64 = 12,
+  B200PHI_COMPLEX128 = 13,
   B200PHI_FLOAT16 = 15,
-  B200PHI_BFLOAT16 = 16
+  B200PHI_BFLOAT16 = 16,
+  /* MAX / AMAX reductions only (the reference registers `max` for them, kps/reduce_kernel.cu:345-355) */
+  B200PHI_FLOAT8_E4M3FN = 17,
+  B200PHI_FLOAT8_E5M2 = 18
 } b200phi_dtype;
 
 typedef enum {

@@ -19,6 +19,7 @@ NOALLOC_SCRATCH_BYTES = 4 << 20  # B200PHI_NOALLOC_SCRATCH_BYTES
 # phi::DataType values (paddle/phi/common/data_type.h:42-85)
 UNDEFINED, BOOL, UINT8, INT8, INT16, INT32, INT64 = 0, 1, 2, 3, 5, 7, 9
 FLOAT32, FLOAT64, FLOAT16, BFLOAT16 = 10, 11, 15, 16
+COMPLEX64, COMPLEX128, FLOAT8_E4M3FN, FLOAT8_E5M2 = 12, 13, 17, 18
 
 SUM, MEAN, MAX, MIN, PROD, ANY, ALL, AMAX, AMIN = range(9)
 SUM_ABS, SUM_SQUARE, L2_NORM, MAX_ABS, MIN_ABS, COUNT_NONZERO = range(9, 15)

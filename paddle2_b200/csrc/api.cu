@@ -71,6 +71,31 @@ static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, c
     if (reinterpret_cast<uintptr_t>(d->workspace) % 256 != 0)
       return set_error(B200PHI_INVALID_ARGUMENT, "workspace must be 256-byte aligned");
   }
+  if (plan.kind == kCastFirst) {
+    // the reference's own Cast pre-pass (gpu/reduce.h:48-69): x -> scratch in the output dtype
+    // (a reduce over an appended extent-1 dim is an element-wise cast), then the reduce proper
+    unsigned char* ws = static_cast<unsigned char*>(d->workspace);
+    b200phi_reduce_desc c = b200phi_reduce_desc();
+    c.op = B200PHI_SUM;
+    c.in_dtype = d->in_dtype;
+    c.out_dtype = plan.ts_tmp_dtype;
+    c.rank = 2;
+    c.dims[0] = plan.in_numel;
+    c.dims[1] = 1;
+    c.naxes = 1;
+    c.axes[0] = 1;
+    c.x = d->x;
+    c.out = ws;
+    rc = run_reduce_stage(&c, 1, stream);
+    if (rc != B200PHI_OK) return rc;
+    b200phi_reduce_desc r = *d;
+    r.in_dtype = plan.ts_tmp_dtype;
+    r.out_dtype = plan.ts_tmp_dtype;
+    r.x = ws;
+    r.workspace = ws + plan.ts_tmp_bytes;
+    r.workspace_bytes = plan.ts_ws2_bytes;
+    return run_reduce_stage(&r, 0, stream);
+  }
   if (plan.kind == kTwoStage) {
     // one reduced dim peeled by a streaming row / column kernel into the scratch, then the rest
     // (itself possibly two stages): [A,K,B] -> row sums of [A*K, B], then the column reduce of [A, K]

@@ -23,6 +23,7 @@ namespace b200phi {
 int set_error(int code, const std::string& msg);
 int cuda_status(cudaError_t e);
 int current_sm_count();
+int run_elementwise(const b200phi_elementwise_desc* d, cudaStream_t stream);
 
 // ---- compute type ------------------------------------------------------------------
 template <typename T>
@@ -706,7 +707,41 @@ static int launch_typed(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
   return launch_runtime<T>(d, bp, inter, s);
 }
 
+// complex64 / complex128: add and subtract are component-wise, so the call is re-issued on the
+// float lanes -- every operand and the output get a trailing dim of 2 (the (re, im) pair), and a
+// lower-rank operand placed with the legacy `axis` offset is first padded with trailing 1s so
+// that plain right-aligned broadcasting puts it where `axis` would (common_shape.h:35-92).
+static int run_elementwise_complex(const b200phi_elementwise_desc* d, cudaStream_t stream) {
+  if (!d) return set_error(B200PHI_INVALID_ARGUMENT, "null descriptor");
+  if ((d->binary != B200PHI_ADD && d->binary != B200PHI_SUBTRACT) || d->act != B200PHI_ACT_NONE ||
+      d->arity < 2 || d->intermediate_out != nullptr)
+    return set_error(B200PHI_UNSUPPORTED, "complex dtypes: add and subtract only");
+  if (d->out_rank >= B200PHI_MAX_RANK)
+    return set_error(B200PHI_UNSUPPORTED, "complex dtypes: rank 9 is not built");
+  b200phi_elementwise_desc f = *d;
+  f.dtype = d->dtype == B200PHI_COMPLEX64 ? B200PHI_FLOAT32 : B200PHI_FLOAT64;
+  f.axis = -1;
+  int max_rank = 0;
+  for (int i = 0; i < d->arity; ++i) max_rank = d->in[i].rank > max_rank ? d->in[i].rank : max_rank;
+  for (int i = 0; i < d->arity; ++i) {
+    b200phi_tensor_view& v = f.in[i];
+    int rank = d->in[i].rank;
+    if (i < 2 && d->axis >= 0 && rank < max_rank) {  // legacy offset: pad with trailing 1s
+      const int trailing = max_rank - d->axis - rank;
+      if (trailing < 0) return set_error(B200PHI_INVALID_ARGUMENT, "Broadcast dimension mismatch.");
+      for (int k = 0; k < trailing; ++k) v.dims[rank++] = 1;
+    }
+    if (rank >= B200PHI_MAX_RANK) return set_error(B200PHI_UNSUPPORTED, "complex dtypes: rank 9 is not built");
+    v.dims[rank++] = 2;
+    v.rank = rank;
+  }
+  f.out_dims[f.out_rank++] = 2;
+  return run_elementwise(&f, stream);
+}
+
 int run_elementwise(const b200phi_elementwise_desc* d, cudaStream_t stream) {
+  if (d && (d->dtype == B200PHI_COMPLEX64 || d->dtype == B200PHI_COMPLEX128))
+    return run_elementwise_complex(d, stream);
   BcastPlan bp;
   std::string err;
   int rc = plan_broadcast(d, &bp, &err);

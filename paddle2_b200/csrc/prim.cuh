@@ -7,6 +7,7 @@
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -67,6 +68,18 @@ __device__ __forceinline__ __half ldg_scalar(const __half* p) {
   return __ushort_as_half(u);
 }
 template <>
+__device__ __forceinline__ __nv_fp8_e4m3 ldg_scalar(const __nv_fp8_e4m3* p) {
+  __nv_fp8_e4m3 v;
+  v.__x = __ldg(reinterpret_cast<const unsigned char*>(p));
+  return v;
+}
+template <>
+__device__ __forceinline__ __nv_fp8_e5m2 ldg_scalar(const __nv_fp8_e5m2* p) {
+  __nv_fp8_e5m2 v;
+  v.__x = __ldg(reinterpret_cast<const unsigned char*>(p));
+  return v;
+}
+template <>
 __device__ __forceinline__ Bool8 ldg_scalar(const Bool8* p) {
   Bool8 b;
   b.v = __ldg(reinterpret_cast<const uint8_t*>(p));
@@ -89,6 +102,14 @@ struct Cvt<Acc, __nv_bfloat16> {
 template <typename Acc>
 struct Cvt<Acc, __half> {
   static __device__ __forceinline__ Acc to(__half v) { return static_cast<Acc>(__half2float(v)); }
+};
+template <typename Acc>
+struct Cvt<Acc, __nv_fp8_e4m3> {
+  static __device__ __forceinline__ Acc to(__nv_fp8_e4m3 v) { return static_cast<Acc>(static_cast<float>(v)); }
+};
+template <typename Acc>
+struct Cvt<Acc, __nv_fp8_e5m2> {
+  static __device__ __forceinline__ Acc to(__nv_fp8_e5m2 v) { return static_cast<Acc>(static_cast<float>(v)); }
 };
 template <typename Acc>
 struct Cvt<Acc, Bool8> {
@@ -437,6 +458,12 @@ __device__ __noinline__ void store_result_slow(void* out, int out_dtype, long lo
       break;
     case 16:
       reinterpret_cast<__nv_bfloat16*>(out)[idx] = __float2bfloat16_rn(static_cast<float>(v));
+      break;
+    case 17:  // FLOAT8_E4M3FN: exact, the value came from the same format
+      reinterpret_cast<__nv_fp8_e4m3*>(out)[idx] = __nv_fp8_e4m3(static_cast<float>(v));
+      break;
+    case 18:
+      reinterpret_cast<__nv_fp8_e5m2*>(out)[idx] = __nv_fp8_e5m2(static_cast<float>(v));
       break;
     default:
       break;

@@ -23,7 +23,13 @@ size_t dtype_size(int dtype) {
       return 4;
     case B200PHI_INT64:
     case B200PHI_FLOAT64:
+    case B200PHI_COMPLEX64:
       return 8;
+    case B200PHI_COMPLEX128:
+      return 16;
+    case B200PHI_FLOAT8_E4M3FN:
+    case B200PHI_FLOAT8_E5M2:
+      return 1;
     default:
       return 0;
   }
@@ -34,6 +40,12 @@ bool dtype_known(int dtype) { return dtype_size(dtype) != 0; }
 bool dtype_is_float(int dtype) {
   return dtype == B200PHI_FLOAT32 || dtype == B200PHI_FLOAT64 || dtype == B200PHI_FLOAT16 ||
          dtype == B200PHI_BFLOAT16;
+}
+static bool dtype_is_complex(int dtype) { return dtype == B200PHI_COMPLEX64 || dtype == B200PHI_COMPLEX128; }
+static bool dtype_is_fp8(int dtype) { return dtype == B200PHI_FLOAT8_E4M3FN || dtype == B200PHI_FLOAT8_E5M2; }
+static bool dtype_is_int(int dtype) {
+  return dtype == B200PHI_UINT8 || dtype == B200PHI_INT8 || dtype == B200PHI_INT16 || dtype == B200PHI_INT32 ||
+         dtype == B200PHI_INT64;
 }
 
 static long long env_ll(const char* name, long long dflt) {
@@ -108,7 +120,7 @@ void two_stage_descs(const ReducePlan& p, const b200phi_reduce_desc* d, void* tm
   // stage 1: the merged tensor, reduced over the peeled dim alone
   *d1 = b200phi_reduce_desc();
   d1->op = p.ts_op1;
-  d1->in_dtype = d->in_dtype;
+  d1->in_dtype = p.in_dtype;
   d1->out_dtype = p.ts_tmp_dtype;
   d1->rank = p.ts_rank;
   for (int i = 0; i < p.ts_rank; ++i) d1->dims[i] = p.ts_dims[i];
@@ -149,31 +161,100 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   int out_dtype = d->out_dtype;
   if (out_dtype == B200PHI_UNDEFINED) out_dtype = logical ? B200PHI_BOOL : d->in_dtype;
   if (!dtype_known(out_dtype)) return fail(err, B200PHI_UNSUPPORTED, "unsupported output dtype");
+
+  // ---- complex64 / complex128: SUM and MEAN are component-wise, so the tensor is planned (and
+  //      run, by the same kernels) as its float lanes: dims + [2] with the trailing 2 kept
+  if (dtype_is_complex(d->in_dtype) || dtype_is_complex(out_dtype)) {
+    if (d->in_dtype != out_dtype)
+      return fail(err, B200PHI_UNSUPPORTED, "complex reductions keep the dtype");
+    if (d->op != B200PHI_SUM && d->op != B200PHI_MEAN)
+      return fail(err, B200PHI_UNSUPPORTED, "complex dtypes: sum and mean only");
+    if (d->rank >= B200PHI_MAX_RANK)
+      return fail(err, B200PHI_UNSUPPORTED, "complex dtypes: rank 9 is not built");
+    b200phi_reduce_desc lanes = *d;
+    lanes.in_dtype = lanes.out_dtype = d->in_dtype == B200PHI_COMPLEX64 ? B200PHI_FLOAT32 : B200PHI_FLOAT64;
+    lanes.rank = d->rank + 1;
+    lanes.dims[d->rank] = 2;
+    lanes.reduce_all = 0;
+    if (d->reduce_all != 0 || d->naxes == 0 || d->rank == 0) {
+      lanes.naxes = d->rank;
+      for (int i = 0; i < d->rank; ++i) lanes.axes[i] = i;
+      if (d->rank == 0) {  // a 0-D complex tensor: one (re, im) pair, nothing to combine
+        lanes.rank = 2;
+        lanes.dims[0] = 1;
+        lanes.dims[1] = 2;
+        lanes.naxes = 1;
+        lanes.axes[0] = 0;
+      }
+    } else {
+      for (int i = 0; i < d->naxes; ++i) {
+        int a = d->axes[i];
+        if (a < -d->rank || a >= d->rank) {
+          snprintf(buf, sizeof(buf),
+                   "The reduce dim index %d should be in the range [ -dimension(X), dimension(X) ) "
+                   "which dimension = %d. But received dim index = %d.",
+                   i, d->rank, a);
+          return fail(err, B200PHI_INVALID_ARGUMENT, buf);
+        }
+        lanes.axes[i] = a < 0 ? a + d->rank : a;
+      }
+    }
+    return plan_reduce(&lanes, t, p, err);
+  }
+
   if (logical && out_dtype != B200PHI_BOOL)
     return fail(err, B200PHI_INVALID_ARGUMENT, "any/all write BOOL");
   if (!logical && out_dtype == B200PHI_BOOL && d->in_dtype != B200PHI_BOOL)
     return fail(err, B200PHI_UNSUPPORTED, "BOOL output needs any/all or a BOOL input");
-  if ((out_dtype == B200PHI_FLOAT16 || out_dtype == B200PHI_BFLOAT16) && out_dtype != d->in_dtype &&
-      !t.allow_narrow_out)
-    return fail(err, B200PHI_UNSUPPORTED,
-                "16-bit float output from a different input dtype is not built");
+  if (dtype_is_fp8(d->in_dtype) || dtype_is_fp8(out_dtype)) {
+    if (d->in_dtype != out_dtype || (d->op != B200PHI_MAX && d->op != B200PHI_AMAX))
+      return fail(err, B200PHI_UNSUPPORTED, "float8 dtypes: max / amax only, same output dtype");
+  }
 
   const bool sum_like = d->op == B200PHI_SUM || d->op == B200PHI_MEAN || d->op == B200PHI_SUM_ABS ||
                         d->op == B200PHI_SUM_SQUARE || d->op == B200PHI_L2_NORM ||
                         d->op == B200PHI_COUNT_NONZERO;
-  if (!sum_like && !logical && out_dtype != d->in_dtype)
-    return fail(err, B200PHI_UNSUPPORTED, "max/min/prod keep the input dtype");
   if (d->op >= B200PHI_SUM_ABS && !dtype_is_float(d->in_dtype))
     return fail(err, B200PHI_UNSUPPORTED, "the norm reductions take floating-point dtypes");
+  if (d->op >= B200PHI_SUM_ABS && out_dtype != d->in_dtype && !t.allow_narrow_out)
+    return fail(err, B200PHI_UNSUPPORTED, "the norm reductions keep the input dtype");
+
+  // ---- out_dtype != x.dtype.  The reference casts x to the output dtype FIRST and reduces that
+  //      (phi::Cast pre-pass, gpu/reduce.h:48-69).  Fused into the load wherever that is the same
+  //      arithmetic: sums (the loader converts each element to the accumulation type of the
+  //      output dtype), and max / min between floating-point types or into a wider integer
+  //      (rounding is monotonic, so max(round(x)) == round(max(x))).  Where it is NOT the same --
+  //      a sum into bf16 / fp16 from another dtype (each element is rounded to 16 bits before it is
+  //      added), a product, a narrowing integer conversion -- the plan is the reference's own: a cast
+  //      pass into scratch of the output dtype, then the reduce (kCastFirst).
+  bool cast_first = false;
+  if (out_dtype != d->in_dtype && !logical && !t.allow_narrow_out) {
+    const bool minmax = d->op == B200PHI_MAX || d->op == B200PHI_MIN || d->op == B200PHI_AMAX ||
+                        d->op == B200PHI_AMIN;
+    const bool out16 = out_dtype == B200PHI_FLOAT16 || out_dtype == B200PHI_BFLOAT16;
+    if (sum_like) {
+      cast_first = out16;
+    } else if (minmax) {
+      const bool both_float = dtype_is_float(d->in_dtype) && dtype_is_float(out_dtype);
+      const bool widening_int = (dtype_is_int(d->in_dtype) || d->in_dtype == B200PHI_BOOL) &&
+                                dtype_is_int(out_dtype) && dtype_size(out_dtype) > dtype_size(d->in_dtype);
+      cast_first = !(both_float || widening_int);
+    } else {
+      cast_first = true;  // prod
+    }
+  }
 
   p->op = d->op;
   p->in_dtype = d->in_dtype;
   p->out_dtype = out_dtype;
+  // accumulation type: sums follow the OUTPUT dtype (the loader converts, which is the reference's
+  // Cast pre-pass); max / min / prod compute in the INPUT dtype's natural type and convert at the store
+  const int acc_of = sum_like ? out_dtype : d->in_dtype;
   if (logical)
     p->acc = 3;
-  else if (out_dtype == B200PHI_FLOAT64)
+  else if (acc_of == B200PHI_FLOAT64)
     p->acc = 1;
-  else if (dtype_is_float(out_dtype))
+  else if (dtype_is_float(acc_of) || dtype_is_fp8(acc_of))
     p->acc = 0;
   else
     p->acc = 2;
@@ -244,6 +325,31 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   }
   p->red_numel = red_numel;
   p->out_numel = out_numel;
+  if (cast_first && red_numel > 1) {  // (a lone cast, reduce_num == 1, converts at the store)
+    // stage 1: the cast, spelled as a reduce over an appended extent-1 dim (reduce_num == 1);
+    // stage 2: the reduce in the output dtype
+    if (d->rank >= B200PHI_MAX_RANK)
+      return fail(err, B200PHI_UNSUPPORTED, "a cast pre-pass on a rank-9 tensor is not built");
+    p->kind = kCastFirst;
+    p->out_numel = 0;
+    p->ts_tmp_dtype = out_dtype;
+    p->ts_tmp_bytes = static_cast<size_t>(round_up(numel * static_cast<long long>(dtype_size(out_dtype)), 256));
+    b200phi_reduce_desc d2 = *d;
+    d2.in_dtype = out_dtype;
+    d2.out_dtype = out_dtype;
+    d2.x = reinterpret_cast<const void*>(static_cast<uintptr_t>(256));
+    ReducePlan p2;
+    int rc2 = plan_reduce(&d2, t, &p2, err);
+    if (rc2 != B200PHI_OK) return rc2;
+    p->out_numel = p2.out_numel;
+    p->red_numel = p2.red_numel;
+    p->ts_ws2_bytes = static_cast<size_t>(round_up(static_cast<long long>(p2.ws_total_bytes), 256));
+    p->ws_partial_bytes = p->ts_tmp_bytes;
+    p->ws_total_bytes = p->ts_tmp_bytes + p->ts_ws2_bytes;
+    p->grid_x = p2.grid_x;
+    p->grid_y = p2.grid_y;
+    return B200PHI_OK;
+  }
 
   const size_t esize = dtype_size(d->in_dtype);
   const int VE = static_cast<int>(16 / esize);

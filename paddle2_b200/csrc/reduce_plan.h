@@ -32,6 +32,8 @@ enum ReduceKind {
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
   kTwoStage = 6,  // two or more reduced dims: one of them peeled by a streaming row / column kernel
                   // into scratch, then the (much smaller) rest reduced by whatever its plan says
+  kCastFirst = 12,  // out_dtype != x.dtype where the reference's Cast pre-pass is not foldable into the
+                    // load (sums into bf16 / fp16, products, narrowing integers): cast into scratch, then reduce
   kTiledKeep = 10,  // any other pattern whose innermost merged dim is kept (tile_keep_kernel)
   kTiledRed = 11    // any other pattern whose innermost merged dim is reduced (tile_red_kernel)
 };

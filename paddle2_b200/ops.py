@@ -30,11 +30,16 @@ _T2P = {
     torch.float64: L.FLOAT64,
     torch.float16: L.FLOAT16,
     torch.bfloat16: L.BFLOAT16,
+    torch.complex64: L.COMPLEX64,      # sum / mean / add / subtract
+    torch.complex128: L.COMPLEX128,
+    torch.float8_e4m3fn: L.FLOAT8_E4M3FN,  # max / amax
+    torch.float8_e5m2: L.FLOAT8_E5M2,
 }
 _NAME2T = {
     "bool": torch.bool, "uint8": torch.uint8, "int8": torch.int8, "int16": torch.int16,
     "int32": torch.int32, "int64": torch.int64, "float32": torch.float32,
     "float64": torch.float64, "float16": torch.float16, "bfloat16": torch.bfloat16,
+    "complex64": torch.complex64, "complex128": torch.complex128,
 }
 
 
@@ -153,12 +158,13 @@ def mean(x, axis=None, keepdim=False):
     return _reduce(L.MEAN, x, axis, keepdim, x.dtype)
 
 
-def max(x, axis=None, keepdim=False, out=None):  # noqa: A001
-    return _reduce(L.MAX, x, axis, keepdim, x.dtype, out)
+def max(x, axis=None, keepdim=False, out=None, dtype=None):  # noqa: A001
+    """`dtype`: the C ABI's out_dtype (phi::Reduce casts x to it first, gpu/reduce.h:48-69)."""
+    return _reduce(L.MAX, x, axis, keepdim, _to_torch_dtype(dtype) or x.dtype, out)
 
 
-def min(x, axis=None, keepdim=False, out=None):  # noqa: A001
-    return _reduce(L.MIN, x, axis, keepdim, x.dtype, out)
+def min(x, axis=None, keepdim=False, out=None, dtype=None):  # noqa: A001
+    return _reduce(L.MIN, x, axis, keepdim, _to_torch_dtype(dtype) or x.dtype, out)
 
 
 def amax(x, axis=None, keepdim=False):

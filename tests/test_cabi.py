@@ -74,11 +74,26 @@ def test_planner_errors_match_reference_messages():
     d = _reduce_desc([2, 3], [2])
     assert lib.b200phi_reduce(C.byref(d), None) == 1
     assert b"should be in the range" in lib.b200phi_last_error()
-    # unknown dtype / unsupported pair
-    d = _reduce_desc([2, 3], [1], in_dtype=12)
+    # unknown dtype / unsupported pairs
+    d = _reduce_desc([2, 3], [1], in_dtype=14)                       # PSTRING
     assert lib.b200phi_reduce(C.byref(d), None) == 2
-    d = _reduce_desc([2, 3], [1], op=2, in_dtype=10, out_dtype=11)  # max keeps the dtype
+    d = _reduce_desc([2, 3], [1], op=0, in_dtype=17)                 # float8: max / amax only
     assert lib.b200phi_reduce(C.byref(d), None) == 2
+    assert b"float8" in lib.b200phi_last_error()
+    d = _reduce_desc([2, 3], [1], op=2, in_dtype=12)                 # complex: sum / mean only
+    assert lib.b200phi_reduce(C.byref(d), None) == 2
+    d = _reduce_desc([2, 3], [1], op=5, in_dtype=10, out_dtype=10)   # any writes BOOL
+    assert lib.b200phi_reduce(C.byref(d), None) == 1
+    # out_dtype != x.dtype where the cast cannot be folded into the load: the reference's Cast pre-pass,
+    # scratch = the tensor in the output dtype (+ what the reduce itself needs)
+    d = _reduce_desc([4096, 512], [0], op=0, in_dtype=10, out_dtype=16)
+    assert lib.b200phi_reduce_plan_kind(C.byref(d)) == 12
+    assert lib.b200phi_reduce_workspace(C.byref(d)) >= 4096 * 512 * 2
+    d = _reduce_desc([4096, 512], [0], op=2, in_dtype=10, out_dtype=16)   # max fp32 -> bf16: converts at the store
+    assert lib.b200phi_reduce_plan_kind(C.byref(d)) == 3
+    # complex: planned as float lanes (dims + [2])
+    d = _reduce_desc([4096, 512], [0], op=0, in_dtype=12)
+    assert lib.b200phi_reduce_plan_kind(C.byref(d)) == 3
     with pytest.raises(_lib.B200PhiError):
         _lib.check(1)
 
