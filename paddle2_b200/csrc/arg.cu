@@ -167,17 +167,22 @@ __global__ void __launch_bounds__(kBlock)
 // ascending index order per lane, so the strict compare keeps the first occurrence.  The scalar
 // kernel above reads such a row with 2-byte loads (bf16 1001 columns: 1.5 TB/s), the peeled
 // arg_row_kernel in three dependent phases (2.7 TB/s).
-template <typename T, typename V, bool kMax, int NV>
+// G < 32: 32 / G rows side by side in a warp (a 201-column bf16 row is 25 vectors); G >= VE - 1 so
+// that every possible head / tail element has a lane.
+template <typename T, typename V, bool kMax, int NV, int G = 32>
 __global__ void __launch_bounds__(kBlock)
     arg_warp_peel_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
                          void* val_out) {
   using Op = ArgOp<V, kMax>;
   constexpr int VE = VecOf<T>::kElems;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  static_assert(G >= VE - 1, "a lane per possible head / tail element");
+  constexpr int kPerWarp = 32 / G;
+  const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = wl % G, sub = wl / G;
   // (loop bound on blockIdx alone: bare shuffles)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * kWarps; c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * kWarps) {
-    const long long row = c0 + warp;
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long row = c0 + warp * kPerWarp + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + (live ? row : 0) * n;
     const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
@@ -193,18 +198,20 @@ __global__ void __launch_bounds__(kBlock)
     V16 buf[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
+      const int v = lane + G * k;
       if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
     }
+    // ascending index order per lane: head, vectors, tail -- the strict compare keeps the first
     ArgPair<V> best = Op::identity();
     if (has_h) Op::visit(best, Cvt<V, T>::to(hv), lane);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
+      const int v = lane + G * k;
       if (live && v < nvec) visit_vec<T, V, kMax>(best, buf[k], head + static_cast<long long>(v) * VE);
     }
     if (has_t) Op::visit(best, Cvt<V, T>::to(tv), tail0 + lane);
-    best = warp_arg<V, Op>(best);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) best = Op::combine(best, shfl_pair(best, m));
     if (live && lane == 0) store_arg<T, V>(out, index_dtype, val_out, row, best);
   }
 }
@@ -252,6 +259,29 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       cudaError_t e0 = cudaGetLastError();
       if (e0 != cudaSuccess) return cuda_status(e0);
       return B200PHI_OK;
+    }
+    if constexpr (sizeof(T) == 2) {
+      // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row,
+      // head element + vectors + tail element per lane (the 2-byte-load kernel: 1.6-2.0 TB/s)
+      const long long nv_row = g.n / VecOf<T>::kElems;
+      if (!aligned && nv_row >= 4 && nv_row <= 128 && g.pre >= 64 && !force_g && !force_u && !arg_knobs().no_peel) {
+        const int lanes = nv_row <= 64 ? 8 : 16;
+        long long pc = (g.pre + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
+        if (pc > sm_cap) pc = sm_cap;
+        const unsigned gp = static_cast<unsigned>(pc);
+        const int c = static_cast<int>(g.n);
+        if (nv_row <= 16)
+          arg_warp_peel_kernel<T, V, kMax, 2, 8><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        else if (nv_row <= 32)
+          arg_warp_peel_kernel<T, V, kMax, 4, 8><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        else if (nv_row <= 64)
+          arg_warp_peel_kernel<T, V, kMax, 8, 8><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        else
+          arg_warp_peel_kernel<T, V, kMax, 8, 16><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        cudaError_t e3 = cudaGetLastError();
+        if (e3 != cudaSuccess) return cuda_status(e3);
+        return B200PHI_OK;
+      }
     }
     // (measured at 1001 columns: fp32 6.5 TB/s against 4.3 for the peeled kernel, bf16 1.5 against
     // 2.7 -- 2-byte scalar loads -- so 16-bit rows stop at 256 columns)

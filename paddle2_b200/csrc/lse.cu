@@ -315,6 +315,77 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// 16-bit rows of 32..1031 columns that are not whole aligned vectors: G = 8 or 16 lanes per row,
+// 32 / G rows side by side in a warp; a lane loads one head element, NV 16-byte vectors from the
+// first aligned address and one tail element together, keeps them in registers for the max sweep
+// and the exp-sum sweep (the 2-byte-load kernel read these at 1.6-2.7 TB/s).
+template <typename T, typename A, int G, int NV>
+__global__ void __launch_bounds__(kBlock)
+    lse_peel_kernel(const T* __restrict__ x, long long rows, int cols, void* out, int out_dtype) {
+  constexpr int VE = VecOf<T>::kElems;
+  static_assert(G >= VE - 1, "a lane per possible head / tail element");
+  constexpr int kPerWarp = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  // (loop bound on blockIdx alone: bare shuffles)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long row = c0 + warp * kPerWarp + sub;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + (live ? row : 0) * cols;
+    int head = static_cast<int>(((16 - (reinterpret_cast<uintptr_t>(r) & 15)) & 15) / sizeof(T));
+    if (head > cols) head = cols;
+    const int nvec = (cols - head) / VE;
+    const int tail0 = head + nvec * VE;
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    const bool has_h = live && g < head, has_t = live && tail0 + g < cols;
+    A hv = LseMath<A>::neg_inf(), tv = LseMath<A>::neg_inf();
+    if (has_h) hv = Cvt<A, T>::to(ldg_scalar(r + g));
+    if (has_t) tv = Cvt<A, T>::to(ldg_scalar(r + tail0 + g));
+    V16 buf[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = g + k * G;
+      if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
+    }
+    A m = hv > tv ? hv : tv;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = g + k * G;
+      if (live && v < nvec) {
+        A val[VE];
+        unpack_vec<T, A>(buf[k], val);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) m = val[e] > m ? val[e] : m;
+      }
+    }
+#pragma unroll
+    for (int k = G / 2; k > 0; k >>= 1) {
+      const A o = shfl_xor(m, k);
+      m = o > m ? o : m;
+    }
+    const A shift = (m > LseMath<A>::neg_inf()) ? m : A(0);  // all -inf: every term exp(-inf) = 0
+    A s0 = LseMath<A>::exp_diff(hv, shift), s1 = LseMath<A>::exp_diff(tv, shift);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = g + k * G;
+      if (live && v < nvec) {
+        A val[VE];
+        unpack_vec<T, A>(buf[k], val);
+#pragma unroll
+        for (int e = 0; e < VE; e += 2) {
+          s0 += LseMath<A>::exp_diff(val[e], shift);
+          s1 += LseMath<A>::exp_diff(val[e + 1], shift);
+        }
+      }
+    }
+    A sum = s0 + s1;
+#pragma unroll
+    for (int k = G / 2; k > 0; k >>= 1) sum += shfl_xor(sum, k);
+    if (live && g == 0) lse_put(out, out_dtype, row, static_cast<double>(m + LseMath<A>::log_(sum)));
+  }
+}
+
 template <typename T, typename A>
 static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   constexpr int VE = VecOf<T>::kElems;
@@ -355,6 +426,28 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
     cudaError_t e0 = cudaGetLastError();
     if (e0 != cudaSuccess) return cuda_status(e0);
     return B200PHI_OK;
+  }
+  if constexpr (sizeof(T) == 2) {
+    static const bool no_peel = getenv("B200PHI_LSE_NO_PEEL") != nullptr;
+    if (!aligned && !no_peel && !env_u && nvec_row >= 17 && nvec_row <= 128 && rows >= 64) {  // (101 columns: the scalar kernel measured faster, 2.46 vs 2.32 TB/s)
+      const int lanes = nvec_row <= 64 ? 8 : 16;
+      long long pc = (rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
+      const long long cap = static_cast<long long>(current_sm_count()) * 8 * 8;
+      if (pc > cap) pc = cap;
+      const unsigned gp = static_cast<unsigned>(pc);
+      const int c = static_cast<int>(cols);
+      if (nvec_row <= 16)
+        lse_peel_kernel<T, A, 8, 2><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
+      else if (nvec_row <= 32)
+        lse_peel_kernel<T, A, 8, 4><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
+      else if (nvec_row <= 64)
+        lse_peel_kernel<T, A, 8, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
+      else
+        lse_peel_kernel<T, A, 16, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
+      cudaError_t e2 = cudaGetLastError();
+      if (e2 != cudaSuccess) return cuda_status(e2);
+      return B200PHI_OK;
+    }
   }
   // (measured: at 1001 columns the peeled vector kernel is faster -- 6.6 vs 2.4 TB/s fp32 -- so the
   // scalar form stops at 256 columns)

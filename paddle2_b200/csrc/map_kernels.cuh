@@ -421,6 +421,87 @@ __global__ void __launch_bounds__(kBlock) map_ragged_kernel(MapFlatParams<Arity>
 }
 
 // ---- launch ---------------------------------------------------------------------------------
+// The ragged case that matters, as in the elementwise engine: a full-shape operand against ONE
+// VALUE PER ROW ([N, C, 49] vs [C, 1]), binary functor.  No run-time operand-kind test, no run-time
+// index into the argument struct, U units per thread with all loads issued first.
+struct MapRaggedScalarParams {
+  const void* full;
+  const void* scalar;
+  void* out;
+  FastDiv inner;
+  unsigned total;
+  int nouter;
+  FastDiv oext[3];
+  unsigned ostride[3];
+};
+
+__device__ __forceinline__ unsigned map_ragged_row_offset(unsigned row, const MapRaggedScalarParams& p) {
+  unsigned off = 0;
+#pragma unroll
+  for (int k = 2; k >= 0; --k) {
+    if (k >= 3 - p.nouter) {
+      const unsigned q = fast_div(row, p.oext[k]);
+      off += (row - q * p.oext[k].d) * p.ostride[k];
+      row = q;
+    }
+  }
+  return off;
+}
+
+template <typename TI, typename TO, typename F, int kScalarIs, int U>
+__global__ void __launch_bounds__(kBlock)
+    map_ragged_rowscalar_kernel(const __grid_constant__ MapRaggedScalarParams p, F f) {
+  using C = typename MapCompute<TI>::type;
+  constexpr int VE = VecOf<TI>::kElems;
+  constexpr int kOutBytes = VE * static_cast<int>(sizeof(TO));
+  const unsigned inner = p.inner.d;
+  const unsigned units = p.total / VE;
+  const TI* __restrict__ sc = static_cast<const TI*>(p.scalar);
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < units + 1;
+       base += gridDim.x * (kBlock * U)) {
+    V16 raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id < units) raw[u] = ldg_stream16(reinterpret_cast<const V16*>(p.full) + id);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id > units) continue;
+      const unsigned e0 = id * VE;
+      if (e0 >= p.total) continue;
+      const unsigned row0 = fast_div(e0, p.inner);
+      const unsigned col0 = e0 - row0 * inner;
+      const C v0 = Cvt<C, TI>::to(ldg_scalar(sc + map_ragged_row_offset(row0, p)));
+      C v1 = v0;
+      if (col0 + VE > inner && (row0 + 1) * inner < p.total)
+        v1 = Cvt<C, TI>::to(ldg_scalar(sc + map_ragged_row_offset(row0 + 1, p)));
+      if (id < units) {
+        typename VecOf<TI>::U w;
+        w.raw = raw[u];
+        struct alignas(kOutBytes) {
+          TO e[VE];
+        } o;
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          const C xv = Cvt<C, TI>::to(w.e[e]);
+          const C sv = (col0 + e >= inner) ? v1 : v0;
+          o.e[e] = map_store_cast<TO>(kScalarIs == 1 ? f(xv, sv, C(0)) : f(sv, xv, C(0)));
+        }
+        store_packed<kOutBytes>(static_cast<TO*>(p.out) + static_cast<size_t>(id) * VE, &o);
+      } else {
+        const TI* __restrict__ fx = static_cast<const TI*>(p.full);
+        for (unsigned e = 0; e0 + e < p.total; ++e) {
+          const C xv = Cvt<C, TI>::to(ldg_scalar(fx + e0 + e));
+          const C sv = (col0 + e >= inner) ? v1 : v0;
+          static_cast<TO*>(p.out)[e0 + e] = map_store_cast<TO>(kScalarIs == 1 ? f(xv, sv, C(0)) : f(sv, xv, C(0)));
+        }
+      }
+    }
+  }
+}
+
 template <typename TI, typename TO, typename F, int Arity>
 int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mode, cudaStream_t stream) {
   const bool vec = mode == 1;  // mode 0: elements, 1: whole vectors per row, 2: ragged rows
@@ -470,7 +551,36 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mod
     const long long cap = static_cast<long long>(current_sm_count()) * 8 * 32;  // grid-stride beyond that
     if (blocks > cap) blocks = cap;
     const unsigned g = static_cast<unsigned>(blocks);
-    if (mode == 2) {
+    bool rowscalar_done = false;
+    if constexpr (Arity == 2) {
+      const int fi = p.kind[0] == 0 ? 0 : (p.kind[1] == 0 ? 1 : -1);
+      const int si = fi < 0 ? -1 : 1 - fi;
+      if (mode == 2 && fi >= 0 && p.kind[si] == 2 && p.istride[si] == 0 && no >= 1 && no <= 3 &&
+          reinterpret_cast<uintptr_t>(p.in[fi]) % 16 == 0) {
+        MapRaggedScalarParams rp;
+        rp.full = p.in[fi];
+        rp.scalar = p.in[si];
+        rp.out = p.out;
+        rp.inner = p.upr;
+        rp.total = p.total;
+        rp.nouter = no;
+        for (int k = 0; k < 3; ++k) {
+          const int src = no - 3 + k;
+          rp.oext[k] = src >= 0 ? p.oext[src] : make_fast_div(1u);
+          rp.ostride[k] = src >= 0 ? p.ostride[si][src] : 0u;
+        }
+        constexpr int RU = 8;
+        long long rb = ((static_cast<long long>(p.total) / VE + 1) + kBlock * RU - 1) / (kBlock * RU);
+        if (rb > cap) rb = cap;
+        if (si == 1)
+          map_ragged_rowscalar_kernel<TI, TO, F, 1, RU><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(rp, f);
+        else
+          map_ragged_rowscalar_kernel<TI, TO, F, 0, RU><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(rp, f);
+        rowscalar_done = true;
+      }
+    }
+    if (rowscalar_done) {
+    } else if (mode == 2) {
       long long rb = ((static_cast<long long>(p.total) + VE - 1) / VE + kBlock * 2 - 1) / (kBlock * 2);
       if (rb > cap) rb = cap;
       map_ragged_kernel<TI, TO, F, Arity, 2><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(p, f);

@@ -274,6 +274,60 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+// Rows of 1- and 2-byte elements that are NOT whole aligned 16-byte vectors (odd hidden sizes: 101 ..
+// 2047 bf16 columns): G = 8, 16 or 32 lanes per row, 32 / G rows side by side in a warp.  A row
+// starts up to VE - 1 elements before a 16-byte boundary and ends up to VE - 1 elements after one, so
+// a lane issues, all together, one head element (lane g < head), NV 16-byte vectors from the first
+// aligned address and one tail element, folds them and joins a shuffle tree inside its G lanes.
+// row_scalar_kernel reads such rows with 2-byte (or paired 4-byte) loads: bf16 201 columns 3.7 TB/s,
+// max on 1001 columns 3.5 TB/s.
+template <typename T, typename Acc, typename Op, int G, int NV>
+__global__ void __launch_bounds__(kBlock)
+    row_peel_kernel(const T* __restrict__ x, long long rows, int cols, Epilogue ep) {
+  constexpr int VE = VecOf<T>::kElems;
+  static_assert(G >= VE - 1, "a lane per possible head / tail element");
+  constexpr int kPerWarp = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane % G, sub = lane / G;
+  // (loop bound on blockIdx alone: bare shuffles, see row_tiny_kernel)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long row = c0 + warp * kPerWarp + sub;
+    const bool live = row < rows;
+    const T* __restrict__ r = x + (live ? row : 0) * cols;
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
+    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
+    if (head > cols) head = cols;
+    const int nvec = (cols - head) / VE;
+    const int tail0 = head + nvec * VE;
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    const bool has_h = live && g < head, has_t = live && tail0 + g < cols;
+    T hv, tv;
+    if (has_h) hv = ldg_scalar(r + g);
+    if (has_t) tv = ldg_scalar(r + tail0 + g);
+    V16 buf[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = g + k * G;
+      if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
+    }
+    Acc acc[kFoldLanes];
+#pragma unroll
+    for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+    if (has_h) acc[0] = Op::combine(acc[0], load_as<Acc, Op>(hv));
+    if (has_t) acc[1] = Op::combine(acc[1], load_as<Acc, Op>(tv));
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = g + k * G;
+      if (live && v < nvec) fold_vec<Acc, Op, T, kFoldLanes>(buf[k], acc);
+    }
+    Acc a = fold_lanes<Acc, Op>(acc);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) a = Op::combine(a, shfl_xor(a, m));
+    if (live && g == 0) store_final<Op>(ep, row, a);
+  }
+}
+
 // Short rows (softmax / classifier widths: a few to ~128 elements): G = 1, 2, 4, 8 or 16 lanes
 // per row, 32/G rows per warp, scalar loads (consecutive rows are contiguous, so a warp still
 // reads one contiguous span and L1 serves the strided revisits), xor-shuffle combine inside the

@@ -155,6 +155,29 @@ static int launch_reduce_typed(const ReduceArgs& a) {
         row_scalar_kernel<T, Acc, Op, 32, 32><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
       break;
     }
+    case kRowPeel: {
+      if constexpr (sizeof(T) <= 2) {  // (the planner picks this kind for 1- and 2-byte elements only)
+        const int c = static_cast<int>(p.cols);
+        constexpr int VE = VecOf<T>::kElems;
+        if constexpr (VE <= 8) {
+          if (p.G == 8 && p.nv == 2)
+            row_peel_kernel<T, Acc, Op, 8, 2><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          else if (p.G == 8 && p.nv == 4)
+            row_peel_kernel<T, Acc, Op, 8, 4><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+          else if (p.G == 8)
+            row_peel_kernel<T, Acc, Op, 8, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+        }
+        if (p.G == 16 && p.nv == 4)
+          row_peel_kernel<T, Acc, Op, 16, 4><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+        else if (p.G == 16)
+          row_peel_kernel<T, Acc, Op, 16, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+        else if (p.G == 32)
+          row_peel_kernel<T, Acc, Op, 32, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+      } else {
+        return B200PHI_UNSUPPORTED;
+      }
+      break;
+    }
     case kRowSmall: {
       const int c = static_cast<int>(p.cols);
       switch (p.G) {

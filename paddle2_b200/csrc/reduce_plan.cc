@@ -66,6 +66,7 @@ static Tunables read_env_tunables() {
   t.no_row_batch = static_cast<int>(env_ll("B200PHI_NO_ROW_BATCH", 0));
   t.row_batch_waves = static_cast<int>(env_ll("B200PHI_ROW_BATCH_WAVES", 8));
   t.no_tiled = static_cast<int>(env_ll("B200PHI_NO_TILED", 0));
+  t.no_row_peel = static_cast<int>(env_ll("B200PHI_NO_ROW_PEEL", 0));
   t.p2p_timeout_ms = env_ll("B200PHI_P2P_TIMEOUT_MS", 4000);
   return t;
 }
@@ -616,6 +617,26 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         p->G = 32, p->nv = 32;
       }
     }
+    // 1- and 2-byte rows that are not whole aligned vectors, 4 .. 256 vectors long: head element,
+    // vectors and tail element per lane (row_peel_kernel) instead of 2-byte loads
+    if ((kind == kRowWarp || kind == kRowBlock || kind == kRowScalar) && esize <= 2 && !p->aligned &&
+        p->cols / VE >= 4 && p->cols / VE <= 256 && p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch &&
+        !t.no_row_peel) {
+      const long long nv_row = p->cols / VE;
+      const int gmin = VE > 8 ? 16 : 8;  // a lane per possible head / tail element
+      kind = kRowPeel;
+      if (nv_row <= 16 && gmin == 8) {
+        p->G = 8, p->nv = 2;
+      } else if (nv_row <= 32 && gmin == 8) {
+        p->G = 8, p->nv = 4;
+      } else if (nv_row <= 64) {
+        p->G = gmin == 8 ? 8 : 16, p->nv = gmin == 8 ? 8 : 4;
+      } else if (nv_row <= 128) {
+        p->G = 16, p->nv = 8;
+      } else {
+        p->G = 32, p->nv = 8;
+      }
+    }
     // short rows: fewer than 32 lanes per row (about 8 elements per lane)
     if (kind == kRowWarp && p->cols <= 128 && p->rows >= 64 && t.force_kind < 0) {
       int g = pow2_ceil(ceil_div(p->cols, 8));
@@ -645,6 +666,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->grid_y = 1;
       break;
     }
+    case kRowPeel:
     case kRowScalar: {
       const long long per_cta = 8LL * (32 / p->G);
       long long ctas = ceil_div(p->rows, per_cta);

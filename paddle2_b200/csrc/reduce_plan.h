@@ -32,6 +32,8 @@ enum ReduceKind {
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
   kTwoStage = 6,  // two or more reduced dims: one of them peeled by a streaming row / column kernel
                   // into scratch, then the (much smaller) rest reduced by whatever its plan says
+  kRowPeel = 13,    // [rows, cols] of 1- / 2-byte elements, rows not whole aligned vectors, up to 256 vectors:
+                    // G = 8..32 lanes per row, head element + NV vectors + tail element per lane
   kCastFirst = 12,  // out_dtype != x.dtype where the reference's Cast pre-pass is not foldable into the
                     // load (sums into bf16 / fp16, products, narrowing integers): cast into scratch, then reduce
   kTiledKeep = 10,  // any other pattern whose innermost merged dim is kept (tile_keep_kernel)
@@ -103,6 +105,7 @@ struct Tunables {
   int no_two_stage;         // env B200PHI_NO_TWO_STAGE: keep [A,K,B] patterns on the generic kernel
   int no_row_batch;         // env B200PHI_NO_ROW_BATCH: keep medium rows on row_reduce_kernel
   int row_batch_waves;      // env B200PHI_ROW_BATCH_WAVES: grid cap = SMs * 8 * this
+  int no_row_peel;          // env B200PHI_NO_ROW_PEEL: keep 16-bit unaligned rows on the scalar-load kernel
   int no_tiled;             // env B200PHI_NO_TILED: keep general keep/reduce patterns on the scalar walk
   long long p2p_timeout_ms; // env B200PHI_P2P_TIMEOUT_MS: how long the peer exchange waits for a flag
 };

@@ -48,7 +48,10 @@ __device__ __forceinline__ void put_stat(void* p, int dtype, long long i, double
 // Measured on C4 (16 KiB rows): G = 128 x 8 vectors reads 5.2 TB/s, G = 256 x 4 reads 4.6 TB/s.
 // NV = 16-byte vectors each thread keeps in registers; the row must satisfy
 // cols <= G*NV*VE, be 16-byte aligned and a multiple of VE (checked on the host).
-template <typename T, typename Acc, int G, int NV>
+// kPeel: rows of any alignment -- up to VE - 1 head elements before the first 16-byte boundary
+// and up to VE - 1 tail elements after the last whole vector, one per thread (g < head, g < ntail),
+// loaded together with the vectors and carried through both register sweeps.
+template <typename T, typename Acc, int G, int NV, bool kPeel = false>
 __global__ void __launch_bounds__(kBlock)
     rowstats_reg_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
                         Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
@@ -59,11 +62,25 @@ __global__ void __launch_bounds__(kBlock)
   const int g = threadIdx.x % G, grp = threadIdx.x / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long rows_per_cta = kBlock / G;
-  const long long nvec = cols / VE;
+  long long nvec = cols / VE;
   int parity = 0;
   for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + grp; row < rows;
        row += static_cast<long long>(gridDim.x) * rows_per_cta) {
-    const V16* __restrict__ vp = reinterpret_cast<const V16*>(x + row * cols);
+    const T* __restrict__ r = x + row * cols;
+    long long head = 0;
+    Acc hval = Acc(0), tval = Acc(0);
+    bool has_h = false, has_t = false;
+    if constexpr (kPeel) {
+      head = static_cast<long long>(((16 - (reinterpret_cast<uintptr_t>(r) & 15)) & 15) / sizeof(T));
+      if (head > cols) head = cols;
+      nvec = (cols - head) / VE;
+      const long long tail0 = head + nvec * VE;
+      has_h = g < head;
+      has_t = tail0 + g < cols;
+      if (has_h) hval = Cvt<Acc, T>::to(ldg_scalar(r + g));
+      if (has_t) tval = Cvt<Acc, T>::to(ldg_scalar(r + tail0 + g));
+    }
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
     V16 buf[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
@@ -71,6 +88,10 @@ __global__ void __launch_bounds__(kBlock)
       if (v < nvec) buf[k] = ldg_stream16(vp + v);
     }
     Acc s[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    if constexpr (kPeel) {
+      if (has_h) s[0] += hval;
+      if (has_t) s[1] += tval;
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const long long v = g + static_cast<long long>(k) * G;
@@ -91,6 +112,10 @@ __global__ void __launch_bounds__(kBlock)
     }
     const Acc mean = sum / cols_acc;
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    if constexpr (kPeel) {
+      if (has_h) q[0] += (hval - mean) * (hval - mean);
+      if (has_t) q[1] += (tval - mean) * (tval - mean);
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const long long v = g + static_cast<long long>(k) * G;
@@ -851,16 +876,22 @@ static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int o
 // vectors per lane from the first aligned address, up to VE-1 tail elements -- so both passes of
 // the two-pass variance read registers, no barrier, no second sweep of L2.  The CTA-per-row
 // sweep kernel above spends two block reductions per 4 KiB row (fp32 1025 columns: 1.6 TB/s).
-template <typename T, typename Acc, int NV>
+// G < 32: 32 / G rows side by side in a warp (16-bit rows of 100..1000 columns are only 12..125
+// vectors: a whole warp per row left most lanes without a load); needs G >= VE - 1 so that every
+// possible head / tail element has a lane.
+template <typename T, typename Acc, int NV, int G = 32>
 __global__ void __launch_bounds__(kBlock)
     rowstats_warp_peel_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
                               Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  static_assert(G >= VE - 1, "a lane per possible head / tail element");
+  constexpr int kPerWarp = 32 / G;
+  const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = wl % G, sub = wl / G;
   // (loop bound on blockIdx alone: the shuffles compile to bare SHFL)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * kWarps; c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * kWarps) {
-    const long long row = c0 + warp;
+  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
+    const long long row = c0 + warp * kPerWarp + sub;
     const bool live = row < rows;
     const T* __restrict__ r = x + (live ? row : 0) * cols;
     const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
@@ -877,23 +908,25 @@ __global__ void __launch_bounds__(kBlock)
     V16 buf[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
+      const int v = lane + G * k;
       if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
     }
     Acc s[4] = {hv, tv, Acc(0), Acc(0)};
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
+      const int v = lane + G * k;
       if (live && v < nvec) fold_vec<Acc, SumOp<Acc>, T, 4>(buf[k], s);
     }
-    const Acc sum = warp_combine<Acc, SumOp<Acc>>((s[0] + s[1]) + (s[2] + s[3]));
+    Acc sum = (s[0] + s[1]) + (s[2] + s[3]);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) sum += shfl_xor(sum, m);
     const Acc mean = sum / cols_acc;
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
     if (has_h) q[0] = (hv - mean) * (hv - mean);
     if (has_t) q[1] = (tv - mean) * (tv - mean);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
+      const int v = lane + G * k;
       if (live && v < nvec) {
         Acc val[VE];
         unpack_vec<T, Acc>(buf[k], val);
@@ -904,7 +937,9 @@ __global__ void __launch_bounds__(kBlock)
         }
       }
     }
-    const Acc ss = warp_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]));
+    Acc ss = (q[0] + q[1]) + (q[2] + q[3]);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) ss += shfl_xor(ss, m);
     if (live && lane == 0) {
       if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
       if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
@@ -1029,7 +1064,27 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-  } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
+  } else if (sizeof(T) == 2 && !aligned && n / VE >= 4 && n / VE <= 128 && d->rows >= 64 &&
+             getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr && getenv("B200PHI_ROWSTATS_PEEL_MIN") == nullptr) {
+    // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row
+    // (the scalar-load kernel read these at 2.0-3.2 TB/s, a whole warp per row at 2.0 on 301 columns)
+    const long long nv_row = n / VE;
+    const int lanes = nv_row <= 64 ? 8 : 16;
+    long long ctas = (d->rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
+    const long long cap = static_cast<long long>(sms) * 8 * 8;
+    if (ctas > cap) ctas = cap;
+    const unsigned gsz = static_cast<unsigned>(ctas);
+    if constexpr (sizeof(T) == 2) {
+      if (nv_row <= 16)
+        rowstats_warp_peel_kernel<T, Acc, 2, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else if (nv_row <= 32)
+        rowstats_warp_peel_kernel<T, Acc, 4, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else if (nv_row <= 64)
+        rowstats_warp_peel_kernel<T, Acc, 8, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else
+        rowstats_warp_peel_kernel<T, Acc, 8, 16><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    }
+  } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 12304 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
     // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
     long long ctas = (d->rows + kWarps - 1) / kWarps;
     const long long cap = static_cast<long long>(sms) * 8 * 8;
@@ -1049,6 +1104,15 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       rowstats_warp_peel_kernel<T, Acc, 32><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
           x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+  } else if (!aligned && row_bytes >= 12304 && row_bytes <= 32768 && d->rows >= 64 &&
+             getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
+    // 12..32 KiB rows that are not whole aligned vectors: the whole CTA on one row, row in
+    // registers (8 vectors per thread + a head / tail element), two register sweeps.  The two-sweep
+    // global kernel read these at 3.0-3.9 TB/s (its second sweep misses L2), the one-sweep stream
+    // kernel at 3.0-4.1.
+    long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
+    rowstats_reg_kernel<T, Acc, 256, 8, true><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (n <= 1023 && d->rows >= 64) {  // (one slot spare: a 16-bit row may start mid-word)
     // short rows that are ragged or unaligned: sub-warp groups, scalar loads, row in registers
     const int c = static_cast<int>(n);
