@@ -1084,7 +1084,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
       else
         rowstats_warp_peel_kernel<T, Acc, 8, 16><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
     }
-  } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 12304 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
+  } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
     // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
     long long ctas = (d->rows + kWarps - 1) / kWarps;
     const long long cap = static_cast<long long>(sms) * 8 * 8;
@@ -1104,9 +1104,9 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       rowstats_warp_peel_kernel<T, Acc, 32><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
           x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-  } else if (!aligned && row_bytes >= 12304 && row_bytes <= 32768 && d->rows >= 64 &&
+  } else if (!aligned && row_bytes >= 16400 && row_bytes <= 32768 && d->rows >= 64 &&
              getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
-    // 12..32 KiB rows that are not whole aligned vectors: the whole CTA on one row, row in
+    // 16..32 KiB rows that are not whole aligned vectors: the whole CTA on one row, row in
     // registers (8 vectors per thread + a head / tail element), two register sweeps.  The two-sweep
     // global kernel read these at 3.0-3.9 TB/s (its second sweep misses L2), the one-sweep stream
     // kernel at 3.0-4.1.
