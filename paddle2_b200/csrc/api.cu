@@ -47,6 +47,25 @@ int current_sm_count() {
 // Tunables of the current device (environment part cached, see reduce_plan.cc).
 Tunables tunables() { return default_tunables(current_sm_count()); }
 
+// Ring depth of the staged short-row kernels (rows_staged.cuh): B200PHI_STAGED_STAGES, read once.
+int staged_stages() {
+  static const int v = [] {
+    const char* e = getenv("B200PHI_STAGED_STAGES");
+    int n = e ? atoi(e) : 2;
+    return n < 1 ? 1 : (n > 4 ? 4 : n);
+  }();
+  return v;
+}
+// Lanes per row of the same kernels: B200PHI_STAGED_LANES (1, 2 or 4; 0 / unset: by row length).
+int staged_lanes() {
+  static const int v = [] {
+    const char* e = getenv("B200PHI_STAGED_LANES");
+    const int n = e ? atoi(e) : 0;
+    return (n == 1 || n == 2 || n == 4) ? n : 0;
+  }();
+  return v;
+}
+
 static int run_reduce_impl(const b200phi_reduce_desc* d, int allow_narrow_out, cudaStream_t stream);
 static int run_reduce_stage(const b200phi_reduce_desc* d, int second, cudaStream_t stream) {
   return run_reduce_impl(d, second, stream);

@@ -11,6 +11,7 @@
 
 #include "../../include/b200phi.h"
 #include "arg_common.cuh"
+#include "rows_staged.cuh"
 #include "arg_plan.h"
 #include "reduce_plan.h"
 
@@ -169,6 +170,13 @@ __global__ void __launch_bounds__(kBlock)
 // arg_row_kernel in three dependent phases (2.7 TB/s).
 // G < 32: 32 / G rows side by side in a warp (a 201-column bf16 row is 25 vectors); G >= VE - 1 so
 // that every possible head / tail element has a lane.
+// The row sits in registers, so the search runs in two sweeps of them: first the extreme VALUE
+// (packed max tree per vector, a value-only shuffle tree), then, only in the lanes that hold it,
+// the lowest position whose value equals it, and an integer min over the lanes.  Carrying (value,
+// index) pairs through every vector and every shuffle step cost 2.3x the instructions, and the
+// kernel is bound by instruction issue (ncu: 74 % issue-slot use at 3.0 TB/s on 101 bf16 columns).
+// "First position equal to the extreme" is what the strict in-order compare of the reference
+// returns (cpu/arg_min_max_kernel.cc:46-59); an all-identity row answers 0.
 template <typename T, typename V, bool kMax, int NV, int G = 32>
 __global__ void __launch_bounds__(kBlock)
     arg_warp_peel_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
@@ -177,16 +185,21 @@ __global__ void __launch_bounds__(kBlock)
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");
   constexpr int kPerWarp = 32 / G;
+  constexpr int kPerCta = kWarps * kPerWarp;
+  constexpr int kNone = 0x7fffffff;
   const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int lane = wl % G, sub = wl / G;
-  // (loop bound on blockIdx alone: bare shuffles)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
-    const long long row = c0 + warp * kPerWarp + sub;
-    const bool live = row < rows;
-    const T* __restrict__ r = x + (live ? row : 0) * n;
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
-    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
+  // (loop bound on blockIdx alone: bare shuffles; 32-bit row arithmetic on a CTA-uniform base)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kPerCta; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kPerCta) {
+    const T* __restrict__ xb = x + c0 * n;
+    const unsigned xlow = static_cast<unsigned>(reinterpret_cast<uintptr_t>(xb)) & 15u;
+    const long long left = rows - c0;
+    const int lr = warp * kPerWarp + sub;
+    const bool live = lr < (left < kPerCta ? static_cast<int>(left) : kPerCta);
+    const unsigned off = static_cast<unsigned>(lr) * static_cast<unsigned>(n);
+    const T* __restrict__ r = xb + off;
+    int head = static_cast<int>(((16u - ((xlow + off * static_cast<unsigned>(sizeof(T))) & 15u)) & 15u) / sizeof(T));
     if (head > n) head = n;
     const int nvec = (n - head) / VE;
     const int tail0 = head + nvec * VE;
@@ -201,20 +214,105 @@ __global__ void __launch_bounds__(kBlock)
       const int v = lane + G * k;
       if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
     }
-    // ascending index order per lane: head, vectors, tail -- the strict compare keeps the first
-    ArgPair<V> best = Op::identity();
-    if (has_h) Op::visit(best, Cvt<V, T>::to(hv), lane);
+    // sweep 1: the extreme value
+    const V ident = Op::identity().v;
+    const V hf = has_h ? Cvt<V, T>::to(hv) : ident, tf = has_t ? Cvt<V, T>::to(tv) : ident;
+    V vm[NV];
+    V m = Op::better(tf, hf) ? tf : hf;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int v = lane + G * k;
-      if (live && v < nvec) visit_vec<T, V, kMax>(best, buf[k], head + static_cast<long long>(v) * VE);
+      vm[k] = (live && v < nvec) ? VecExtreme<T, V, kMax>::of(buf[k]) : ident;
+      m = Op::better(vm[k], m) ? vm[k] : m;
     }
-    if (has_t) Op::visit(best, Cvt<V, T>::to(tv), tail0 + lane);
+    V best = m;
 #pragma unroll
-    for (int m = G / 2; m > 0; m >>= 1) best = Op::combine(best, shfl_pair(best, m));
-    if (live && lane == 0) store_arg<T, V>(out, index_dtype, val_out, row, best);
+    for (int s = G / 2; s > 0; s >>= 1) {
+      const V o = shfl_xor(best, s);
+      best = Op::better(o, best) ? o : best;
+    }
+    // sweep 2: the lowest position that holds it -- head, vectors in ascending order, tail
+    int idx = kNone;
+    if (m == best) {
+      if (has_h && hf == best) idx = lane;
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = lane + G * k;
+        if (idx == kNone && live && v < nvec && vm[k] == best) {
+          typename VecOf<T>::U w;
+          w.raw = buf[k];
+          int first = 0;
+#pragma unroll
+          for (int e = VE - 1; e >= 0; --e)
+            if (Cvt<V, T>::to(w.e[e]) == best) first = e;
+          idx = head + v * VE + first;
+        }
+      }
+      if (idx == kNone && has_t && tf == best) idx = tail0 + lane;
+    }
+#pragma unroll
+    for (int s = G / 2; s > 0; s >>= 1) {
+      const int o = shfl_xor(idx, s);
+      idx = o < idx ? o : idx;
+    }
+    if (live && lane == 0) {
+      ArgPair<V> p;
+      p.v = best;
+      p.i = idx == kNone ? 0 : idx;
+      store_arg<T, V>(out, index_dtype, val_out, c0 + lr, p);
+    }
   }
 }
+
+// argmax / argmin consumer of rows_staged_kernel (rows_staged.cuh): one thread scans its row in
+// ascending order with the strict compare, so it keeps the first occurrence.
+template <typename T, typename V, bool kMax>
+struct StagedArg {
+  struct Params {
+    void* out;
+    int index_dtype;
+    void* val_out;
+  };
+  template <int L>
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
+                                             long long row, int h, const Params& p) {
+    using Op = ArgOp<V, kMax>;
+    constexpr int kNone = 0x7fffffff;
+    V bv = Op::identity().v;
+    int idx = kNone;
+    if constexpr (Is16Float<T>::value && std::is_same<V, float>::value) {
+      smem_walk16<T>(sp, i0, i1, [&](int i, float v, int) {
+        if (Op::better(v, bv)) {
+          bv = v;
+          idx = i;
+        }
+      });
+    } else {
+#pragma unroll 4
+      for (int i = i0; i < i1; ++i) {
+        const V v = Cvt<V, T>::to(sp[i]);
+        if (Op::better(v, bv)) {
+          bv = v;
+          idx = i;
+        }
+      }
+    }
+#pragma unroll
+    for (int m = L / 2; m > 0; m >>= 1) {  // better value, else lower index
+      const V ov = __shfl_xor_sync(0xffffffffu, bv, m);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, m);
+      const bool take = Op::better(ov, bv) || (ov == bv && oi < idx);
+      bv = take ? ov : bv;
+      idx = take ? oi : idx;
+    }
+    if (live && h == 0) {
+      ArgPair<V> best;
+      best.v = bv;
+      best.i = idx == kNone ? 0 : idx;  // an all-identity row answers 0
+      store_arg<T, V>(p.out, p.index_dtype, p.val_out, row, best);
+    }
+  }
+};
 
 struct ArgGeom {
   long long pre, n, post;
@@ -259,6 +357,12 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       cudaError_t e0 = cudaGetLastError();
       if (e0 != cudaSuccess) return cuda_status(e0);
       return B200PHI_OK;
+    }
+    // short rows that are not whole aligned vectors: a thread per row out of shared memory
+    static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
+    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes)) {
+      typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
+      return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
     }
     if constexpr (sizeof(T) == 2) {
       // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row,

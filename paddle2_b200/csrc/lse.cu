@@ -13,6 +13,7 @@
 
 #include "../../include/b200phi.h"
 #include "prim.cuh"
+#include "rows_staged.cuh"
 
 namespace b200phi {
 
@@ -30,12 +31,23 @@ struct LseMath<float> {
     return exp2f((a - b) * 1.4426950408889634f);
   }
   static __device__ __forceinline__ float log_(float v) { return logf(v); }
+  // exp(a - shift) as 2^(a log2e - shift log2e): bias(shift) once per row, then one FFMA and one
+  // MUFU.EX2 per element (exp2f() spends five more instructions on range handling per call, which
+  // made the short-row kernels issue-bound: 16 instructions per element on bf16 501 columns)
+  static __device__ __forceinline__ float bias(float shift) { return shift * 1.4426950408889634f; }
+  static __device__ __forceinline__ float term(float a, float b) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(a, 1.4426950408889634f, -b)));
+    return r;
+  }
 };
 template <>
 struct LseMath<double> {
   static __device__ __forceinline__ double neg_inf() { return -INFINITY; }
   static __device__ __forceinline__ double exp_diff(double a, double b) { return exp(a - b); }
   static __device__ __forceinline__ double log_(double v) { return log(v); }
+  static __device__ __forceinline__ double bias(double shift) { return shift; }
+  static __device__ __forceinline__ double term(double a, double b) { return exp(a - b); }
 };
 
 // max of one 16-byte vector; 16-bit floats use the packed max on the raw pairs
@@ -109,6 +121,19 @@ __device__ __forceinline__ void lse_fold_scalar(T v, A& m, A& s) {
   m = mn;
 }
 
+__device__ __forceinline__ void lse_put(void* p, int dtype, long long i, float v) {
+  switch (dtype) {
+    case B200PHI_FLOAT32:
+      reinterpret_cast<float*>(p)[i] = v;
+      break;
+    case B200PHI_FLOAT16:
+      reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
+      break;
+    default:
+      reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
+      break;
+  }
+}
 __device__ __forceinline__ void lse_put(void* p, int dtype, long long i, double v) {
   switch (dtype) {
     case B200PHI_FLOAT32:
@@ -193,7 +218,7 @@ __global__ void __launch_bounds__(kBlock)
     const A S = group_combine<A, SumOp<A>, G>(scaled, smem + kWarps);
     if (g == 0) {
       // all -inf: max = -inf, sum = 0 -> -inf + log(0) = -inf, as the reference's expression gives
-      lse_put(out, out_dtype, row, static_cast<double>(M + LseMath<A>::log_(S)));
+      lse_put(out, out_dtype, row, M + LseMath<A>::log_(S));
     }
   }
 }
@@ -260,7 +285,7 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
     if (g == 0) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
-        if (r0 + r < rows) lse_put(out, out_dtype, r0 + r, static_cast<double>(M[r] + LseMath<A>::log_(s[r])));
+        if (r0 + r < rows) lse_put(out, out_dtype, r0 + r, M[r] + LseMath<A>::log_(s[r]));
     }
   }
 }
@@ -299,10 +324,11 @@ __global__ void __launch_bounds__(kBlock)
       m = o > m ? o : m;
     }
     const A shift = (m > LseMath<A>::neg_inf()) ? m : A(0);  // all -inf: every term exp(-inf) = 0
+    const A bias = LseMath<A>::bias(shift);
     A s0 = A(0), s1 = A(0);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-      const A t = LseMath<A>::exp_diff(val[k], shift);
+      const A t = LseMath<A>::term(val[k], bias);
       if (k & 1)
         s1 += t;
       else
@@ -311,7 +337,7 @@ __global__ void __launch_bounds__(kBlock)
     A sum = s0 + s1;
 #pragma unroll
     for (int k = G / 2; k > 0; k >>= 1) sum += shfl_xor(sum, k);
-    if (live && g == 0) lse_put(out, out_dtype, row, static_cast<double>(m + LseMath<A>::log_(sum)));
+    if (live && g == 0) lse_put(out, out_dtype, row, m + LseMath<A>::log_(sum));
   }
 }
 
@@ -325,15 +351,21 @@ __global__ void __launch_bounds__(kBlock)
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");
   constexpr int kPerWarp = 32 / G;
+  constexpr int kPerCta = kWarps * kPerWarp;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
-  // (loop bound on blockIdx alone: bare shuffles)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
-    const long long row = c0 + warp * kPerWarp + sub;
-    const bool live = row < rows;
-    const T* __restrict__ r = x + (live ? row : 0) * cols;
-    int head = static_cast<int>(((16 - (reinterpret_cast<uintptr_t>(r) & 15)) & 15) / sizeof(T));
+  // (loop bound on blockIdx alone: bare shuffles; 32-bit row arithmetic on a CTA-uniform base:
+  // the kernel is bound by instruction issue, not by memory)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kPerCta; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kPerCta) {
+    const T* __restrict__ xb = x + c0 * cols;
+    const unsigned xlow = static_cast<unsigned>(reinterpret_cast<uintptr_t>(xb)) & 15u;
+    const long long left = rows - c0;
+    const int lr = warp * kPerWarp + sub;
+    const bool live = lr < (left < kPerCta ? static_cast<int>(left) : kPerCta);
+    const unsigned off = static_cast<unsigned>(lr) * static_cast<unsigned>(cols);
+    const T* __restrict__ r = xb + off;
+    int head = static_cast<int>(((16u - ((xlow + off * static_cast<unsigned>(sizeof(T))) & 15u)) & 15u) / sizeof(T));
     if (head > cols) head = cols;
     const int nvec = (cols - head) / VE;
     const int tail0 = head + nvec * VE;
@@ -354,9 +386,9 @@ __global__ void __launch_bounds__(kBlock)
       const int v = g + k * G;
       if (live && v < nvec) {
         A val[VE];
-        unpack_vec<T, A>(buf[k], val);
-#pragma unroll
-        for (int e = 0; e < VE; ++e) m = val[e] > m ? val[e] : m;
+        if constexpr (sizeof(T) != 2) unpack_vec<T, A>(buf[k], val);
+        const A vm = LseVecMax<T, A>::of(buf[k], val);  // packed max on 16-bit pairs
+        m = vm > m ? vm : m;
       }
     }
 #pragma unroll
@@ -365,7 +397,8 @@ __global__ void __launch_bounds__(kBlock)
       m = o > m ? o : m;
     }
     const A shift = (m > LseMath<A>::neg_inf()) ? m : A(0);  // all -inf: every term exp(-inf) = 0
-    A s0 = LseMath<A>::exp_diff(hv, shift), s1 = LseMath<A>::exp_diff(tv, shift);
+    const A bias = LseMath<A>::bias(shift);
+    A s0 = LseMath<A>::term(hv, bias), s1 = LseMath<A>::term(tv, bias);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int v = g + k * G;
@@ -374,17 +407,76 @@ __global__ void __launch_bounds__(kBlock)
         unpack_vec<T, A>(buf[k], val);
 #pragma unroll
         for (int e = 0; e < VE; e += 2) {
-          s0 += LseMath<A>::exp_diff(val[e], shift);
-          s1 += LseMath<A>::exp_diff(val[e + 1], shift);
+          s0 += LseMath<A>::term(val[e], bias);
+          s1 += LseMath<A>::term(val[e + 1], bias);
         }
       }
     }
     A sum = s0 + s1;
 #pragma unroll
     for (int k = G / 2; k > 0; k >>= 1) sum += shfl_xor(sum, k);
-    if (live && g == 0) lse_put(out, out_dtype, row, static_cast<double>(m + LseMath<A>::log_(sum)));
+    if (live && g == 0) lse_put(out, out_dtype, c0 + lr, m + LseMath<A>::log_(sum));
   }
 }
+
+// logsumexp consumer of rows_staged_kernel (rows_staged.cuh): a max sweep and an exp-sum sweep over
+// the thread's own row in shared memory.
+template <typename T, typename A>
+struct StagedLse {
+  struct Params {
+    void* out;
+    int dtype;
+  };
+  template <int L>
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
+                                             long long row, int h, const Params& p) {
+    A m[4] = {LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf()};
+    if constexpr (Is16Float<T>::value && std::is_same<A, float>::value) {
+      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { m[slot % 4] = fmaxf(m[slot % 4], v); });
+      A mx16 = group_all<L>(fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])), [](A a, A b) { return b > a ? b : a; });
+      const A shift16 = (mx16 > LseMath<A>::neg_inf()) ? mx16 : A(0);
+      const A bias16 = LseMath<A>::bias(shift16);
+      A t[4] = {A(0), A(0), A(0), A(0)};
+      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { t[slot % 4] += LseMath<A>::term(v, bias16); });
+      const A sum16 = group_all<L>((t[0] + t[1]) + (t[2] + t[3]), [](A a, A b) { return a + b; });
+      if (live && h == 0) lse_put(p.out, p.dtype, row, mx16 + LseMath<A>::log_(sum16));
+      return;
+    }
+    int i = i0;
+    for (; i + 8 <= i1; i += 8) {
+      T raw[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const A a = Cvt<A, T>::to(raw[j]);
+        m[j % 4] = a > m[j % 4] ? a : m[j % 4];
+      }
+    }
+    for (; i < i1; ++i) {
+      const A a = Cvt<A, T>::to(sp[i]);
+      m[0] = a > m[0] ? a : m[0];
+    }
+    A mx = m[1] > m[0] ? m[1] : m[0];
+    const A my = m[3] > m[2] ? m[3] : m[2];
+    mx = my > mx ? my : mx;
+    mx = group_all<L>(mx, [](A a, A b) { return b > a ? b : a; });
+    const A shift = (mx > LseMath<A>::neg_inf()) ? mx : A(0);
+    const A bias = LseMath<A>::bias(shift);
+    A s[4] = {A(0), A(0), A(0), A(0)};
+    i = i0;
+    for (; i + 8 <= i1; i += 8) {
+      T raw[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j % 4] += LseMath<A>::term(Cvt<A, T>::to(raw[j]), bias);
+    }
+    for (; i < i1; ++i) s[0] += LseMath<A>::term(Cvt<A, T>::to(sp[i]), bias);
+    const A sum = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](A a, A b) { return a + b; });
+    if (live && h == 0) lse_put(p.out, p.dtype, row, mx + LseMath<A>::log_(sum));
+  }
+};
 
 template <typename T, typename A>
 static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
@@ -408,6 +500,12 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
       env_u ? env_u : ((G == kBlock && row_bytes > 64LL * kBlock && sizeof(T) == 2) ? 4 : 8);
   const long long nvec_row = cols / VE;
   static const bool no_multi = getenv("B200PHI_LSE_NO_MULTI") != nullptr;
+  static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
+  if (!no_staged && !no_multi && !env_u && staged_rows_ok(rows, row_bytes)) {
+    // short rows that are not whole aligned vectors: a thread per row out of shared memory
+    typename StagedLse<T, A>::Params sp{d->out, d->dtype};
+    return launch_rows_staged<T, StagedLse<T, A>>(x, rows, static_cast<int>(cols), sp, stream);
+  }
   if (aligned && !no_multi && !env_u && nvec_row <= 128 && rows >= 64) {
     // several rows per warp (lse_multi_kernel)
     // lanes per row G, vectors per lane NV, rounds R (R * NV = 8 loads in flight)
@@ -429,7 +527,8 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   }
   if constexpr (sizeof(T) == 2) {
     static const bool no_peel = getenv("B200PHI_LSE_NO_PEEL") != nullptr;
-    if (!aligned && !no_peel && !env_u && nvec_row >= 17 && nvec_row <= 128 && rows >= 64) {  // (101 columns: the scalar kernel measured faster, 2.46 vs 2.32 TB/s)
+    static const int peel_min = getenv("B200PHI_LSE_PEEL_MIN") ? atoi(getenv("B200PHI_LSE_PEEL_MIN")) : 4;
+    if (!aligned && !no_peel && !env_u && nvec_row >= peel_min && nvec_row <= 128 && rows >= 64) {
       const int lanes = nvec_row <= 64 ? 8 : 16;
       long long pc = (rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
       const long long cap = static_cast<long long>(current_sm_count()) * 8 * 8;

@@ -12,6 +12,7 @@
 #include <stdint.h>
 
 #include <limits>
+#include <type_traits>
 
 namespace b200phi {
 
@@ -240,23 +241,49 @@ struct OpPre<MinAbsOp<Acc>> {
 
 // Load one element as the accumulation type, honouring the any/all truthiness rule and the
 // operator's element transform.
+// The operator's element transform on a value that is already of the accumulation type.
+template <typename Acc, typename Op>
+__device__ __forceinline__ Acc pre_as(Acc a) {
+  if constexpr (OpPre<Op>::value == kPreAbs) {
+    return a < Acc(0) ? -a : a;
+  } else if constexpr (OpPre<Op>::value == kPreSquare) {
+    return a * a;
+  } else if constexpr (OpPre<Op>::value == kPreNonzero) {
+    return a != Acc(0) ? Acc(1) : Acc(0);
+  } else {
+    return a;
+  }
+}
 template <typename Acc, typename Op, typename T>
 __device__ __forceinline__ Acc load_as(T v) {
   if constexpr (Op::kLogical) {
     return static_cast<Acc>(truthy(v));
   } else {
-    const Acc a = Cvt<Acc, T>::to(v);
-    if constexpr (OpPre<Op>::value == kPreAbs) {
-      return a < Acc(0) ? -a : a;
-    } else if constexpr (OpPre<Op>::value == kPreSquare) {
-      return a * a;
-    } else if constexpr (OpPre<Op>::value == kPreNonzero) {
-      return a != Acc(0) ? Acc(1) : Acc(0);
-    } else {
-      return a;
-    }
+    return pre_as<Acc, Op>(Cvt<Acc, T>::to(v));
   }
 }
+
+// +1 for the max family, -1 for the min family, 0 otherwise
+template <typename Op>
+struct OpMinMax {
+  static constexpr int value = 0;
+};
+template <typename Acc>
+struct OpMinMax<MaxOp<Acc>> {
+  static constexpr int value = 1;
+};
+template <typename Acc>
+struct OpMinMax<MaxAbsOp<Acc>> {
+  static constexpr int value = 1;
+};
+template <typename Acc>
+struct OpMinMax<MinOp<Acc>> {
+  static constexpr int value = -1;
+};
+template <typename Acc>
+struct OpMinMax<MinAbsOp<Acc>> {
+  static constexpr int value = -1;
+};
 
 // ---- 16-byte vector of T ------------------------------------------------------
 template <typename T>
@@ -289,13 +316,56 @@ __device__ __forceinline__ void unpack_vec<__nv_bfloat16, float>(const V16& raw,
 }
 
 // Fold a 16-byte vector into kLanes independent accumulators (shorter add chains).
+// 16-bit floats take two shortcuts, because their kernels are bound by instruction issue before
+// they are bound by memory (ncu: 77-87 % issue-slot use on short bf16 rows):
+//   * max / min (and their |x| forms): the vector's eight values are reduced as packed pairs
+//     (three HMNMX2), only the surviving pair is widened -- 7 instructions instead of ~28.  The
+//     result is the same value: widening is exact and max / min pick one of the inputs.
+//   * bf16 otherwise: a pair is widened with one ALU op per element (w << 16, w & 0xffff0000).
 template <typename Acc, typename Op, typename T, int kLanes>
 __device__ __forceinline__ void fold_vec(const V16& raw, Acc (&acc)[kLanes]) {
-  typename VecOf<T>::U u;
-  u.raw = raw;
+  constexpr bool k16 = std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value;
+  if constexpr (k16 && std::is_same<Acc, float>::value && OpMinMax<Op>::value != 0 &&
+                (OpPre<Op>::value == kPreNone || OpPre<Op>::value == kPreAbs)) {
+    using P = typename std::conditional<std::is_same<T, __half>::value, __half2, __nv_bfloat162>::type;
+    P p[4];
 #pragma unroll
-  for (int e = 0; e < VecOf<T>::kElems; ++e) {
-    acc[e % kLanes] = Op::combine(acc[e % kLanes], load_as<Acc, Op>(u.e[e]));
+    for (int k = 0; k < 4; ++k) {
+      uint32_t w = raw.w[k];
+      if constexpr (OpPre<Op>::value == kPreAbs) w &= 0x7fff7fffu;
+      p[k] = *reinterpret_cast<const P*>(&w);
+    }
+    P m;
+    if constexpr (OpMinMax<Op>::value > 0) {
+      m = __hmax2(__hmax2(p[0], p[1]), __hmax2(p[2], p[3]));
+    } else {
+      m = __hmin2(__hmin2(p[0], p[1]), __hmin2(p[2], p[3]));
+    }
+    float lo, hi;
+    if constexpr (std::is_same<T, __half>::value) {
+      const float2 f = __half22float2(m);
+      lo = f.x, hi = f.y;
+    } else {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(&m);
+      lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xffff0000u);
+    }
+    acc[0] = Op::combine(acc[0], lo);
+    acc[1 % kLanes] = Op::combine(acc[1 % kLanes], hi);
+  } else if constexpr (std::is_same<T, __nv_bfloat16>::value && std::is_same<Acc, float>::value &&
+                       !Op::kLogical) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float lo = __uint_as_float(raw.w[k] << 16), hi = __uint_as_float(raw.w[k] & 0xffff0000u);
+      acc[(2 * k) % kLanes] = Op::combine(acc[(2 * k) % kLanes], pre_as<Acc, Op>(lo));
+      acc[(2 * k + 1) % kLanes] = Op::combine(acc[(2 * k + 1) % kLanes], pre_as<Acc, Op>(hi));
+    }
+  } else {
+    typename VecOf<T>::U u;
+    u.raw = raw;
+#pragma unroll
+    for (int e = 0; e < VecOf<T>::kElems; ++e) {
+      acc[e % kLanes] = Op::combine(acc[e % kLanes], load_as<Acc, Op>(u.e[e]));
+    }
   }
 }
 
@@ -303,6 +373,65 @@ __device__ __forceinline__ void fold_vec(const V16& raw, Acc (&acc)[kLanes]) {
 template <typename Acc>
 __device__ __forceinline__ Acc shfl_xor(Acc v, int m) {
   return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+// Walk elements [i0, i1) of a row that lies in shared memory, in ascending order, handing
+// f(index, value widened to float, slot) -- slot is a compile-time 0..7 inside the unrolled rounds
+// (for independent accumulators), 0 elsewhere.  16-bit floats are read as aligned 32-bit words, four words
+// per round (a 2-byte load moves 64 bytes per warp instruction, half of what the shared-memory
+// pipe can deliver: the thread-per-row kernels were bound by exactly that), with one element
+// peeled at either end when the range does not start / end on a word.
+template <typename T>
+struct Is16Float {
+  static constexpr bool value = std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value;
+};
+template <typename T>
+__device__ __forceinline__ void widen_pair(uint32_t w, float& lo, float& hi) {
+  if constexpr (std::is_same<T, __half>::value) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    lo = f.x, hi = f.y;
+  } else {
+    lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xffff0000u);
+  }
+}
+template <typename T, typename F>
+__device__ __forceinline__ void smem_walk16(const T* __restrict__ sp, int i0, int i1, F f) {
+  static_assert(Is16Float<T>::value, "16-bit floats");
+  int i = i0;
+  if (i < i1 && (reinterpret_cast<uintptr_t>(sp + i) & 2)) {
+    f(i, Cvt<float, T>::to(sp[i]), 0);
+    ++i;
+  }
+  const uint32_t* __restrict__ w = reinterpret_cast<const uint32_t*>(sp + i);
+  const int nw = (i1 - i) >> 1;
+  int k = 0;
+  for (; k + 4 <= nw; k += 4) {
+    uint32_t r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) r[j] = w[k + j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float lo, hi;
+      widen_pair<T>(r[j], lo, hi);
+      f(i + 2 * (k + j), lo, 2 * j);
+      f(i + 2 * (k + j) + 1, hi, 2 * j + 1);
+    }
+  }
+  for (; k < nw; ++k) {
+    float lo, hi;
+    widen_pair<T>(w[k], lo, hi);
+    f(i + 2 * k, lo, 0);
+    f(i + 2 * k + 1, hi, 1);
+  }
+  if ((i1 - i) & 1) f(i1 - 1, Cvt<float, T>::to(sp[i1 - 1]), 0);
+}
+
+// All-reduce of v over the L consecutive lanes that share a row.
+template <int L, typename V, typename F>
+__device__ __forceinline__ V group_all(V v, F combine) {
+#pragma unroll
+  for (int m = L / 2; m > 0; m >>= 1) v = combine(v, __shfl_xor_sync(0xffffffffu, v, m));
+  return v;
 }
 
 template <typename Acc, typename Op>
@@ -496,6 +625,27 @@ __device__ __forceinline__ void store_final(const Epilogue& ep, long long idx, A
   store_result(ep, idx, v);
 }
 
+// The same store for kernels that only run on 16-bit inputs: the usual output there is the input
+// type, which store_result would reach through its out-of-line switch once per row.
+template <typename Op, typename T, typename Acc>
+__device__ __forceinline__ void store_final_16(const Epilogue& ep, long long idx, Acc v) {
+  if constexpr (std::is_same<Acc, float>::value &&
+                (std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value)) {
+    constexpr int kId = std::is_same<T, __half>::value ? 15 : 16;
+    if (ep.out_dtype == kId) {
+      if constexpr (OpPost<Op>::kSqrt) v = sqrt(v);
+      if (ep.is_mean) v = v / ep.count_f;
+      if constexpr (std::is_same<T, __half>::value) {
+        reinterpret_cast<__half*>(ep.out)[idx] = __float2half_rn(v);
+      } else {
+        reinterpret_cast<__nv_bfloat16*>(ep.out)[idx] = __float2bfloat16_rn(v);
+      }
+      return;
+    }
+  }
+  store_final<Op>(ep, idx, v);
+}
+
 // Element k of the NE a lane holds of a short row of any alignment (scalar sub-warp kernels):
 // which element index it is, and the loads.  4- and 8-byte types: lane g holds elements
 // g + k*G.  2-byte types: 4-byte words from the row's aligned-down base instead of 2-byte loads
@@ -528,7 +678,17 @@ __device__ __forceinline__ void short_row_load(const T* __restrict__ r, int cols
       const int w = g + j * G;
       const int i0 = 2 * w - odd;
       uint32_t bits = 0;
-      if (live && i0 + 1 >= 0 && i0 < cols) bits = __ldg(wbase + w);
+      if (live && i0 + 1 >= 0 && i0 < cols) {
+        // a word that straddles the row's first or last element is read as that one element: the
+        // other half belongs to the neighbouring row, or lies outside the tensor at its two ends
+        const unsigned short* __restrict__ h = reinterpret_cast<const unsigned short*>(r);
+        if (i0 < 0)
+          bits = static_cast<uint32_t>(__ldg(h)) << 16;
+        else if (i0 + 1 >= cols)
+          bits = __ldg(h + i0);
+        else
+          bits = __ldg(wbase + w);
+      }
       const T* pe = reinterpret_cast<const T*>(&bits);
       raw[2 * j] = pe[0];
       raw[2 * j + 1] = pe[1];

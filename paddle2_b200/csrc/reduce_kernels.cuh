@@ -281,52 +281,105 @@ __global__ void __launch_bounds__(kBlock)
 // aligned address and one tail element, folds them and joins a shuffle tree inside its G lanes.
 // row_scalar_kernel reads such rows with 2-byte (or paired 4-byte) loads: bf16 201 columns 3.7 TB/s,
 // max on 1001 columns 3.5 TB/s.
-template <typename T, typename Acc, typename Op, int G, int NV>
+// RB rows per lane group are loaded before any is folded.  The kernel is bound by instruction
+// issue (ncu: 85 % issue-slot use on 101 bf16 columns), so the per-row address arithmetic is 32-bit:
+// a CTA-uniform 64-bit base per iteration plus (row within the iteration) * cols.
+template <typename T, typename Acc, typename Op, int G, int NV, int RB = 1>
 __global__ void __launch_bounds__(kBlock)
     row_peel_kernel(const T* __restrict__ x, long long rows, int cols, Epilogue ep) {
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");
   constexpr int kPerWarp = 32 / G;
+  constexpr int kPerCta = kWarps * kPerWarp * RB;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
   // (loop bound on blockIdx alone: bare shuffles, see row_tiny_kernel)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
-    const long long row = c0 + warp * kPerWarp + sub;
-    const bool live = row < rows;
-    const T* __restrict__ r = x + (live ? row : 0) * cols;
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
-    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
-    if (head > cols) head = cols;
-    const int nvec = (cols - head) / VE;
-    const int tail0 = head + nvec * VE;
-    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
-    const bool has_h = live && g < head, has_t = live && tail0 + g < cols;
-    T hv, tv;
-    if (has_h) hv = ldg_scalar(r + g);
-    if (has_t) tv = ldg_scalar(r + tail0 + g);
-    V16 buf[NV];
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kPerCta; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kPerCta) {
+    const T* __restrict__ xb = x + c0 * cols;  // CTA-uniform
+    const unsigned xlow = static_cast<unsigned>(reinterpret_cast<uintptr_t>(xb)) & 15u;
+    const long long left = rows - c0;
+    const int nlive = left < kPerCta ? static_cast<int>(left) : kPerCta;
+    bool live[RB], has_h[RB], has_t[RB];
+    int nvec[RB];
+    T hv[RB], tv[RB];
+    V16 buf[RB][NV];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = g + k * G;
-      if (live && v < nvec) buf[k] = ldg_stream16(vp + v);
+    for (int b = 0; b < RB; ++b) {
+      const int lr = (warp * RB + b) * kPerWarp + sub;
+      live[b] = lr < nlive;
+      const unsigned off = static_cast<unsigned>(lr) * static_cast<unsigned>(cols);  // elements
+      const T* __restrict__ r = xb + off;
+      int head = static_cast<int>(((16u - ((xlow + off * static_cast<unsigned>(sizeof(T))) & 15u)) & 15u) /
+                                  sizeof(T));
+      if (head > cols) head = cols;
+      nvec[b] = (cols - head) / VE;
+      const int tail0 = head + nvec[b] * VE;
+      const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+      has_h[b] = live[b] && g < head;
+      has_t[b] = live[b] && tail0 + g < cols;
+      if (has_h[b]) hv[b] = ldg_scalar(r + g);
+      if (has_t[b]) tv[b] = ldg_scalar(r + tail0 + g);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = g + k * G;
+        if (live[b] && v < nvec[b]) buf[b][k] = ldg_stream16(vp + v);
+      }
     }
-    Acc acc[kFoldLanes];
 #pragma unroll
-    for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
-    if (has_h) acc[0] = Op::combine(acc[0], load_as<Acc, Op>(hv));
-    if (has_t) acc[1] = Op::combine(acc[1], load_as<Acc, Op>(tv));
+    for (int b = 0; b < RB; ++b) {
+      Acc acc[kFoldLanes];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = g + k * G;
-      if (live && v < nvec) fold_vec<Acc, Op, T, kFoldLanes>(buf[k], acc);
+      for (int i = 0; i < kFoldLanes; ++i) acc[i] = Op::identity();
+      if (has_h[b]) acc[2] = Op::combine(acc[2], load_as<Acc, Op>(hv[b]));
+      if (has_t[b]) acc[3] = Op::combine(acc[3], load_as<Acc, Op>(tv[b]));
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = g + k * G;
+        if (live[b] && v < nvec[b]) fold_vec<Acc, Op, T, kFoldLanes>(buf[b][k], acc);
+      }
+      Acc a = fold_lanes<Acc, Op>(acc);
+#pragma unroll
+      for (int m = G / 2; m > 0; m >>= 1) a = Op::combine(a, shfl_xor(a, m));
+      if (live[b] && g == 0) store_final_16<Op, T>(ep, c0 + (warp * RB + b) * kPerWarp + sub, a);
     }
-    Acc a = fold_lanes<Acc, Op>(acc);
-#pragma unroll
-    for (int m = G / 2; m > 0; m >>= 1) a = Op::combine(a, shfl_xor(a, m));
-    if (live && g == 0) store_final<Op>(ep, row, a);
   }
 }
+
+// The reduce family's consumer for rows_staged_kernel: one thread folds its whole row out of shared
+// memory into four accumulators (the element order inside a row is the thread's own business: sums
+// are compared at the family's tolerance, every other operator is order-independent).
+template <typename T, typename Acc, typename Op>
+struct StagedReduce {
+  using Params = Epilogue;
+  template <int L>
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int cols, int i0, int i1, bool live,
+                                             long long row, int h, const Epilogue& ep) {
+    Acc a[kFoldLanes];
+#pragma unroll
+    for (int i = 0; i < kFoldLanes; ++i) a[i] = Op::identity();
+    if constexpr (Is16Float<T>::value && std::is_same<Acc, float>::value && !Op::kLogical) {
+      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) {
+        a[slot % kFoldLanes] = Op::combine(a[slot % kFoldLanes], pre_as<Acc, Op>(v));
+      });
+      const Acc v = group_all<L>(fold_lanes<Acc, Op>(a), [](Acc p, Acc q) { return Op::combine(p, q); });
+      if (live && h == 0) store_final_16<Op, T>(ep, row, v);
+      return;
+    }
+    int i = i0;
+    for (; i + 2 * kFoldLanes <= i1; i += 2 * kFoldLanes) {
+      T raw[2 * kFoldLanes];
+#pragma unroll
+      for (int j = 0; j < 2 * kFoldLanes; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 2 * kFoldLanes; ++j)
+        a[j % kFoldLanes] = Op::combine(a[j % kFoldLanes], load_as<Acc, Op>(raw[j]));
+    }
+    for (; i < i1; ++i) a[0] = Op::combine(a[0], load_as<Acc, Op>(sp[i]));
+    const Acc v = group_all<L>(fold_lanes<Acc, Op>(a), [](Acc p, Acc q) { return Op::combine(p, q); });
+    if (live && h == 0) store_final_16<Op, T>(ep, row, v);
+  }
+};
 
 // Short rows (softmax / classifier widths: a few to ~128 elements): G = 1, 2, 4, 8 or 16 lanes
 // per row, 32/G rows per warp, scalar loads (consecutive rows are contiguous, so a warp still

@@ -67,6 +67,7 @@ static Tunables read_env_tunables() {
   t.row_batch_waves = static_cast<int>(env_ll("B200PHI_ROW_BATCH_WAVES", 8));
   t.no_tiled = static_cast<int>(env_ll("B200PHI_NO_TILED", 0));
   t.no_row_peel = static_cast<int>(env_ll("B200PHI_NO_ROW_PEEL", 0));
+  t.no_row_staged = static_cast<int>(env_ll("B200PHI_NO_ROW_STAGED", 0));
   t.p2p_timeout_ms = env_ll("B200PHI_P2P_TIMEOUT_MS", 4000);
   return t;
 }
@@ -636,6 +637,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       } else {
         p->G = 32, p->nv = 8;
       }
+      p->rpg = 1;
     }
     // short rows: fewer than 32 lanes per row (about 8 elements per lane)
     if (kind == kRowWarp && p->cols <= 128 && p->rows >= 64 && t.force_kind < 0) {
@@ -643,6 +645,12 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->G = std::min(16, std::max(1, g));
       kind = kRowSmall;
     }
+  }
+  // short rows that are not whole aligned vectors, whatever the element type: a thread per row out
+  // of shared memory (the sub-warp kernels above are bound by instruction issue there)
+  if ((kind == kRowSmall || kind == kRowScalar || kind == kRowPeel || kind == kRowWarp) && t.force_kind < 0 &&
+      !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize))) {
+    kind = kRowStaged;
   }
   p->kind = kind;
 
@@ -657,6 +665,10 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
       p->grid_y = 1;
       break;
     }
+    case kRowStaged:  // (the launcher sizes the persistent grid from the ring's shared memory)
+      p->grid_x = 1;
+      p->grid_y = 1;
+      break;
     case kRowTiny: {
       const long long per_cta = 8LL * (32 / p->G) * p->rpg;
       long long ctas = ceil_div(p->rows, per_cta);
@@ -668,7 +680,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     }
     case kRowPeel:
     case kRowScalar: {
-      const long long per_cta = 8LL * (32 / p->G);
+      const long long per_cta = 8LL * (32 / p->G) * (kind == kRowPeel ? p->rpg : 1);
       long long ctas = ceil_div(p->rows, per_cta);
       const long long cap = static_cast<long long>(t.sm_count) * 8 * std::max(1, t.row_batch_waves);
       if (ctas > cap) ctas = cap;

@@ -32,6 +32,8 @@ enum ReduceKind {
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
   kTwoStage = 6,  // two or more reduced dims: one of them peeled by a streaming row / column kernel
                   // into scratch, then the (much smaller) rest reduced by whatever its plan says
+  kRowStaged = 14,  // [rows, cols], rows of at most 384 bytes that are not whole aligned vectors: spans of 128 rows
+                    // bulk-copied into shared memory, a thread per row (rows_staged.cuh)
   kRowPeel = 13,    // [rows, cols] of 1- / 2-byte elements, rows not whole aligned vectors, up to 256 vectors:
                     // G = 8..32 lanes per row, head element + NV vectors + tail element per lane
   kCastFirst = 12,  // out_dtype != x.dtype where the reference's Cast pre-pass is not foldable into the
@@ -106,10 +108,27 @@ struct Tunables {
   int no_row_batch;         // env B200PHI_NO_ROW_BATCH: keep medium rows on row_reduce_kernel
   int row_batch_waves;      // env B200PHI_ROW_BATCH_WAVES: grid cap = SMs * 8 * this
   int no_row_peel;          // env B200PHI_NO_ROW_PEEL: keep 16-bit unaligned rows on the scalar-load kernel
+  int no_row_staged;        // env B200PHI_NO_ROW_STAGED: keep short ragged rows off the shared-memory thread-per-row kernel
   int no_tiled;             // env B200PHI_NO_TILED: keep general keep/reduce patterns on the scalar walk
   long long p2p_timeout_ms; // env B200PHI_P2P_TIMEOUT_MS: how long the peer exchange waits for a flag
 };
 Tunables default_tunables(int sm_count);
+
+// ---- short rows through shared memory, a thread per row (rows_staged.cuh) --------------------
+constexpr int kStThreads = 128;  // rows per span = threads per CTA
+// Bytes of one ring stage for rows of `row_bytes`.
+inline int staged_stage_bytes(long long row_bytes) {
+  return static_cast<int>(((static_cast<long long>(kStThreads) * row_bytes + 15) & ~15LL) + 32);
+}
+// Can rows of this geometry take the staged kernels?  Short rows only (a span must fit a ring
+// stage), enough rows to fill the machine, and a row pitch that does not put the threads of a
+// warp on the same shared-memory bank: thread t reads word (t * row_bytes + i) / 4, so a pitch that
+// is a multiple of 16 bytes (4 words) maps four or more lanes to one bank.
+inline bool staged_rows_ok(long long rows, long long row_bytes) {
+  if (row_bytes < 2 || row_bytes > 512 || rows < 4096) return false;
+  if (row_bytes % 16 == 0) return false;
+  return true;
+}
 
 // Fills *plan. Returns B200PHI_OK or a status with *err set.
 int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* plan,

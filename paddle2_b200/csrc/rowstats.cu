@@ -12,6 +12,7 @@
 
 #include "../../include/b200phi.h"
 #include "prim.cuh"
+#include "rows_staged.cuh"
 #include "tma.cuh"
 
 namespace b200phi {
@@ -25,6 +26,21 @@ __device__ __forceinline__ Acc group_sum(Acc v, Acc* smem) {
   return group_combine<Acc, SumOp<Acc>, G>(v, smem);
 }
 
+__device__ __forceinline__ void put_stat(void* p, int dtype, long long i, float v) {
+  switch (dtype) {
+    case B200PHI_FLOAT32:
+      reinterpret_cast<float*>(p)[i] = v;
+      break;
+    case B200PHI_FLOAT16:
+      reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
+      break;
+    case B200PHI_BFLOAT16:
+      reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
+      break;
+    default:
+      break;
+  }
+}
 __device__ __forceinline__ void put_stat(void* p, int dtype, long long i, double v) {
   switch (dtype) {
     case B200PHI_FLOAT32:
@@ -51,9 +67,13 @@ __device__ __forceinline__ void put_stat(void* p, int dtype, long long i, double
 // kPeel: rows of any alignment -- up to VE - 1 head elements before the first 16-byte boundary
 // and up to VE - 1 tail elements after the last whole vector, one per thread (g < head, g < ntail),
 // loaded together with the vectors and carried through both register sweeps.
-template <typename T, typename Acc, int G, int NV, bool kPeel = false>
-__global__ void __launch_bounds__(kBlock)
-    rowstats_reg_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+// kFull: slots 0 .. kFull - 1 are held by every thread of the row (the host guarantees
+// nvec >= kFull * G), so only NV - kFull slots carry a predicate.  With eight per-slot predicates
+// next to the head / tail ones the compiler ran out of predicate registers and issued the last
+// loads after the first loaded value had been consumed: two memory round trips per row.
+template <typename T, typename Acc, int G, int NV, bool kPeel = false, int kFull = 0>
+__global__ void __launch_bounds__(kBlock, kFull > 0 ? 4 : 1)  // (kFull: 64 registers, four CTAs per SM)
+    rowstats_reg_kernel(const T* __restrict__ x, long long rows, long long cols64, Acc denom,
                         Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
   constexpr int kW = G / 32;
@@ -62,40 +82,46 @@ __global__ void __launch_bounds__(kBlock)
   const int g = threadIdx.x % G, grp = threadIdx.x / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long rows_per_cta = kBlock / G;
-  long long nvec = cols / VE;
+  // A row is at most G * NV vectors (+ head and tail): everything inside a row is 32-bit, and a
+  // slot's liveness is one compare against nl (64-bit slot indices recomputed in the load loop and
+  // in both sweeps: ~100 instructions per vector for ~40 of arithmetic on bf16).
+  const int cols = static_cast<int>(cols64);
+  int nvec = cols / VE;
   int parity = 0;
   for (long long row = static_cast<long long>(blockIdx.x) * rows_per_cta + grp; row < rows;
        row += static_cast<long long>(gridDim.x) * rows_per_cta) {
-    const T* __restrict__ r = x + row * cols;
-    long long head = 0;
-    Acc hval = Acc(0), tval = Acc(0);
+    const T* __restrict__ r = x + row * cols64;
+    int head = 0;
+    T hraw, traw;
     bool has_h = false, has_t = false;
     if constexpr (kPeel) {
-      head = static_cast<long long>(((16 - (reinterpret_cast<uintptr_t>(r) & 15)) & 15) / sizeof(T));
+      head = static_cast<int>(((16u - (static_cast<unsigned>(reinterpret_cast<uintptr_t>(r)) & 15u)) & 15u) / sizeof(T));
       if (head > cols) head = cols;
       nvec = (cols - head) / VE;
-      const long long tail0 = head + nvec * VE;
+      const int tail0 = head + nvec * VE;
       has_h = g < head;
       has_t = tail0 + g < cols;
-      if (has_h) hval = Cvt<Acc, T>::to(ldg_scalar(r + g));
-      if (has_t) tval = Cvt<Acc, T>::to(ldg_scalar(r + tail0 + g));
+      if (has_h) hraw = ldg_scalar(r + g);
+      if (has_t) traw = ldg_scalar(r + tail0 + g);
     }
-    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
+    const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head) + g;
+    const int nl = nvec > g ? (nvec - g + G - 1) / G : 0;  // this thread's live slots: 0 .. nl - 1
     V16 buf[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) buf[k] = ldg_stream16(vp + v);
+      if (k < kFull || k < nl) buf[k] = ldg_stream16(vp + k * G);
     }
-    Acc s[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    // (the head / tail elements are widened only now: their conversion ahead of the vector loads
+    // made every warp wait for a 2-byte load before it issued the 16-byte ones)
+    Acc hval = Acc(0), tval = Acc(0);
     if constexpr (kPeel) {
-      if (has_h) s[0] += hval;
-      if (has_t) s[1] += tval;
+      if (has_h) hval = Cvt<Acc, T>::to(hraw);
+      if (has_t) tval = Cvt<Acc, T>::to(traw);
     }
+    Acc s[4] = {hval, tval, Acc(0), Acc(0)};
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) {
+      if (k < kFull || k < nl) {
         Acc val[VE];
         unpack_vec<T, Acc>(buf[k], val);
 #pragma unroll
@@ -113,13 +139,12 @@ __global__ void __launch_bounds__(kBlock)
     const Acc mean = sum / cols_acc;
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
     if constexpr (kPeel) {
-      if (has_h) q[0] += (hval - mean) * (hval - mean);
-      if (has_t) q[1] += (tval - mean) * (tval - mean);
+      if (has_h) q[0] = (hval - mean) * (hval - mean);
+      if (has_t) q[1] = (tval - mean) * (tval - mean);
     }
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-      const long long v = g + static_cast<long long>(k) * G;
-      if (v < nvec) {
+      if (k < kFull || k < nl) {
         Acc val[VE];
         unpack_vec<T, Acc>(buf[k], val);
 #pragma unroll
@@ -141,8 +166,8 @@ __global__ void __launch_bounds__(kBlock)
     }
     parity ^= 1;
     if (g == 0) {
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, ss / denom);
     }
   }
 }
@@ -266,8 +291,8 @@ __global__ void __launch_bounds__(kBlock, 4)  // 64 registers: four CTAs per SM
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         if (r0 + r < rows) {
-          if (mean_out) put_stat(mean_out, out_dtype, r0 + r, static_cast<double>(mean[r]));
-          if (var_out) put_stat(var_out, out_dtype, r0 + r, static_cast<double>(ss[r] / denom));
+          if (mean_out) put_stat(mean_out, out_dtype, r0 + r, mean[r]);
+          if (var_out) put_stat(var_out, out_dtype, r0 + r, ss[r] / denom);
         }
       }
     }
@@ -360,8 +385,8 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
       for (int w = 1; w < kWarps; ++w) ss += part[1][parity][w];
       const long long row = blockIdx.x + k * static_cast<long long>(gridDim.x);
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, ss / denom);
     }
     parity ^= 1;
   }
@@ -444,8 +469,8 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
     for (int m = G / 2; m > 0; m >>= 1) ss += shfl_xor(ss, m);
     if (live && g == 0) {
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, ss / denom);
     }
   }
 }
@@ -564,8 +589,8 @@ __global__ void __launch_bounds__(kBlock)
         b.m2 = sm[2][w];
         moments_merge<Acc>(a, b);
       }
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(a.mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(a.m2 / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, a.mean);
+      if (var_out) put_stat(var_out, out_dtype, row, a.m2 / denom);
     }
     __syncthreads();
   }
@@ -642,8 +667,8 @@ __global__ void __launch_bounds__(kBlock, 4)
         mean += delta * (Acc(1) / (w + 1));
         m2 += oq + delta * delta * (c * Acc(w) / (w + 1));
       }
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(m2 / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, m2 / denom);
     }
     parity ^= 1;
   }
@@ -720,8 +745,8 @@ __global__ void __launch_bounds__(kBlock)
     }
     const Acc ss = block_combine<Acc, SumOp<Acc>>((q[0] + q[1]) + (q[2] + q[3]), smem);
     if (threadIdx.x == 0) {
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, ss / denom);
     }
   }
 }
@@ -847,8 +872,8 @@ __global__ void __launch_bounds__(kBlock + 32)
 #pragma unroll
       for (int w = 1; w < kWarps; ++w) ss += s_part[1][w];
       const long long row = blockIdx.x + k * static_cast<long long>(gridDim.x);
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, row, mean);
+      if (var_out) put_stat(var_out, out_dtype, row, ss / denom);
     }
   }
 }
@@ -881,25 +906,31 @@ static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int o
 // possible head / tail element has a lane.
 template <typename T, typename Acc, int NV, int G = 32>
 __global__ void __launch_bounds__(kBlock)
-    rowstats_warp_peel_kernel(const T* __restrict__ x, long long rows, long long cols, Acc denom,
+    rowstats_warp_peel_kernel(const T* __restrict__ x, long long rows, long long cols64, Acc denom,
                               Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");
   constexpr int kPerWarp = 32 / G;
+  constexpr int kPerCta = kWarps * kPerWarp;
   const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int lane = wl % G, sub = wl / G;
-  // (loop bound on blockIdx alone: the shuffles compile to bare SHFL)
-  for (long long c0 = static_cast<long long>(blockIdx.x) * (kWarps * kPerWarp); c0 < rows;
-       c0 += static_cast<long long>(gridDim.x) * (kWarps * kPerWarp)) {
-    const long long row = c0 + warp * kPerWarp + sub;
-    const bool live = row < rows;
-    const T* __restrict__ r = x + (live ? row : 0) * cols;
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(r);
-    int head = static_cast<int>(((16 - (addr & 15)) & 15) / sizeof(T));
-    if (head > cols) head = static_cast<int>(cols);
-    const int nvec = static_cast<int>((cols - head) / VE);
+  const int cols = static_cast<int>(cols64);  // (rows of at most 16 KiB)
+  // (loop bound on blockIdx alone: the shuffles compile to bare SHFL; 32-bit row arithmetic on a
+  // CTA-uniform base: on short 16-bit rows the kernel is bound by instruction issue)
+  for (long long c0 = static_cast<long long>(blockIdx.x) * kPerCta; c0 < rows;
+       c0 += static_cast<long long>(gridDim.x) * kPerCta) {
+    const T* __restrict__ xb = x + c0 * cols64;
+    const unsigned xlow = static_cast<unsigned>(reinterpret_cast<uintptr_t>(xb)) & 15u;
+    const long long left = rows - c0;
+    const int lr = warp * kPerWarp + sub;
+    const bool live = lr < (left < kPerCta ? static_cast<int>(left) : kPerCta);
+    const unsigned off = static_cast<unsigned>(lr) * static_cast<unsigned>(cols);
+    const T* __restrict__ r = xb + off;
+    int head = static_cast<int>(((16u - ((xlow + off * static_cast<unsigned>(sizeof(T))) & 15u)) & 15u) / sizeof(T));
+    if (head > cols) head = cols;
+    const int nvec = (cols - head) / VE;
     const int tail0 = head + nvec * VE;
-    const int ntail = static_cast<int>(cols) - tail0;
+    const int ntail = cols - tail0;
     const V16* __restrict__ vp = reinterpret_cast<const V16*>(r + head);
     const bool has_h = live && lane < head, has_t = live && lane < ntail;
     Acc hv = Acc(0), tv = Acc(0);
@@ -933,7 +964,7 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
         for (int e = 0; e < VE; ++e) {
           const Acc dlt = val[e] - mean;
-          q[e % 4] += dlt * dlt;
+          q[e % 4] = fma(dlt, dlt, q[e % 4]);
         }
       }
     }
@@ -941,11 +972,76 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
     for (int m = G / 2; m > 0; m >>= 1) ss += shfl_xor(ss, m);
     if (live && lane == 0) {
-      if (mean_out) put_stat(mean_out, out_dtype, row, static_cast<double>(mean));
-      if (var_out) put_stat(var_out, out_dtype, row, static_cast<double>(ss / denom));
+      if (mean_out) put_stat(mean_out, out_dtype, c0 + lr, mean);
+      if (var_out) put_stat(var_out, out_dtype, c0 + lr, ss / denom);
     }
   }
 }
+
+// mean / variance consumer of rows_staged_kernel (rows_staged.cuh): the two sweeps of the two-pass
+// form over the thread's own row in shared memory.
+template <typename T, typename Acc>
+struct StagedStats {
+  struct Params {
+    Acc denom, cols_acc;
+    void* mean_out;
+    void* var_out;
+    int out_dtype;
+  };
+  template <int L>
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
+                                             long long row, int h, const Params& p) {
+    Acc s[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    if constexpr (Is16Float<T>::value && std::is_same<Acc, float>::value) {
+      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { s[slot % 4] += v; });
+      const Acc sum16 = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](Acc a, Acc b) { return a + b; });
+      const Acc mean16 = sum16 / p.cols_acc;
+      Acc q16[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) {
+        const Acc dlt = v - mean16;
+        q16[slot % 4] += dlt * dlt;
+      });
+      const Acc ss16 = group_all<L>((q16[0] + q16[1]) + (q16[2] + q16[3]), [](Acc a, Acc b) { return a + b; });
+      if (live && h == 0) {
+        if (p.mean_out) put_stat(p.mean_out, p.out_dtype, row, mean16);
+        if (p.var_out) put_stat(p.var_out, p.out_dtype, row, ss16 / p.denom);
+      }
+      return;
+    }
+    int i = i0;
+    for (; i + 8 <= i1; i += 8) {
+      T raw[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j % 4] += Cvt<Acc, T>::to(raw[j]);
+    }
+    for (; i < i1; ++i) s[0] += Cvt<Acc, T>::to(sp[i]);
+    const Acc sum = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](Acc a, Acc b) { return a + b; });
+    const Acc mean = sum / p.cols_acc;
+    Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+    i = i0;
+    for (; i + 8 <= i1; i += 8) {
+      T raw[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const Acc dlt = Cvt<Acc, T>::to(raw[j]) - mean;
+        q[j % 4] += dlt * dlt;
+      }
+    }
+    for (; i < i1; ++i) {
+      const Acc dlt = Cvt<Acc, T>::to(sp[i]) - mean;
+      q[0] += dlt * dlt;
+    }
+    const Acc ss = group_all<L>((q[0] + q[1]) + (q[2] + q[3]), [](Acc a, Acc b) { return a + b; });
+    if (live && h == 0) {
+      if (p.mean_out) put_stat(p.mean_out, p.out_dtype, row, mean);
+      if (p.var_out) put_stat(p.var_out, p.out_dtype, row, ss / p.denom);
+    }
+  }
+};
 
 // Smallest row, in bytes, that takes the warp-per-row peel kernel rather than the sub-warp scalar
 // one (B200PHI_ROWSTATS_PEEL_MIN overrides, for measurement).
@@ -989,6 +1085,12 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const bool no_async = getenv("B200PHI_ROWSTATS_ASYNC") == nullptr;
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
+  static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
+  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes)) {
+    // short rows that are not whole aligned vectors: a thread per row out of shared memory
+    typename StagedStats<T, Acc>::Params sp{denom, static_cast<Acc>(n), d->mean, d->var, out_dtype};
+    return launch_rows_staged<T, StagedStats<T, Acc>>(x, d->rows, static_cast<int>(n), sp, stream);
+  }
   if (aligned && (nvec == 128 * 8 || nvec == 64 * 8 || nvec == 32 * 8) && force_g == 0 && d->rows >= 64 &&
       getenv("B200PHI_ROWSTATS_TWO_SWEEP") == nullptr) {
     // full power-of-two rows (the common hidden sizes): one sweep of the registers, one barrier
@@ -1111,8 +1213,18 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     // global kernel read these at 3.0-3.9 TB/s (its second sweep misses L2), the one-sweep stream
     // kernel at 3.0-4.1.
     long long ctas = d->rows > 0x7fffffffLL ? 0x7fffffffLL : d->rows;
-    rowstats_reg_kernel<T, Acc, 256, 8, true><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
-        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    // every row holds at least (n - (VE - 1)) / VE whole vectors: 4 full slots per thread from
+    // 1024 of them (16 KiB), 6 from 1536 (24 KiB)
+    const long long min_nvec = (n - (VE - 1)) / VE;
+    if (min_nvec >= 6 * 256)
+      rowstats_reg_kernel<T, Acc, 256, 8, true, 6><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else if (min_nvec >= 4 * 256)
+      rowstats_reg_kernel<T, Acc, 256, 8, true, 4><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    else
+      rowstats_reg_kernel<T, Acc, 256, 8, true><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+          x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (n <= 1023 && d->rows >= 64) {  // (one slot spare: a 16-bit row may start mid-word)
     // short rows that are ragged or unaligned: sub-warp groups, scalar loads, row in registers
     const int c = static_cast<int>(n);

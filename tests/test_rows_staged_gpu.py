@@ -1,0 +1,151 @@
+"""Short rows that are not whole aligned 16-byte vectors (classifier widths, odd hidden sizes):
+rows_staged_kernel -- spans of 128 rows bulk-copied into shared memory, a thread per row -- for the
+reduce family, argmax / argmin, row statistics and logsumexp, against the oracle.  The shapes
+exercise a last span that is not full, a tensor whose first / last bytes are not 16-byte aligned
+(the byte-copied edges), every element size, and ties for the arg kernels."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import gpu_util as G
+import paddle2_b200 as pb
+from paddle2_b200 import _lib as L
+from paddle2_b200 import ops
+
+pytestmark = pytest.mark.gpu
+
+STAGED = 14
+
+
+def plan_kind(x, op=L.SUM):
+    d = L.ReduceDesc()
+    d.op, d.in_dtype, d.out_dtype, d.rank = op, ops._phi_dtype(x.dtype), 0, x.dim()
+    for i, s in enumerate(x.shape):
+        d.dims[i] = s
+    d.naxes = 1
+    d.axes[0] = x.dim() - 1
+    d.x = x.data_ptr()
+    return L.lib().b200phi_reduce_plan_kind(C.byref(d))
+
+
+def offset_view(flat, rows, cols, off):
+    """[rows, cols] view that starts `off` elements into a fresh allocation (an unaligned base)."""
+    buf = torch.empty(rows * cols + off + 16, dtype=flat.dtype, device="cuda")
+    v = buf[off:off + rows * cols].view(rows, cols)
+    v.copy_(flat.view(rows, cols))
+    return v
+
+
+# (rows, cols): row bytes 2..384, never a multiple of 16
+SHAPES_16 = [(5000, 2), (4096, 3), (7777, 33), (20001, 101), (4100, 191)]
+SHAPES_32 = [(6000, 2), (4096, 7), (9999, 10), (5003, 33), (4500, 95)]
+SHAPES_64 = [(5000, 3), (4097, 47)]
+
+
+@pytest.mark.parametrize("rows,cols", SHAPES_32)
+@pytest.mark.parametrize("off", [0, 1, 3])
+@pytest.mark.parametrize("op", ["sum", "mean", "max", "min", "prod"])
+def test_fp32_reduce(oracle, rows, cols, off, op):
+    rng = np.random.default_rng(rows + cols + off)
+    x = rng.random((rows, cols)).astype(np.float32)
+    if op == "prod":
+        x = (0.9 + 0.2 * x).astype(np.float32)
+    xt = offset_view(G.to_dev(x).flatten(), rows, cols, off)
+    assert plan_kind(xt, getattr(L, op.upper())) == STAGED
+    got = G.to_np(getattr(pb, op)(xt, axis=-1))
+    want = oracle.reduce(op, x, [-1])
+    G.assert_reduce_close(got, want, x, [-1], op, max(G.FP32_RTOL, cols * 2.0 ** -24 if op == "prod" else 0))
+
+
+@pytest.mark.parametrize("rows,cols", SHAPES_16)
+@pytest.mark.parametrize("off", [0, 1, 5])
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+def test_16bit_reduce_arg_stats_lse(oracle, rows, cols, off, dt):
+    rng = np.random.default_rng(rows * 3 + cols + off)
+    x32 = torch.from_numpy(rng.standard_normal((rows, cols)).astype(np.float32)).to(dt).float().numpy()
+    xt = offset_view(torch.from_numpy(x32).cuda().to(dt).flatten(), rows, cols, off)
+    assert plan_kind(xt) == STAGED
+    tol = G.BF16_RTOL
+    np.testing.assert_allclose(pb.sum(xt, axis=-1).float().cpu().numpy(), oracle.reduce("sum", x32, [-1]),
+                               rtol=tol, atol=tol * np.abs(x32).sum(-1).max())
+    np.testing.assert_allclose(pb.sum(xt, axis=-1, dtype="float32").cpu().numpy(), oracle.reduce("sum", x32, [-1]),
+                               rtol=1e-5, atol=1e-5 * np.abs(x32).sum(-1).max())
+    assert np.array_equal(pb.max(xt, axis=-1).float().cpu().numpy(), oracle.reduce("max", x32, [-1]))
+    assert np.array_equal(pb.min(xt, axis=-1).float().cpu().numpy(), oracle.reduce("min", x32, [-1]))
+    # 16-bit values tie often: lowest index
+    idx, val = pb.argmax_with_value(xt, axis=-1)
+    assert np.array_equal(idx.cpu().numpy(), oracle.argreduce("argmax", x32, -1))
+    assert np.array_equal(val.float().cpu().numpy(), oracle.reduce("max", x32, [-1]))
+    assert np.array_equal(pb.argmin(xt, axis=-1, dtype="int32").cpu().numpy(),
+                          oracle.argreduce("argmin", x32, -1).astype(np.int32))
+    if cols > 1:
+        m, v = pb.row_mean_var(xt, out_dtype="float32")
+        mean, var = oracle.rowstats_f32(x32, unbiased=True)
+        np.testing.assert_allclose(m.cpu().numpy(), mean, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(v.cpu().numpy(), var, rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(ops.logsumexp(xt, -1).float().cpu().numpy(), oracle.logsumexp(x32, [-1]),
+                               rtol=tol)
+
+
+@pytest.mark.parametrize("rows,cols", SHAPES_64 + SHAPES_32[:3])
+@pytest.mark.parametrize("off", [0, 1])
+def test_integers_bit_exact(oracle, rows, cols, off):
+    rng = np.random.default_rng(rows + 7 * cols + off)
+    for npdt in (np.int64, np.int32, np.int16, np.uint8, np.int8):
+        if np.dtype(npdt).itemsize * cols % 16 == 0 or np.dtype(npdt).itemsize * cols < 2:
+            continue
+        x = rng.integers(0 if npdt == np.uint8 else -100, 100, size=(rows, cols)).astype(npdt)
+        xt = offset_view(G.to_dev(x).flatten(), rows, cols, off)
+        assert plan_kind(xt) == STAGED
+        # int32 sums promote to int64 (SumRawInferMeta); the other integers keep their type and wrap
+        sum_dt = np.int64 if npdt in (np.int32, np.int64) else npdt
+        assert np.array_equal(G.to_np(pb.sum(xt, axis=-1)), oracle.reduce("sum", x, [-1], out_dtype=sum_dt))
+        assert np.array_equal(G.to_np(pb.max(xt, axis=-1)), oracle.reduce("max", x, [-1]))
+        if npdt in (np.int64, np.int32, np.int16, np.uint8):
+            assert np.array_equal(G.to_np(pb.argmax(xt, axis=-1)), oracle.argreduce("argmax", x, -1))
+            assert np.array_equal(G.to_np(pb.argmin(xt, axis=-1)), oracle.argreduce("argmin", x, -1))
+    xb = rng.random((rows, cols)) > 0.9
+    xt = offset_view(G.to_dev(xb).flatten(), rows, cols, off)
+    assert np.array_equal(G.to_np(pb.any(xt, axis=-1)), oracle.reduce("any", xb, [-1]))
+    assert np.array_equal(G.to_np(pb.all(offset_view(G.to_dev(~xb).flatten(), rows, cols, off), axis=-1)),
+                          oracle.reduce("all", ~xb, [-1]))
+
+
+def test_fp64_and_fp32_stats_lse(oracle):
+    rng = np.random.default_rng(5)
+    xd = rng.standard_normal((4321, 13))
+    xt = offset_view(G.to_dev(xd).flatten(), 4321, 13, 1)
+    np.testing.assert_allclose(G.to_np(pb.sum(xt, axis=-1)), oracle.reduce("sum", xd, [-1]), rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(G.to_np(ops.logsumexp(xt, -1)), oracle.logsumexp(xd, [-1]), rtol=1e-11)
+    xf = rng.standard_normal((8191, 21)).astype(np.float32)
+    xt = offset_view(G.to_dev(xf).flatten(), 8191, 21, 2)
+    m, v = pb.row_mean_var(xt)
+    mean, var = oracle.rowstats_f32(xf, unbiased=True)
+    np.testing.assert_allclose(m.cpu().numpy(), mean, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(v.cpu().numpy(), var, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(G.to_np(ops.logsumexp(xt, -1)), oracle.logsumexp(xf, [-1]), rtol=1e-5, atol=1e-6)
+    # all -inf row and a row with one huge element
+    xf[5, :] = -np.inf
+    xf[6, 3] = 80.0
+    xt = offset_view(G.to_dev(xf).flatten(), 8191, 21, 2)
+    got = G.to_np(ops.logsumexp(xt, -1))
+    assert got[5] == -np.inf
+    np.testing.assert_allclose(got[6], oracle.logsumexp(xf, [-1])[6], rtol=1e-5)
+
+
+def test_large_and_canaries():
+    """Many spans per CTA (the ring wraps many times), outputs framed by sentinels."""
+    rows, cols = 3_000_001, 37
+    x = torch.randn(rows * cols + 3, device="cuda")[3:].view(rows, cols)
+    frame = torch.full((rows + 64,), 12345.0, device="cuda")
+    out = frame[32:32 + rows]
+    pb.sum(x, axis=-1, out=out)
+    want = x.double().sum(-1)
+    assert torch.all((out.double() - want).abs() <= 1e-5 * x.double().abs().sum(-1) + 1e-30)
+    assert torch.all(frame[:32] == 12345.0) and torch.all(frame[32 + rows:] == 12345.0)
+    a = pb.sum(x, axis=-1)
+    assert torch.equal(a, pb.sum(x, axis=-1))
+    idx = pb.argmax(x, axis=-1)
+    assert torch.equal(idx, x.argmax(-1))

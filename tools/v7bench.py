@@ -19,7 +19,9 @@ def t(fn, n=3):
 
 
 N = 1 << 30
-for cols in (101, 201, 301, 501, 1001):
+SHORT = len(sys.argv) > 1 and sys.argv[1] == "short"   # only the short-row section (knob sweeps)
+STATS = len(sys.argv) > 1 and sys.argv[1] == "stats"   # only the long statistics rows
+for cols in (() if STATS else (101, 201, 301, 501, 1001)):
     rows = N // cols
     x = torch.randn(rows, cols, device="cuda").bfloat16()
     for name, fn in (("sum", lambda: pb.sum(x, axis=-1)), ("max", lambda: pb.max(x, axis=-1)),
@@ -28,18 +30,22 @@ for cols in (101, 201, 301, 501, 1001):
         us = t(fn)
         print(f"{name:10s} bf16 [{rows},{cols}] {us:9.1f} us {x.numel()*2/us/1e6:6.2f} TB/s", flush=True)
     del x
+if SHORT:
+    sys.exit(0)
 for cols in (8193, 9001, 10001, 12289):
     rows = N // cols
     x = torch.randn(rows, cols, device="cuda").bfloat16()
     us = t(lambda: pb.row_mean_var(x))
     print(f"mean+var   bf16 [{rows},{cols}] {cols*2:6d} B/row {us:9.1f} us {x.numel()*2/us/1e6:6.2f} TB/s", flush=True)
     del x
-for cols in (4097, 5001, 6001):
+for cols in (4097, 5001, 6001, 7001, 8191):
     rows = N // cols
     x = torch.randn(rows, cols, device="cuda")
     us = t(lambda: pb.row_mean_var(x))
     print(f"mean+var   fp32 [{rows},{cols}] {cols*4:6d} B/row {us:9.1f} us {x.numel()*4/us/1e6:6.2f} TB/s", flush=True)
     del x
+if STATS:
+    sys.exit(0)
 for dt in (torch.bfloat16, torch.float32):
     for hw in (49, 196):
         n = (1 << 30) // (64 * hw)
