@@ -51,17 +51,19 @@ Tunables tunables() { return default_tunables(current_sm_count()); }
 int staged_stages() {
   static const int v = [] {
     const char* e = getenv("B200PHI_STAGED_STAGES");
-    int n = e ? atoi(e) : 2;
+    int n = e ? atoi(e) : 1;
     return n < 1 ? 1 : (n > 4 ? 4 : n);
   }();
   return v;
 }
-// Lanes per row of the same kernels: B200PHI_STAGED_LANES (1, 2 or 4; 0 / unset: by row length).
+// Lanes per row of the same kernels: B200PHI_STAGED_LANES (1, 2 or 4).  One lane measured best
+// at every row length tried (101 bf16 columns: sum 6.2 / 6.0 / 4.1 TB/s, mean+var 5.2 / 4.1 / 2.7
+// for 1 / 2 / 4 lanes).
 int staged_lanes() {
   static const int v = [] {
     const char* e = getenv("B200PHI_STAGED_LANES");
-    const int n = e ? atoi(e) : 0;
-    return (n == 1 || n == 2 || n == 4) ? n : 0;
+    const int n = e ? atoi(e) : 1;
+    return (n == 1 || n == 2 || n == 4) ? n : 1;
   }();
   return v;
 }

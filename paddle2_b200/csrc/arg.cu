@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kBlock)
 // "First position equal to the extreme" is what the strict in-order compare of the reference
 // returns (cpu/arg_min_max_kernel.cc:46-59); an all-identity row answers 0.
 template <typename T, typename V, bool kMax, int NV, int G = 32>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, NV <= 8 ? 4 : 1)
     arg_warp_peel_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
                          void* val_out) {
   using Op = ArgOp<V, kMax>;
@@ -360,7 +360,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     }
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes)) {
+    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes, static_cast<int>(sizeof(T)), false)) {
       typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
       return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
     }

@@ -72,6 +72,11 @@ static Tunables read_env_tunables() {
   return t;
 }
 
+long long staged_max_row_bytes() {
+  static const long long v = env_ll("B200PHI_STAGED_MAX_BYTES", 0);
+  return v;
+}
+
 Tunables default_tunables(int sm_count) {
   static const Tunables env = read_env_tunables();
   Tunables t = env;
@@ -649,7 +654,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   // short rows that are not whole aligned vectors, whatever the element type: a thread per row out
   // of shared memory (the sub-warp kernels above are bound by instruction issue there)
   if ((kind == kRowSmall || kind == kRowScalar || kind == kRowPeel || kind == kRowWarp) && t.force_kind < 0 &&
-      !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize))) {
+      !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize), esize, true)) {
     kind = kRowStaged;
   }
   p->kind = kind;

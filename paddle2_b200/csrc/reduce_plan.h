@@ -32,7 +32,7 @@ enum ReduceKind {
   kRowBatch = 7,  // [rows, cols], aligned rows under ~16 KiB: all loads of R rows in one round
   kTwoStage = 6,  // two or more reduced dims: one of them peeled by a streaming row / column kernel
                   // into scratch, then the (much smaller) rest reduced by whatever its plan says
-  kRowStaged = 14,  // [rows, cols], rows of at most 384 bytes that are not whole aligned vectors: spans of 128 rows
+  kRowStaged = 14,  // [rows, cols], rows of at most 512 bytes that are not whole aligned vectors: spans of 128 rows
                     // bulk-copied into shared memory, a thread per row (rows_staged.cuh)
   kRowPeel = 13,    // [rows, cols] of 1- / 2-byte elements, rows not whole aligned vectors, up to 256 vectors:
                     // G = 8..32 lanes per row, head element + NV vectors + tail element per lane
@@ -120,12 +120,20 @@ constexpr int kStThreads = 128;  // rows per span = threads per CTA
 inline int staged_stage_bytes(long long row_bytes) {
   return static_cast<int>(((static_cast<long long>(kStThreads) * row_bytes + 15) & ~15LL) + 32);
 }
-// Can rows of this geometry take the staged kernels?  Short rows only (a span must fit a ring
-// stage), enough rows to fill the machine, and a row pitch that does not put the threads of a
-// warp on the same shared-memory bank: thread t reads word (t * row_bytes + i) / 4, so a pitch that
-// is a multiple of 16 bytes (4 words) maps four or more lanes to one bank.
-inline bool staged_rows_ok(long long rows, long long row_bytes) {
-  if (row_bytes < 2 || row_bytes > 512 || rows < 4096) return false;
+// Can rows of this geometry take the staged kernels?  Short rows only (a span must fit shared
+// memory a few times over), enough rows to fill the machine, and a row pitch that does not put the
+// threads of a warp on the same shared-memory bank: thread t reads word (t * row_bytes + i) / 4, so
+// a pitch that is a multiple of 16 bytes (4 words) maps four or more lanes to one bank.
+// Measured limits (tools/stagedbench.py, profiles/r02_stagedbench_raw.txt): 16-bit rows up to 512
+// bytes, wider elements up to 832; below 32 / 64 bytes the plain reductions (sum, max ...) are
+// faster on the sub-warp scalar kernels (a thread per 12-byte row spends its time on the row's
+// fixed costs), while argmax, statistics and logsumexp gain at every length.
+long long staged_max_row_bytes();  // B200PHI_STAGED_MAX_BYTES overrides both upper limits (reduce_plan.cc)
+inline bool staged_rows_ok(long long rows, long long row_bytes, int esize, bool plain_reduce) {
+  const long long env_max = staged_max_row_bytes();
+  const long long max_bytes = env_max > 0 ? env_max : (esize <= 2 ? 512 : 832);
+  const long long min_bytes = plain_reduce ? (esize <= 2 ? 32 : 64) : 2;
+  if (row_bytes < min_bytes || row_bytes > max_bytes || rows < 4096) return false;
   if (row_bytes % 16 == 0) return false;
   return true;
 }

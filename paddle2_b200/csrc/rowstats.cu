@@ -905,7 +905,7 @@ static int launch_rowstats_tma(const T* x, const b200phi_rowstats_desc* d, int o
 // vectors: a whole warp per row left most lanes without a load); needs G >= VE - 1 so that every
 // possible head / tail element has a lane.
 template <typename T, typename Acc, int NV, int G = 32>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, NV <= 8 ? 4 : 1)
     rowstats_warp_peel_kernel(const T* __restrict__ x, long long rows, long long cols64, Acc denom,
                               Acc cols_acc, void* mean_out, void* var_out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
@@ -1086,7 +1086,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes)) {
+  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), false)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     typename StagedStats<T, Acc>::Params sp{denom, static_cast<Acc>(n), d->mean, d->var, out_dtype};
     return launch_rows_staged<T, StagedStats<T, Acc>>(x, d->rows, static_cast<int>(n), sp, stream);

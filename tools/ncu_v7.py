@@ -1,7 +1,7 @@
 """One launch of each kernel that serves the shapes VERDICT r1 #7 names (16-bit rows that are not
 whole vectors, unaligned 16-32 KiB statistics rows, ragged broadcasts against a per-row scalar),
 for an ncu capture:
-  ncu --set full --clock-control none -k regex:'peel|scalar_kernel|rowstats_reg|ragged_rowscalar' \
+  ncu --set full --clock-control none -k regex:'peel|scalar_kernel|rowstats_reg|ragged_rowscalar|rows_staged' \
       -o /tmp/v7 python tools/ncu_v7.py && python tools/ncu_summary.py /tmp/v7.ncu-rep
 ~1 GiB tensors (ncu replays each kernel ~40 times)."""
 import sys
