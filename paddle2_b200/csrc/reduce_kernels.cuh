@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(kBlock)
     }
     v = group_combine_leader<Acc, Op, G>(v, smem, parity);
     parity ^= 1;
-    if (g == 0) store_final<Op>(ep, row, v);
+    if (g == 0) store_final_16<Op, T>(ep, row, v);
   }
 }
 
@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(kBlock)
     if (g == 0) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
-        if (r0 + r < rows) store_final<Op>(ep, r0 + r, a[r]);
+        if (r0 + r < rows) store_final_16<Op, T>(ep, r0 + r, a[r]);
     }
   }
 }
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         const int row = first + r * kPerWarp;
-        if (row < live) store_final<Op>(ep, c0 + row, a[r]);
+        if (row < live) store_final_16<Op, T>(ep, c0 + row, a[r]);
       }
     }
   }
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(kBlock)
     Acc v = Op::combine(acc[0], acc[1]);
 #pragma unroll
     for (int m = G / 2; m > 0; m >>= 1) v = Op::combine(v, shfl_xor(v, m));
-    if (live && g == 0) store_final<Op>(ep, row, v);
+    if (live && g == 0) store_final_16<Op, T>(ep, row, v);
   }
 }
 
@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(kBlock)
     }
 #pragma unroll
     for (int m = G >> 1; m > 0; m >>= 1) acc = Op::combine(acc, shfl_xor(acc, m));
-    if (valid && g == 0) store_final<Op>(ep, row, acc);
+    if (valid && g == 0) store_final_16<Op, T>(ep, row, acc);
   }
 }
 
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(kBlock)
     r = Op::combine(r, __ldcg(&partial[row * splits + s]));
   r = block_combine<Acc, Op>(r, smem);
   if (threadIdx.x == 0) {
-    store_final<Op>(ep, row, r);
+    store_final_16<Op, T>(ep, row, r);
     tickets[row] = 0;
   }
 }
@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(kBlock)
   if (splits == 1) {
     if (ty == 0 && live) {
 #pragma unroll
-      for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
+      for (int e = 0; e < VE; ++e) store_final_16<Op, T>(ep, out_base + e, smem[tx * VE + e]);
     }
     return;
   }
@@ -592,7 +592,7 @@ __global__ void __launch_bounds__(kBlock)
   }
   if (ty == 0 && live) {
 #pragma unroll
-    for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
+    for (int e = 0; e < VE; ++e) store_final_16<Op, T>(ep, out_base + e, smem[tx * VE + e]);
   }
   if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
 }
@@ -664,7 +664,7 @@ __global__ void __launch_bounds__(kBlock)
       smem[ty * TX + tx] = Op::combine(smem[ty * TX + tx], smem[(ty + half) * TX + tx]);
     __syncthreads();
   }
-  if (ty == 0 && o < gd.out_numel) store_final<Op>(ep, o, smem[tx]);
+  if (ty == 0 && o < gd.out_numel) store_final_16<Op, T>(ep, o, smem[tx]);
 }
 
 }  // namespace b200phi

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(kBlock)
   if (splits == 1) {
     if (ty == 0 && live) {
 #pragma unroll
-      for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
+      for (int e = 0; e < VE; ++e) store_final_16<Op, T>(ep, out_base + e, smem[tx * VE + e]);
     }
     return;
   }
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(kBlock)
   tree();
   if (ty == 0 && live) {
 #pragma unroll
-    for (int e = 0; e < VE; ++e) store_final<Op>(ep, out_base + e, smem[tx * VE + e]);
+    for (int e = 0; e < VE; ++e) store_final_16<Op, T>(ep, out_base + e, smem[tx * VE + e]);
   }
   if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
 }
@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(kBlock)
     v = block_combine<Acc, Op>(v, smem);
   }
   if (splits == 1) {
-    if (g == 0 && valid) store_final<Op>(ep, o, v);
+    if (g == 0 && valid) store_final_16<Op, T>(ep, o, v);
     return;
   }
   if (g == 0 && valid) partial[static_cast<long long>(blockIdx.y) * out_numel + o] = v;
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(kBlock)
   } else {
     r = block_combine<Acc, Op>(r, smem);
   }
-  if (g == 0 && valid) store_final<Op>(ep, o, r);
+  if (g == 0 && valid) store_final_16<Op, T>(ep, o, r);
   if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
 }
 
