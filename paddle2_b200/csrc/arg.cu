@@ -274,28 +274,30 @@ struct StagedArg {
     void* val_out;
   };
   template <int L>
-  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
-                                             long long row, int h, const Params& p) {
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, int rot,
+                                             bool live, long long row, int h, const Params& p) {
     using Op = ArgOp<V, kMax>;
     constexpr int kNone = 0x7fffffff;
     V bv = Op::identity().v;
     int idx = kNone;
-    if constexpr (Is16Float<T>::value && std::is_same<V, float>::value) {
-      smem_walk16<T>(sp, i0, i1, [&](int i, float v, int) {
+    if (rot >= 0) {
+      // wrapped visit: not in index order, so equal values are settled by the lower index
+      smem_visit<T>(sp, n, i0, i1, rot, [&](int i, auto x, int) {
+        const V v = Cvt<V, decltype(x)>::to(x);
+        if (Op::better(v, bv) || (v == bv && i < idx)) {
+          bv = v;
+          idx = i;
+        }
+      });
+      if (idx != kNone && !Op::better(bv, Op::identity().v)) idx = kNone;  // nothing beat the identity
+    } else {
+      smem_walk_range<T>(sp, i0, i1, [&](int i, auto x, int) {  // ascending: strict compare keeps the first
+        const V v = Cvt<V, decltype(x)>::to(x);
         if (Op::better(v, bv)) {
           bv = v;
           idx = i;
         }
       });
-    } else {
-#pragma unroll 4
-      for (int i = i0; i < i1; ++i) {
-        const V v = Cvt<V, T>::to(sp[i]);
-        if (Op::better(v, bv)) {
-          bv = v;
-          idx = i;
-        }
-      }
     }
 #pragma unroll
     for (int m = L / 2; m > 0; m >>= 1) {  // better value, else lower index
@@ -341,6 +343,12 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     const bool aligned = reinterpret_cast<uintptr_t>(x) % 16 == 0 && row_bytes % 16 == 0;
     const bool no_multi = arg_knobs().no_multi;
     const long long nvec_row = row_bytes / 16;
+    // short rows of any alignment: a thread per row out of shared memory (rows_staged.cuh)
+    static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
+    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes, static_cast<int>(sizeof(T)), kStagedArg, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
+      typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
+      return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
+    }
     if (aligned && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
       const int LG = nvec_row <= 32 ? 8 : 16;
       const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
@@ -357,12 +365,6 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       cudaError_t e0 = cudaGetLastError();
       if (e0 != cudaSuccess) return cuda_status(e0);
       return B200PHI_OK;
-    }
-    // short rows that are not whole aligned vectors: a thread per row out of shared memory
-    static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes, static_cast<int>(sizeof(T)), false)) {
-      typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
-      return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
     }
     if constexpr (sizeof(T) == 2) {
       // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row,

@@ -428,51 +428,23 @@ struct StagedLse {
     int dtype;
   };
   template <int L>
-  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
-                                             long long row, int h, const Params& p) {
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, int rot,
+                                             bool live, long long row, int h, const Params& p) {
     A m[4] = {LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf()};
-    if constexpr (Is16Float<T>::value && std::is_same<A, float>::value) {
-      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { m[slot % 4] = fmaxf(m[slot % 4], v); });
-      A mx16 = group_all<L>(fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])), [](A a, A b) { return b > a ? b : a; });
-      const A shift16 = (mx16 > LseMath<A>::neg_inf()) ? mx16 : A(0);
-      const A bias16 = LseMath<A>::bias(shift16);
-      A t[4] = {A(0), A(0), A(0), A(0)};
-      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { t[slot % 4] += LseMath<A>::term(v, bias16); });
-      const A sum16 = group_all<L>((t[0] + t[1]) + (t[2] + t[3]), [](A a, A b) { return a + b; });
-      if (live && h == 0) lse_put(p.out, p.dtype, row, mx16 + LseMath<A>::log_(sum16));
-      return;
-    }
-    int i = i0;
-    for (; i + 8 <= i1; i += 8) {
-      T raw[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const A a = Cvt<A, T>::to(raw[j]);
-        m[j % 4] = a > m[j % 4] ? a : m[j % 4];
-      }
-    }
-    for (; i < i1; ++i) {
-      const A a = Cvt<A, T>::to(sp[i]);
-      m[0] = a > m[0] ? a : m[0];
-    }
+    smem_visit<T>(sp, n, i0, i1, rot, [&](int, auto x, int slot) {
+      const A a = Cvt<A, decltype(x)>::to(x);
+      m[slot % 4] = a > m[slot % 4] ? a : m[slot % 4];
+    });
     A mx = m[1] > m[0] ? m[1] : m[0];
     const A my = m[3] > m[2] ? m[3] : m[2];
     mx = my > mx ? my : mx;
     mx = group_all<L>(mx, [](A a, A b) { return b > a ? b : a; });
-    const A shift = (mx > LseMath<A>::neg_inf()) ? mx : A(0);
+    const A shift = (mx > LseMath<A>::neg_inf()) ? mx : A(0);  // all -inf: every term exp(-inf) = 0
     const A bias = LseMath<A>::bias(shift);
     A s[4] = {A(0), A(0), A(0), A(0)};
-    i = i0;
-    for (; i + 8 <= i1; i += 8) {
-      T raw[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s[j % 4] += LseMath<A>::term(Cvt<A, T>::to(raw[j]), bias);
-    }
-    for (; i < i1; ++i) s[0] += LseMath<A>::term(Cvt<A, T>::to(sp[i]), bias);
+    smem_visit<T>(sp, n, i0, i1, rot, [&](int, auto x, int slot) {
+      s[slot % 4] += LseMath<A>::term(Cvt<A, decltype(x)>::to(x), bias);
+    });
     const A sum = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](A a, A b) { return a + b; });
     if (live && h == 0) lse_put(p.out, p.dtype, row, mx + LseMath<A>::log_(sum));
   }
@@ -501,7 +473,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   const long long nvec_row = cols / VE;
   static const bool no_multi = getenv("B200PHI_LSE_NO_MULTI") != nullptr;
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-  if (!no_staged && !no_multi && !env_u && staged_rows_ok(rows, row_bytes, static_cast<int>(sizeof(T)), false)) {
+  if (!no_staged && !no_multi && !env_u && staged_rows_ok(rows, row_bytes, static_cast<int>(sizeof(T)), kStagedLse, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     typename StagedLse<T, A>::Params sp{d->out, d->dtype};
     return launch_rows_staged<T, StagedLse<T, A>>(x, rows, static_cast<int>(cols), sp, stream);

@@ -426,6 +426,81 @@ __device__ __forceinline__ void smem_walk16(const T* __restrict__ sp, int i0, in
   if ((i1 - i) & 1) f(i1 - 1, Cvt<float, T>::to(sp[i1 - 1]), 0);
 }
 
+// The same walk for any element type: 16-bit floats as above (value handed as float), every other
+// type element by element in rounds of eight loads (value handed as T).
+template <typename T, typename F>
+__device__ __forceinline__ void smem_walk_range(const T* __restrict__ sp, int i0, int i1, F f) {
+  if constexpr (Is16Float<T>::value) {
+    smem_walk16<T>(sp, i0, i1, f);
+  } else {
+    int i = i0;
+    for (; i + 8 <= i1; i += 8) {
+      T raw[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f(i + j, raw[j], j);
+    }
+    for (; i < i1; ++i) f(i, sp[i], 0);
+  }
+}
+// Visit a whole row of n elements starting `rot` units into it and wrapping around (a unit is an
+// element of 4 or 8 bytes, or a 32-bit word of two 16-bit floats): rows whose pitch is a multiple
+// of 16 bytes put the threads of a warp on a few shared-memory banks when they all start at element
+// 0; started at staggered units they spread over all 32 (see rows_staged.cuh).  Every thread runs
+// the same loop -- the wrap is arithmetic on the unit index, not a second loop, so threads with
+// different starts do not diverge.  rot < 0: the plain ascending walk of [i0, i1).
+template <typename T, typename F>
+__device__ __forceinline__ void smem_visit(const T* __restrict__ sp, int n, int i0, int i1, int rot, F f) {
+  if (rot < 0) {
+    smem_walk_range<T>(sp, i0, i1, f);
+    return;
+  }
+  if constexpr (Is16Float<T>::value) {
+    const uint32_t* __restrict__ w = reinterpret_cast<const uint32_t*>(sp);  // (the row is 4-byte aligned)
+    const int nu = n >> 1;  // a multiple of 4: the row is whole 16-byte vectors
+    int u = rot;
+    for (int k = 0; k < nu; k += 4) {
+      uint32_t r[4];
+      int uu[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uu[j] = u + j;
+        if (uu[j] >= nu) uu[j] -= nu;
+        r[j] = w[uu[j]];
+      }
+      u += 4;
+      if (u >= nu) u -= nu;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float lo, hi;
+        widen_pair<T>(r[j], lo, hi);
+        f(2 * uu[j], lo, 2 * j);
+        f(2 * uu[j] + 1, hi, 2 * j + 1);
+      }
+    }
+  } else if constexpr (sizeof(T) >= 4) {
+    constexpr int kU = sizeof(T) == 4 ? 4 : 2;  // n is a multiple of kU
+    int u = rot;
+    for (int k = 0; k < n; k += kU) {
+      T r[kU];
+      int uu[kU];
+#pragma unroll
+      for (int j = 0; j < kU; ++j) {
+        uu[j] = u + j;
+        if (uu[j] >= n) uu[j] -= n;
+        r[j] = sp[uu[j]];
+      }
+      u += kU;
+      if (u >= n) u -= n;
+#pragma unroll
+      for (int j = 0; j < kU; ++j) f(uu[j], r[j], j);
+    }
+  } else {
+    smem_walk_range<T>(sp, i0, i1, f);
+  }
+}
+
 // All-reduce of v over the L consecutive lanes that share a row.
 template <int L, typename V, typename F>
 __device__ __forceinline__ V group_all(V v, F combine) {

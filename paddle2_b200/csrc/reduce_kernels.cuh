@@ -353,29 +353,24 @@ template <typename T, typename Acc, typename Op>
 struct StagedReduce {
   using Params = Epilogue;
   template <int L>
-  static __device__ __forceinline__ void run(const T* __restrict__ sp, int cols, int i0, int i1, bool live,
-                                             long long row, int h, const Epilogue& ep) {
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int cols, int i0, int i1, int rot,
+                                             bool live, long long row, int h, const Epilogue& ep) {
     Acc a[kFoldLanes];
 #pragma unroll
     for (int i = 0; i < kFoldLanes; ++i) a[i] = Op::identity();
-    if constexpr (Is16Float<T>::value && std::is_same<Acc, float>::value && !Op::kLogical) {
-      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) {
-        a[slot % kFoldLanes] = Op::combine(a[slot % kFoldLanes], pre_as<Acc, Op>(v));
-      });
-      const Acc v = group_all<L>(fold_lanes<Acc, Op>(a), [](Acc p, Acc q) { return Op::combine(p, q); });
-      if (live && h == 0) store_final_16<Op, T>(ep, row, v);
-      return;
-    }
-    int i = i0;
-    for (; i + 2 * kFoldLanes <= i1; i += 2 * kFoldLanes) {
-      T raw[2 * kFoldLanes];
-#pragma unroll
-      for (int j = 0; j < 2 * kFoldLanes; ++j) raw[j] = sp[i + j];
-#pragma unroll
-      for (int j = 0; j < 2 * kFoldLanes; ++j)
-        a[j % kFoldLanes] = Op::combine(a[j % kFoldLanes], load_as<Acc, Op>(raw[j]));
-    }
-    for (; i < i1; ++i) a[0] = Op::combine(a[0], load_as<Acc, Op>(sp[i]));
+    smem_visit<T>(sp, cols, i0, i1, rot, [&](int, auto v, int slot) {
+      Acc w;
+      if constexpr (Is16Float<T>::value) {  // v is the element widened to float
+        if constexpr (Op::kLogical) {
+          w = static_cast<Acc>(v != 0.f ? 1 : 0);
+        } else {
+          w = pre_as<Acc, Op>(static_cast<Acc>(v));
+        }
+      } else {
+        w = load_as<Acc, Op>(v);
+      }
+      a[slot % kFoldLanes] = Op::combine(a[slot % kFoldLanes], w);
+    });
     const Acc v = group_all<L>(fold_lanes<Acc, Op>(a), [](Acc p, Acc q) { return Op::combine(p, q); });
     if (live && h == 0) store_final_16<Op, T>(ep, row, v);
   }

@@ -77,6 +77,11 @@ long long staged_max_row_bytes() {
   return v;
 }
 
+int staged_aligned_mode() {
+  static const int v = static_cast<int>(env_ll("B200PHI_STAGED_ALIGNED", 1));
+  return v;
+}
+
 Tunables default_tunables(int sm_count) {
   static const Tunables env = read_env_tunables();
   Tunables t = env;
@@ -653,8 +658,11 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
   }
   // short rows that are not whole aligned vectors, whatever the element type: a thread per row out
   // of shared memory (the sub-warp kernels above are bound by instruction issue there)
-  if ((kind == kRowSmall || kind == kRowScalar || kind == kRowPeel || kind == kRowWarp) && t.force_kind < 0 &&
-      !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize), esize, true)) {
+  if ((kind == kRowSmall || kind == kRowScalar || kind == kRowPeel || kind == kRowWarp || kind == kRowTiny ||
+       kind == kRowBatch) &&
+      t.force_kind < 0 &&
+      !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize), esize, kStagedReduce,
+                     reinterpret_cast<uintptr_t>(d->x) % 4 == 0)) {
     kind = kRowStaged;
   }
   p->kind = kind;

@@ -22,10 +22,17 @@
 //
 // A consumer C provides
 //   using Params = ...;                                   (passed by value to the kernel)
-//   template <int L> static __device__ void run(const T* row_in_smem, int cols, int i0, int i1,
+//   template <int L> static __device__ void run(const T* row_in_smem, int cols, int i0, int i1, int rot,
 //                                               bool live, long long row, int h, const Params&);
 // for lane h of the row's L lanes and its element range [i0, i1); every thread of the CTA calls
 // it (dead rows with i0 == i1 and live == false), so that it may use group_all<L>.
+//
+// Rows that ARE whole 16-byte vectors have a pitch of 4k words: started at element 0, the 32
+// threads of a warp would hit 32 / gcd-many banks (a 128-byte row: one bank, a 32-way conflict).
+// Such rows are visited from a staggered start `rot` and wrapped around (smem_visit): thread t
+// starts floor(t * min(pitch_words, 32) / 32) units into its row, which spreads a warp over all the
+// banks (at most 2-way conflicts for any pitch; simulated for every pitch up to 1 KiB).  Consumers
+// whose result depends on the visiting order (argmax ties) compare indices explicitly then.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -40,7 +47,7 @@ namespace b200phi {
 template <typename T, typename C, int L>
 __global__ void __launch_bounds__(kStThreads * L)
     rows_staged_kernel(const T* __restrict__ x, long long rows, int cols, int stages, int stage_bytes,
-                       typename C::Params prm) {
+                       int rot_pitch, typename C::Params prm) {
   extern __shared__ __align__(128) unsigned char st_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem + static_cast<size_t>(stages) * stage_bytes);
   const int tid = threadIdx.x;
@@ -58,6 +65,14 @@ __global__ void __launch_bounds__(kStThreads * L)
   const int chunk = (cols + L - 1) / L;
   const int i0 = h * chunk < cols ? h * chunk : cols;
   const int i1 = i0 + chunk < cols ? i0 + chunk : cols;
+  // staggered start, in visiting units (smem_visit), for rows whose pitch is a multiple of 16
+  // bytes; rot_pitch = min(pitch in 4-byte words, 32), 0 for every other row (rot = -1: plain walk)
+  int rot = -1;
+  if (L == 1 && rot_pitch > 0 && sizeof(T) >= 2) {
+    constexpr int kUnit = sizeof(T) >= 4 ? static_cast<int>(sizeof(T)) : 4;  // bytes per visiting unit
+    const int nu = static_cast<int>(row_bytes) / kUnit;
+    rot = (((tid & 31) * rot_pitch) >> 5) % nu;
+  }
 
   // Start the copy of this CTA's i-th span into stage i % stages (every thread calls).
   auto issue = [&](long long i) {
@@ -96,7 +111,7 @@ __global__ void __launch_bounds__(kStThreads * L)
     const bool live = row0 + r < rows;
     const unsigned char* sp = st_smem + static_cast<size_t>(s) * stage_bytes + (b0 & 15) +
                               static_cast<size_t>(r) * static_cast<size_t>(row_bytes);
-    C::template run<L>(reinterpret_cast<const T*>(sp), cols, live ? i0 : 0, live ? i1 : 0, live, row0 + r, h, prm);
+    C::template run<L>(reinterpret_cast<const T*>(sp), cols, live ? i0 : 0, live ? i1 : 0, rot, live, row0 + r, h, prm);
   }
 }
 
@@ -130,7 +145,8 @@ int launch_rows_staged_l(const T* x, long long rows, int cols, const typename C:
   if (per_sm < 1) per_sm = 1;
   long long ctas = static_cast<long long>(current_sm_count()) * per_sm;
   if (ctas > ntiles) ctas = ntiles;
-  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, prm);
+  const int rot_pitch = (row_bytes % 16 == 0) ? static_cast<int>(row_bytes / 4 < 32 ? row_bytes / 4 : 32) : 0;
+  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, rot_pitch, prm);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);
   return 0;
@@ -140,7 +156,7 @@ template <typename T, typename C>
 int launch_rows_staged(const T* x, long long rows, int cols, const typename C::Params& prm, cudaStream_t stream) {
   const long long row_bytes = static_cast<long long>(cols) * static_cast<long long>(sizeof(T));
   int lanes = staged_lanes();
-  if (lanes == 0) lanes = row_bytes <= 64 ? 1 : (row_bytes <= 160 ? 2 : 4);
+  if (lanes == 0 || row_bytes % 16 == 0) lanes = 1;  // (the staggered start is per row)
   if (lanes == 1) return launch_rows_staged_l<T, C, 1>(x, rows, cols, prm, stream);
   if (lanes == 2) return launch_rows_staged_l<T, C, 2>(x, rows, cols, prm, stream);
   return launch_rows_staged_l<T, C, 4>(x, rows, cols, prm, stream);

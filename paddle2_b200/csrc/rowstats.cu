@@ -989,52 +989,17 @@ struct StagedStats {
     int out_dtype;
   };
   template <int L>
-  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, bool live,
-                                             long long row, int h, const Params& p) {
+  static __device__ __forceinline__ void run(const T* __restrict__ sp, int n, int i0, int i1, int rot,
+                                             bool live, long long row, int h, const Params& p) {
     Acc s[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
-    if constexpr (Is16Float<T>::value && std::is_same<Acc, float>::value) {
-      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) { s[slot % 4] += v; });
-      const Acc sum16 = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](Acc a, Acc b) { return a + b; });
-      const Acc mean16 = sum16 / p.cols_acc;
-      Acc q16[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
-      smem_walk16<T>(sp, i0, i1, [&](int, float v, int slot) {
-        const Acc dlt = v - mean16;
-        q16[slot % 4] += dlt * dlt;
-      });
-      const Acc ss16 = group_all<L>((q16[0] + q16[1]) + (q16[2] + q16[3]), [](Acc a, Acc b) { return a + b; });
-      if (live && h == 0) {
-        if (p.mean_out) put_stat(p.mean_out, p.out_dtype, row, mean16);
-        if (p.var_out) put_stat(p.var_out, p.out_dtype, row, ss16 / p.denom);
-      }
-      return;
-    }
-    int i = i0;
-    for (; i + 8 <= i1; i += 8) {
-      T raw[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s[j % 4] += Cvt<Acc, T>::to(raw[j]);
-    }
-    for (; i < i1; ++i) s[0] += Cvt<Acc, T>::to(sp[i]);
+    smem_visit<T>(sp, n, i0, i1, rot, [&](int, auto x, int slot) { s[slot % 4] += Cvt<Acc, decltype(x)>::to(x); });
     const Acc sum = group_all<L>((s[0] + s[1]) + (s[2] + s[3]), [](Acc a, Acc b) { return a + b; });
     const Acc mean = sum / p.cols_acc;
     Acc q[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
-    i = i0;
-    for (; i + 8 <= i1; i += 8) {
-      T raw[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) raw[j] = sp[i + j];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const Acc dlt = Cvt<Acc, T>::to(raw[j]) - mean;
-        q[j % 4] += dlt * dlt;
-      }
-    }
-    for (; i < i1; ++i) {
-      const Acc dlt = Cvt<Acc, T>::to(sp[i]) - mean;
-      q[0] += dlt * dlt;
-    }
+    smem_visit<T>(sp, n, i0, i1, rot, [&](int, auto x, int slot) {
+      const Acc dlt = Cvt<Acc, decltype(x)>::to(x) - mean;
+      q[slot % 4] += dlt * dlt;
+    });
     const Acc ss = group_all<L>((q[0] + q[1]) + (q[2] + q[3]), [](Acc a, Acc b) { return a + b; });
     if (live && h == 0) {
       if (p.mean_out) put_stat(p.mean_out, p.out_dtype, row, mean);
@@ -1086,7 +1051,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), false)) {
+  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), kStagedStats, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     typename StagedStats<T, Acc>::Params sp{denom, static_cast<Acc>(n), d->mean, d->var, out_dtype};
     return launch_rows_staged<T, StagedStats<T, Acc>>(x, d->rows, static_cast<int>(n), sp, stream);

@@ -155,3 +155,67 @@ def test_large_and_canaries():
     assert torch.equal(a, pb.sum(x, axis=-1))
     idx = pb.argmax(x, axis=-1)
     assert torch.equal(idx, x.argmax(-1))
+
+
+# ---- rows that ARE whole 16-byte vectors: visited from staggered starts, wrapped around ---------
+ALIGNED_16 = [(5000, 8), (4096, 16), (6001, 24), (4500, 64), (4099, 96), (5000, 128), (4097, 256)]
+ALIGNED_32 = [(5000, 4), (4096, 8), (6001, 24), (4500, 40), (4099, 64), (4200, 128), (4097, 208)]
+
+
+@pytest.mark.parametrize("rows,cols", ALIGNED_16)
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+def test_aligned_16bit_rows(oracle, rows, cols, dt):
+    rng = np.random.default_rng(rows + cols)
+    # few distinct values: every row has its extreme several times, on both sides of the wrap
+    x32 = rng.integers(-3, 4, size=(rows, cols)).astype(np.float32)
+    x32[7, :] = -np.inf           # nothing beats the identity: index 0
+    x32[8, :] = 2.0               # all equal: index 0
+    xt = torch.from_numpy(x32).cuda().to(dt)
+    idx, val = pb.argmax_with_value(xt, axis=-1)
+    assert np.array_equal(idx.cpu().numpy(), oracle.argreduce("argmax", x32, -1))
+    assert np.array_equal(val.float().cpu().numpy()[9:], oracle.reduce("max", x32, [-1])[9:])
+    assert np.array_equal(pb.argmin(xt, axis=-1).cpu().numpy()[9:], oracle.argreduce("argmin", x32, -1)[9:])
+    xr = torch.from_numpy(rng.standard_normal((rows, cols)).astype(np.float32)).to(dt)
+    xr32 = xr.float().numpy()
+    xd = xr.cuda()
+    m, v = pb.row_mean_var(xd, out_dtype="float32")
+    mean, var = oracle.rowstats_f32(xr32, unbiased=True)
+    np.testing.assert_allclose(m.cpu().numpy(), mean, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(v.cpu().numpy(), var, rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(ops.logsumexp(xd, -1).float().cpu().numpy(), oracle.logsumexp(xr32, [-1]),
+                               rtol=G.BF16_RTOL)
+    np.testing.assert_allclose(pb.sum(xd, axis=-1, dtype="float32").cpu().numpy(), oracle.reduce("sum", xr32, [-1]),
+                               rtol=1e-5, atol=1e-5 * np.abs(xr32).sum(-1).max())
+    assert np.array_equal(pb.max(xd, axis=-1).float().cpu().numpy(), oracle.reduce("max", xr32, [-1]))
+    assert np.array_equal(idx.cpu().numpy()[:7], oracle.argreduce("argmax", x32, -1)[:7])
+
+
+@pytest.mark.parametrize("rows,cols", ALIGNED_32)
+def test_aligned_fp32_int_rows(oracle, rows, cols):
+    rng = np.random.default_rng(rows * 5 + cols)
+    xi = rng.integers(-2, 3, size=(rows, cols)).astype(np.int32)
+    xt = G.to_dev(xi)
+    assert np.array_equal(G.to_np(pb.argmax(xt, axis=-1)), oracle.argreduce("argmax", xi, -1))
+    assert np.array_equal(G.to_np(pb.argmin(xt, axis=-1, dtype="int32")), oracle.argreduce("argmin", xi, -1).astype(np.int32))
+    assert np.array_equal(G.to_np(pb.sum(xt, axis=-1)), oracle.reduce("sum", xi, [-1], out_dtype=np.int64))
+    if cols % 2 == 0:
+        xl = rng.integers(-2, 3, size=(rows, cols // 2)).astype(np.int64)
+        assert np.array_equal(G.to_np(pb.argmax(G.to_dev(xl), axis=-1)), oracle.argreduce("argmax", xl, -1))
+        assert np.array_equal(G.to_np(pb.min(G.to_dev(xl), axis=-1)), oracle.reduce("min", xl, [-1]))
+    xf = rng.standard_normal((rows, cols)).astype(np.float32)
+    xf[3, :] = -np.inf
+    xd = G.to_dev(xf)
+    assert np.array_equal(G.to_np(pb.argmax(xd, axis=-1)), oracle.argreduce("argmax", xf, -1))
+    got = G.to_np(ops.logsumexp(xd, -1))
+    want = oracle.logsumexp(xf, [-1])
+    assert got[3] == -np.inf
+    np.testing.assert_allclose(np.delete(got, 3), np.delete(want, 3), rtol=1e-5, atol=1e-6)
+    xf[3, :] = 1.0
+    xd = G.to_dev(xf)
+    m, v = pb.row_mean_var(xd)
+    mean, var = oracle.rowstats_f32(xf, unbiased=True)
+    np.testing.assert_allclose(m.cpu().numpy(), mean, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(v.cpu().numpy(), var, rtol=1e-5, atol=1e-7)
+    for op in ("sum", "max", "min", "mean"):
+        got = G.to_np(getattr(pb, op)(xd, axis=-1))
+        G.assert_reduce_close(got, oracle.reduce(op, xf, [-1]), xf, [-1], op, G.FP32_RTOL)

@@ -23,11 +23,12 @@ def t(fn, n=3):
 
 
 COLS = [int(c) for c in sys.argv[1].split(",")] if len(sys.argv) > 1 else [3, 7, 10, 21, 33, 49, 101, 127]
+ALIGNED_TOO = len(sys.argv) > 2 and sys.argv[2] == "all"   # also rows that are whole 16-byte vectors
 NBYTES = 1 << 30
 for dt in (torch.float32, torch.bfloat16, torch.int64):
     es = torch.empty((), dtype=dt).element_size()
     for cols in COLS:
-        if cols * es % 16 == 0 or cols * es > 1024:
+        if (cols * es % 16 == 0 and not ALIGNED_TOO) or cols * es > 1024:
             continue
         rows = NBYTES // (cols * es)
         if dt == torch.int64:
