@@ -345,7 +345,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
     const long long nvec_row = row_bytes / 16;
     // short rows of any alignment: a thread per row out of shared memory (rows_staged.cuh)
     static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes, static_cast<int>(sizeof(T)), kStagedArg, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
+    if (!no_staged && !no_multi && !force_g && !force_u && staged_rows_ok(g.pre, row_bytes, static_cast<int>(sizeof(T)), kStagedArg, reinterpret_cast<uintptr_t>(x) % 16 == 0)) {
       typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
       return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
     }

@@ -473,7 +473,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   const long long nvec_row = cols / VE;
   static const bool no_multi = getenv("B200PHI_LSE_NO_MULTI") != nullptr;
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-  if (!no_staged && !no_multi && !env_u && staged_rows_ok(rows, row_bytes, static_cast<int>(sizeof(T)), kStagedLse, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
+  if (!no_staged && !no_multi && !env_u && staged_rows_ok(rows, row_bytes, static_cast<int>(sizeof(T)), kStagedLse, reinterpret_cast<uintptr_t>(x) % 16 == 0)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     typename StagedLse<T, A>::Params sp{d->out, d->dtype};
     return launch_rows_staged<T, StagedLse<T, A>>(x, rows, static_cast<int>(cols), sp, stream);

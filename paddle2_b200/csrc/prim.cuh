@@ -444,60 +444,41 @@ __device__ __forceinline__ void smem_walk_range(const T* __restrict__ sp, int i0
     for (; i < i1; ++i) f(i, sp[i], 0);
   }
 }
-// Visit a whole row of n elements starting `rot` units into it and wrapping around (a unit is an
-// element of 4 or 8 bytes, or a 32-bit word of two 16-bit floats): rows whose pitch is a multiple
-// of 16 bytes put the threads of a warp on a few shared-memory banks when they all start at element
-// 0; started at staggered units they spread over all 32 (see rows_staged.cuh).  Every thread runs
-// the same loop -- the wrap is arithmetic on the unit index, not a second loop, so threads with
-// different starts do not diverge.  rot < 0: the plain ascending walk of [i0, i1).
+// Visit a whole row of n elements that is whole, 16-byte aligned vectors, starting `rot` VECTORS
+// into it and wrapping around: such rows have a pitch of nv * 16 bytes, so threads that all start at
+// vector 0 share 8 / gcd(nv, 8) of the 8 bank groups a 16-byte shared load is served from; started
+// at staggered vectors (rows_staged.cuh) the 8 threads of a load phase hit 8 different groups.  One
+// LDS.128 per vector and one wrap test per vector; every thread runs the same loop, so threads
+// with different starts do not diverge.  rot < 0: the plain ascending walk of [i0, i1).
 template <typename T, typename F>
 __device__ __forceinline__ void smem_visit(const T* __restrict__ sp, int n, int i0, int i1, int rot, F f) {
   if (rot < 0) {
     smem_walk_range<T>(sp, i0, i1, f);
     return;
   }
-  if constexpr (Is16Float<T>::value) {
-    const uint32_t* __restrict__ w = reinterpret_cast<const uint32_t*>(sp);  // (the row is 4-byte aligned)
-    const int nu = n >> 1;  // a multiple of 4: the row is whole 16-byte vectors
-    int u = rot;
-    for (int k = 0; k < nu; k += 4) {
-      uint32_t r[4];
-      int uu[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uu[j] = u + j;
-        if (uu[j] >= nu) uu[j] -= nu;
-        r[j] = w[uu[j]];
-      }
-      u += 4;
-      if (u >= nu) u -= nu;
+  constexpr int VE = 16 / static_cast<int>(sizeof(T));
+  const V16* __restrict__ vp = reinterpret_cast<const V16*>(sp);
+  const int nv = n / VE;
+  int v = rot;
+  for (int k = 0; k < nv; ++k) {
+    const V16 raw = vp[v];
+    const int e0 = v * VE;
+    if constexpr (Is16Float<T>::value) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float lo, hi;
-        widen_pair<T>(r[j], lo, hi);
-        f(2 * uu[j], lo, 2 * j);
-        f(2 * uu[j] + 1, hi, 2 * j + 1);
+        widen_pair<T>(raw.w[j], lo, hi);
+        f(e0 + 2 * j, lo, 2 * j);
+        f(e0 + 2 * j + 1, hi, 2 * j + 1);
       }
-    }
-  } else if constexpr (sizeof(T) >= 4) {
-    constexpr int kU = sizeof(T) == 4 ? 4 : 2;  // n is a multiple of kU
-    int u = rot;
-    for (int k = 0; k < n; k += kU) {
-      T r[kU];
-      int uu[kU];
+    } else {
+      typename VecOf<T>::U u;
+      u.raw = raw;
 #pragma unroll
-      for (int j = 0; j < kU; ++j) {
-        uu[j] = u + j;
-        if (uu[j] >= n) uu[j] -= n;
-        r[j] = sp[uu[j]];
-      }
-      u += kU;
-      if (u >= n) u -= n;
-#pragma unroll
-      for (int j = 0; j < kU; ++j) f(uu[j], r[j], j);
+      for (int j = 0; j < VE; ++j) f(e0 + j, u.e[j], j);
     }
-  } else {
-    smem_walk_range<T>(sp, i0, i1, f);
+    ++v;
+    if (v >= nv) v = 0;
   }
 }
 

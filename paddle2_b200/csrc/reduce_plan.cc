@@ -662,7 +662,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
        kind == kRowBatch) &&
       t.force_kind < 0 &&
       !t.no_row_staged && !t.no_row_batch && staged_rows_ok(p->rows, p->cols * static_cast<long long>(esize), esize, kStagedReduce,
-                     reinterpret_cast<uintptr_t>(d->x) % 4 == 0)) {
+                     reinterpret_cast<uintptr_t>(d->x) % 16 == 0)) {
     kind = kRowStaged;
   }
   p->kind = kind;

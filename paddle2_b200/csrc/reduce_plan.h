@@ -131,14 +131,16 @@ inline int staged_stage_bytes(long long row_bytes) {
 long long staged_max_row_bytes();  // B200PHI_STAGED_MAX_BYTES overrides both upper limits (reduce_plan.cc)
 int staged_aligned_mode();         // B200PHI_STAGED_ALIGNED: 0 never, 1 (default) see below, 2 wherever possible
 enum StagedFamily { kStagedReduce = 0, kStagedArg = 1, kStagedStats = 2, kStagedLse = 3 };
-// Rows that are whole 16-byte vectors (pitch a multiple of 16 bytes) are visited from staggered
-// starts (rows_staged.cuh).  They have vector kernels of their own, so the staged kernels take them
-// only where those measured slower (tools/stagedbench.py ... all, profiles/r02_stagedbench_aligned_raw.txt):
-// argmax / statistics up to 256 bytes per row, logsumexp up to 192, and the plain reductions
-// between 64 and 256 bytes when the row is not a power-of-two number of vectors (row_tiny_kernel
-// rounds its lanes up: 40 fp32 columns 4.6 -> 5.8 TB/s).
-// base4: the tensor starts on a 4-byte boundary (16-bit rows are read as 32-bit words).
-inline bool staged_rows_ok(long long rows, long long row_bytes, int esize, int family, bool base4) {
+// Rows that are whole 16-byte vectors (and start on 16-byte boundaries) are visited vector by vector
+// from staggered starts (rows_staged.cuh).  They have vector kernels of their own, so the staged
+// kernels take them only where those measured slower (tools/stagedbench.py ... all,
+// profiles/r02_stagedbench_aligned_raw.txt): statistics at every length, argmax / logsumexp at every
+// length for 4- and 8-byte elements and up to 416 bytes per row for 16-bit ones, the plain
+// reductions when the row is not a power-of-two number of vectors (row_tiny_kernel rounds its lanes
+// up) -- from 64 bytes; 16-bit rows up to 256 bytes -- and, for 4- and 8-byte elements, any row of
+// 192 bytes or more.
+// base16: the tensor starts on a 16-byte boundary (such rows are read with 16-byte shared loads).
+inline bool staged_rows_ok(long long rows, long long row_bytes, int esize, int family, bool base16) {
   const bool plain_reduce = family == kStagedReduce;
   const long long env_max = staged_max_row_bytes();
   const long long max_bytes = env_max > 0 ? env_max : (esize <= 2 ? 512 : 832);
@@ -146,12 +148,17 @@ inline bool staged_rows_ok(long long rows, long long row_bytes, int esize, int f
   if (row_bytes < min_bytes || row_bytes > max_bytes || rows < 4096) return false;
   if (row_bytes % 16 == 0) {
     const int mode = staged_aligned_mode();
-    if (mode == 0 || !base4 || esize < 2) return false;  // (1-byte rows have no staggered walk)
+    if (mode == 0 || !base16) return false;
     if (mode == 1) {
       const long long nvec = row_bytes / 16;
-      if (plain_reduce && ((nvec & (nvec - 1)) == 0 || row_bytes < 64 || row_bytes > 256)) return false;
-      if ((family == kStagedArg || family == kStagedStats) && row_bytes > 256) return false;
-      if (family == kStagedLse && row_bytes > 192) return false;
+      const bool pow2 = (nvec & (nvec - 1)) == 0;
+      if (plain_reduce) {
+        const bool ok = esize >= 4 ? ((!pow2 && row_bytes >= 64) || row_bytes >= 192)
+                                   : (!pow2 && row_bytes >= 64 && row_bytes <= 256);
+        if (!ok) return false;
+      } else if (family != kStagedStats && esize < 4 && row_bytes > 416) {
+        return false;
+      }
     }
   }
   return true;

@@ -27,12 +27,13 @@
 // for lane h of the row's L lanes and its element range [i0, i1); every thread of the CTA calls
 // it (dead rows with i0 == i1 and live == false), so that it may use group_all<L>.
 //
-// Rows that ARE whole 16-byte vectors have a pitch of 4k words: started at element 0, the 32
-// threads of a warp would hit 32 / gcd-many banks (a 128-byte row: one bank, a 32-way conflict).
-// Such rows are visited from a staggered start `rot` and wrapped around (smem_visit): thread t
-// starts floor(t * min(pitch_words, 32) / 32) units into its row, which spreads a warp over all the
-// banks (at most 2-way conflicts for any pitch; simulated for every pitch up to 1 KiB).  Consumers
-// whose result depends on the visiting order (argmax ties) compare indices explicitly then.
+// Rows that ARE whole 16-byte vectors (and start on 16-byte boundaries) are read with 16-byte
+// shared loads, which are served 8 threads at a time from 8 groups of 4 banks: with a pitch of nv
+// vectors, threads that all start at vector 0 share 8 / gcd(nv, 8) groups (a 128-byte row: one
+// group, an 8-way conflict).  Such rows are visited from a staggered start and wrapped around
+// (smem_visit): thread t starts floor((t mod 8) * gcd(nv, 8) / 8) vectors into its row, which
+// puts the 8 threads of a phase on 8 different groups.  Consumers whose result depends on the
+// visiting order (argmax ties) compare indices explicitly then.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -47,7 +48,7 @@ namespace b200phi {
 template <typename T, typename C, int L>
 __global__ void __launch_bounds__(kStThreads * L)
     rows_staged_kernel(const T* __restrict__ x, long long rows, int cols, int stages, int stage_bytes,
-                       int rot_pitch, typename C::Params prm) {
+                       int rot_share, typename C::Params prm) {
   extern __shared__ __align__(128) unsigned char st_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem + static_cast<size_t>(stages) * stage_bytes);
   const int tid = threadIdx.x;
@@ -65,14 +66,12 @@ __global__ void __launch_bounds__(kStThreads * L)
   const int chunk = (cols + L - 1) / L;
   const int i0 = h * chunk < cols ? h * chunk : cols;
   const int i1 = i0 + chunk < cols ? i0 + chunk : cols;
-  // staggered start, in visiting units (smem_visit), for rows whose pitch is a multiple of 16
-  // bytes; rot_pitch = min(pitch in 4-byte words, 32), 0 for every other row (rot = -1: plain walk)
+  // staggered start, in 16-byte vectors (smem_visit), for rows that are whole aligned vectors:
+  // rot_share = gcd(vectors per row, 8) threads of a load phase share a bank group when they all
+  // start at vector 0, so thread t starts floor((t mod 8) * rot_share / 8) vectors in.
+  // rot_share = 0 for every other row (rot = -1: plain walk).
   int rot = -1;
-  if (L == 1 && rot_pitch > 0 && sizeof(T) >= 2) {
-    constexpr int kUnit = sizeof(T) >= 4 ? static_cast<int>(sizeof(T)) : 4;  // bytes per visiting unit
-    const int nu = static_cast<int>(row_bytes) / kUnit;
-    rot = (((tid & 31) * rot_pitch) >> 5) % nu;
-  }
+  if (L == 1 && rot_share > 0) rot = (((tid & 7) * rot_share) >> 3) % (static_cast<int>(row_bytes) >> 4);
 
   // Start the copy of this CTA's i-th span into stage i % stages (every thread calls).
   auto issue = [&](long long i) {
@@ -145,8 +144,12 @@ int launch_rows_staged_l(const T* x, long long rows, int cols, const typename C:
   if (per_sm < 1) per_sm = 1;
   long long ctas = static_cast<long long>(current_sm_count()) * per_sm;
   if (ctas > ntiles) ctas = ntiles;
-  const int rot_pitch = (row_bytes % 16 == 0) ? static_cast<int>(row_bytes / 4 < 32 ? row_bytes / 4 : 32) : 0;
-  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, rot_pitch, prm);
+  int rot_share = 0;  // rows that are whole vectors AND start on 16-byte boundaries: staggered vector walk
+  if (row_bytes % 16 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0) {
+    const long long nv = row_bytes / 16;
+    rot_share = (nv % 8 == 0) ? 8 : ((nv % 4 == 0) ? 4 : ((nv % 2 == 0) ? 2 : 1));
+  }
+  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, rot_share, prm);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);
   return 0;

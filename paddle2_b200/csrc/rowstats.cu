@@ -1051,7 +1051,7 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
-  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), kStagedStats, reinterpret_cast<uintptr_t>(x) % 4 == 0)) {
+  if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), kStagedStats, reinterpret_cast<uintptr_t>(x) % 16 == 0)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
     typename StagedStats<T, Acc>::Params sp{denom, static_cast<Acc>(n), d->mean, d->var, out_dtype};
     return launch_rows_staged<T, StagedStats<T, Acc>>(x, d->rows, static_cast<int>(n), sp, stream);
