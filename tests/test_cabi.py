@@ -98,6 +98,39 @@ def test_planner_errors_match_reference_messages():
         _lib.check(1)
 
 
+def test_short_rows_take_the_staged_plan_by_the_measured_limits():
+    """kRowStaged (14): rows of 128 bulk-copied into shared memory, a thread per row
+    (rows_staged.cuh).  Selection is host logic (reduce_plan.h: staged_rows_ok)."""
+    from paddle2_b200 import _lib
+    lib = _lib.lib()
+    STAGED = 14
+
+    def kind(rows, cols, dt, x=0, op=0):
+        d = _reduce_desc([rows, cols], [1], op=op, in_dtype=dt)
+        d.x = x
+        return lib.b200phi_reduce_plan_kind(C.byref(d)), lib.b200phi_reduce_workspace(C.byref(d))
+
+    A = 1 << 20                                            # a 16-byte aligned address, B = A + 2 is not
+    assert kind(100000, 101, 16, A) == (STAGED, 0)          # bf16 202-byte rows, ragged
+    assert kind(100000, 101, 16, A + 2) == (STAGED, 0)      # ... whatever the base alignment
+    assert kind(100000, 21, 10, A)[0] == STAGED             # fp32 84-byte rows
+    assert kind(100000, 10, 10, A)[0] != STAGED             # plain reductions under 64 bytes: sub-warp kernel
+    assert kind(100000, 301, 16, A)[0] != STAGED            # 602 bytes: beyond the 16-bit limit (512)
+    assert kind(100000, 201, 10, A)[0] == STAGED            # fp32 804 bytes: within 832
+    assert kind(100000, 251, 10, A)[0] != STAGED
+    assert kind(1000, 101, 16, A)[0] != STAGED              # too few rows to fill the machine
+    # rows that are whole 16-byte vectors: only where the vector kernels are weak, and only from a
+    # 16-byte aligned base (they are read with 16-byte shared loads)
+    assert kind(100000, 32, 10, A)[0] != STAGED             # fp32 128 bytes = 8 vectors: row_tiny_kernel
+    assert kind(100000, 40, 10, A)[0] == STAGED             # 10 vectors: not a power of two
+    assert kind(100000, 40, 10, A + 4)[0] != STAGED
+    assert kind(100000, 64, 10, A)[0] == STAGED             # 256 bytes: from 192 bytes on for 4-byte elements
+    assert kind(100000, 96, 16, A)[0] == STAGED             # bf16 192 bytes = 12 vectors
+    assert kind(100000, 128, 16, A)[0] != STAGED            # bf16 256 bytes = 16 vectors
+    # every plan of this family needs no scratch, whatever the pointer
+    assert kind(100000, 40, 10, 0)[1] == 0
+
+
 def test_workspace_query_is_pure_host_logic():
     from paddle2_b200 import _lib
     lib = _lib.lib()
