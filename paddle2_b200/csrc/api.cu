@@ -56,6 +56,15 @@ int staged_stages() {
   }();
   return v;
 }
+// Rows per thread and span of the same kernels: B200PHI_STAGED_RPT (1..8; 0: by row length).
+int staged_rows_per_thread() {
+  static const int v = [] {
+    const char* e = getenv("B200PHI_STAGED_RPT");
+    const int n = e ? atoi(e) : 0;
+    return n < 0 ? 0 : (n > 8 ? 8 : n);
+  }();
+  return v;
+}
 // Lanes per row of the same kernels: B200PHI_STAGED_LANES (1, 2 or 4).  One lane measured best
 // at every row length tried (101 bf16 columns: sum 6.2 / 6.0 / 4.1 TB/s, mean+var 5.2 / 4.1 / 2.7
 // for 1 / 2 / 4 lanes).

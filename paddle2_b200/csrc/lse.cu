@@ -432,8 +432,9 @@ struct StagedLse {
                                              bool live, long long row, int h, const Params& p) {
     A m[4] = {LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf(), LseMath<A>::neg_inf()};
     smem_visit<T>(sp, n, i0, i1, rot, [&](int, auto x, int slot) {
-      const A a = Cvt<A, decltype(x)>::to(x);
-      m[slot % 4] = a > m[slot % 4] ? a : m[slot % 4];
+      // (fmax: one FMNMX where the compare / select pair is two instructions; a NaN still reaches
+      // the result through the exponent sweep)
+      m[slot % 4] = fmax(m[slot % 4], Cvt<A, decltype(x)>::to(x));
     });
     A mx = m[1] > m[0] ? m[1] : m[0];
     const A my = m[3] > m[2] ? m[3] : m[2];

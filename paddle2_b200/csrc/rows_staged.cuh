@@ -48,13 +48,18 @@ namespace b200phi {
 template <typename T, typename C, int L>
 __global__ void __launch_bounds__(kStThreads * L)
     rows_staged_kernel(const T* __restrict__ x, long long rows, int cols, int stages, int stage_bytes,
-                       int rot_share, typename C::Params prm) {
+                       int rot_share, int rpt, typename C::Params prm) {
   extern __shared__ __align__(128) unsigned char st_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem + static_cast<size_t>(stages) * stage_bytes);
   const int tid = threadIdx.x;
   const int r = tid / L, h = tid % L;
   const long long row_bytes = static_cast<long long>(cols) * static_cast<long long>(sizeof(T));
-  const long long ntiles = (rows + kStThreads - 1) / kStThreads;
+  // rpt rows per thread and span (very short rows: a span's fixed costs -- barrier, mbarrier wait,
+  // window arithmetic -- would otherwise be paid once per 16-byte row); thread t takes rows
+  // t, t + 128, ... of the span, so the bank pattern and the coalesced result stores stay those of
+  // one row per thread
+  const int span_rows = kStThreads * rpt;
+  const long long ntiles = (rows + span_rows - 1) / span_rows;
   const long long my = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
@@ -76,9 +81,9 @@ __global__ void __launch_bounds__(kStThreads * L)
   // Start the copy of this CTA's i-th span into stage i % stages (every thread calls).
   auto issue = [&](long long i) {
     const int s = static_cast<int>(i % stages);
-    const long long row0 = (blockIdx.x + i * static_cast<long long>(gridDim.x)) * kStThreads;
+    const long long row0 = (blockIdx.x + i * static_cast<long long>(gridDim.x)) * span_rows;
     const long long left = rows - row0;
-    const int n = left < kStThreads ? static_cast<int>(left) : kStThreads;
+    const int n = left < span_rows ? static_cast<int>(left) : span_rows;
     const uintptr_t b0 = xb + static_cast<uintptr_t>(row0 * row_bytes);
     const uintptr_t b1 = b0 + static_cast<uintptr_t>(n * row_bytes);
     const uintptr_t a0 = b0 & ~static_cast<uintptr_t>(15);
@@ -105,12 +110,15 @@ __global__ void __launch_bounds__(kStThreads * L)
     if (stages == 1) __syncthreads();  // (the byte-copied edges of THIS span were stored just now)
     const int s = static_cast<int>(i % stages);
     mbar_wait(&full[s], static_cast<uint32_t>((i / stages) & 1));
-    const long long row0 = (blockIdx.x + i * static_cast<long long>(gridDim.x)) * kStThreads;
+    const long long row0 = (blockIdx.x + i * static_cast<long long>(gridDim.x)) * span_rows;
     const uintptr_t b0 = xb + static_cast<uintptr_t>(row0 * row_bytes);
-    const bool live = row0 + r < rows;
-    const unsigned char* sp = st_smem + static_cast<size_t>(s) * stage_bytes + (b0 & 15) +
-                              static_cast<size_t>(r) * static_cast<size_t>(row_bytes);
-    C::template run<L>(reinterpret_cast<const T*>(sp), cols, live ? i0 : 0, live ? i1 : 0, rot, live, row0 + r, h, prm);
+    const unsigned char* base = st_smem + static_cast<size_t>(s) * stage_bytes + (b0 & 15);
+    for (int j = 0; j < rpt; ++j) {
+      const int rs = j * kStThreads + r;  // row of the span
+      const bool live = row0 + rs < rows;
+      const unsigned char* sp = base + static_cast<size_t>(rs) * static_cast<size_t>(row_bytes);
+      C::template run<L>(reinterpret_cast<const T*>(sp), cols, live ? i0 : 0, live ? i1 : 0, rot, live, row0 + rs, h, prm);
+    }
   }
 }
 
@@ -121,11 +129,20 @@ int cuda_status(cudaError_t e);
 // (1, 2 or 4; default by row length).
 int staged_stages();
 int staged_lanes();
+int staged_rows_per_thread();  // B200PHI_STAGED_RPT (1..8; 0 / unset: about 256 bytes of rows per thread)
 
 template <typename T, typename C, int L>
 int launch_rows_staged_l(const T* x, long long rows, int cols, const typename C::Params& prm, cudaStream_t stream) {
   const long long row_bytes = static_cast<long long>(cols) * static_cast<long long>(sizeof(T));
-  const int stage_bytes = staged_stage_bytes(row_bytes);
+  // rows per thread: about 256 bytes of rows per thread and span (one lane per row only)
+  int rpt = 1;
+  if (L == 1) {
+    const int want = staged_rows_per_thread();
+    rpt = want > 0 ? want : static_cast<int>(256 / row_bytes);
+    rpt = rpt < 1 ? 1 : (rpt > 8 ? 8 : rpt);
+    while (rpt > 1 && row_bytes * rpt * kStThreads > 48 * 1024) --rpt;  // (a span stays under 48 KiB)
+  }
+  const int stage_bytes = staged_stage_bytes(row_bytes * rpt);
   int stages = staged_stages();
   while (stages > 1 && static_cast<long long>(stages) * stage_bytes > 100 * 1024) --stages;
   const size_t smem = static_cast<size_t>(stages) * stage_bytes + 64;
@@ -137,7 +154,7 @@ int launch_rows_staged_l(const T* x, long long rows, int cols, const typename C:
     if (ea != cudaSuccess) return cuda_status(ea);
     attr_set[dev] = true;
   }
-  const long long ntiles = (rows + kStThreads - 1) / kStThreads;
+  const long long ntiles = (rows + static_cast<long long>(kStThreads) * rpt - 1) / (static_cast<long long>(kStThreads) * rpt);
   long long per_sm = static_cast<long long>(220 * 1024) / static_cast<long long>(smem + 1024);
   const long long by_threads = 2048 / (kStThreads * L);
   if (per_sm > by_threads) per_sm = by_threads;
@@ -149,7 +166,7 @@ int launch_rows_staged_l(const T* x, long long rows, int cols, const typename C:
     const long long nv = row_bytes / 16;
     rot_share = (nv % 8 == 0) ? 8 : ((nv % 4 == 0) ? 4 : ((nv % 2 == 0) ? 2 : 1));
   }
-  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, rot_share, prm);
+  rows_staged_kernel<T, C, L><<<static_cast<unsigned>(ctas), kStThreads * L, smem, stream>>>(x, rows, cols, stages, stage_bytes, rot_share, rpt, prm);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_status(e);
   return 0;
