@@ -77,6 +77,11 @@ long long staged_max_row_bytes() {
   return v;
 }
 
+long long staged_min_row_bytes() {
+  static const long long v = env_ll("B200PHI_STAGED_MIN_BYTES", 0);
+  return v;
+}
+
 int staged_aligned_mode() {
   static const int v = static_cast<int>(env_ll("B200PHI_STAGED_ALIGNED", 1));
   return v;

@@ -125,10 +125,11 @@ inline int staged_stage_bytes(long long row_bytes) {
 // threads of a warp on the same shared-memory bank: thread t reads word (t * row_bytes + i) / 4, so
 // a pitch that is a multiple of 16 bytes (4 words) maps four or more lanes to one bank.
 // Measured limits (tools/stagedbench.py, profiles/r02_stagedbench_raw.txt): 16-bit rows up to 512
-// bytes, wider elements up to 832; below 32 / 64 bytes the plain reductions (sum, max ...) are
-// faster on the sub-warp scalar kernels (a thread per 12-byte row spends its time on the row's
-// fixed costs), while argmax, statistics and logsumexp gain at every length.
+// bytes, wider elements up to 832; below 16 / 32 / 64 bytes (2- / 4- / 8-byte elements) the plain
+// reductions (sum, max ...) are faster on the sub-warp scalar kernels, while argmax, statistics and
+// logsumexp gain at every length.
 long long staged_max_row_bytes();  // B200PHI_STAGED_MAX_BYTES overrides both upper limits (reduce_plan.cc)
+long long staged_min_row_bytes();  // B200PHI_STAGED_MIN_BYTES overrides the plain reductions' lower limits
 int staged_aligned_mode();         // B200PHI_STAGED_ALIGNED: 0 never, 1 (default) see below, 2 wherever possible
 enum StagedFamily { kStagedReduce = 0, kStagedArg = 1, kStagedStats = 2, kStagedLse = 3 };
 // Rows that are whole 16-byte vectors (and start on 16-byte boundaries) are visited vector by vector
@@ -144,7 +145,8 @@ inline bool staged_rows_ok(long long rows, long long row_bytes, int esize, int f
   const bool plain_reduce = family == kStagedReduce;
   const long long env_max = staged_max_row_bytes();
   const long long max_bytes = env_max > 0 ? env_max : (esize <= 2 ? 512 : 832);
-  const long long min_bytes = plain_reduce ? (esize <= 2 ? 32 : 64) : 2;
+  const long long env_min = staged_min_row_bytes();
+  const long long min_bytes = plain_reduce ? (env_min > 0 ? env_min : (esize <= 2 ? 16 : (esize == 4 ? 32 : 64))) : 2;
   if (row_bytes < min_bytes || row_bytes > max_bytes || rows < 4096) return false;
   if (row_bytes % 16 == 0) {
     const int mode = staged_aligned_mode();

@@ -114,7 +114,9 @@ def test_short_rows_take_the_staged_plan_by_the_measured_limits():
     assert kind(100000, 101, 16, A) == (STAGED, 0)          # bf16 202-byte rows, ragged
     assert kind(100000, 101, 16, A + 2) == (STAGED, 0)      # ... whatever the base alignment
     assert kind(100000, 21, 10, A)[0] == STAGED             # fp32 84-byte rows
-    assert kind(100000, 10, 10, A)[0] != STAGED             # plain reductions under 64 bytes: sub-warp kernel
+    assert kind(100000, 10, 10, A)[0] == STAGED             # fp32 40 bytes
+    assert kind(100000, 7, 10, A)[0] != STAGED              # plain reductions under 32 bytes (fp32): sub-warp kernel
+    assert kind(100000, 7, 9, A)[0] != STAGED               # ... under 64 bytes for 8-byte elements
     assert kind(100000, 301, 16, A)[0] != STAGED            # 602 bytes: beyond the 16-bit limit (512)
     assert kind(100000, 201, 10, A)[0] == STAGED            # fp32 804 bytes: within 832
     assert kind(100000, 251, 10, A)[0] != STAGED

@@ -20,9 +20,11 @@ STAGED = 14
 
 
 def staged_expected(x):
-    """The plain reductions leave rows under 32 bytes (16-bit) / 64 bytes to the sub-warp kernels."""
+    """The plain reductions leave rows under 16 / 32 / 64 bytes (2- / 4- / 8-byte elements) to the
+    sub-warp kernels."""
     row_bytes = x.shape[-1] * x.element_size()
-    return row_bytes >= (32 if x.element_size() <= 2 else 64)
+    es = x.element_size()
+    return row_bytes >= (16 if es <= 2 else (32 if es == 4 else 64))
 
 
 def plan_kind(x, op=L.SUM):
