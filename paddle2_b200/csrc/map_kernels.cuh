@@ -420,6 +420,64 @@ __global__ void __launch_bounds__(kBlock) map_ragged_kernel(MapFlatParams<Arity>
   }
 }
 
+// The flat cases that matter, as in the elementwise engine (bcast_flat_row_kernel): the first
+// operand has the output's shape and the other one or two are ONE ROW shared by every row -- a
+// compare against a row vector, max_grad along axis 0 (x against the row of maxima and the row of
+// upstream gradients).  No run-time operand-kind tests, no per-element "streamed or splat" selects
+// (map_flat_kernel with three operands: 92 registers, 23 % of the warp slots).  kRows: 1 or 2 shared
+// rows; kFullIs: which functor argument the full-shape operand is (binary form only).
+struct MapFlatRowParams {
+  const void* full;
+  const void* row[2];
+  void* out;
+  FastDiv upr;     // vectors per row
+  unsigned total;  // vectors in this slice of the output
+};
+template <typename TI, typename TO, typename F, int kRows, int kFullIs, int U>
+__global__ void __launch_bounds__(kBlock) map_flat_row_kernel(const __grid_constant__ MapFlatRowParams p, F f) {
+  using C = typename MapCompute<TI>::type;
+  constexpr int VE = VecOf<TI>::kElems;
+  constexpr int kOutBytes = VE * static_cast<int>(sizeof(TO));
+  const V16* __restrict__ xf = static_cast<const V16*>(p.full);
+  const V16* __restrict__ r0 = static_cast<const V16*>(p.row[0]);
+  const V16* __restrict__ r1 = static_cast<const V16*>(p.row[kRows - 1]);
+  for (unsigned base = blockIdx.x * (kBlock * U) + threadIdx.x; base < p.total; base += gridDim.x * (kBlock * U)) {
+    V16 a[U], b[U], c[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id < p.total) {
+        const unsigned col = id - fast_div(id, p.upr) * p.upr.d;
+        a[u] = ldg_stream16(xf + id);
+        b[u] = ldg_cached16(r0 + col);  // (the rows repeat: L1 serves them)
+        if constexpr (kRows == 2) c[u] = ldg_cached16(r1 + col);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned id = base + u * kBlock;
+      if (id >= p.total) continue;
+      typename VecOf<TI>::U wa, wb, wc;
+      wa.raw = a[u];
+      wb.raw = b[u];
+      if constexpr (kRows == 2) wc.raw = c[u];
+      struct alignas(kOutBytes) {
+        TO e[VE];
+      } o;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) {
+        const C xv = Cvt<C, TI>::to(wa.e[e]), rv = Cvt<C, TI>::to(wb.e[e]);
+        if constexpr (kRows == 2) {
+          o.e[e] = map_store_cast<TO>(f(xv, rv, Cvt<C, TI>::to(wc.e[e])));
+        } else {
+          o.e[e] = map_store_cast<TO>(kFullIs == 0 ? f(xv, rv, C(0)) : f(rv, xv, C(0)));
+        }
+      }
+      store_packed<kOutBytes>(reinterpret_cast<unsigned char*>(p.out) + static_cast<size_t>(id) * kOutBytes, &o);
+    }
+  }
+}
+
 // ---- launch ---------------------------------------------------------------------------------
 // The ragged case that matters, as in the elementwise engine: a full-shape operand against ONE
 // VALUE PER ROW ([N, C, 49] vs [C, 1]), binary functor.  No run-time operand-kind test, no run-time
@@ -579,6 +637,37 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mod
         rowscalar_done = true;
       }
     }
+    static const bool no_flat_row = getenv("B200PHI_NO_FLAT_ROW") != nullptr;
+    if constexpr (Arity == 2) {
+      const int fi = p.kind[0] == 0 ? 0 : (p.kind[1] == 0 ? 1 : -1);
+      const int si = fi < 0 ? -1 : 1 - fi;
+      if (!rowscalar_done && vec && fi >= 0 && p.kind[si] == 1 && !no_flat_row) {
+        MapFlatRowParams rp;
+        rp.full = p.in[fi];
+        rp.row[0] = rp.row[1] = p.in[si];
+        rp.out = p.out;
+        rp.upr = p.upr;
+        rp.total = p.total;
+        if (fi == 0)
+          map_flat_row_kernel<TI, TO, F, 1, 0, U><<<g, kBlock, 0, stream>>>(rp, f);
+        else
+          map_flat_row_kernel<TI, TO, F, 1, 1, U><<<g, kBlock, 0, stream>>>(rp, f);
+        rowscalar_done = true;
+      }
+    }
+    if constexpr (Arity == 3) {
+      if (vec && p.kind[0] == 0 && p.kind[1] == 1 && p.kind[2] == 1 && !no_flat_row) {
+        MapFlatRowParams rp;
+        rp.full = p.in[0];
+        rp.row[0] = p.in[1];
+        rp.row[1] = p.in[2];
+        rp.out = p.out;
+        rp.upr = p.upr;
+        rp.total = p.total;
+        map_flat_row_kernel<TI, TO, F, 2, 0, U><<<g, kBlock, 0, stream>>>(rp, f);
+        rowscalar_done = true;
+      }
+    }
     if (rowscalar_done) {
     } else if (mode == 2) {
       long long rb = ((static_cast<long long>(p.total) + VE - 1) / VE + kBlock * 2 - 1) / (kBlock * 2);
@@ -606,7 +695,28 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
   for (int i = 0; i < Arity; ++i)
     if (bp.stride[i][bp.ndim - 1] != 0)
       whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
-  const bool tile_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 512;
+  // a full-shape first operand against one or two shared rows has its own flat kernel
+  // (map_flat_row_kernel), which also beats the row kernel on longer rows (fp32 4096 columns:
+  // less_than 5.6 -> 6.3 TB/s, max_grad along axis 0 5.6 -> 6.3)
+  bool flat_row_pattern = Arity >= 2 && bp.ndim >= 2;
+  if (flat_row_pattern) {
+    int nfull = 0, nshared = 0, full_idx = -1;
+    for (int i = 0; i < Arity; ++i) {
+      bool same = bp.stride[i][bp.ndim - 1] == 1, shared = same;
+      long long r = bp.inner;
+      for (int k = bp.ndim - 2; k >= 0; --k) {
+        same = same && bp.stride[i][k] == r;
+        shared = shared && bp.stride[i][k] == 0;
+        r *= bp.extent[k];
+      }
+      nfull += same ? 1 : 0;
+      nshared += shared ? 1 : 0;
+      if (same) full_idx = i;
+    }
+    flat_row_pattern = nfull == 1 && nshared == Arity - 1 && (Arity == 2 || full_idx == 0);
+  }
+  const long long tile_vec_max = flat_row_pattern ? (1LL << 16) : 512;
+  const bool tile_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= tile_vec_max;
   const bool tile_scalar = !tile_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
   // ragged rows: the output and the full-shape operands as aligned units, the rest gathered
   bool tile_ragged = tile_scalar && Arity > 1 && bp.inner >= VE &&
