@@ -711,14 +711,17 @@ static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F
       // full-shape operand against one value per row: the specialised kernel
       const int fi = p.kind[0] == 0 ? 0 : (p.kind[1] == 0 ? 1 : -1);
       const int si = fi < 0 ? -1 : 1 - fi;
-      if (mode == 2 && fi >= 0 && p.kind[si] == 2 && p.istride[si] == 0 && no >= 1 && no <= 3 &&
+      // (rows that are whole vectors take the same kernel: its units then never straddle two rows;
+      // the general flat kernel unravels the row and tests the operand kinds per unit -- relu(x+y)
+      // fp32 [10699,64,196]+[64,1] 5.75 TB/s)
+      if ((mode == 2 || mode == 1) && fi >= 0 && p.kind[si] == 2 && p.istride[si] == 0 && no >= 1 && no <= 3 &&
           reinterpret_cast<uintptr_t>(p.in[fi]) % 16 == 0) {
         RaggedScalarParams rp;
         rp.full = p.in[fi];
         rp.scalar = p.in[si];
         rp.out = p.out;
-        rp.inner = p.upr;
-        rp.total = p.total;
+        rp.inner = mode == 2 ? p.upr : make_fast_div(static_cast<unsigned>(bp.inner));  // elements per row
+        rp.total = mode == 2 ? p.total : p.total * VE;                                  // elements
         rp.nouter = no;
         for (int k = 0; k < 3; ++k) {
           const int src = no - 3 + k;
@@ -726,7 +729,7 @@ static int launch_flat(const b200phi_elementwise_desc* d, const BcastPlan& bp, F
           rp.ostride[k] = src >= 0 ? p.ostride[si][src] : 0u;
         }
         constexpr int RU = 8;
-        long long rb = ((static_cast<long long>(p.total) / VE + 1) + kBlock * RU - 1) / (kBlock * RU);
+        long long rb = ((static_cast<long long>(rp.total) / VE + 1) + kBlock * RU - 1) / (kBlock * RU);
         if (rb > cap) rb = cap;
         if (si == 1)
           bcast_ragged_rowscalar_kernel<T, F, 1, RU><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(rp, f);
@@ -780,7 +783,24 @@ static int launch_bcast(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
   for (int i = 0; i < Arity; ++i)
     if (bp.stride[i][bp.ndim - 1] != 0)
       whole_vectors = whole_vectors && reinterpret_cast<uintptr_t>(d->in[i].data) % 16 == 0;
-  const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= 512;
+  // a full-shape operand against one value per row ([N,C,H*W] + [C,1]) keeps its flat kernel up to
+  // 1024 vectors per row (the row kernel's CTAs are short-lived there: 784-vector rows 5.8 TB/s)
+  bool row_scalar_pattern = Arity == 2 && !F::kInter && bp.ndim >= 2 && bp.ndim <= 4;
+  if (row_scalar_pattern) {
+    int nfull = 0, nscalar = 0;
+    for (int i = 0; i < Arity; ++i) {
+      bool same = bp.stride[i][bp.ndim - 1] == 1;
+      long long r = bp.inner;
+      for (int k = bp.ndim - 2; k >= 0; --k) {
+        same = same && bp.stride[i][k] == r;
+        r *= bp.extent[k];
+      }
+      nfull += same ? 1 : 0;
+      nscalar += bp.stride[i][bp.ndim - 1] == 0 ? 1 : 0;
+    }
+    row_scalar_pattern = nfull == 1 && nscalar == 1;
+  }
+  const bool flat_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= (row_scalar_pattern ? 1024 : 512);
   const bool flat_scalar = !flat_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
   // ragged rows: the output and the full-shape operands as aligned vectors, the rest gathered
   bool flat_ragged = flat_scalar && bp.inner >= VE && reinterpret_cast<uintptr_t>(d->out) % 16 == 0 &&

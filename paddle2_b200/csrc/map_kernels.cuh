@@ -613,14 +613,15 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mod
     if constexpr (Arity == 2) {
       const int fi = p.kind[0] == 0 ? 0 : (p.kind[1] == 0 ? 1 : -1);
       const int si = fi < 0 ? -1 : 1 - fi;
-      if (mode == 2 && fi >= 0 && p.kind[si] == 2 && p.istride[si] == 0 && no >= 1 && no <= 3 &&
+      // (rows that are whole vectors take the same kernel: its units then never straddle two rows)
+      if ((mode == 2 || mode == 1) && fi >= 0 && p.kind[si] == 2 && p.istride[si] == 0 && no >= 1 && no <= 3 &&
           reinterpret_cast<uintptr_t>(p.in[fi]) % 16 == 0) {
         MapRaggedScalarParams rp;
         rp.full = p.in[fi];
         rp.scalar = p.in[si];
         rp.out = p.out;
-        rp.inner = p.upr;
-        rp.total = p.total;
+        rp.inner = mode == 2 ? p.upr : make_fast_div(static_cast<unsigned>(bp.inner));  // elements per row
+        rp.total = mode == 2 ? p.total : p.total * VE;                                  // elements
         rp.nouter = no;
         for (int k = 0; k < 3; ++k) {
           const int src = no - 3 + k;
@@ -628,7 +629,7 @@ int launch_map_tile(const b200phi_map_desc* d, const BcastPlan& bp, F f, int mod
           rp.ostride[k] = src >= 0 ? p.ostride[si][src] : 0u;
         }
         constexpr int RU = 8;
-        long long rb = ((static_cast<long long>(p.total) / VE + 1) + kBlock * RU - 1) / (kBlock * RU);
+        long long rb = ((static_cast<long long>(rp.total) / VE + 1) + kBlock * RU - 1) / (kBlock * RU);
         if (rb > cap) rb = cap;
         if (si == 1)
           map_ragged_rowscalar_kernel<TI, TO, F, 1, RU><<<static_cast<unsigned>(rb), kBlock, 0, stream>>>(rp, f);
@@ -715,7 +716,23 @@ int launch_map(const b200phi_map_desc* d, const BcastPlan& bp, F f, cudaStream_t
     }
     flat_row_pattern = nfull == 1 && nshared == Arity - 1 && (Arity == 2 || full_idx == 0);
   }
-  const long long tile_vec_max = flat_row_pattern ? (1LL << 16) : 512;
+  // ... and so does a full-shape operand against one value per row, up to 1024 vectors per row
+  bool row_scalar_pattern = Arity == 2 && bp.ndim >= 2 && bp.ndim <= 4;
+  if (row_scalar_pattern) {
+    int nfull = 0, nscalar = 0;
+    for (int i = 0; i < Arity; ++i) {
+      bool same = bp.stride[i][bp.ndim - 1] == 1;
+      long long r = bp.inner;
+      for (int k = bp.ndim - 2; k >= 0; --k) {
+        same = same && bp.stride[i][k] == r;
+        r *= bp.extent[k];
+      }
+      nfull += same ? 1 : 0;
+      nscalar += bp.stride[i][bp.ndim - 1] == 0 ? 1 : 0;
+    }
+    row_scalar_pattern = nfull == 1 && nscalar == 1;
+  }
+  const long long tile_vec_max = flat_row_pattern ? (1LL << 16) : (row_scalar_pattern ? 1024 : 512);
   const bool tile_vec = whole_vectors && bp.rows > 1 && bp.inner / VE <= tile_vec_max;
   const bool tile_scalar = !tile_vec && bp.rows > 1 && !whole_vectors && bp.inner <= 1024;
   // ragged rows: the output and the full-shape operands as aligned units, the rest gathered
