@@ -349,7 +349,12 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       typename StagedArg<T, V, kMax>::Params sp{out, index_dtype, val_out};
       return launch_rows_staged<T, StagedArg<T, V, kMax>>(x, g.pre, static_cast<int>(g.n), sp, stream);
     }
-    if (aligned && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
+    // (16-bit rows of 33..128 vectors go to the value-sweep + position-sweep kernel below whether
+    // aligned or not -- bf16 512 / 1024 columns 7.1 TB/s against 5.8 / 6.4 on arg_multi_kernel, 256
+    // columns 5.75 against 6.02; B200PHI_ARG_PEEL_ALIGNED=0 keeps aligned rows on arg_multi_kernel)
+    static const bool peel_aligned = !(getenv("B200PHI_ARG_PEEL_ALIGNED") && atoi(getenv("B200PHI_ARG_PEEL_ALIGNED")) == 0);
+    const bool to_peel = sizeof(T) == 2 && peel_aligned && nvec_row > 32 && !arg_knobs().no_peel;
+    if (aligned && !to_peel && !no_multi && !force_g && !force_u && nvec_row <= 128 && g.pre >= 64) {
       const int LG = nvec_row <= 32 ? 8 : 16;
       const long long rows_per_warp = (32 / LG) * (nvec_row <= 64 ? 2 : 1);
       long long mc = (g.pre + kWarps * rows_per_warp - 1) / (kWarps * rows_per_warp);
@@ -370,7 +375,7 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row,
       // head element + vectors + tail element per lane (the 2-byte-load kernel: 1.6-2.0 TB/s)
       const long long nv_row = g.n / VecOf<T>::kElems;
-      if (!aligned && nv_row >= 4 && nv_row <= 128 && g.pre >= 64 && !force_g && !force_u && !arg_knobs().no_peel) {
+      if ((!aligned || (peel_aligned && nv_row > 32)) && nv_row >= 4 && nv_row <= 128 && g.pre >= 64 && !force_g && !force_u && !arg_knobs().no_peel) {
         const int lanes = nv_row <= 64 ? 8 : 16;
         long long pc = (g.pre + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
         if (pc > sm_cap) pc = sm_cap;

@@ -479,7 +479,12 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
     typename StagedLse<T, A>::Params sp{d->out, d->dtype};
     return launch_rows_staged<T, StagedLse<T, A>>(x, rows, static_cast<int>(cols), sp, stream);
   }
-  if (aligned && !no_multi && !env_u && nvec_row <= 128 && rows >= 64) {
+  // aligned 16-bit rows of more than this many vectors (and at most 128) take the peel kernel
+  // instead of lse_multi_kernel (B200PHI_LSE_PEEL_ALIGNED_MIN overrides)
+  static const long long lse_peel_aligned_min =
+      getenv("B200PHI_LSE_PEEL_ALIGNED_MIN") ? atoll(getenv("B200PHI_LSE_PEEL_ALIGNED_MIN")) : 16;  // (bf16 512 columns 5.5 -> 6.6 TB/s)
+  const bool lse_to_peel = sizeof(T) == 2 && nvec_row > lse_peel_aligned_min && nvec_row <= 128;
+  if (aligned && !lse_to_peel && !no_multi && !env_u && nvec_row <= 128 && rows >= 64) {
     // several rows per warp (lse_multi_kernel)
     // lanes per row G, vectors per lane NV, rounds R (R * NV = 8 loads in flight)
     const int LG = nvec_row <= 32 ? 8 : 16;
@@ -501,7 +506,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   if constexpr (sizeof(T) == 2) {
     static const bool no_peel = getenv("B200PHI_LSE_NO_PEEL") != nullptr;
     static const int peel_min = getenv("B200PHI_LSE_PEEL_MIN") ? atoi(getenv("B200PHI_LSE_PEEL_MIN")) : 4;
-    if (!aligned && !no_peel && !env_u && nvec_row >= peel_min && nvec_row <= 128 && rows >= 64) {
+    if ((!aligned || lse_to_peel) && !no_peel && !env_u && nvec_row >= peel_min && nvec_row <= 128 && rows >= 64) {
       const int lanes = nvec_row <= 64 ? 8 : 16;
       long long pc = (rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
       const long long cap = static_cast<long long>(current_sm_count()) * 8 * 8;

@@ -1050,6 +1050,10 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const bool no_async = getenv("B200PHI_ROWSTATS_ASYNC") == nullptr;
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
+  // aligned 16-bit rows of more than this many vectors (and at most 128) take the sub-warp peel
+  // kernel instead of rowstats_multi_kernel (B200PHI_ROWSTATS_PEEL_ALIGNED_MIN overrides)
+  static const long long rs_peel_aligned_min =
+      getenv("B200PHI_ROWSTATS_PEEL_ALIGNED_MIN") ? atoll(getenv("B200PHI_ROWSTATS_PEEL_ALIGNED_MIN")) : 32;  // (bf16 384 / 512 columns 4.8 / 5.7 -> 6.1 / 6.9 TB/s)
   static const bool no_staged = getenv("B200PHI_NO_ROW_STAGED") != nullptr;
   if (!no_staged && !no_multi && force_g == 0 && staged_rows_ok(d->rows, row_bytes, static_cast<int>(sizeof(T)), kStagedStats, reinterpret_cast<uintptr_t>(x) % 16 == 0)) {
     // short rows that are not whole aligned vectors: a thread per row out of shared memory
@@ -1070,7 +1074,28 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
       rowstats_moments_kernel<T, Acc, 64, 8><<<gr, kBlock, 0, stream>>>(x, d->rows, n, denom, d->mean, d->var, out_dtype);
     else
       rowstats_moments_kernel<T, Acc, 32, 8><<<gr, kBlock, 0, stream>>>(x, d->rows, n, denom, d->mean, d->var, out_dtype);
-  } else if (aligned && !no_multi && force_g == 0 && (nvec <= 128 || (nvec > 256 && nvec <= 512)) && d->rows >= 64) {
+  } else if (sizeof(T) == 2 && (!aligned || nvec > rs_peel_aligned_min) && n / VE >= 4 && n / VE <= 128 && d->rows >= 64 &&
+             getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr && getenv("B200PHI_ROWSTATS_PEEL_MIN") == nullptr) {
+    // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row
+    // (the scalar-load kernel read these at 2.0-3.2 TB/s, a whole warp per row at 2.0 on 301 columns)
+    const long long nv_row = n / VE;
+    const int lanes = nv_row <= 64 ? 8 : 16;
+    long long ctas = (d->rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
+    const long long cap = static_cast<long long>(sms) * 8 * 8;
+    if (ctas > cap) ctas = cap;
+    const unsigned gsz = static_cast<unsigned>(ctas);
+    if constexpr (sizeof(T) == 2) {
+      if (nv_row <= 16)
+        rowstats_warp_peel_kernel<T, Acc, 2, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else if (nv_row <= 32)
+        rowstats_warp_peel_kernel<T, Acc, 4, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else if (nv_row <= 64)
+        rowstats_warp_peel_kernel<T, Acc, 8, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+      else
+        rowstats_warp_peel_kernel<T, Acc, 8, 16><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
+    }
+  } else if (aligned && !no_multi && force_g == 0 && (nvec <= 128 || (nvec > 256 && nvec <= 512)) && d->rows >= 64 &&
+             !(sizeof(T) == 2 && nvec > rs_peel_aligned_min && nvec <= 128)) {
     // R rows per group so that all eight load slots are used (see rowstats_multi_kernel)
     const Acc na = static_cast<Acc>(n);
 #define B200PHI_RS_MULTI(GG, NN, RR)                                                          \
@@ -1131,26 +1156,6 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;
     rowstats_reg_kernel<T, Acc, 128, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
         x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-  } else if (sizeof(T) == 2 && !aligned && n / VE >= 4 && n / VE <= 128 && d->rows >= 64 &&
-             getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr && getenv("B200PHI_ROWSTATS_PEEL_MIN") == nullptr) {
-    // 16-bit rows of 32..1031 columns that are not whole aligned vectors: 8 or 16 lanes per row
-    // (the scalar-load kernel read these at 2.0-3.2 TB/s, a whole warp per row at 2.0 on 301 columns)
-    const long long nv_row = n / VE;
-    const int lanes = nv_row <= 64 ? 8 : 16;
-    long long ctas = (d->rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
-    const long long cap = static_cast<long long>(sms) * 8 * 8;
-    if (ctas > cap) ctas = cap;
-    const unsigned gsz = static_cast<unsigned>(ctas);
-    if constexpr (sizeof(T) == 2) {
-      if (nv_row <= 16)
-        rowstats_warp_peel_kernel<T, Acc, 2, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-      else if (nv_row <= 32)
-        rowstats_warp_peel_kernel<T, Acc, 4, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-      else if (nv_row <= 64)
-        rowstats_warp_peel_kernel<T, Acc, 8, 8><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-      else
-        rowstats_warp_peel_kernel<T, Acc, 8, 16><<<gsz, kBlock, 0, stream>>>(x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
-    }
   } else if (!aligned && row_bytes >= peel_min_bytes(sizeof(T)) && row_bytes < 16400 && d->rows >= 64 && getenv("B200PHI_ROWSTATS_NO_PEEL") == nullptr) {
     // 1..16 KiB rows that are not whole aligned vectors: a warp per row, row in registers
     long long ctas = (d->rows + kWarps - 1) / kWarps;
