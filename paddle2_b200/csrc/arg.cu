@@ -422,7 +422,11 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       const bool no_peel = arg_knobs().no_peel;
       // (measured, bf16: 1001 columns 4.89 TB/s against 2.65 for the peeled row kernel; at 4097
       // columns a 16-vector form was slower, 4.78 against 5.39, so rows stop at 4 KiB here)
-      if (!aligned && !no_peel && g.n >= 256 && row_bytes < 4112 && g.pre >= 64 && !force_g && !force_u) {
+      // (aligned rows of 2..4 KiB too: B200PHI_ARG_WARP_PEEL_ALIGNED=0 keeps them on arg_row_kernel)
+      static const bool warp_peel_aligned =
+          !(getenv("B200PHI_ARG_WARP_PEEL_ALIGNED") && atoi(getenv("B200PHI_ARG_WARP_PEEL_ALIGNED")) == 0);
+      if ((!aligned || (warp_peel_aligned && nvec_row > 128)) && !no_peel && g.n >= 256 && row_bytes < 4112 &&
+          g.pre >= 64 && !force_g && !force_u) {
         long long pc = (g.pre + kWarps - 1) / kWarps;
         if (pc > sm_cap) pc = sm_cap;
         const unsigned gp = static_cast<unsigned>(pc);

@@ -483,7 +483,9 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   // instead of lse_multi_kernel (B200PHI_LSE_PEEL_ALIGNED_MIN overrides)
   static const long long lse_peel_aligned_min =
       getenv("B200PHI_LSE_PEEL_ALIGNED_MIN") ? atoll(getenv("B200PHI_LSE_PEEL_ALIGNED_MIN")) : 16;  // (bf16 512 columns 5.5 -> 6.6 TB/s)
-  const bool lse_to_peel = sizeof(T) == 2 && nvec_row > lse_peel_aligned_min && nvec_row <= 128;
+  // B200PHI_LSE_PEEL_MAX: longest row, in vectors, of the peel kernel (a warp per row from 129)
+  static const long long lse_peel_max = getenv("B200PHI_LSE_PEEL_MAX") ? atoll(getenv("B200PHI_LSE_PEEL_MAX")) : 256;
+  const bool lse_to_peel = sizeof(T) == 2 && nvec_row > lse_peel_aligned_min && nvec_row <= lse_peel_max;
   if (aligned && !lse_to_peel && !no_multi && !env_u && nvec_row <= 128 && rows >= 64) {
     // several rows per warp (lse_multi_kernel)
     // lanes per row G, vectors per lane NV, rounds R (R * NV = 8 loads in flight)
@@ -506,8 +508,8 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
   if constexpr (sizeof(T) == 2) {
     static const bool no_peel = getenv("B200PHI_LSE_NO_PEEL") != nullptr;
     static const int peel_min = getenv("B200PHI_LSE_PEEL_MIN") ? atoi(getenv("B200PHI_LSE_PEEL_MIN")) : 4;
-    if ((!aligned || lse_to_peel) && !no_peel && !env_u && nvec_row >= peel_min && nvec_row <= 128 && rows >= 64) {
-      const int lanes = nvec_row <= 64 ? 8 : 16;
+    if ((!aligned || lse_to_peel) && !no_peel && !env_u && nvec_row >= peel_min && nvec_row <= lse_peel_max && rows >= 64) {
+      const int lanes = nvec_row <= 64 ? 8 : (nvec_row <= 128 ? 16 : 32);
       long long pc = (rows + kWarps * (32 / lanes) - 1) / (kWarps * (32 / lanes));
       const long long cap = static_cast<long long>(current_sm_count()) * 8 * 8;
       if (pc > cap) pc = cap;
@@ -519,8 +521,10 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
         lse_peel_kernel<T, A, 8, 4><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
       else if (nvec_row <= 64)
         lse_peel_kernel<T, A, 8, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
-      else
+      else if (nvec_row <= 128)
         lse_peel_kernel<T, A, 16, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
+      else
+        lse_peel_kernel<T, A, 32, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
       cudaError_t e2 = cudaGetLastError();
       if (e2 != cudaSuccess) return cuda_status(e2);
       return B200PHI_OK;

@@ -1050,6 +1050,8 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
   static const bool no_async = getenv("B200PHI_ROWSTATS_ASYNC") == nullptr;
   static const int force_g = getenv("B200PHI_ROWSTATS_G") ? atoi(getenv("B200PHI_ROWSTATS_G")) : 0;
   static const bool no_multi = getenv("B200PHI_ROWSTATS_NO_MULTI") != nullptr;
+  static const bool rs_warp_peel_aligned =
+      !(getenv("B200PHI_ROWSTATS_WARP_PEEL_ALIGNED") && atoi(getenv("B200PHI_ROWSTATS_WARP_PEEL_ALIGNED")) == 0);
   // aligned 16-bit rows of more than this many vectors (and at most 128) take the sub-warp peel
   // kernel instead of rowstats_multi_kernel (B200PHI_ROWSTATS_PEEL_ALIGNED_MIN overrides)
   static const long long rs_peel_aligned_min =
@@ -1115,6 +1117,14 @@ static int launch_rowstats(const b200phi_rowstats_desc* d, int out_dtype, cudaSt
     else
       B200PHI_RS_MULTI(64, 8, 1)
 #undef B200PHI_RS_MULTI
+  } else if (sizeof(T) == 2 && aligned && nvec > 128 && nvec < 256 && d->rows >= 64 && rs_warp_peel_aligned) {
+    // aligned 16-bit rows of 2..4 KiB that are not the moments kernel's power of two: the warp-per-row
+    // peel kernel (head and tail empty) instead of the two-barrier register kernel
+    long long ctas = (d->rows + kWarps - 1) / kWarps;
+    const long long cap = static_cast<long long>(sms) * 8 * 8;
+    if (ctas > cap) ctas = cap;
+    rowstats_warp_peel_kernel<T, Acc, 8><<<static_cast<unsigned>(ctas), kBlock, 0, stream>>>(
+        x, d->rows, n, denom, static_cast<Acc>(n), d->mean, d->var, out_dtype);
   } else if (aligned && nvec <= 32 * 8 && d->rows >= static_cast<long long>(sms) * 16) {
     long long ctas = (d->rows + kWarps - 1) / kWarps;
     if (ctas > 0x7fffffffLL) ctas = 0x7fffffffLL;

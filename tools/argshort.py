@@ -1,4 +1,4 @@
-"""argmax over aligned 16-bit rows of 64..1024 columns (2 GiB tensors)."""
+"""argmax over aligned 16-bit rows of 64..2048 columns (2 GiB tensors)."""
 import sys, torch
 sys.path.insert(0, '.')
 import paddle2_b200 as pb
@@ -12,7 +12,7 @@ def t(fn, n=3):
     return a.elapsed_time(b) / n * 1e3
 N = 1 << 30
 for dt in (torch.bfloat16, torch.float16):
-    for cols in (64, 128, 256, 384, 512, 768, 1024):
+    for cols in (64, 128, 256, 384, 512, 768, 1024, 1280, 1536, 2048):
         x = torch.randn(N // cols, cols, device="cuda").to(dt)
         us = t(lambda: pb.argmax(x, axis=-1))
         us2 = t(lambda: pb.argmax_with_value(x, axis=-1))
