@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kBlock)
 // "First position equal to the extreme" is what the strict in-order compare of the reference
 // returns (cpu/arg_min_max_kernel.cc:46-59); an all-identity row answers 0.
 template <typename T, typename V, bool kMax, int NV, int G = 32>
-__global__ void __launch_bounds__(kBlock, NV <= 8 ? 4 : 1)
+__global__ void __launch_bounds__(kBlock, NV <= 8 ? 4 : 2)
     arg_warp_peel_kernel(const T* __restrict__ x, long long rows, int n, void* out, int index_dtype,
                          void* val_out) {
   using Op = ArgOp<V, kMax>;
@@ -425,16 +425,19 @@ static int launch_arg(const T* x, const ArgGeom& g, void* out, int index_dtype, 
       // (aligned rows of 2..4 KiB too: B200PHI_ARG_WARP_PEEL_ALIGNED=0 keeps them on arg_row_kernel)
       static const bool warp_peel_aligned =
           !(getenv("B200PHI_ARG_WARP_PEEL_ALIGNED") && atoi(getenv("B200PHI_ARG_WARP_PEEL_ALIGNED")) == 0);
-      if ((!aligned || (warp_peel_aligned && nvec_row > 128)) && !no_peel && g.n >= 256 && row_bytes < 4112 &&
-          g.pre >= 64 && !force_g && !force_u) {
+      static const long long warp_peel_max = getenv("B200PHI_ARG_WARP_PEEL_MAX") ? atoll(getenv("B200PHI_ARG_WARP_PEEL_MAX")) : 8208;
+      if (((!aligned && row_bytes < warp_peel_max) || (warp_peel_aligned && nvec_row > 128 && row_bytes < 4112)) && !no_peel &&
+          g.n >= 256 && g.pre >= 64 && !force_g && !force_u) {
         long long pc = (g.pre + kWarps - 1) / kWarps;
         if (pc > sm_cap) pc = sm_cap;
         const unsigned gp = static_cast<unsigned>(pc);
         const int c = static_cast<int>(g.n);
         if (row_bytes < 2064)
           arg_warp_peel_kernel<T, V, kMax, 4><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
-        else
+        else if (row_bytes < 4112)
           arg_warp_peel_kernel<T, V, kMax, 8><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
+        else
+          arg_warp_peel_kernel<T, V, kMax, 16><<<gp, kBlock, 0, stream>>>(x, g.pre, c, out, index_dtype, val_out);
         cudaError_t e2 = cudaGetLastError();
         if (e2 != cudaSuccess) return cuda_status(e2);
         return B200PHI_OK;

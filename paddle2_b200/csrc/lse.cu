@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(kBlock)
 // first aligned address and one tail element together, keeps them in registers for the max sweep
 // and the exp-sum sweep (the 2-byte-load kernel read these at 1.6-2.7 TB/s).
 template <typename T, typename A, int G, int NV>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 4)  // (64 registers: an explicit bound of 1 let the compiler take 86)
     lse_peel_kernel(const T* __restrict__ x, long long rows, int cols, void* out, int out_dtype) {
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");
@@ -523,7 +523,7 @@ static int launch_lse(const b200phi_logsumexp_desc* d, cudaStream_t stream) {
         lse_peel_kernel<T, A, 8, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
       else if (nvec_row <= 128)
         lse_peel_kernel<T, A, 16, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
-      else
+      else  // (a 16-vector form for 4..8 KiB rows measured 2.5 TB/s on 4097 bf16 columns, lse_rows_kernel 4.5)
         lse_peel_kernel<T, A, 32, 8><<<gp, kBlock, 0, stream>>>(x, rows, c, d->out, d->dtype);
       cudaError_t e2 = cudaGetLastError();
       if (e2 != cudaSuccess) return cuda_status(e2);

@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(kBlock)
 // issue (ncu: 85 % issue-slot use on 101 bf16 columns), so the per-row address arithmetic is 32-bit:
 // a CTA-uniform 64-bit base per iteration plus (row within the iteration) * cols.
 template <typename T, typename Acc, typename Op, int G, int NV, int RB = 1>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, NV * RB >= 16 ? 2 : 4)  // (64 registers; 16 vectors per lane: 128, two CTAs per SM)
     row_peel_kernel(const T* __restrict__ x, long long rows, int cols, Epilogue ep) {
   constexpr int VE = VecOf<T>::kElems;
   static_assert(G >= VE - 1, "a lane per possible head / tail element");

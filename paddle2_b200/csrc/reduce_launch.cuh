@@ -176,6 +176,8 @@ static int launch_reduce_typed(const ReduceArgs& a) {
           row_peel_kernel<T, Acc, Op, 16, 4><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
         else if (p.G == 16)
           row_peel_kernel<T, Acc, Op, 16, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
+        else if (p.G == 32 && p.nv == 16)
+          row_peel_kernel<T, Acc, Op, 32, 16><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
         else if (p.G == 32)
           row_peel_kernel<T, Acc, Op, 32, 8><<<p.grid_x, kBlock, 0, a.stream>>>(x, p.rows, c, ep);
       } else {

@@ -636,7 +636,7 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
     // 1- and 2-byte rows that are not whole aligned vectors, 4 .. 256 vectors long: head element,
     // vectors and tail element per lane (row_peel_kernel) instead of 2-byte loads
     if ((kind == kRowWarp || kind == kRowBlock || kind == kRowScalar) && esize <= 2 && !p->aligned &&
-        p->cols / VE >= 4 && p->cols / VE <= 256 && p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch &&
+        p->cols / VE >= 4 && p->cols / VE <= 512 && p->rows >= 64 && t.force_kind < 0 && !t.no_row_batch &&
         !t.no_row_peel) {
       const long long nv_row = p->cols / VE;
       const int gmin = VE > 8 ? 16 : 8;  // a lane per possible head / tail element
@@ -649,8 +649,10 @@ int plan_reduce(const b200phi_reduce_desc* d, const Tunables& t, ReducePlan* p, 
         p->G = gmin == 8 ? 8 : 16, p->nv = gmin == 8 ? 8 : 4;
       } else if (nv_row <= 128) {
         p->G = 16, p->nv = 8;
-      } else {
+      } else if (nv_row <= 256) {
         p->G = 32, p->nv = 8;
+      } else {
+        p->G = 32, p->nv = 16;  // 4..8 KiB rows: a warp per row, 16 vectors per lane
       }
       p->rpg = 1;
     }
