@@ -434,7 +434,8 @@ struct MapFlatRowParams {
   unsigned total;  // vectors in this slice of the output
 };
 template <typename TI, typename TO, typename F, int kRows, int kFullIs, int U>
-__global__ void __launch_bounds__(kBlock) map_flat_row_kernel(const __grid_constant__ MapFlatRowParams p, F f) {
+__global__ void __launch_bounds__(kBlock, kRows == 2 ? 4 : 5)  // (two rows: 64 registers instead of 70; one row: its own 48)
+    map_flat_row_kernel(const __grid_constant__ MapFlatRowParams p, F f) {
   using C = typename MapCompute<TI>::type;
   constexpr int VE = VecOf<TI>::kElems;
   constexpr int kOutBytes = VE * static_cast<int>(sizeof(TO));
