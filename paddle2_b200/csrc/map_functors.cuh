@@ -54,6 +54,24 @@ __device__ __forceinline__ float attr_as(float v) {
   return v;
 }
 
+// 16-bit inputs: sigmoid / silu / tanh through the special-function unit's exp2 and reciprocal
+// (relative error ~2^-21, against the 2^-9 the result is rounded to anyway) instead of expf and an
+// IEEE division -- ~25 instructions per element, which made these functors issue-bound at twice
+// the elements per byte (bf16 silu 4.2 TB/s where relu runs 6.4).  fp32 / fp64 keep the exact forms.
+__device__ __forceinline__ float map_ex2_approx(float v) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float map_rcp_approx(float v) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float map_fast_sigmoid(float a) {
+  return map_rcp_approx(1.f + map_ex2_approx(a * -1.4426950408889634f));
+}
+
 template <int kOp, typename T>
 struct MapF {
   float p0, p1;
@@ -200,9 +218,23 @@ struct MapF {
       else if constexpr (kOp == B200PHI_MAP_RECIPROCAL) return one / a;
       else if constexpr (kOp == B200PHI_MAP_SIN) return sin(a);
       else if constexpr (kOp == B200PHI_MAP_COS) return cos(a);
-      else if constexpr (kOp == B200PHI_MAP_TANH) return tanh(a);
-      else if constexpr (kOp == B200PHI_MAP_SIGMOID) return one / (one + exp(-a));
-      else if constexpr (kOp == B200PHI_MAP_SILU) return a / (one + exp(-a));
+      else if constexpr (kOp == B200PHI_MAP_TANH) {
+        if constexpr (sizeof(T) == 2) {  // (see map_fast_sigmoid)
+          const float x = fabsf(a);
+          const float t = map_ex2_approx(x * -2.8853900817779268f);  // e^(-2|a|)
+          const float big = (1.f - t) * map_rcp_approx(1.f + t);
+          const float small = x * (1.f - x * x * 0.3333333333f);      // |a| < 0.04: no cancellation
+          return copysignf(x < 0.04f ? small : big, a);
+        } else {
+          return tanh(a);
+        }
+      } else if constexpr (kOp == B200PHI_MAP_SIGMOID) {
+        if constexpr (sizeof(T) == 2) return map_fast_sigmoid(a);
+        else return one / (one + exp(-a));
+      } else if constexpr (kOp == B200PHI_MAP_SILU) {
+        if constexpr (sizeof(T) == 2) return a * map_fast_sigmoid(a);
+        else return a / (one + exp(-a));
+      }
       else if constexpr (kOp == B200PHI_MAP_LEAKY_RELU)
         return a > zero ? a : static_cast<C>(attr_as<T>(p0)) * a;
       else if constexpr (kOp == B200PHI_MAP_ELU)
