@@ -14,6 +14,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <string>
 
 #include "../../include/b200phi.h"
@@ -904,6 +905,19 @@ static int launch_typed(const b200phi_elementwise_desc* d, const BcastPlan& bp, 
     }
     if (d->act == B200PHI_ACT_RELU && d->binary == B200PHI_ADD)
       return launch_bcast<T, StaticF<B200PHI_ADD, B200PHI_ACT_RELU>, 2>(d, bp, {}, nullptr, s);
+    // the other unary functors of fused_elemwise_add_activation over x + y (bias + gelu ...): with
+    // the functor ids as kernel arguments every element walks two switches (fp32 2.1 TB/s, bf16 0.9)
+    if constexpr (std::is_floating_point<T>::value || std::is_same<T, __nv_bfloat16>::value ||
+                  std::is_same<T, __half>::value) {
+      if (d->binary == B200PHI_ADD) {
+        if (d->act == B200PHI_ACT_GELU)
+          return launch_bcast<T, StaticF<B200PHI_ADD, B200PHI_ACT_GELU>, 2>(d, bp, {}, nullptr, s);
+        if (d->act == B200PHI_ACT_SIGMOID)
+          return launch_bcast<T, StaticF<B200PHI_ADD, B200PHI_ACT_SIGMOID>, 2>(d, bp, {}, nullptr, s);
+        if (d->act == B200PHI_ACT_TANH)
+          return launch_bcast<T, StaticF<B200PHI_ADD, B200PHI_ACT_TANH>, 2>(d, bp, {}, nullptr, s);
+      }
+    }
   }
   return launch_runtime<T>(d, bp, inter, s);
 }
