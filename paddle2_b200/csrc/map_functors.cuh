@@ -255,7 +255,10 @@ struct MapF {
         const C t = a * static_cast<C>(attr_as<T>(p0)) + static_cast<C>(attr_as<T>(p1));
         const C hi = t > zero ? t : zero;
         return hi < one ? hi : one;
-      } else if constexpr (kOp == B200PHI_MAP_SWISH) return a / (one + exp(-static_cast<C>(p0) * a));
+      } else if constexpr (kOp == B200PHI_MAP_SWISH) {
+        if constexpr (sizeof(T) == 2) return a * map_fast_sigmoid(static_cast<C>(p0) * a);
+        else return a / (one + exp(-static_cast<C>(p0) * a));
+      }
       else if constexpr (kOp == B200PHI_MAP_MISH) {
         const C sp = a > static_cast<C>(p0) ? a : log(one + exp(a));
         return a * tanh(sp);
